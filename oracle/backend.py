@@ -1,0 +1,127 @@
+"""Layer-level oracle: TorchCUDASDPABackendImpl.forward restated on CPU tensors.
+TEST INFRASTRUCTURE ONLY.
+
+Follows vllm/attention/backends/torch_cuda_sdpa.py:812-1064 (forward),
+1222-1296 (prompt prune), 1375-1433 / 1478-1560 (decode prune), 1562-1586 (table
+compaction) with the declared deviations of DESIGN.md:
+  D1  value_l2 is computed in fp32, fixed order, on the TRUE V layout (oracle/scoring.py)
+  D2  a block is scored when it FILLS, after this step's cache write (the reference
+      scores before the write, so slot bs-1 is stale) and every full prompt block is
+      scored unconditionally
+  D3  the victim's score is deleted with the victim (v1 semantics,
+      torch_cuda_sdpa_v1.py:1541), so score index == table index
+  D4  compaction is v1 / HEAD-row-0 semantics for every row
+  D5  streamingLLM trigger steps attend over the COMPACTED table.  HEAD/v1 compute it
+      but never use it (`is_pruned_decode` vs `is_prune_decode` typo,
+      torch_cuda_sdpa.py:903,910 vs 858,1046); `head_compat_uncompacted=True`
+      reproduces that for the golden traces.
+State is per layer, keyed by request id, like BlockL2NormManager.
+"""
+from __future__ import annotations
+
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+
+from . import paged_ops, policy, scoring
+from .policy import Policy
+
+
+class OracleLayer:
+    def __init__(self, num_heads: int, head_size: int, scale: float, num_kv_heads: int,
+                 pol: Optional[Policy], head_compat_uncompacted: bool = False):
+        self.Hq, self.D, self.scale, self.Hkv = num_heads, head_size, float(scale), num_kv_heads
+        self.pol = pol
+        self.compat = head_compat_uncompacted
+        # req_id -> list of per-head partial scores [Hkv] fp32, index == table index
+        self.scores: Dict[str, List[np.ndarray]] = {}
+        self.last = {}
+
+    # -------------------------------------------------------------- prefill
+    def prefill(self, query, key, value, kv_cache, seq_lens: Sequence[int],
+                block_tables: Sequence[Sequence[int]], req_ids: Sequence[str]) -> torch.Tensor:
+        """query [sumL, Hq*D], key/value [sumL, Hkv*D]; block_tables = post-prune host
+        tables.  Returns out [sumL, Hq*D]."""
+        p, bs = self.pol, self.pol.block_size
+        q = query.view(-1, self.Hq, self.D)
+        k = key.view(-1, self.Hkv, self.D)
+        v = value.view(-1, self.Hkv, self.D)
+        kc, vc = paged_ops.split_kv_cache(kv_cache, self.Hkv, self.D)
+        gidx, kept, slots = [], [], []
+        s = 0
+        for L, tab in zip(seq_lens, block_tables):
+            gi = policy.prompt_gather_index(L, p)
+            gidx.append(torch.from_numpy(gi) + s)
+            kept.append(len(gi))
+            slots.extend(policy.prefill_slot_mapping(list(tab), L, bs))
+            s += L
+        gidx = torch.cat(gidx)
+        kp, vp = k[gidx], v[gidx]
+        assert len(slots) == kp.shape[0]
+        paged_ops.reshape_and_cache(kp, vp, kc, vc, torch.tensor(slots, dtype=torch.long))
+        # scores of every FULL cached prompt block (D2)
+        s = 0
+        for L, rid in zip(kept, req_ids) if p.decode_evict_method == "value_l2" else ():
+            vr = vp[s:s + L].float().numpy()
+            self.scores[rid] = [scoring.per_head_block_score(vr[j * bs:(j + 1) * bs])
+                                for j in range(L // bs)]
+            s += L
+        if p.disable_evict_prefill:
+            out = paged_ops.prefill_attention(q, k, v, seq_lens, seq_lens, self.scale)
+        else:
+            out = paged_ops.prefill_attention(q, kp, vp, seq_lens, kept, self.scale)
+        self.last = {"slots": slots, "kept": kept}
+        return out.view(-1, self.Hq * self.D)
+
+    # -------------------------------------------------------------- decode
+    def decode(self, query, key, value, kv_cache, seq_lens: Sequence[int],
+               kv_lens: Sequence[int], block_tables: Sequence[Sequence[int]],
+               req_ids: Sequence[str]):
+        """One decode step.  seq_lens = logical lengths incl. this token; kv_lens =
+        physical lengths as the host passes them (already -= bs on trigger rows,
+        model_runner.py:540-543); block_tables = host tables (not compacted).
+        -> (out [B, Hq*D], rmv {row: (req_id, idx)}, attn_tables list-of-lists)"""
+        p, bs = self.pol, self.pol.block_size
+        B = len(seq_lens)
+        kc, vc = paged_ops.split_kv_cache(kv_cache, self.Hkv, self.D)
+        rmv: Dict[int, Tuple[str, int]] = {}
+        attn_tables: List[List[int]] = []
+        slots = []
+        for r in range(B):
+            tab = list(block_tables[r])
+            n = len(tab)
+            slots.append(policy.decode_slot_mapping(tab, seq_lens[r] - 1, bs))
+            if policy.decode_trigger(seq_lens[r], n * bs, p):
+                lo, hi = policy.victim_candidates(n, p)
+                if p.decode_evict_method == "streamingLLM":
+                    idx = 1
+                else:
+                    sc = scoring.combine_heads(np.stack(self.scores[req_ids[r]][:n - 1]))
+                    idx = policy.argmin_lowest_index(sc, lo, hi)
+                rmv[r] = (req_ids[r], idx)
+                if req_ids[r] in self.scores and len(self.scores[req_ids[r]]) > idx:
+                    del self.scores[req_ids[r]][idx]                      # D3
+                if not (self.compat and p.decode_evict_method == "streamingLLM"):
+                    del tab[idx]
+            attn_tables.append(tab)
+        k = key.view(-1, self.Hkv, self.D)
+        v = value.view(-1, self.Hkv, self.D)
+        paged_ops.reshape_and_cache(k, v, kc, vc, torch.tensor(slots, dtype=torch.long))
+        out = paged_ops.paged_attention(query.view(-1, self.Hq, self.D), kc, vc,
+                                        attn_tables, list(kv_lens), self.scale)
+        for r in range(B):                                                # D2
+            if p.decode_evict_method == "value_l2" and policy.score_trigger(seq_lens[r], p):
+                last_blk = block_tables[r][-1]
+                vb = paged_ops.depage_v_block(vc, last_blk).float().numpy()
+                lst = self.scores.setdefault(req_ids[r], [])
+                n_after = len(block_tables[r]) - (1 if r in rmv else 0)
+                assert len(lst) == n_after - 1, (len(lst), n_after)
+                lst.append(scoring.per_head_block_score(vb))
+        self.last = {"slots": slots}
+        return out.view(-1, self.Hq * self.D), rmv, attn_tables
+
+    def drop_finished(self, live_req_ids):
+        for rid in list(self.scores):
+            if rid not in live_req_ids:
+                del self.scores[rid]

@@ -1,0 +1,456 @@
+#!/usr/bin/env python
+"""Generate tests/golden/* by executing the REFERENCE's own code in this container.
+
+Run from the repo root (needs /root/reference and oracle/_ref built):
+    python tests/golden/make_golden.py
+
+Nothing here runs on the GPU box; only the produced fixtures travel.  What is executed:
+  * the reference's Python classes imported from /root/reference (KVCachePruner,
+    page_evict_kv_util(+_bak), kvcache_prunner_old, BlockTable + naive allocator,
+    TorchCUDASDPAMetadataBuilder._compute_slot_mapping, TorchCUDASDPABackendImpl
+    (HEAD and _v1) driven on CPU tensors);
+  * the reference's own CPU kernels (csrc/cpu/{attention,cache}.cpp compiled to
+    oracle/_ref/libpc_ref_cpu.so) standing in for the two native ops the Python
+    calls (`reshape_and_cache`, `paged_attention_v1`).
+Patches applied to run on CPU (no reference file is modified): triton-cache shim,
+torch.cuda.{current_device,stream,current_stream,Stream} null objects,
+TmpCacheSingleton on "cpu", PagedAttention.write_to_paged_cache / forward_decode ->
+oracle/_ref ops, enable_random_evict=False where the L2 branch is exercised.
+"""
+import contextlib
+import json
+import os
+import sys
+import types
+
+import numpy as np
+
+REPO = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, REPO)
+sys.path.insert(0, "/root/reference")
+OUT = os.path.join(REPO, "tests", "golden")
+
+import triton.runtime.cache as _trc  # noqa: E402
+
+for _n in ("default_cache_dir", "default_dump_dir", "default_override_dir"):
+    if not hasattr(_trc, _n):
+        setattr(_trc, _n, lambda: "/tmp/triton_stub")
+
+import torch  # noqa: E402
+
+from oracle import ref_cpu  # noqa: E402
+
+assert ref_cpu.available(), ref_cpu.why_unavailable()
+
+import importlib.util  # noqa: E402
+
+import vllm.attention.backends.torch_cuda_sdpa as HEAD  # noqa: E402
+import vllm.attention.backends.torch_cuda_sdpa_v1 as V1  # noqa: E402
+from vllm.attention.kvcache_prunner import KVCachePruner  # noqa: E402
+from vllm.config import CacheConfig, PagedEvictConfig  # noqa: E402
+from vllm.core.block.block_table import BlockTable  # noqa: E402
+from vllm.core.block.cpu_gpu_block_allocator import CpuGpuBlockAllocator  # noqa: E402
+from vllm.core.page_evict_kv_util import get_num_required_blocks_after_prune_promt  # noqa: E402
+from vllm.worker.tmp_cache_singleton import TmpCacheSingleton  # noqa: E402
+
+
+def _load(path, name):
+    spec = importlib.util.spec_from_file_location(name, path)
+    m = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(m)
+    return m
+
+
+BAK = _load("/root/reference/vllm/core/page_evict_kv_util_bak.py", "pe_bak")
+OLD = _load("/root/reference/vllm/attention/kvcache_prunner_old.py", "pruner_old")
+
+
+# ------------------------------------------------------------------ CPU patches
+class _NullStream:
+    def wait_stream(self, s):
+        pass
+
+
+torch.cuda.current_device = lambda: 0
+torch.cuda.stream = lambda s: contextlib.nullcontext()
+torch.cuda.current_stream = lambda *a, **k: _NullStream()
+
+
+class _StreamMgr:
+    def get_streams(self):
+        return [_NullStream()]
+
+
+CAPTURE = {}
+
+
+def _write_to_paged_cache(key, value, key_cache, value_cache, slot_mapping,
+                          kv_cache_dtype, k_scale, v_scale):
+    ref_cpu.reshape_and_cache(key.contiguous(), value.contiguous(), key_cache,
+                              value_cache, slot_mapping.flatten().contiguous())
+
+
+def _forward_decode(query, key_cache, value_cache, block_tables, seq_lens, max_seq_len,
+                    kv_cache_dtype, num_kv_heads, scale, alibi_slopes, k_scale, v_scale,
+                    *a, **k):
+    CAPTURE["decode_block_tables"] = block_tables.clone()
+    CAPTURE["decode_kv_lens"] = seq_lens.clone()
+    out = torch.empty_like(query)
+    bs = value_cache.shape[3]
+    ref_cpu.paged_attention_v1(out, query.contiguous(), key_cache, value_cache,
+                               num_kv_heads, scale, block_tables.contiguous(),
+                               seq_lens.contiguous(), bs, block_tables.shape[1] * bs)
+    return out
+
+
+for _m in (HEAD, V1):
+    _m.CudaStreamManager.get_instance = staticmethod(lambda dev: _StreamMgr())
+    _m.PagedAttention.write_to_paged_cache = staticmethod(_write_to_paged_cache)
+    _m.PagedAttention.forward_decode = staticmethod(_forward_decode)
+
+
+def make_impl(mod, evict_method, budget, bs, Hq, Hkv, D, topk=3,
+              disable_evict_prefill=False, random_evict=False, dtype=torch.bfloat16):
+    TmpCacheSingleton._instance = None
+    TmpCacheSingleton(64, D, Hkv, dtype, "cpu")
+    pe = PagedEvictConfig(disable_evict_prefill, "budget", evict_method, budget, topk)
+    cc = CacheConfig(bs, 0.9, 0, "auto", paged_evict_config=pe)
+    impl = mod.TorchCUDASDPABackendImpl(Hq, D, D ** -0.5, Hkv, None, None, "auto",
+                                        cache_config=cc, prefix="model.layers.0.self_attn")
+    impl.enable_random_evict = random_evict
+    return impl, pe, cc
+
+
+def rnd(seed, *shape):
+    """Platform-stable synthetic data: numpy RandomState normal -> bf16."""
+    a = np.random.RandomState(seed).standard_normal(shape).astype(np.float32)
+    return torch.from_numpy(a).to(torch.bfloat16)
+
+
+# ------------------------------------------------------------------ integer KATs
+def policy_kats():
+    g = {}
+    # P1: block-manager util + pruner length (budget mode)
+    rows = []
+    for bs in (8, 16, 32):
+        for budget in (128, 256, 512, 1024):
+            pe = PagedEvictConfig(False, "budget", "streamingLLM", budget, 3)
+            pr = KVCachePruner("budget", "streamingLLM", bs, budget, 1)
+            for q in list(range(1, 200, 7)) + list(range(budget - 40, budget + 80)) + \
+                    [1000, 1024, 1030, 2048, 4099, 8192]:
+                if q < 1:
+                    continue
+                nb, kept = get_num_required_blocks_after_prune_promt(q, pe, bs)
+                rows.append([bs, budget, q, nb, kept, pr.get_pruned_length(q)])
+    g["budget_lengths"] = rows  # [bs, budget, q_len, num_blocks, kept(util), kept(pruner)]
+
+    # R1: which source rows survive prune_prompt_inplace (budget, streamingLLM)
+    rows = []
+    for bs, budget, q in [(16, 128, 200), (16, 128, 131), (16, 512, 1024), (16, 512, 1030),
+                          (32, 256, 777), (8, 128, 129), (16, 128, 128), (16, 128, 100),
+                          (16, 256, 4099)]:
+        pr = KVCachePruner("budget", "streamingLLM", bs, budget, 1)
+        k = torch.arange(q, dtype=torch.float32).view(q, 1, 1).repeat(1, 2, 4)
+        L = pr.get_pruned_length(q)
+        ok, ov = torch.empty(L, 2, 4), torch.empty(L, 2, 4)
+        pr.prune_prompt_inplace(k, k + 0.5, ok, ov)
+        assert torch.equal(ov, ok + 0.5)
+        rows.append({"bs": bs, "budget": budget, "q_len": q,
+                     "kept_src": ok[:, 0, 0].to(torch.int64).tolist()})
+    g["budget_gather"] = rows
+
+    # P2: percentage / evict_freq mode (dead files _bak / _old)
+    rows = []
+    for bs in (16, 32):
+        for freq in (2, 3, 4, 8):
+            cfg = types.SimpleNamespace(initial_blocks=1, num_block_merge=2,
+                                        original_block_size=bs,
+                                        prompt_evict_method="streamingLLM",
+                                        cache_prune_type="percentage", evict_freq=freq,
+                                        cache_budget=0)
+            old = object.__new__(OLD.KVCachePruner)   # ctor is broken upstream
+            old.cache_prune_type = "percentage"
+            old.prompt_evict_method = "streamingLLM"
+            old.orig_block_size = bs
+            old.initial_blocks = 1
+            old.num_block_merge = 2
+            old.evict_frequency = freq
+            for q in [1, 17, 3 * bs, 3 * bs + 1, 100, 333, 544, 1000, 1024, 1030, 4099, 8192]:
+                nb, kept = BAK.get_num_required_blocks_after_prune_promt(q, cfg)
+                k = torch.arange(q, dtype=torch.float32).view(q, 1, 1).repeat(1, 2, 4)
+                rk, rv = old.prune_prompt(k, k)
+                src = rk[:, 0, 0].to(torch.int64).tolist()
+                assert len(src) == kept, (q, kept, len(src))
+                # compress: first index where src jumps, and the jump
+                jump_at, jump = -1, 0
+                for i in range(1, len(src)):
+                    if src[i] != src[i - 1] + 1:
+                        jump_at, jump = i, src[i] - src[i - 1] - 1
+                rows.append([bs, freq, q, nb, kept, jump_at, jump])
+    g["percentage_lengths"] = rows  # [bs, evict_freq, q_len, num_blocks, kept, first, pruned]
+
+    # C3: slot mapping
+    fake = types.SimpleNamespace(sliding_window=None)
+    rows = []
+    for bs, qlen, table in [(16, 40, [7, 3, 9]), (16, 32, [5, 1]), (8, 19, [2, 0, 4]),
+                            (16, 1030, list(range(40, 73))), (32, 64, [9, 8])]:
+        sm = []
+        HEAD.TorchCUDASDPAMetadataBuilder._compute_slot_mapping(
+            fake, False, True, sm, 0, qlen, 0, bs, {0: table})
+        rows.append({"bs": bs, "is_prompt": True, "query_len": qlen, "context_len": 0,
+                     "table": table, "slots": sm})
+    for bs, ctx, table in [(16, 40, [7, 3, 9]), (16, 1039, [5, 1, 8]), (8, 7, [2]),
+                           (32, 95, [1, 2, 3])]:
+        sm = []
+        HEAD.TorchCUDASDPAMetadataBuilder._compute_slot_mapping(
+            fake, False, False, sm, 0, 1, ctx, bs, {0: table})
+        rows.append({"bs": bs, "is_prompt": False, "query_len": 1, "context_len": ctx,
+                     "table": table, "slots": sm})
+    g["slot_mapping"] = rows
+
+    # T4: BlockTable bookkeeping trace (allocate -> append/free loop)
+    rows = []
+    for bs, budget, q, steps in [(16, 512, 1024, 70), (16, 128, 200, 50), (16, 128, 100, 80),
+                                 (16, 128, 131, 40), (32, 256, 1000, 100)]:
+        pe = PagedEvictConfig(False, "budget", "streamingLLM", budget, 3)
+        alloc = CpuGpuBlockAllocator.create("naive", 512, 0, bs)
+        bt = BlockTable(bs, alloc, paged_evict_config=pe)
+        toks = list(range(q))
+        bt.allocate(toks)
+        trace = [{"seq_len": q, "kv_len": bt.get_seq_kv_len(),
+                  "ids": list(bt.physical_block_ids)}]
+        for s in range(steps):
+            toks.append(q + s)
+            bt.append_token_ids([q + s])
+            seq_len = len(toks)
+            kv = bt.get_seq_kv_len()
+            ids = list(bt.physical_block_ids)
+            trig = seq_len > budget and seq_len % bs == 0      # model_runner.py:540-543
+            rec = {"seq_len": seq_len, "kv_len": kv, "ids": ids, "trigger": trig}
+            if trig:
+                bt.free_prunned_blocks(1)                       # scheduler.py:1879-1890
+                rec["kv_len_after_free"] = bt.get_seq_kv_len()
+                rec["ids_after_free"] = list(bt.physical_block_ids)
+            trace.append(rec)
+        rows.append({"bs": bs, "budget": budget, "q_len": q, "trace": trace})
+    g["block_table_trace"] = rows
+
+    # C1: compaction. HEAD function on B=1 rows (row-0 semantics) + v1 list semantics.
+    impl, _, _ = make_impl(HEAD, "streamingLLM", 128, 16, 8, 2, 64)
+    rows = []
+    for table, idx in [([10, 11, 12, 13, 14], 1), ([3, 9, 4, 7], 2), ([5, 6, 7], 1),
+                       (list(range(100, 140)), 17)]:
+        t = torch.tensor([table], dtype=torch.int32)
+        out = impl._create_updated_block_tables(t, {0: idx})
+        rows.append({"table": table, "idx": idx, "out": out[0].tolist()})
+    g["compact_row0"] = rows
+    from vllm.attention.block_l2norm_manager import BlockL2NormManager
+    from vllm.utils import make_tensor_with_pad
+    mgr = BlockL2NormManager()
+    tabs = {"a": {0: [10, 11, 12, 13, 14]}, "b": {1: [20, 21, 22]}, "c": {2: [30, 31, 32, 33, 34]}}
+    mgr.update_reqs(tabs)
+    upd = [mgr.get_updated_block_tables(0, 1), mgr.get_req_block_tables(1),
+           mgr.get_updated_block_tables(2, 3)]
+    g["compact_v1"] = {"tables": [tabs["a"][0], tabs["b"][1], tabs["c"][2]],
+                       "victims": {"0": 1, "2": 3},
+                       "out": make_tensor_with_pad(upd, pad=0, dtype=torch.int).tolist()}
+
+    # S4: argmin / candidate windows via HEAD _prune_decode_reqs_topk, L2 branch
+    rows = []
+    rs = np.random.RandomState(7)
+    for method, topk in (("global", 3), ("local", 3), ("local", 5)):
+        for case in range(6):
+            n = int(rs.randint(9, 30))
+            impl, pe, cc = make_impl(HEAD, method, 128, 16, 8, 2, 64, topk=topk)
+            scores = [float(x) for x in rs.rand(n - 1).astype(np.float32)]
+            if case % 2 == 1:            # ties
+                scores[3] = scores[2]
+                scores[1] = scores[2] if case == 3 else scores[1]
+                scores[5] = min(scores[1:n - 1]) if n > 7 else scores[5]
+            table = list(range(50, 50 + n))
+            tabs = {"r0": {0: table}}
+            impl.block_l2norm_mgr.update_reqs(tabs)
+            impl.block_l2norm_mgr.update_block_l2norms(0, list(scores))
+            kv = torch.zeros(2, 128, 16 * 2 * 64, dtype=torch.bfloat16)
+            md = types.SimpleNamespace(
+                seq_lens=[16 * 20], reqid_mapping_blocktables=tabs,
+                decode_metadata=types.SimpleNamespace(
+                    block_tables=torch.tensor([table], dtype=torch.int32)))
+            upd, mapping, pruned = impl._prune_decode_reqs_topk(kv, md)
+            assert pruned
+            rows.append({"method": method, "topk": topk, "n_blocks": n,
+                         # list the function scanned = given scores + appended last-block score (0.0)
+                         "scores": scores + [0.0], "rmv_idx": mapping[0][1],
+                         "out_table": upd[0].tolist()})
+    g["argmin"] = rows
+    return g
+
+
+# ------------------------------------------------------------------ native-op KATs
+def ops_kats():
+    out = {}
+    nb, bs, Hkv, Hq, D = 48, 16, 2, 8, 64
+    kv = torch.zeros(2, nb, bs * Hkv * D, dtype=torch.bfloat16)
+    kc, vc = HEAD.PagedAttention.split_kv_cache(kv, Hkv, D)
+    N = 200
+    slots = np.random.RandomState(1).permutation(nb * bs)[:N].astype(np.int64)
+    slots[11] = -1
+    k, v = rnd(2, N, Hkv, D), rnd(3, N, Hkv, D)
+    ref_cpu.reshape_and_cache(k, v, kc, vc, torch.from_numpy(slots))
+    out["rc_slots"] = slots
+    out["rc_kv_cache"] = kv.view(torch.int16).numpy().copy()      # seeds: k=2, v=3
+    # paged attention over that cache
+    B = 4
+    q = (rnd(4, B, Hq, D).float() * 0.3).to(torch.bfloat16)
+    lens = np.array([1, 16, 37, 160], dtype=np.int32)
+    bt = np.stack([np.random.RandomState(10 + i).permutation(nb)[:10] for i in range(B)]).astype(np.int32)
+    # make the cache dense so every slot read is defined
+    kv2 = (rnd(5, 2, nb, bs * Hkv * D).float() * 0.5).to(torch.bfloat16)
+    kc2, vc2 = HEAD.PagedAttention.split_kv_cache(kv2, Hkv, D)
+    o = torch.empty_like(q)
+    ref_cpu.paged_attention_v1(o, q, kc2, vc2, Hkv, D ** -0.5, torch.from_numpy(bt),
+                               torch.from_numpy(lens), bs, 160)
+    out["pa_block_tables"] = bt
+    out["pa_kv_lens"] = lens
+    out["pa_out"] = o.float().numpy()                               # seeds: q=4*0.3, kv=5*0.5
+    # value_l2 reference formula (fp32, de-paged) for a handful of blocks
+    pr = KVCachePruner("budget", "global", bs, 128, 1)
+    sc = []
+    for blk in range(6):
+        vb = vc2[blk].permute(2, 0, 1).contiguous().float()         # [bs,Hkv,D]
+        sc.append(float(pr.get_block_score(None, vb, "global")))
+    out["score_ref_fp32"] = np.array(sc, dtype=np.float64)
+    return out
+
+
+# ------------------------------------------------------------------ forward() traces
+def drive_forward(mod, method, budget, bs, Hq, Hkv, D, prompt_lens, steps, seed,
+                  disable_evict_prefill=False, random_evict=False, record_scores=False):
+    """Mini engine loop around the reference impl: reference BlockTable for the host
+    bookkeeping, reference builder logic for slot mapping / kv-len adjust, reference
+    forward() for the layer.  One layer (layer 0 is the only one the host listens to)."""
+    impl, pe, cc = make_impl(mod, method, budget, bs, Hq, Hkv, D,
+                             disable_evict_prefill=disable_evict_prefill,
+                             random_evict=random_evict)
+    nblocks = 256
+    kv_cache = torch.zeros(2, nblocks, bs * Hkv * D, dtype=torch.bfloat16)
+    alloc = CpuGpuBlockAllocator.create("naive", nblocks, 0, bs)
+    fake = types.SimpleNamespace(sliding_window=None)
+    B = len(prompt_lens)
+    bts, toks = [], []
+    for q in prompt_lens:
+        bt = BlockTable(bs, alloc, paged_evict_config=pe)
+        t = list(range(q))
+        bt.allocate(t)
+        bts.append(bt)
+        toks.append(t)
+    trace = {"cfg": dict(method=method, budget=budget, bs=bs, Hq=Hq, Hkv=Hkv, D=D,
+                         prompt_lens=prompt_lens, steps=steps, seed=seed,
+                         disable_evict_prefill=disable_evict_prefill, module=mod.__name__),
+             "steps": []}
+    arrays = {}
+
+    def run(is_prompt, step):
+        seq_lens = [len(t) for t in toks]
+        tabs = {f"r{i}": {i: list(bts[i].physical_block_ids)} for i in range(B)}
+        kv_lens = [bts[i].get_seq_kv_len() for i in range(B)]
+        slot = []
+        if is_prompt:
+            n_tok = sum(seq_lens)
+            for i in range(B):
+                HEAD.TorchCUDASDPAMetadataBuilder._compute_slot_mapping(
+                    fake, False, True, slot, i, seq_lens[i], 0, bs, tabs[f"r{i}"])
+        else:
+            n_tok = B
+            for i in range(B):
+                if seq_lens[i] > budget and seq_lens[i] % bs == 0:   # model_runner.py:540-543
+                    kv_lens[i] -= bs
+                HEAD.TorchCUDASDPAMetadataBuilder._compute_slot_mapping(
+                    fake, False, False, slot, i, 1, seq_lens[i] - 1, bs, tabs[f"r{i}"])
+        q = (rnd(seed * 1000 + step * 3 + 0, n_tok, Hq * D).float() * 0.5).to(torch.bfloat16)
+        k = (rnd(seed * 1000 + step * 3 + 1, n_tok, Hkv * D).float() * 0.5).to(torch.bfloat16)
+        v = rnd(seed * 1000 + step * 3 + 2, n_tok, Hkv * D)
+        from vllm.utils import make_tensor_with_pad
+        block_tables = make_tensor_with_pad(
+            [[] if is_prompt else tabs[f"r{i}"][i] for i in range(B)], pad=0, dtype=torch.int)
+        md = mod.TorchCUDASDPAMetadata(
+            num_prefills=B if is_prompt else 0,
+            num_prefill_tokens=n_tok if is_prompt else 0,
+            num_decode_tokens=0 if is_prompt else B,
+            slot_mapping=torch.tensor(slot, dtype=torch.long),
+            multi_modal_placeholder_index_maps=None,
+            seq_lens_tensor=torch.tensor(seq_lens, dtype=torch.int),
+            max_prefill_seq_len=max(seq_lens) if is_prompt else 0,
+            max_decode_seq_len=0 if is_prompt else max(seq_lens),
+            use_cuda_graph=False,
+            seq_lens=seq_lens,
+            seq_start_loc=None, context_lens_tensor=None,
+            max_query_len=max(seq_lens) if is_prompt else 1,
+            max_decode_query_len=1, query_start_loc=None,
+            block_tables=block_tables,
+            seq_kv_lens=kv_lens,
+            seq_kv_lens_tensor=torch.tensor(kv_lens, dtype=torch.int),
+            reqid_mapping_blocktables=tabs)
+        CAPTURE.clear()
+        out = impl.forward(q, k, v, kv_cache, md)
+        rmv = impl.get_rmv_block_idx()
+        rec = {"is_prompt": is_prompt, "seq_lens": seq_lens, "kv_lens": kv_lens,
+               "tables": [tabs[f"r{i}"][i] for i in range(B)], "slots": slot,
+               "rmv": {str(kk): [vv[0], int(vv[1])] for kk, vv in rmv.items()}}
+        if "decode_block_tables" in CAPTURE:
+            rec["attn_tables"] = CAPTURE["decode_block_tables"].tolist()
+            rec["attn_kv_lens"] = CAPTURE["decode_kv_lens"].tolist()
+        if record_scores:
+            rec["l2norms"] = {rid: [float(x) for x in d[int(rid[1:])]]
+                              for rid, d in impl.block_l2norm_mgr.reqid_mapping_block_l2norms.items()}
+        arrays[f"out_{step}"] = out.float().numpy()
+        trace["steps"].append(rec)
+        # engine feedback (llm_engine.py:1179-1193 -> scheduler.py:1879-1890)
+        for row, (rid, idx) in rmv.items():
+            bts[int(rid[1:])].free_prunned_blocks(idx)
+
+    run(True, 0)
+    for s in range(1, steps + 1):
+        for i in range(B):
+            toks[i].append(len(toks[i]))
+            bts[i].append_token_ids([toks[i][-1]])
+        run(False, s)
+    arrays["kv_cache_final"] = kv_cache.view(torch.int16).numpy().copy()
+    return trace, arrays
+
+
+def main():
+    os.makedirs(OUT, exist_ok=True)
+    with open(os.path.join(OUT, "ref_policy.json"), "w") as f:
+        json.dump(policy_kats(), f, separators=(",", ":"))
+    np.savez_compressed(os.path.join(OUT, "ref_ops.npz"), **ops_kats())
+
+    traces = {}
+    arrs = {}
+    runs = {
+        # HEAD, single row (HEAD's compaction is only correct for row 0)
+        "head_stream_b1": (HEAD, "streamingLLM", 128, 16, 8, 2, 64, [200], 40, 1, False),
+        # v1 module: list-based compaction, correct for every row
+        "v1_stream_b3": (V1, "streamingLLM", 128, 16, 8, 2, 64, [200, 131, 100], 60, 2, False),
+        # prune after attention (what scripts/*.sh use)
+        "v1_stream_b2_noprefillevict": (V1, "streamingLLM", 128, 16, 4, 4, 128, [150, 128], 20, 3, True),
+    }
+    for name, (mod, m, bud, bs, Hq, Hkv, D, pl, st, seed, dep) in runs.items():
+        tr, ar = drive_forward(mod, m, bud, bs, Hq, Hkv, D, pl, st, seed, disable_evict_prefill=dep)
+        traces[name] = tr
+        for k, v in ar.items():
+            arrs[f"{name}__{k}"] = v.astype(np.float16) if v.dtype == np.float32 else v
+    # HEAD global with the L2 branch switched on: kept for the argmin bookkeeping only
+    # (scores carry the reference's layout/dtype/ordering quirks).
+    tr, _ = drive_forward(HEAD, "global", 128, 16, 8, 2, 64, [200], 40, 4, False,
+                          random_evict=False, record_scores=True)
+    traces["head_global_b1_quirks"] = tr
+    with open(os.path.join(OUT, "ref_forward.json"), "w") as f:
+        json.dump(traces, f, separators=(",", ":"))
+    np.savez_compressed(os.path.join(OUT, "ref_forward.npz"), **arrs)
+    for fn in sorted(os.listdir(OUT)):
+        print(fn, os.path.getsize(os.path.join(OUT, fn)))
+
+
+if __name__ == "__main__":
+    main()

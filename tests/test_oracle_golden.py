@@ -1,0 +1,171 @@
+"""Pin the oracle against vectors produced by the REFERENCE's own code
+(tests/golden/make_golden.py ran /root/reference's Python classes and its CPU kernels).
+CPU only."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import paged_ops, policy, scoring
+from oracle.backend import OracleLayer
+from oracle.policy import Policy
+from tests.util import load_json, load_npz, rnd, step_inputs
+
+POL = load_json("ref_policy.json")
+
+
+def test_budget_lengths():
+    # page_evict_kv_util.py:6-36 and kvcache_prunner.py:284-326
+    for bs, budget, q, nb, kept_util, kept_pruner in POL["budget_lengths"]:
+        p = Policy(block_size=bs, cache_prune_type="budget", cache_budget=budget)
+        assert policy.num_required_blocks_after_prune(q, p) == (nb, kept_util), (bs, budget, q)
+        assert policy.prompt_prune_layout(q, p)[0] == kept_pruner, (bs, budget, q)
+
+
+def test_budget_gather():
+    # kvcache_prunner.py:183-218
+    for row in POL["budget_gather"]:
+        p = Policy(block_size=row["bs"], cache_budget=row["budget"])
+        assert policy.prompt_gather_index(row["q_len"], p).tolist() == row["kept_src"]
+
+
+def test_percentage_lengths():
+    # page_evict_kv_util_bak.py:6-31, kvcache_prunner_old.py:141-200
+    for bs, freq, q, nb, kept, first, pruned in POL["percentage_lengths"]:
+        p = Policy(block_size=bs, cache_prune_type="percentage", evict_freq=freq)
+        k, pr, f = policy.prompt_prune_layout(q, p)
+        assert k == kept and policy.cdiv(k, bs) == nb, (bs, freq, q)
+        if pruned:
+            assert (f, pr) == (first, pruned), (bs, freq, q)
+            gi = policy.prompt_gather_index(q, p)
+            assert gi[first - 1] == first - 1 and gi[first] == first + pruned
+        else:
+            assert pr == 0
+
+
+def test_readme_eviction_fractions():
+    # q_len 1024, bs 16 -> freq 2 keeps 544, freq 4 keeps 784
+    assert policy.prompt_prune_layout(1024, Policy(cache_prune_type="percentage", evict_freq=2))[0] == 544
+    assert policy.prompt_prune_layout(1024, Policy(cache_prune_type="percentage", evict_freq=4))[0] == 784
+
+
+def test_slot_mapping():
+    # torch_cuda_sdpa.py:565-598
+    for row in POL["slot_mapping"]:
+        if row["is_prompt"]:
+            got = policy.prefill_slot_mapping(row["table"], row["query_len"], row["bs"])
+        else:
+            got = [policy.decode_slot_mapping(row["table"], row["context_len"], row["bs"])]
+        assert got == row["slots"]
+
+
+def test_compaction():
+    # torch_cuda_sdpa.py:1562-1586 (row 0) and torch_cuda_sdpa_v1.py list semantics
+    for row in POL["compact_row0"]:
+        t = np.array([row["table"]], dtype=np.int32)
+        out = policy.compact_block_tables(t, [len(row["table"])], {0: row["idx"]})
+        assert out[0, :len(row["out"])].tolist() == row["out"]
+        assert out[0, len(row["out"]):].tolist() == [0] * (t.shape[1] - len(row["out"]))
+    c = POL["compact_v1"]
+    M = max(len(t) for t in c["tables"])
+    t = np.zeros((len(c["tables"]), M), dtype=np.int32)
+    for i, row in enumerate(c["tables"]):
+        t[i, :len(row)] = row
+    n = [len(r) for r in c["tables"]]
+    vict = {int(k): v for k, v in c["victims"].items()}
+    out = policy.compact_block_tables(t, n, vict)
+    n_after = [n[i] - (1 if i in vict else 0) for i in range(len(n))]
+    assert policy.narrow_compacted(out, n_after).tolist() == c["out"]
+
+
+def test_argmin_and_windows():
+    # torch_cuda_sdpa.py:1528-1544
+    for row in POL["argmin"]:
+        p = Policy(decode_evict_method="value_l2",
+                   topk_blocks=-1 if row["method"] == "global" else row["topk"])
+        lo, hi = policy.victim_candidates(row["n_blocks"], p)
+        sc = np.array(row["scores"], dtype=np.float32)
+        idx = policy.argmin_lowest_index(sc, lo, hi)
+        assert idx == row["rmv_idx"], row
+        t = np.arange(50, 50 + row["n_blocks"], dtype=np.int32)[None]
+        out = policy.compact_block_tables(t, [row["n_blocks"]], {0: idx})
+        assert out[0, :row["n_blocks"] - 1].tolist() == row["out_table"]
+
+
+def test_decode_trigger_matches_block_table_trace():
+    # model_runner.py:540-543 + block_table.py:136-196,462-466
+    for row in POL["block_table_trace"]:
+        p = Policy(block_size=row["bs"], cache_budget=row["budget"], decode_evict_method="streamingLLM")
+        first = row["trace"][0]
+        nb, kept = policy.num_required_blocks_after_prune(row["q_len"], p)
+        assert kept == first["kv_len"] and nb == len(first["ids"])
+        for rec in row["trace"][1:]:
+            assert policy.decode_trigger(rec["seq_len"], rec["kv_len"], p) == rec["trigger"]
+
+
+def test_native_ops_against_reference_cpu_kernels():
+    g = load_npz("ref_ops.npz")
+    nb, bs, Hkv, Hq, D = 48, 16, 2, 8, 64
+    kv = torch.zeros(2, nb, bs * Hkv * D, dtype=torch.bfloat16)
+    kc, vc = paged_ops.split_kv_cache(kv, Hkv, D)
+    paged_ops.reshape_and_cache(rnd(2, 200, Hkv, D), rnd(3, 200, Hkv, D), kc, vc,
+                                torch.from_numpy(g["rc_slots"]))
+    assert np.array_equal(kv.view(torch.int16).numpy(), g["rc_kv_cache"])     # exact
+    q = (rnd(4, 4, Hq, D).float() * 0.3).to(torch.bfloat16)
+    kv2 = (rnd(5, 2, nb, bs * Hkv * D).float() * 0.5).to(torch.bfloat16)
+    kc2, vc2 = paged_ops.split_kv_cache(kv2, Hkv, D)
+    o = paged_ops.paged_attention(q, kc2, vc2, g["pa_block_tables"].tolist(),
+                                  g["pa_kv_lens"].tolist(), D ** -0.5)
+    # reference test bar: atol 1e-3 (tests/kernels/test_attention.py:323-328) on fp32 math;
+    # both sides round the output to bf16 here, so allow one bf16 ulp at |x|<0.5 (2^-9)
+    np.testing.assert_allclose(o.float().numpy(), g["pa_out"], atol=2e-3, rtol=0)
+    # value_l2 definition vs get_block_score (kvcache_prunner.py:55) evaluated in fp32
+    for blk, ref in enumerate(g["score_ref_fp32"]):
+        vb = paged_ops.depage_v_block(vc2, blk).float().numpy()
+        got = float(scoring.block_score(vb))
+        assert abs(got - ref) <= 2e-5 * abs(ref), (blk, got, ref)
+        assert abs(scoring.reference_formula_fp32(vb) - ref) <= 2e-5 * abs(ref)
+
+
+@pytest.mark.parametrize("name", ["head_stream_b1", "v1_stream_b3", "v1_stream_b2_noprefillevict"])
+def test_forward_trace_streaming(name):
+    """Replay the reference forward() traces through the oracle layer: slot mappings,
+    victims, tables handed to attention, kv lens are exact; outputs within bf16 tol."""
+    tr = load_json("ref_forward.json")[name]
+    arr = load_npz("ref_forward.npz")
+    c = tr["cfg"]
+    p = Policy(block_size=c["bs"], cache_budget=c["budget"], decode_evict_method="streamingLLM",
+               disable_evict_prefill=c["disable_evict_prefill"])
+    layer = OracleLayer(c["Hq"], c["D"], c["D"] ** -0.5, c["Hkv"], p, head_compat_uncompacted=True)
+    kv = torch.zeros(2, 256, c["bs"] * c["Hkv"] * c["D"], dtype=torch.bfloat16)
+    B = len(c["prompt_lens"])
+    rids = [f"r{i}" for i in range(B)]
+    for step, rec in enumerate(tr["steps"]):
+        n_tok = sum(rec["seq_lens"]) if rec["is_prompt"] else B
+        q, k, v = step_inputs(c["seed"], step, n_tok, c["Hq"], c["Hkv"], c["D"])
+        if rec["is_prompt"]:
+            out = layer.prefill(q, k, v, kv, rec["seq_lens"], rec["tables"], rids)
+            assert layer.last["kept"] == rec["kv_lens"]
+        else:
+            out, rmv, attn_tables = layer.decode(q, k, v, kv, rec["seq_lens"], rec["kv_lens"],
+                                                 rec["tables"], rids)
+            assert {str(r): [rid, idx] for r, (rid, idx) in rmv.items()} == rec["rmv"]
+            assert rec["attn_kv_lens"] == rec["kv_lens"]
+            for r in range(B):      # tables the reference handed to paged_attention (0-padded)
+                n = len(attn_tables[r])
+                assert rec["attn_tables"][r][:n] == attn_tables[r]
+        assert layer.last["slots"] == rec["slots"]
+        ref = arr[f"{name}__out_{step}"].astype(np.float32)
+        np.testing.assert_allclose(out.float().numpy(), ref, atol=2e-2, rtol=0)
+    assert np.array_equal(kv.view(torch.int16).numpy(), arr[f"{name}__kv_cache_final"])
+
+
+def test_value_l2_definition_properties():
+    rs = np.random.RandomState(0)
+    v = torch.from_numpy(rs.standard_normal((16, 8, 128)).astype(np.float32)).to(torch.bfloat16).float().numpy()
+    ph = scoring.per_head_block_score(v)
+    assert ph.dtype == np.float32 and ph.shape == (8,)
+    # per-head partials are independent (TP sharding by kv head relies on it)
+    for h in range(8):
+        assert scoring.per_head_block_score(v[:, h:h + 1])[0] == ph[h]
+    ref = scoring.reference_formula_fp32(v)
+    assert abs(float(scoring.combine_heads(ph)) - ref) < 1e-5 * ref
