@@ -1,0 +1,166 @@
+/*
+ * pagedevict_b200.h -- C ABI of libpagedevict_b200.so: the B200 (sm_100a) native
+ * implementation of the PagedCompression / "paged eviction" hot path of
+ * krishnateja95/vllm-Paged-Compression.
+ *
+ * This is the drop-in boundary.  The reference binds this path through a torch C++
+ * extension (TORCH_LIBRARY ops called from vllm/_custom_ops.py); each entry point
+ * below states the reference interface it replaces.  Plain pointers and sizes only:
+ * every pointer is a CUDA DEVICE pointer unless marked HOST; `stream` is a
+ * cudaStream_t passed as void* (NULL = legacy default stream).  All calls are
+ * asynchronous on `stream`.  No call allocates or frees device memory, keeps a
+ * reference to caller memory after returning, or synchronises the device.
+ *
+ * Error convention: every function returns 0 on success or a negative pc_status; the
+ * message is available from pc_last_error() (thread-local).  This mirrors the
+ * reference's TORCH_CHECK(false, "...") -> RuntimeError convention
+ * (csrc/attention/paged_attention_v1.cu:108-110,160-162); the Python host raises
+ * RuntimeError(pc_last_error()).
+ *
+ * Layouts (vllm/attention/ops/paged_attn.py:40-62), element type bf16:
+ *   key_cache   [num_blocks][num_kv_heads][head_size/8][block_size][8]
+ *   value_cache [num_blocks][num_kv_heads][head_size][block_size]
+ * kv_block_stride = elements between consecutive blocks (num_kv_heads*head_size*block_size
+ * for a dense pool).  Supported: head_size 64|128, block_size 16|32, dtype bf16.
+ */
+#ifndef PAGEDEVICT_B200_H_
+#define PAGEDEVICT_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PC_ABI_VERSION 1
+
+typedef enum pc_status {
+  PC_OK = 0,
+  PC_ERR_INVALID = -1,     /* bad argument (shape, alignment, null pointer) */
+  PC_ERR_UNSUPPORTED = -2, /* head size / block size / dtype not built */
+  PC_ERR_CUDA = -3         /* CUDA runtime error at launch */
+} pc_status;
+
+typedef enum pc_dtype { PC_BF16 = 0 } pc_dtype;
+
+/* Eviction policy = vllm/config.py:933-991 PagedEvictConfig (budget mode, HEAD) plus
+ * the README-era percentage / evict_freq fields (benchmarks/llama3.1_8b_test.txt:1). */
+typedef struct pc_evict_policy {
+  int32_t prune_type;      /* 0 = budget, 1 = percentage (evict_freq) */
+  int32_t block_size;
+  int32_t cache_budget;    /* budget mode */
+  int32_t evict_freq;      /* percentage mode: one block per evict_freq blocks */
+  int32_t initial_blocks;  /* sink blocks, reference hard-codes 1 */
+  int32_t num_block_merge; /* percentage mode lower bound, reference default 2 */
+  int32_t decode_method;   /* 0 = streamingLLM (victim = block 1), 1 = value_l2 argmin */
+  int32_t topk_blocks;     /* <0: global window [1, n-1); >0: local window [1, 1+topk) */
+} pc_evict_policy;
+
+int pc_abi_version(void);
+const char* pc_last_error(void);
+/* SM count of the current device (grid sizing is derived from it). */
+int pc_device_sm_count(void);
+
+/* ---- W1: reshape_and_cache --------------------------------------------------------
+ * Replaces _C_cache_ops::reshape_and_cache (csrc/torch_bindings.cpp:444-450,
+ * csrc/cache_kernels.cu:152-205,263-287; python vllm/_custom_ops.py:984-996).
+ * key/value [num_tokens][num_kv_heads][head_size] with row strides key_stride /
+ * value_stride (elements, multiples of 8, 16-byte aligned rows).  slot_mapping int64
+ * [num_tokens]; slot < 0 = skip (PAD_SLOT_ID).  Bit-exact copy. */
+int pc_reshape_and_cache(const void* key, const void* value, void* key_cache, void* value_cache,
+                         const int64_t* slot_mapping, int32_t num_tokens, int32_t num_kv_heads,
+                         int32_t head_size, int32_t block_size, int64_t key_stride,
+                         int64_t value_stride, int64_t kv_block_stride, int32_t dtype,
+                         void* stream);
+
+/* ---- R1 + W1 + S3: prompt prune, cache write and prompt block scoring in one pass ---
+ * Replaces _prune_prompts_keys_and_values_new + prune_prompt_inplace + _update_kvcache
+ * (vllm/attention/backends/torch_cuda_sdpa.py:1222-1296,1129-1171;
+ * vllm/attention/kvcache_prunner.py:167-218) and the prompt block scoring loop
+ * (torch_cuda_sdpa.py:1278-1288).  No intermediate pruned K/V tensor is materialised.
+ * req_meta int32 [num_reqs][5] = {src_start, kept, first, pruned, dst_start}: request r
+ * keeps source rows src_start + (j < first ? j : j + pruned), j in [0, kept), written
+ * at slot_mapping[dst_start + j].  tile_offsets int32 [num_reqs+1] = prefix sum of
+ * ceil(kept/block_size).  score_table may be NULL (no scoring); otherwise every FULL
+ * kept block j of request r gets score_table[score_slots[r]][j][h] (fp32 per-head
+ * value_l2 partial, fixed reduction order, see csrc/score_common.cuh). */
+int pc_prune_prompt_and_cache(const void* key, const void* value, void* key_cache,
+                              void* value_cache, const int64_t* slot_mapping,
+                              const int32_t* req_meta, const int32_t* tile_offsets,
+                              int32_t num_reqs, int32_t total_tiles, int32_t num_kv_heads,
+                              int32_t head_size, int32_t block_size, int64_t key_stride,
+                              int64_t value_stride, int64_t kv_block_stride, float* score_table,
+                              const int32_t* score_slots, int32_t score_max_blocks,
+                              int32_t dtype, void* stream);
+
+/* ---- P3 + S4 + C1 + C2: decode trigger, victim argmin, table/score compaction -------
+ * Replaces _prune_decode_reqs_streamingLLM / _prune_decode_reqs_topk /
+ * _create_updated_block_tables (torch_cuda_sdpa.py:1375-1433,1478-1586) and
+ * BlockL2NormManager.get_updated_block_tables (block_l2norm_manager.py:95-106).
+ * Row r owns n_blocks[r] table entries.  Triggered rows (policy on seq_lens[r] and
+ * n_blocks[r]*block_size) lose entry out_victim[r]: out_tables row = input row with that
+ * column deleted, shifted left, 0-padded to out_stride; the score row is compacted the
+ * same way in place.  Other rows are copied; out_victim = -1.  out_kv_lens[r] =
+ * kv_lens[r] - (triggered && !kv_lens_pre_adjusted ? block_size : 0).  Ties in the
+ * argmin go to the lowest index (strict <, torch_cuda_sdpa.py:1536-1541). */
+int pc_evict_select_compact(const int32_t* block_tables, int64_t table_stride,
+                            const int32_t* n_blocks, const int32_t* seq_lens,
+                            const int32_t* kv_lens, int32_t batch,
+                            const pc_evict_policy* policy /* HOST */, float* score_table,
+                            const int32_t* score_slots, int32_t score_max_blocks,
+                            int32_t num_kv_heads, int32_t* out_tables, int64_t out_stride,
+                            int32_t* out_kv_lens, int32_t* out_victim,
+                            int32_t kv_lens_pre_adjusted, void* stream);
+
+/* ---- A2 + S2: paged decode attention with fused last-block scoring ------------------
+ * Replaces _C::paged_attention_v1 / paged_attention_v2 (csrc/torch_bindings.cpp:27-51,
+ * csrc/attention/attention_kernels.cuh:86-668, python vllm/_custom_ops.py:70-130,
+ * vllm/attention/ops/paged_attn.py:87-191) and the last-block scoring read of
+ * torch_cuda_sdpa.py:1518-1526.  query/out [batch][num_heads][head_size] with row
+ * strides q_stride / out_stride (elements).  kv_lens = physical KV lengths.  If
+ * score_table != NULL and seq_lens != NULL, rows with seq_lens[b] % block_size == 0
+ * get score_table[score_slots[b]][ceil(kv_len/bs)-1][h] for every kv head h.
+ * workspace: pc_paged_decode_workspace_bytes() bytes, 256-byte aligned, reusable. */
+size_t pc_paged_decode_workspace_bytes(int32_t batch, int32_t num_heads, int32_t num_kv_heads,
+                                       int32_t head_size, int32_t block_size,
+                                       int32_t max_kv_len);
+int pc_paged_decode_attn_score(void* out, const void* query, const void* key_cache,
+                               const void* value_cache, const int32_t* block_tables,
+                               int64_t table_stride, const int32_t* kv_lens, int32_t batch,
+                               int32_t num_heads, int32_t num_kv_heads, int32_t head_size,
+                               int32_t block_size, int32_t max_kv_len, float scale,
+                               int64_t q_stride, int64_t out_stride, int64_t kv_block_stride,
+                               const int32_t* seq_lens, float* score_table,
+                               const int32_t* score_slots, int32_t score_max_blocks,
+                               void* workspace, size_t workspace_bytes, int32_t dtype,
+                               void* stream);
+
+/* ---- A1: prefill attention, TOP-LEFT aligned causal mask over the pruned prompt -----
+ * Replaces _run_sdpa_forward (torch_cuda_sdpa.py:1069-1127): per request
+ * scaled_dot_product_attention(q[Lq], k[Lkv], v[Lkv], is_causal=True), GQA by head
+ * grouping instead of repeat_interleave; query i sees kv j <= i.
+ * K/V rows are read through the same gather as pc_prune_prompt_and_cache, so the
+ * pruned K/V never exists in memory.  req_meta int32 [num_reqs][6] =
+ * {q_start, q_len, kv_src_start, kv_len(kept), first, pruned}. */
+int pc_prefill_attn_topleft_causal(void* out, const void* query, const void* key,
+                                   const void* value, const int32_t* req_meta,
+                                   int32_t num_reqs, int32_t max_q_len, int32_t num_heads,
+                                   int32_t num_kv_heads, int32_t head_size, float scale,
+                                   int64_t q_stride, int64_t out_stride, int64_t key_stride,
+                                   int64_t value_stride, int32_t dtype, void* stream);
+
+/* ---- block maintenance (backend surface, torch_cuda_sdpa.py:75-88) ------------------
+ * pc_copy_blocks replaces _C_cache_ops::copy_blocks (csrc/cache_kernels.cu:69-150) for
+ * one layer: pairs int64 [num_pairs][2] = {src_block, dst_block}, same pool.
+ * pc_swap_blocks replaces swap_blocks (csrc/cache_kernels.cu:24-66): block-granular
+ * copies between two pools (either may be pinned host memory); pairs is a HOST array. */
+int pc_copy_blocks(void* key_cache, void* value_cache, const int64_t* pairs, int32_t num_pairs,
+                   int64_t block_bytes, void* stream);
+int pc_swap_blocks(const void* src, void* dst, const int64_t* pairs /* HOST */,
+                   int32_t num_pairs, int64_t block_bytes, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PAGEDEVICT_B200_H_ */
