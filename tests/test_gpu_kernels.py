@@ -1,0 +1,425 @@
+"""GPU parity tests: every kernel through the C ABI (vllm_paged_compression_b200.ops)
+against the CPU oracle on the same seeded inputs.  Integer/byte/index results are
+bit-exact; attention outputs within the bf16 tolerance of BASELINE.json (atol 2e-2; the
+tests use the tighter bars noted inline where the arithmetic allows).
+
+Mirrors the reference's own kernel tests: tests/kernels/test_cache.py:121-205
+(reshape_and_cache, exact) and tests/kernels/test_attention.py:122-330 (paged attention
+vs ref_single_query_cached_kv_attention).
+"""
+import numpy as np
+import pytest
+import torch
+
+from oracle import paged_ops, policy, scoring
+from oracle.policy import Policy
+from tests.util import load_npz, rnd
+
+pytestmark = pytest.mark.gpu
+
+DEV = "cuda:0"
+
+
+def _ops():
+    from vllm_paged_compression_b200 import ops
+    return ops
+
+
+def _pool(seed, nb, bs, Hkv, D, scale=0.5):
+    kv = (rnd(seed, 2, nb, bs * Hkv * D).float() * scale).to(torch.bfloat16)
+    return kv
+
+
+def _bits(t):
+    return t.detach().cpu().contiguous().view(torch.int16).numpy()
+
+
+# --------------------------------------------------------------------------- W1
+@pytest.mark.parametrize("D", [64, 128])
+@pytest.mark.parametrize("bs", [16, 32])
+@pytest.mark.parametrize("n_tok", [1, 7, 200, 1000])
+def test_reshape_and_cache_exact(D, bs, n_tok):
+    ops = _ops()
+    Hkv, nb = 4, 96
+    rs = np.random.RandomState(n_tok * 7 + D + bs)
+    slots = rs.permutation(nb * bs)[:n_tok].astype(np.int64)
+    slots[rs.rand(n_tok) < 0.1] = -1                      # PAD_SLOT_ID rows are skipped
+    key, value = rnd(1, n_tok, Hkv, D), rnd(2, n_tok, Hkv, D)
+    kv_ref = _pool(3, nb, bs, Hkv, D)
+    kv_dev = kv_ref.clone().to(DEV)
+    kc, vc = paged_ops.split_kv_cache(kv_ref, Hkv, D)
+    paged_ops.reshape_and_cache(key, value, kc, vc, torch.from_numpy(slots))
+    kcd, vcd = paged_ops.split_kv_cache(kv_dev, Hkv, D)
+    ops.reshape_and_cache(key.to(DEV), value.to(DEV), kcd, vcd, torch.from_numpy(slots).to(DEV))
+    torch.cuda.synchronize()
+    assert np.array_equal(_bits(kv_dev), _bits(kv_ref))
+
+
+def test_reshape_and_cache_contiguous_block_fast_path_and_strided_rows():
+    """Whole-block tiles take the vectorised V path; key/value are column slices of a
+    fused qkv activation (row stride > Hkv*D) as in llama.py:195-207."""
+    ops = _ops()
+    Hkv, D, bs, nb = 8, 128, 16, 64
+    n_tok = 5 * bs
+    qkv = rnd(11, n_tok, (32 + 2 * Hkv) * D)
+    key = qkv[:, 32 * D:(32 + Hkv) * D]
+    value = qkv[:, (32 + Hkv) * D:]
+    blocks = [9, 3, 40, 41, 7]
+    slots = torch.tensor([b * bs + i for b in blocks for i in range(bs)], dtype=torch.int64)
+    kv_ref = torch.zeros(2, nb, bs * Hkv * D, dtype=torch.bfloat16)
+    kv_dev = kv_ref.clone().to(DEV)
+    kc, vc = paged_ops.split_kv_cache(kv_ref, Hkv, D)
+    paged_ops.reshape_and_cache(key.reshape(n_tok, Hkv, D), value.reshape(n_tok, Hkv, D), kc, vc, slots)
+    qkv_d = qkv.to(DEV)
+    kcd, vcd = paged_ops.split_kv_cache(kv_dev, Hkv, D)
+    ops.reshape_and_cache(qkv_d[:, 32 * D:(32 + Hkv) * D], qkv_d[:, (32 + Hkv) * D:], kcd, vcd,
+                          slots.to(DEV))
+    torch.cuda.synchronize()
+    assert np.array_equal(_bits(kv_dev), _bits(kv_ref))
+
+
+def test_reshape_and_cache_empty_and_errors():
+    ops = _ops()
+    Hkv, D, bs, nb = 2, 64, 16, 4
+    kv = torch.zeros(2, nb, bs * Hkv * D, dtype=torch.bfloat16, device=DEV)
+    kc, vc = paged_ops.split_kv_cache(kv, Hkv, D)
+    e = torch.empty(0, Hkv, D, dtype=torch.bfloat16, device=DEV)
+    ops.reshape_and_cache(e, e, kc, vc, torch.empty(0, dtype=torch.int64, device=DEV))   # no-op
+    with pytest.raises(RuntimeError):      # fp8 / scales rejected like torch_cuda_sdpa.py:769-772
+        ops.reshape_and_cache(e, e, kc, vc, torch.empty(0, dtype=torch.int64, device=DEV), "fp8")
+    kv96 = torch.zeros(2, nb, bs * Hkv * 96, dtype=torch.bfloat16, device=DEV)
+    kc96, vc96 = paged_ops.split_kv_cache(kv96, Hkv, 96)
+    k96 = torch.zeros(1, Hkv, 96, dtype=torch.bfloat16, device=DEV)
+    with pytest.raises(RuntimeError, match="Unsupported head size"):
+        ops.reshape_and_cache(k96, k96, kc96, vc96, torch.zeros(1, dtype=torch.int64, device=DEV))
+
+
+def test_reshape_and_cache_golden_from_reference_cpu_kernel():
+    """tests/golden/ref_ops.npz was written by the reference's csrc/cpu/cache.cpp."""
+    ops = _ops()
+    g = load_npz("ref_ops.npz")
+    nb, bs, Hkv, D = 48, 16, 2, 64
+    kv = torch.zeros(2, nb, bs * Hkv * D, dtype=torch.bfloat16, device=DEV)
+    kc, vc = paged_ops.split_kv_cache(kv, Hkv, D)
+    ops.reshape_and_cache(rnd(2, 200, Hkv, D).to(DEV), rnd(3, 200, Hkv, D).to(DEV), kc, vc,
+                          torch.from_numpy(g["rc_slots"]).to(DEV))
+    torch.cuda.synchronize()
+    assert np.array_equal(_bits(kv), g["rc_kv_cache"])
+
+
+# --------------------------------------------------------------------- R1 + W1 + S3
+def _prompt_batch(prompt_lens, pol, nb, rs):
+    """Host-side metadata the backend builds for a prefill batch."""
+    bs = pol.block_size
+    free = list(rs.permutation(nb))
+    tables, slots, meta, tile_off = [], [], [], [0]
+    src = dst = 0
+    for L in prompt_lens:
+        kept, pruned, first = policy.prompt_prune_layout(L, pol)
+        n = policy.cdiv(kept, bs)
+        tab = [int(free.pop()) for _ in range(n)]
+        tables.append(tab)
+        s = policy.prefill_slot_mapping(tab, L, bs)
+        assert len(s) == kept
+        slots.extend(s)
+        meta.append([src, kept, first, pruned, dst])
+        tile_off.append(tile_off[-1] + n)
+        src += L
+        dst += kept
+    return tables, slots, meta, tile_off
+
+
+@pytest.mark.parametrize("D,bs", [(64, 16), (128, 16), (128, 32)])
+@pytest.mark.parametrize("mode", ["budget", "percentage"])
+def test_prune_prompt_and_cache(D, bs, mode):
+    ops = _ops()
+    Hkv, nb = 4, 256
+    pol = Policy(block_size=bs, cache_prune_type=mode, cache_budget=8 * bs, evict_freq=2)
+    prompt_lens = [5, bs, 8 * bs, 8 * bs + 1, 13 * bs + 5, 20 * bs]
+    rs = np.random.RandomState(D + bs)
+    tables, slots, meta, tile_off = _prompt_batch(prompt_lens, pol, nb, rs)
+    T = sum(prompt_lens)
+    key, value = rnd(21, T, Hkv, D), rnd(22, T, Hkv, D)
+    # oracle: gather -> reshape_and_cache -> per-block scores
+    kv_ref = torch.zeros(2, nb, bs * Hkv * D, dtype=torch.bfloat16)
+    kc, vc = paged_ops.split_kv_cache(kv_ref, Hkv, D)
+    gidx, s = [], 0
+    for L in prompt_lens:
+        gidx.append(torch.from_numpy(policy.prompt_gather_index(L, pol)) + s)
+        s += L
+    gidx = torch.cat(gidx)
+    paged_ops.reshape_and_cache(key[gidx], value[gidx], kc, vc, torch.tensor(slots))
+    max_blocks = 32
+    ref_scores = np.zeros((len(prompt_lens), max_blocks, Hkv), dtype=np.float32)
+    vp = value[gidx].float().numpy()
+    for r, m in enumerate(meta):
+        for j in range(m[1] // bs):
+            ref_scores[r, j] = scoring.per_head_block_score(vp[m[4] + j * bs: m[4] + (j + 1) * bs])
+    # device
+    kv_dev = torch.zeros_like(kv_ref, device=DEV)
+    kcd, vcd = paged_ops.split_kv_cache(kv_dev, Hkv, D)
+    score = torch.zeros(len(prompt_lens), max_blocks, Hkv, dtype=torch.float32, device=DEV)
+    ops.prune_prompt_and_cache(
+        key.to(DEV), value.to(DEV), kcd, vcd, torch.tensor(slots, dtype=torch.int64, device=DEV),
+        torch.tensor(meta, dtype=torch.int32, device=DEV),
+        torch.tensor(tile_off, dtype=torch.int32, device=DEV), tile_off[-1], score,
+        torch.arange(len(prompt_lens), dtype=torch.int32, device=DEV))
+    torch.cuda.synchronize()
+    assert np.array_equal(_bits(kv_dev), _bits(kv_ref))
+    assert np.array_equal(score.cpu().numpy().view(np.int32), ref_scores.view(np.int32))   # bit-exact
+
+
+# ------------------------------------------------------------------ P3 + S4 + C1 + C2
+def _evict_case(B, M, pol, rs, tie=False):
+    bs = pol.block_size
+    n_blocks = rs.randint(1, M + 1, size=B).astype(np.int32)
+    n_blocks[0] = M
+    tables = np.zeros((B, M), dtype=np.int32)
+    for r in range(B):
+        tables[r, :n_blocks[r]] = rs.permutation(100000)[:n_blocks[r]] + 1
+    # logical lengths: mix of trigger / non-trigger steps
+    seq_lens = np.zeros(B, dtype=np.int32)
+    for r in range(B):
+        base = int(n_blocks[r]) * bs + int(rs.randint(0, 40)) * bs
+        seq_lens[r] = base if rs.rand() < 0.6 else base - int(rs.randint(1, bs))
+    Hkv = 4
+    scores = rs.rand(B, M, Hkv).astype(np.float32) * 50
+    if tie:
+        scores[:, 2:, :] = scores[:, 2:3, :]           # all candidates >= 2 tie; lowest index must win
+    return tables, n_blocks, seq_lens, scores, Hkv
+
+
+@pytest.mark.parametrize("method,topk", [("streamingLLM", -1), ("value_l2", -1), ("value_l2", 3)])
+@pytest.mark.parametrize("mode", ["budget", "percentage"])
+@pytest.mark.parametrize("tie", [False, True])
+def test_evict_select_compact_bit_exact(method, topk, mode, tie):
+    ops = _ops()
+    from vllm_paged_compression_b200._lib import PcEvictPolicy
+    bs, B, M = 16, 37, 70
+    pol = Policy(block_size=bs, cache_prune_type=mode, cache_budget=128, evict_freq=2,
+                 decode_evict_method=method, topk_blocks=topk)
+    rs = np.random.RandomState(5 + (13 if tie else 0))
+    tables, n_blocks, seq_lens, scores, Hkv = _evict_case(B, M, pol, rs, tie)
+    kv_lens = (n_blocks * bs - rs.randint(0, bs, size=B)).astype(np.int32)
+    # oracle
+    victims = {}
+    ref_scores = scores.copy()
+    for r in range(B):
+        n = int(n_blocks[r])
+        if n >= 3 and policy.decode_trigger(int(seq_lens[r]), n * bs, pol):
+            lo, hi = policy.victim_candidates(n, pol)
+            if method == "streamingLLM":
+                victims[r] = 1
+            else:
+                victims[r] = policy.argmin_lowest_index(scoring.combine_heads(scores[r, :n - 1]), lo, hi)
+                v = victims[r]
+                ref_scores[r, v:n - 2] = scores[r, v + 1:n - 1]
+    ref_tables = policy.compact_block_tables(tables, n_blocks, victims)
+    ref_victim = np.array([victims.get(r, -1) for r in range(B)], dtype=np.int32)
+    ref_kv = np.array([kv_lens[r] - (bs if r in victims else 0) for r in range(B)], dtype=np.int32)
+    # device
+    cpol = PcEvictPolicy(0 if mode == "budget" else 1, bs, 128, 2, 1, 2,
+                         0 if method == "streamingLLM" else 1, topk)
+    d = lambda a: torch.from_numpy(a).to(DEV)
+    out_t = torch.full((B, M), -7, dtype=torch.int32, device=DEV)
+    out_kv = torch.zeros(B, dtype=torch.int32, device=DEV)
+    out_v = torch.zeros(B, dtype=torch.int32, device=DEV)
+    sc = d(scores.copy())
+    ops.evict_select_compact(d(tables), d(n_blocks), d(seq_lens), d(kv_lens), cpol, Hkv, out_t, out_kv,
+                             out_v, sc, torch.arange(B, dtype=torch.int32, device=DEV),
+                             kv_lens_pre_adjusted=False)
+    torch.cuda.synchronize()
+    assert np.array_equal(out_v.cpu().numpy(), ref_victim)
+    assert np.array_equal(out_t.cpu().numpy(), ref_tables)
+    assert np.array_equal(out_kv.cpu().numpy(), ref_kv)
+    if method == "value_l2":
+        got = sc.cpu().numpy()
+        for r in range(B):   # live score entries [0, n_after - 1) must equal the compacted oracle row
+            n_after = int(n_blocks[r]) - (1 if r in victims else 0)
+            assert np.array_equal(got[r, :max(n_after - 1, 0)], ref_scores[r, :max(n_after - 1, 0)])
+    assert len(victims) > 3
+
+
+def test_compaction_known_answer_from_survey():
+    """SURVEY.md 8c KAT: [[10..14],[20..24],[30..34]], victim 1 in every row ->
+    [[10,12,13,14],[20,22,23,24],[30,32,33,34]] (v1 semantics; HEAD rows>=1 are buggy)."""
+    ops = _ops()
+    from vllm_paged_compression_b200._lib import PcEvictPolicy
+    t = torch.tensor([[10, 11, 12, 13, 14], [20, 21, 22, 23, 24], [30, 31, 32, 33, 34]],
+                     dtype=torch.int32, device=DEV)
+    n = torch.full((3,), 5, dtype=torch.int32, device=DEV)
+    seq = torch.full((3,), 160, dtype=torch.int32, device=DEV)
+    out_t = torch.zeros(3, 5, dtype=torch.int32, device=DEV)
+    out_v = torch.zeros(3, dtype=torch.int32, device=DEV)
+    ops.evict_select_compact(t, n, seq, None, PcEvictPolicy(0, 16, 128, 2, 1, 2, 0, -1), 1, out_t, None, out_v)
+    assert out_t.cpu().tolist() == [[10, 12, 13, 14, 0], [20, 22, 23, 24, 0], [30, 32, 33, 34, 0]]
+    assert out_v.cpu().tolist() == [1, 1, 1]
+
+
+# ------------------------------------------------------------------------- A2 + S2
+def _decode_case(B, Hq, Hkv, D, bs, max_len, seed, ragged=True, nb=None):
+    rs = np.random.RandomState(seed)
+    kv_lens = (rs.randint(1, max_len + 1, size=B) if ragged else np.full(B, max_len)).astype(np.int32)
+    kv_lens[0] = max_len
+    M = policy.cdiv(max_len, bs)
+    need = int(sum(policy.cdiv(int(l), bs) for l in kv_lens))
+    nb = nb or need + 8
+    perm = rs.permutation(nb)
+    tables = np.zeros((B, M), dtype=np.int32)
+    o = 0
+    for r in range(B):
+        n = policy.cdiv(int(kv_lens[r]), bs)
+        tables[r, :n] = perm[o:o + n]
+        o += n
+    scale = D ** -0.5
+    kv = (rnd(seed + 1, 2, nb, bs * Hkv * D).float() * 0.5).to(torch.bfloat16)
+    q = (rnd(seed + 2, B, Hq, D).float() * 0.5).to(torch.bfloat16)
+    return q, kv, tables, kv_lens, scale
+
+
+@pytest.mark.parametrize("Hq,Hkv,D,bs", [(32, 8, 128, 16), (32, 8, 64, 16), (8, 2, 128, 32), (16, 2, 64, 32),
+                                          (8, 8, 128, 16), (32, 2, 128, 16), (40, 8, 128, 16)])
+@pytest.mark.parametrize("B,max_len", [(1, 40), (3, 700), (16, 2100)])
+def test_paged_decode_attention(Hq, Hkv, D, bs, B, max_len):
+    ops = _ops()
+    q, kv, tables, kv_lens, scale = _decode_case(B, Hq, Hkv, D, bs, max_len, seed=B * 31 + D + bs + Hq)
+    kc, vc = paged_ops.split_kv_cache(kv, Hkv, D)
+    ref = paged_ops.paged_attention(q, kc, vc, tables.tolist(), kv_lens.tolist(), scale).float()
+    kvd = kv.to(DEV)
+    kcd, vcd = paged_ops.split_kv_cache(kvd, Hkv, D)
+    out = torch.full((B, Hq, D), float("nan"), dtype=torch.bfloat16, device=DEV)
+    ops.paged_decode_attn_score(out, q.to(DEV), kcd, vcd, torch.from_numpy(tables).to(DEV),
+                                torch.from_numpy(kv_lens).to(DEV), scale, max_len)
+    torch.cuda.synchronize()
+    got = out.float().cpu()
+    assert torch.isfinite(got).all()
+    # reference kernel test bar is atol 1e-3 on values ~U(-s, s); here outputs are bf16-rounded
+    # averages of N(0, 0.5) values: one bf16 ulp at |x| < 1 is 2^-8 = 3.9e-3
+    np.testing.assert_allclose(got.numpy(), ref.numpy(), atol=8e-3, rtol=0)
+
+
+def test_paged_decode_golden_from_reference_cpu_kernel():
+    """pa_out in ref_ops.npz came from the reference's csrc/cpu/attention.cpp paged_attention_v1."""
+    ops = _ops()
+    g = load_npz("ref_ops.npz")
+    nb, bs, Hkv, Hq, D = 48, 16, 2, 8, 64
+    q = (rnd(4, 4, Hq, D).float() * 0.3).to(torch.bfloat16)
+    kv2 = (rnd(5, 2, nb, bs * Hkv * D).float() * 0.5).to(torch.bfloat16).to(DEV)
+    kc2, vc2 = paged_ops.split_kv_cache(kv2, Hkv, D)
+    out = torch.empty(4, Hq, D, dtype=torch.bfloat16, device=DEV)
+    bt = torch.from_numpy(g["pa_block_tables"].astype(np.int32)).to(DEV)
+    kl = torch.from_numpy(g["pa_kv_lens"].astype(np.int32)).to(DEV)
+    ops.paged_attention_v1(out, q.to(DEV), kc2, vc2, Hkv, D ** -0.5, bt, kl, bs, int(g["pa_kv_lens"].max()))
+    np.testing.assert_allclose(out.float().cpu().numpy(), g["pa_out"], atol=4e-3, rtol=0)
+    out2 = torch.empty_like(out)
+    ops.paged_attention_v2(out2, None, None, None, q.to(DEV), kc2, vc2, Hkv, D ** -0.5, bt, kl, bs,
+                           int(g["pa_kv_lens"].max()))
+    assert torch.equal(out, out2)
+
+
+def test_paged_decode_empty_sequence_and_determinism():
+    ops = _ops()
+    B, Hq, Hkv, D, bs = 4, 32, 8, 128, 16
+    q, kv, tables, kv_lens, scale = _decode_case(B, Hq, Hkv, D, bs, 4096, seed=77)
+    kv_lens[2] = 0
+    kvd = kv.to(DEV)
+    kcd, vcd = paged_ops.split_kv_cache(kvd, Hkv, D)
+    outs = []
+    for _ in range(3):
+        out = torch.full((B, Hq, D), float("nan"), dtype=torch.bfloat16, device=DEV)
+        ops.paged_decode_attn_score(out, q.to(DEV), kcd, vcd, torch.from_numpy(tables).to(DEV),
+                                    torch.from_numpy(kv_lens).to(DEV), scale, 4096)
+        outs.append(out.cpu())
+    assert (outs[0][2] == 0).all()
+    assert torch.equal(outs[0], outs[1]) and torch.equal(outs[0], outs[2])   # split-KV combine is ordered
+
+
+@pytest.mark.parametrize("Hkv,D,bs", [(8, 128, 16), (8, 64, 16), (2, 128, 32), (4, 64, 32)])
+def test_fused_last_block_score_bit_exact(Hkv, D, bs):
+    """Rows with seq_len % bs == 0 get score_table[slot][nblk-1][h] = per-head value_l2 of
+    their last (just filled) block, bit-identical to oracle/scoring.py."""
+    ops = _ops()
+    B, Hq, M = 9, Hkv * 4, 40
+    rs = np.random.RandomState(D + bs)
+    nblk = rs.randint(1, M + 1, size=B)
+    nblk[0] = M
+    full = rs.rand(B) < 0.6
+    full[0] = True
+    kv_lens = np.array([n * bs if f else n * bs - int(rs.randint(1, bs)) for n, f in zip(nblk, full)],
+                       dtype=np.int32)
+    seq_lens = (kv_lens + rs.randint(0, 5, size=B) * bs).astype(np.int32)     # logical >= physical
+    nb = int(nblk.sum()) + 4
+    perm = rs.permutation(nb)
+    tables = np.zeros((B, M), dtype=np.int32)
+    o = 0
+    for r in range(B):
+        tables[r, :nblk[r]] = perm[o:o + nblk[r]]
+        o += nblk[r]
+    kv = rnd(9, 2, nb, bs * Hkv * D)
+    q = rnd(10, B, Hq, D)
+    kc, vc = paged_ops.split_kv_cache(kv, Hkv, D)
+    slots = rs.permutation(B).astype(np.int32)
+    ref = np.full((B, M, Hkv), -1.0, dtype=np.float32)
+    for r in range(B):
+        if seq_lens[r] % bs == 0:
+            vb = paged_ops.depage_v_block(vc, int(tables[r, nblk[r] - 1])).float().numpy()
+            ref[slots[r], nblk[r] - 1] = scoring.per_head_block_score(vb)
+    kvd = kv.to(DEV)
+    kcd, vcd = paged_ops.split_kv_cache(kvd, Hkv, D)
+    score = torch.full((B, M, Hkv), -1.0, dtype=torch.float32, device=DEV)
+    out = torch.empty(B, Hq, D, dtype=torch.bfloat16, device=DEV)
+    ops.paged_decode_attn_score(out, q.to(DEV), kcd, vcd, torch.from_numpy(tables).to(DEV),
+                                torch.from_numpy(kv_lens).to(DEV), D ** -0.5, M * bs,
+                                torch.from_numpy(seq_lens).to(DEV), score, torch.from_numpy(slots).to(DEV))
+    torch.cuda.synchronize()
+    assert np.array_equal(score.cpu().numpy().view(np.int32), ref.view(np.int32))
+
+
+# ------------------------------------------------------------------------------ A1
+@pytest.mark.parametrize("Hq,Hkv,D", [(8, 2, 64), (8, 2, 128), (4, 4, 128)])
+@pytest.mark.parametrize("mode", ["budget", "percentage", "none"])
+def test_prefill_attention_topleft_causal(Hq, Hkv, D, mode):
+    ops = _ops()
+    bs = 16
+    pol = Policy(block_size=bs, cache_prune_type="budget" if mode == "none" else mode,
+                 cache_budget=(1 << 20) if mode == "none" else 128, evict_freq=2)
+    prompt_lens = [1, 17, 128, 200, 333]
+    T = sum(prompt_lens)
+    q = (rnd(31, T, Hq, D).float() * 0.5).to(torch.bfloat16)
+    k = (rnd(32, T, Hkv, D).float() * 0.5).to(torch.bfloat16)
+    v = rnd(33, T, Hkv, D)
+    meta, gidx, kept_l, s = [], [], [], 0
+    for L in prompt_lens:
+        kept, pruned, first = policy.prompt_prune_layout(L, pol)
+        meta.append([s, L, s, kept, first, pruned])
+        gidx.append(torch.from_numpy(policy.prompt_gather_index(L, pol)) + s)
+        kept_l.append(kept)
+        s += L
+    gidx = torch.cat(gidx)
+    ref = paged_ops.prefill_attention(q, k[gidx], v[gidx], prompt_lens, kept_l, D ** -0.5).float()
+    out = torch.full((T, Hq, D), float("nan"), dtype=torch.bfloat16, device=DEV)
+    ops.prefill_attn_topleft_causal(out, q.to(DEV), k.to(DEV), v.to(DEV),
+                                    torch.tensor(meta, dtype=torch.int32, device=DEV), max(prompt_lens),
+                                    D ** -0.5)
+    torch.cuda.synchronize()
+    got = out.float().cpu()
+    assert torch.isfinite(got).all()
+    np.testing.assert_allclose(got.numpy(), ref.numpy(), atol=2e-2, rtol=0)
+
+
+# ------------------------------------------------------------------ block maintenance
+def test_copy_and_swap_blocks():
+    ops = _ops()
+    Hkv, D, bs, nb = 2, 64, 16, 32
+    kv = rnd(41, 2, nb, bs * Hkv * D).to(DEV)
+    ref = kv.clone()
+    kc, vc = paged_ops.split_kv_cache(kv, Hkv, D)
+    pairs = torch.tensor([[0, 5], [0, 6], [9, 1]], dtype=torch.int64)
+    ops.copy_blocks(kc, vc, pairs.to(DEV))
+    for s, d in pairs.tolist():
+        ref[:, d] = ref[:, s]
+    assert torch.equal(kv, ref)
+    host = torch.zeros(nb, bs * Hkv * D, dtype=torch.bfloat16).pin_memory()
+    ops.swap_blocks(kv[0], host, torch.tensor([[3, 7], [4, 0]]))
+    torch.cuda.synchronize()
+    assert torch.equal(host[7], kv[0, 3].cpu()) and torch.equal(host[0], kv[0, 4].cpu())
