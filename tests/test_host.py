@@ -1,0 +1,191 @@
+"""CPU tests of the product's host side: policy arithmetic and block bookkeeping against
+the golden vectors recorded from the reference's own classes, the metadata builder, the
+CLI flag mapping, the score-row map, and the C-ABI library (loads, exports every symbol
+include/pagedevict_b200.h declares -- no compute calls without a GPU)."""
+import argparse
+import ctypes
+import os
+import re
+
+import numpy as np
+import pytest
+
+from oracle import policy as opolicy
+from oracle.policy import Policy
+from tests.util import load_json
+from vllm_paged_compression_b200 import policy
+from vllm_paged_compression_b200.block_manager import BlockTable, NaiveBlockAllocator, SelfAttnBlockSpaceManager
+from vllm_paged_compression_b200.config import (CacheConfig, PagedEvictConfig, add_cli_args,
+                                                paged_evict_config_from_args)
+
+POL = load_json("ref_policy.json")
+REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _budget(budget):
+    return PagedEvictConfig(cache_prune_type="budget", evict_method="streamingLLM", cache_budget=budget)
+
+
+def _pct(freq):
+    return PagedEvictConfig(cache_prune_type="percentage", prompt_evict_method="streamingLLM",
+                            decode_evict_method="value_l2", evict_freq=freq)
+
+
+def test_budget_lengths_golden():
+    for bs, budget, q, nb, kept_util, kept_pruner in POL["budget_lengths"]:
+        cfg = _budget(budget)
+        assert policy.num_required_blocks_after_prune(q, cfg, bs) == (nb, kept_util)
+        assert policy.prompt_prune_layout(q, cfg, bs)[0] == kept_pruner
+
+
+def test_percentage_lengths_golden():
+    for bs, freq, q, nb, kept, first, pruned in POL["percentage_lengths"]:
+        k, pr, f = policy.prompt_prune_layout(q, _pct(freq), bs)
+        assert (k, policy.cdiv(k, bs)) == (kept, nb)
+        if pruned:
+            assert (f, pr) == (first, pruned)
+
+
+def test_policy_matches_oracle_exhaustively():
+    for bs in (16, 32):
+        for q in list(range(1, 700)) + [1024, 4096, 8191, 8192]:
+            for budget in (128, 256, 512):
+                if budget < 3 * bs:
+                    continue
+                o = Policy(block_size=bs, cache_prune_type="budget", cache_budget=budget)
+                assert policy.prompt_prune_layout(q, _budget(budget), bs) == opolicy.prompt_prune_layout(q, o)
+                assert policy.num_required_blocks_after_prune(q, _budget(budget), bs) == \
+                    opolicy.num_required_blocks_after_prune(q, o)
+            for freq in (1, 2, 3, 4):
+                o = Policy(block_size=bs, cache_prune_type="percentage", evict_freq=freq)
+                assert policy.prompt_prune_layout(q, _pct(freq), bs) == opolicy.prompt_prune_layout(q, o)
+
+
+def test_block_table_trace_golden():
+    """BlockTable allocate / append / free_prunned_blocks against the reference's BlockTable
+    (ids, kv lens, trigger steps)."""
+    for row in POL["block_table_trace"]:
+        bs, cfg = row["bs"], _budget(row["budget"])
+        bt = BlockTable(bs, NaiveBlockAllocator(4096), cfg)
+        bt.allocate(row["q_len"])
+        first = row["trace"][0]
+        assert bt.physical_block_ids == first["ids"] and bt.get_seq_kv_len() == first["kv_len"]
+        for rec in row["trace"][1:]:
+            bt.append_slots(1)
+            assert bt.num_full_slots == rec["seq_len"] and bt.get_seq_kv_len() == rec["kv_len"]
+            assert bt.physical_block_ids[:len(rec["ids"])] == rec["ids"]
+            trig = policy.decode_trigger(rec["seq_len"], bt.get_seq_kv_len(), cfg, bs)
+            assert trig == rec["trigger"]
+            if trig:
+                bt.free_prunned_blocks(1)
+                assert bt.get_seq_kv_len() == rec["kv_len_after_free"]
+                assert bt.physical_block_ids == rec["ids_after_free"]
+
+
+def test_block_manager_accounting():
+    bm = SelfAttnBlockSpaceManager(16, 40, _budget(128))
+    assert bm.can_allocate(1024)            # 8 blocks after pruning, not 64
+    bm.allocate(0, 1024)
+    assert len(bm.get_block_table(0)) == 8 and bm.get_seq_kv_len(0) == 128
+    assert not SelfAttnBlockSpaceManager(16, 7, _budget(128)).can_allocate(1024)
+    free0 = bm.allocator.get_num_free_blocks()
+    bm.append_slots(0)
+    bm.free_prunned_blocks(0, 1)
+    assert bm.allocator.get_num_free_blocks() == free0 and bm.get_seq_kv_len(0) == 113
+    bm.free(0)
+    assert bm.allocator.get_num_free_blocks() == 40
+
+
+def test_slot_mapping_builder_golden():
+    from vllm_paged_compression_b200.backend import prefill_slots_np
+    for row in POL["slot_mapping"]:
+        if row["is_prompt"]:
+            assert prefill_slots_np(row["table"], row["query_len"], row["bs"]).tolist() == row["slots"]
+        else:
+            assert [row["table"][-1] * row["bs"] + row["context_len"] % row["bs"]] == row["slots"]
+
+
+def test_cli_flag_sets():
+    p = add_cli_args(argparse.ArgumentParser())
+    # README flags (README.md:38-45)
+    a = p.parse_args("--enable-paged-eviction --cache-prune-type percentage --prompt-evict-method streamingLLM "
+                     "--decode-evict-method value_l2 --evict-freq 4 --block-size 16".split())
+    c = paged_evict_config_from_args(a)
+    assert (c.cache_prune_type, c.prompt_evict_method, c.decode_evict_method, c.evict_freq, c.topk_blocks) == \
+        ("percentage", "streamingLLM", "value_l2", 4, -1)
+    # HEAD flags (scripts/latency_test.sh:57-72)
+    a = p.parse_args("--enable-paged-eviction --cache-prune-type budget --evict-method global --cache-budget 512 "
+                     "--disable-evict-prefill".split())
+    c = paged_evict_config_from_args(a)
+    assert (c.decode_evict_method, c.cache_budget, c.topk_blocks, c.disable_evict_prefill) == ("value_l2", 512, -1, True)
+    a = p.parse_args("--enable-paged-eviction --evict-method local --topk-blocks 5".split())
+    c = paged_evict_config_from_args(a)
+    assert (c.decode_evict_method, c.topk_blocks) == ("value_l2", 5)
+    a = p.parse_args("--enable-paged-eviction --evict-method streamingLLM --cache-budget 64".split())
+    assert paged_evict_config_from_args(a).cache_budget == 128            # floored, vllm/config.py:977-980
+    assert paged_evict_config_from_args(p.parse_args([])) is None
+    with pytest.raises(NotImplementedError):
+        paged_evict_config_from_args(p.parse_args("--enable-paged-eviction --evict-method inverse_key_l2".split()))
+    with pytest.raises(ValueError):
+        CacheConfig(block_size=16, paged_evict_config=_budget(200))       # budget % block_size != 0
+
+
+def test_score_slot_map():
+    from vllm_paged_compression_b200.backend import ScoreSlotMap
+    m = ScoreSlotMap(4)
+    s1, fresh = m.assign([("a", 0), ("b", 1)])
+    assert sorted(fresh) == sorted(s1) and len(set(s1)) == 2
+    s2, fresh = m.assign([("c", 2)])                      # a, b absent from this batch keep their rows
+    assert fresh == s2 and m.assign([("a", 0), ("b", 1)])[0] == s1
+    m.assign([("d", 3)])
+    s5, fresh = m.assign([("e", 4)])                      # full: least recently seen ("c") is recycled
+    assert fresh == s5 == s2
+    m.release("a")
+    assert ("a", 0) not in m.slot_of
+    with pytest.raises(RuntimeError):
+        m.assign([(str(i), i) for i in range(10)])
+
+
+def test_backend_surface_names():
+    from vllm_paged_compression_b200.backend import (PagedAttention, TorchCUDASDPABackend,
+                                                     TorchCUDASDPABackendImpl, TorchCUDASDPAMetadata,
+                                                     TorchCUDASDPAMetadataBuilder)
+    B = TorchCUDASDPABackend
+    assert B.get_name() == "TORCH_SDPA"
+    assert B.get_impl_cls() is TorchCUDASDPABackendImpl and B.get_metadata_cls() is TorchCUDASDPAMetadata
+    assert B.get_builder_cls() is TorchCUDASDPAMetadataBuilder
+    assert B.get_kv_cache_shape(10, 16, 8, 128) == (2, 10, 16 * 8 * 128)
+    impl = TorchCUDASDPABackendImpl(32, 128, 0.088, 8, None, None, "auto",
+                                    cache_config=CacheConfig(16, paged_evict_config=_pct(2)),
+                                    prefix="model.layers.7.self_attn.attn")
+    assert impl.layer_idx == 7 and impl.enabled_paged_eviction and impl.get_rmv_block_idx() == {}
+    with pytest.raises(NotImplementedError):
+        TorchCUDASDPABackendImpl(32, 128, 0.088, 8, None, None, "fp8")
+    with pytest.raises(ValueError):
+        TorchCUDASDPABackendImpl(32, 80, 0.1, 8, None, None, "auto")
+    import torch
+    kv = torch.zeros(2, 3, 16 * 8 * 128, dtype=torch.bfloat16)
+    kc, vc = PagedAttention.split_kv_cache(kv, 8, 128)
+    assert kc.shape == (3, 8, 16, 16, 8) and vc.shape == (3, 8, 128, 16)
+
+
+def test_c_abi_library_exports_every_declared_symbol():
+    from vllm_paged_compression_b200 import _lib
+    hdr = open(os.path.join(REPO, "include", "pagedevict_b200.h")).read()
+    declared = set(re.findall(r"\b(pc_[a-z0-9_]+)\s*\(", hdr)) - {"pc_status", "pc_dtype"}
+    assert declared == set(_lib.PROTOTYPES), declared ^ set(_lib.PROTOTYPES)
+    lib = ctypes.CDLL(_lib.LIB_PATH)
+    for name in declared:
+        assert hasattr(lib, name), name
+    assert _lib.load().pc_abi_version() == _lib.ABI_VERSION
+    assert ctypes.sizeof(_lib.PcEvictPolicy) == 32
+
+
+def test_ops_refuse_cpu_tensors():
+    import torch
+    from vllm_paged_compression_b200 import ops
+    kv = torch.zeros(2, 2, 16 * 2 * 64, dtype=torch.bfloat16)
+    kc, vc = kv[0].view(2, 2, 8, 16, 8), kv[1].view(2, 2, 64, 16)
+    k = torch.zeros(1, 2, 64, dtype=torch.bfloat16)
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        ops.reshape_and_cache(k, k, kc, vc, torch.zeros(1, dtype=torch.int64))
