@@ -1,0 +1,518 @@
+#!/usr/bin/env python
+"""bench.py -- decode throughput of the paged-eviction hot path on B200.
+
+Contract (driver):  python bench.py --gpus N --steps K --warmup W [--impl reference]
+  N > 1 is launched by torch.distributed.run (one rank per GPU, NCCL).
+
+Workload (BASELINE.json configs[2], the configuration "decode tok/s at 25%/50% eviction"
+is quoted on): Llama-3.1-8B attention shapes (32 layers, 32 q heads, 8 kv heads, head 128,
+bf16), 64 prompts x 1024 tokens in, decode steps out, block 16, percentage pruning with
+streamingLLM at prompt time and value_l2 block eviction every `evict_freq` blocks at
+decode time.  One "step" = ONE decode step of the whole batch through the hot path of all
+32 layers: reshape_and_cache -> [trigger / argmin / table compaction on eviction steps]
+-> paged decode attention with fused value_l2 scoring, plus the host side either side of
+it (scheduler bookkeeping, metadata build, layer-0 victim readback, block free).  The
+model's linear layers / sampler are not part of the path: q/k/v per layer
+are seeded synthetic activations.
+
+  value     : tok/s with q/k/v already resident in HBM when the timed region starts.
+  e2e       : same metric through the plugin API with HOST (pinned) q/k/v and host result
+              buffers: H2D of every layer's q/k/v and D2H of every layer's attention
+              output inside the timed region.
+  roofline  : the dominant kernel (paged_decode_attn_score) timed alone with CUDA events,
+              back to back over the 32 layers' pools (5+ GB >> 126 MB L2), algorithmic
+              bytes = sum_seqs kv_len * Hkv * D * 2 (K,V) * 2 B per launch.
+  cpu_baseline : the reference's own CPU kernels (oracle/_ref, kind "reference") or the
+              oracle port, driven by the oracle's restatement of the reference's Python
+              logic, on a bounded sample (a few of the 32 layers, scaled).
+  --impl reference : that CPU arm alone, same JSON line.
+
+Multi-GPU (N > 1): tensor parallel over KV heads (rank r owns Hkv/N kv heads and their q
+heads); the batch grows with N (64*N prompts) so per-GPU KV bytes stay fixed ("weak").
+The only exchange is the all-gather of per-head value_l2 partials of freshly filled
+blocks (see DESIGN.md "Multi-GPU").
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import tempfile
+import time
+
+REPO = os.path.dirname(os.path.abspath(__file__))
+if REPO not in sys.path:
+    sys.path.insert(0, REPO)
+
+MODEL = dict(name="Llama-3.1-8B", layers=32, Hq=32, Hkv=8, D=128)
+METRIC = "decode_tok_per_s_paged_eviction_hot_path"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=64)
+    ap.add_argument("--warmup", type=int, default=8)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--evict-freq", type=int, default=2,
+                    help="README flag: 2 (labelled 25%%) or 4 (labelled 50%%); 0 = eviction off")
+    ap.add_argument("--batch", type=int, default=64, help="prompts per GPU")
+    ap.add_argument("--prompt-len", type=int, default=1024)
+    ap.add_argument("--layers", type=int, default=MODEL["layers"])
+    ap.add_argument("--block-size", type=int, default=16)
+    ap.add_argument("--cpu-layers", type=int, default=2,
+                    help="layers per step in the CPU sample (scaled to the full layer count)")
+    ap.add_argument("--cpu-steps", type=int, default=0, help="0 = derive from a ~15 s budget")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-graph", action="store_true", help="disable CUDA-graph replay of the step")
+    ap.add_argument("--sweep", action="store_true",
+                    help="kernel microbench (BASELINE.json configs[1]) -> table on stdout")
+    return ap.parse_args()
+
+
+# ------------------------------------------------------------------------ configuration
+def make_cache_config(args, max_num_seqs):
+    from vllm_paged_compression_b200.config import CacheConfig, PagedEvictConfig
+    if args.evict_freq <= 0:
+        return CacheConfig(block_size=args.block_size, max_num_seqs=max_num_seqs)
+    pe = PagedEvictConfig(cache_prune_type="percentage", evict_method=None,
+                          prompt_evict_method="streamingLLM", decode_evict_method="value_l2",
+                          evict_freq=args.evict_freq, topk_blocks=-1)
+    pe.topk_blocks = -1
+    return CacheConfig(block_size=args.block_size, paged_evict_config=pe, max_num_seqs=max_num_seqs)
+
+
+def workload_name(args, world):
+    ev = f"evict-freq {args.evict_freq}" if args.evict_freq > 0 else "no eviction"
+    return (f"{MODEL['name']} attention hot path, {args.layers} layers, {args.batch * world} prompts x "
+            f"{args.prompt_len} in, decode steps, block {args.block_size}, percentage/streamingLLM prompt + "
+            f"value_l2 decode, {ev}")
+
+
+# ------------------------------------------------------------------------ clocks sampler
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        self.p = None
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", f"--id={gpu_index}", f"--query-gpu={self.Q}",
+                                       "--format=csv,noheader,nounits", "-lms", "50"],
+                                      stdout=self.f, stderr=subprocess.DEVNULL)
+        except OSError:
+            self.p = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.p is None:
+            return out
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.p.kill()
+        self.f.flush()
+        self.f.seek(0)
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in self.f.read().splitlines():
+            parts = [x.strip() for x in line.split(",")]
+            if len(parts) < 6:
+                continue
+            try:
+                sm.append(float(parts[0]))
+                mx.append(float(parts[1]))
+            except ValueError:
+                continue
+            for n, v in zip(names, parts[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        self.f.close()
+        os.unlink(self.f.name)
+        if sm:
+            out.update(sm_mhz=statistics.median(sm), sm_max_mhz=max(mx), reasons=sorted(reasons),
+                       samples=len(sm))
+        return out
+
+
+# ------------------------------------------------------------------------ B200 arm
+class Arm:
+    """One engine + synthetic per-layer activations; a step = PagedEvictEngine.step()."""
+
+    def __init__(self, args, device, rank, world, host_io: bool):
+        import torch
+        from vllm_paged_compression_b200.engine import PagedEvictEngine
+        self.torch = torch
+        self.args, self.device, self.host_io = args, device, host_io
+        self.L = args.layers
+        self.Hq, self.Hkv, self.D = MODEL["Hq"] // world, MODEL["Hkv"] // world, MODEL["D"]
+        self.B = args.batch * world
+        bs = args.block_size
+        cc = make_cache_config(args, self.B)
+        blocks_per_seq = -(-(args.prompt_len + args.steps + args.warmup + 2 * bs) // bs) + 2
+        self.eng = PagedEvictEngine(self.L, self.Hq, self.Hkv, self.D, cc, self.B * blocks_per_seq + 8,
+                                    device=device, tp_rank=rank, tp_size=world)
+        for i in range(self.B):
+            self.eng.add_request(f"r{i}", args.prompt_len)
+        g = torch.Generator(device=device)
+        g.manual_seed(1234 + rank)
+        self.gen = g
+        s = self.D ** -0.5
+        # decode activations: one [B, ...] set per layer, resident in HBM (value) or in
+        # pinned host memory (e2e); U(-s, s) like tests/kernels/test_attention.py:146-148
+        def u(*shape):
+            return (torch.rand(*shape, device=device, generator=g) * 2 * s - s).to(torch.bfloat16)
+        self.q = [u(self.B, self.Hq * self.D) for _ in range(self.L)]
+        self.k = [u(self.B, self.Hkv * self.D) for _ in range(self.L)]
+        # layer- and row-dependent V magnitude so victims differ between rows / layers
+        row = (1.0 + 0.5 * torch.rand(self.B, 1, device=device, generator=g))
+        self.v = [(u(self.B, self.Hkv * self.D).float() * row * (1 + 0.1 * l)).to(torch.bfloat16)
+                  for l in range(self.L)]
+        self.h2d = self.d2h = 0
+        if host_io:
+            pin = lambda t: t.cpu().pin_memory()
+            self.qh, self.kh, self.vh = [[pin(t) for t in x] for x in (self.q, self.k, self.v)]
+            self.oh = [torch.empty(self.B, self.Hq * self.D, dtype=torch.bfloat16).pin_memory()
+                       for _ in range(self.L)]
+            self.h2d = sum(t.numel() * 2 for x in (self.qh, self.kh, self.vh) for t in x)
+            self.d2h = sum(t.numel() * 2 for t in self.oh)
+
+    def prefill(self):
+        """One untimed prefill batch (chunked by request so activations stay small)."""
+        torch = self.torch
+        s = self.D ** -0.5
+        g = self.gen
+
+        def qkv(layer, n_tok):
+            u = lambda w: (torch.rand(n_tok, w, device=self.device, generator=g) * 2 * s - s).to(torch.bfloat16)
+            v = (u(self.Hkv * self.D).float() * (1 + 0.1 * layer)).to(torch.bfloat16)
+            return u(self.Hq * self.D), u(self.Hkv * self.D), v
+        self.eng.max_num_batched_tokens = 16 * self.args.prompt_len
+        while self.eng.waiting:
+            so = self.eng.step(qkv, keep_outputs=False)
+            assert so.is_prompt
+        torch.cuda.synchronize()
+
+    def step(self):
+        if not self.host_io:
+            return self.eng.step(lambda l, n: (self.q[l], self.k[l], self.v[l]), keep_outputs=False)
+
+        def qkv(l, n):
+            return (self.qh[l].to(self.device, non_blocking=True),
+                    self.kh[l].to(self.device, non_blocking=True),
+                    self.vh[l].to(self.device, non_blocking=True))
+
+        def out(l, o):
+            self.oh[l].copy_(o, non_blocking=True)
+        so = self.eng.step(qkv, keep_outputs=False, out_fn=out)
+        self.torch.cuda.current_stream().synchronize()     # the caller owns the host result now
+        return so
+
+
+def timed_steps(torch, dist, arm, K, W, world):
+    """W warm-up + K timed steps, barrier + synchronize either side, CUDA events, max over
+    ranks.  -> (seconds, evictions, launches)"""
+    from vllm_paged_compression_b200 import ops
+    for _ in range(W):
+        arm.step()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    n0 = ops.launch_count
+    evictions = 0
+    e0.record()
+    for _ in range(K):
+        so = arm.step()
+        evictions += len(so.rmv)
+    e1.record()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    sec = e0.elapsed_time(e1) / 1e3
+    if world > 1:
+        t = torch.tensor([sec], device=arm.device, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        sec = float(t.item())
+    return sec, evictions, ops.launch_count - n0
+
+
+def roofline_leg(torch, arm, reps=20):
+    """The decode-attention + scoring kernel alone, back to back over every layer's pool
+    (distinct memory per launch, total >> L2), on the state the timed region ended in."""
+    from vllm_paged_compression_b200 import ops
+    from vllm_paged_compression_b200.backend import PagedAttention
+    eng = arm.eng
+    md = eng.build_metadata(False, list(eng.running))
+    kv_lens_host = list(md.seq_kv_lens or md.seq_lens)
+    kv_lens = md.seq_kv_lens_tensor if md.seq_kv_lens_tensor is not None else md.seq_lens_tensor
+    max_kv = max(kv_lens_host)
+    caches = [PagedAttention.split_kv_cache(kv, arm.Hkv, arm.D) for kv in eng.kv_caches]
+    outs = torch.empty(arm.B, arm.Hq, arm.D, dtype=torch.bfloat16, device=arm.device)
+    qs = [q.view(arm.B, arm.Hq, arm.D) for q in arm.q]
+    scale = arm.D ** -0.5
+
+    def run_all():
+        for l in range(arm.L):
+            ops.paged_decode_attn_score(outs, qs[l], caches[l][0], caches[l][1], md.block_tables,
+                                        kv_lens, scale, max_kv)
+    for _ in range(3):
+        run_all()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        run_all()
+    e1.record()
+    torch.cuda.synchronize()
+    per_launch_s = e0.elapsed_time(e1) / 1e3 / (reps * arm.L)
+    alg_bytes = sum(kv_lens_host) * arm.Hkv * arm.D * 2 * 2
+    return per_launch_s, alg_bytes, kv_lens_host
+
+
+def load_peaks():
+    p = os.path.join(REPO, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+# ------------------------------------------------------------------------ CPU arm
+class CpuArm:
+    """The reference path on host cores: the oracle's restatement of the reference's
+    Python logic (oracle/backend.py, oracle/policy.py) over the reference's OWN compiled
+    CPU kernels (oracle/_ref: csrc/cpu/attention.cpp, cache.cpp) when available
+    (kind "reference"), else the torch restatement (kind "port").  Bounded sample:
+    `cpu_layers` of the model's layers per step, full batch."""
+
+    def __init__(self, args, world=1):
+        import numpy as np
+        import torch
+        from oracle import policy as opol
+        from oracle import ref_cpu
+        from oracle.backend import OracleLayer
+        from oracle.policy import Policy
+        self.torch, self.np, self.opol = torch, np, opol
+        self.args = args
+        self.cores = os.cpu_count() or 1
+        torch.set_num_threads(self.cores)
+        self.Lc = max(1, min(args.cpu_layers, args.layers))
+        self.Hq, self.Hkv, self.D = MODEL["Hq"], MODEL["Hkv"], MODEL["D"]
+        self.B = args.batch * world
+        bs = self.bs = args.block_size
+        self.kind = "reference" if (bs == 16 and ref_cpu.available()) else "port"
+        native = ref_cpu.RefCpuOps if self.kind == "reference" else None
+        self.pol = Policy(block_size=bs, cache_prune_type="percentage",
+                          evict_freq=max(args.evict_freq, 1), decode_evict_method="value_l2", topk_blocks=-1)
+        self.evict = args.evict_freq > 0
+        if not self.evict:
+            # eviction off: nothing is ever pruned or triggered
+            self.pol = Policy(block_size=bs, cache_prune_type="budget", cache_budget=1 << 30,
+                              decode_evict_method="streamingLLM")
+        self.layers = [OracleLayer(self.Hq, self.D, self.D ** -0.5, self.Hkv, self.pol, native_ops=native)
+                       for _ in range(self.Lc)]
+        P = args.prompt_len
+        nblk, kept = opol.num_required_blocks_after_prune(P, self.pol)
+        per_seq = nblk + (args.steps + args.warmup) // bs + 4
+        self.num_blocks = self.B * per_seq + 8
+        self.kv = [torch.zeros(2, self.num_blocks, bs * self.Hkv * self.D, dtype=torch.bfloat16)
+                   for _ in range(self.Lc)]
+        self.free = list(range(self.num_blocks - 1, -1, -1))
+        self.tables = [[self.free.pop() for _ in range(nblk)] for _ in range(self.B)]
+        self.seq_len = [P] * self.B
+        self.kv_len = [kept] * self.B
+        self.req = [f"r{i}" for i in range(self.B)]
+        g = torch.Generator().manual_seed(1234)
+        s = self.D ** -0.5
+        u = lambda *sh: (torch.rand(*sh, generator=g) * 2 * s - s).to(torch.bfloat16)
+        # prompt KV straight into the cache + prompt block scores (no prefill attention: the
+        # metric is decode throughput); chunked so host memory stays small
+        for l, lay in enumerate(self.layers):
+            for c0 in range(0, self.B, 8):
+                rows = range(c0, min(c0 + 8, self.B))
+                n = len(rows) * P
+                lay.prefill(torch.empty(0), u(n, self.Hkv * self.D),
+                            (u(n, self.Hkv * self.D).float() * (1 + 0.1 * l)).to(torch.bfloat16),
+                            self.kv[l], [P] * len(rows), [self.tables[r] for r in rows],
+                            [self.req[r] for r in rows], compute_attention=False)
+        self.q = [u(self.B, self.Hq * self.D) for _ in range(self.Lc)]
+        self.k = [u(self.B, self.Hkv * self.D) for _ in range(self.Lc)]
+        self.v = [u(self.B, self.Hkv * self.D) for _ in range(self.Lc)]
+
+    def step(self):
+        opol, bs = self.opol, self.bs
+        kv_pass = []
+        for r in range(self.B):                       # scheduler + model-runner side
+            if self.kv_len[r] % bs == 0:
+                self.tables[r].append(self.free.pop())
+            self.seq_len[r] += 1
+            self.kv_len[r] += 1
+            trig = self.evict and opol.decode_trigger(self.seq_len[r], len(self.tables[r]) * bs, self.pol)
+            kv_pass.append(self.kv_len[r] - (bs if trig else 0))
+        rmv0 = {}
+        for l, lay in enumerate(self.layers):
+            _, rmv, _ = lay.decode(self.q[l], self.k[l], self.v[l], self.kv[l], self.seq_len, kv_pass,
+                                   self.tables, self.req)
+            if l == 0:
+                rmv0 = rmv
+        for r, (_, idx) in rmv0.items():              # engine feedback: free the victim
+            self.free.append(self.tables[r].pop(idx))
+            self.kv_len[r] -= bs
+        return len(rmv0)
+
+    def run(self, K, W):
+        for _ in range(W):
+            self.step()
+        t0 = time.perf_counter()
+        for _ in range(K):
+            self.step()
+        dt = time.perf_counter() - t0
+        scale = self.args.layers / self.Lc
+        sec_per_step = dt / K * scale
+        return dict(value=self.B / sec_per_step, ms_per_step=sec_per_step * 1e3, kind=self.kind,
+                    cores=self.cores,
+                    sample=(f"{K} decode steps x {self.Lc} of {self.args.layers} layers x full batch {self.B} "
+                            f"(time scaled x{scale:g} to all layers), {W} warm-up steps"))
+
+
+def run_reference(args, rank, world):
+    if rank != 0:
+        return
+    arm = CpuArm(args, world)
+    K, W = args.steps, max(args.warmup, 1)
+    r = arm.run(K, W)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": r["value"], "unit": "tok/s",
+        "n_gpus": args.gpus, "steps": K, "warmup": W, "ms_per_step": r["ms_per_step"],
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
+        "data": "synthetic", "config": {"workload": workload_name(args, world),
+                                        "global_batch": arm.B, "parallelism": "host cores"},
+        "cpu_baseline": {"value": r["value"], "unit": "tok/s", "cores": r["cores"], "kind": r["kind"],
+                         "sample": r["sample"]},
+        "e2e": {"value": r["value"], "unit": "tok/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------ main
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus and world > 1:
+        args.gpus = world
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+    if args.gpus > 1 and world == 1:
+        raise SystemExit("--gpus N > 1 must be launched with torch.distributed.run (one rank per GPU)")
+
+    import torch
+    import torch.distributed as dist
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product path has no CPU fallback "
+                         "(use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local_rank)
+    device = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=device)
+    if MODEL["Hkv"] % world != 0:
+        raise SystemExit(f"tensor parallel size {world} must divide {MODEL['Hkv']} kv heads")
+    from vllm_paged_compression_b200 import _lib
+    _lib.load()                                        # fail loudly if the CUDA library is missing
+
+    if args.sweep:
+        from vllm_paged_compression_b200 import microbench
+        microbench.sweep(device)
+        return
+
+    K, W = args.steps, args.warmup
+    # ---- value: inputs resident in HBM
+    arm = Arm(args, device, rank, world, host_io=False)
+    arm.prefill()
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    sec, evictions, launches = timed_steps(torch, dist, arm, K, W, world)
+    clocks = sampler.stop() if sampler else None
+    per_launch_s, alg_bytes, kv_lens_host = roofline_leg(torch, arm)
+    if world > 1:
+        t = torch.tensor([per_launch_s], device=device, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        per_launch_s = float(t.item())
+    B = arm.B
+    kept_prompt = None
+    if args.evict_freq > 0:
+        from vllm_paged_compression_b200.policy import prompt_prune_layout
+        kept_prompt = prompt_prune_layout(args.prompt_len, arm.eng.cache_config.paged_evict_config,
+                                          args.block_size)[0]
+    del arm
+    torch.cuda.empty_cache()
+
+    # ---- e2e: host buffers through the plugin API
+    e2e = None
+    if not args.no_e2e:
+        arm = Arm(args, device, rank, world, host_io=True)
+        arm.prefill()
+        sec_e, _, _ = timed_steps(torch, dist, arm, K, W, world)
+        e2e = {"value": B * K / sec_e, "unit": "tok/s", "h2d_bytes_per_step": arm.h2d,
+               "d2h_bytes_per_step": arm.d2h, "ms_per_step": sec_e / K * 1e3}
+        del arm
+        torch.cuda.empty_cache()
+
+    peak, peak_src = load_peaks()
+    achieved = alg_bytes / per_launch_s / 1e9
+    line = {
+        "metric": METRIC, "value": B * K / sec, "unit": "tok/s", "n_gpus": world, "steps": K, "warmup": W,
+        "ms_per_step": sec / K * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "bf16", "data": "synthetic",
+        "config": {"workload": workload_name(args, world), "global_batch": B,
+                   "parallelism": f"tp{world}" if world > 1 else "single GPU",
+                   "l2": "inputs larger than L2 (per-layer KV pools, {:.1f} GB touched per step)".format(
+                       alg_bytes * args.layers / 1e9),
+                   "prompt_tokens_kept": kept_prompt, "evictions_in_timed_region": evictions,
+                   "mean_kv_len": sum(kv_lens_host) / len(kv_lens_host)},
+        "clocks": clocks,
+        "e2e": e2e,
+        "gpu_launches": launches,
+        "roofline": {"bound": "hbm", "kernel": "paged_decode_attn_score_kernel", "achieved": achieved,
+                     "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                     "peak_source": peak_src, "algorithmic_bytes_per_launch": alg_bytes,
+                     "us_per_launch": per_launch_s * 1e6},
+    }
+    # ncu-measured DRAM traffic of the same launch shape, when a summary is committed
+    tpath = os.path.join(REPO, "profiles", "decode_traffic.json")
+    if os.path.exists(tpath):
+        with open(tpath) as f:
+            tj = json.load(f)
+        line["roofline"]["traffic"] = tj.get("dram_bytes_per_launch")
+        line["roofline"]["traffic_source"] = tj.get("source")
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cpu_args = argparse.Namespace(**vars(args))
+        carm = CpuArm(cpu_args, 1)
+        t0 = time.perf_counter()
+        carm.step()
+        one = time.perf_counter() - t0
+        ck = args.cpu_steps or max(3, min(32, int(15.0 / max(one, 1e-3))))
+        line["cpu_baseline"] = {k: v for k, v in carm.run(ck, 1).items() if k != "ms_per_step"}
+        line["cpu_baseline"]["unit"] = "tok/s"
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -30,9 +30,13 @@ from .policy import Policy
 
 class OracleLayer:
     def __init__(self, num_heads: int, head_size: int, scale: float, num_kv_heads: int,
-                 pol: Optional[Policy], head_compat_uncompacted: bool = False):
+                 pol: Optional[Policy], head_compat_uncompacted: bool = False, native_ops=None):
+        """native_ops: object providing reshape_and_cache / paged_attention with the
+        signatures of oracle/paged_ops.py (default: that torch restatement;
+        oracle/ref_cpu.RefCpuOps = the reference's own compiled CPU kernels)."""
         self.Hq, self.D, self.scale, self.Hkv = num_heads, head_size, float(scale), num_kv_heads
         self.pol = pol
+        self.ops = native_ops if native_ops is not None else paged_ops
         self.compat = head_compat_uncompacted
         # req_id -> list of per-head partial scores [Hkv] fp32, index == table index
         self.scores: Dict[str, List[np.ndarray]] = {}
@@ -40,9 +44,11 @@ class OracleLayer:
 
     # -------------------------------------------------------------- prefill
     def prefill(self, query, key, value, kv_cache, seq_lens: Sequence[int],
-                block_tables: Sequence[Sequence[int]], req_ids: Sequence[str]) -> torch.Tensor:
+                block_tables: Sequence[Sequence[int]], req_ids: Sequence[str],
+                compute_attention: bool = True) -> Optional[torch.Tensor]:
         """query [sumL, Hq*D], key/value [sumL, Hkv*D]; block_tables = post-prune host
-        tables.  Returns out [sumL, Hq*D]."""
+        tables.  Returns out [sumL, Hq*D] (None when compute_attention is False: cache
+        write + prompt scoring only, used to set up decode state for timing)."""
         p, bs = self.pol, self.pol.block_size
         q = query.view(-1, self.Hq, self.D)
         k = key.view(-1, self.Hkv, self.D)
@@ -59,7 +65,7 @@ class OracleLayer:
         gidx = torch.cat(gidx)
         kp, vp = k[gidx], v[gidx]
         assert len(slots) == kp.shape[0]
-        paged_ops.reshape_and_cache(kp, vp, kc, vc, torch.tensor(slots, dtype=torch.long))
+        self.ops.reshape_and_cache(kp, vp, kc, vc, torch.tensor(slots, dtype=torch.long))
         # scores of every FULL cached prompt block (D2)
         s = 0
         for L, rid in zip(kept, req_ids) if p.decode_evict_method == "value_l2" else ():
@@ -67,11 +73,13 @@ class OracleLayer:
             self.scores[rid] = [scoring.per_head_block_score(vr[j * bs:(j + 1) * bs])
                                 for j in range(L // bs)]
             s += L
+        self.last = {"slots": slots, "kept": kept}
+        if not compute_attention:
+            return None
         if p.disable_evict_prefill:
             out = paged_ops.prefill_attention(q, k, v, seq_lens, seq_lens, self.scale)
         else:
             out = paged_ops.prefill_attention(q, kp, vp, seq_lens, kept, self.scale)
-        self.last = {"slots": slots, "kept": kept}
         return out.view(-1, self.Hq * self.D)
 
     # -------------------------------------------------------------- decode
@@ -107,8 +115,8 @@ class OracleLayer:
             attn_tables.append(tab)
         k = key.view(-1, self.Hkv, self.D)
         v = value.view(-1, self.Hkv, self.D)
-        paged_ops.reshape_and_cache(k, v, kc, vc, torch.tensor(slots, dtype=torch.long))
-        out = paged_ops.paged_attention(query.view(-1, self.Hq, self.D), kc, vc,
+        self.ops.reshape_and_cache(k, v, kc, vc, torch.tensor(slots, dtype=torch.long))
+        out = self.ops.paged_attention(query.view(-1, self.Hq, self.D), kc, vc,
                                         attn_tables, list(kv_lens), self.scale)
         for r in range(B):                                                # D2
             if p.decode_evict_method == "value_l2" and policy.score_trigger(seq_lens[r], p):

@@ -71,3 +71,37 @@ def reshape_and_cache(key, value, key_cache, value_cache, slot_mapping):
     assert available(), why_unavailable()
     torch.ops.pc_ref_cpu.reshape_and_cache(key, value, key_cache, value_cache,
                                            slot_mapping, "auto", 1.0, 1.0)
+
+
+class RefCpuOps:
+    """reshape_and_cache / paged_attention with the call shapes of oracle/paged_ops.py,
+    executed by the reference's own compiled CPU kernels (block_size 16 only).  The
+    v1/v2 choice follows PagedAttention.forward_decode (paged_attn.py:117-127)."""
+
+    @staticmethod
+    def reshape_and_cache(key, value, key_cache, value_cache, slot_mapping):
+        reshape_and_cache(key.contiguous(), value.contiguous(), key_cache, value_cache,
+                          slot_mapping.flatten().to(torch.long))
+
+    @staticmethod
+    def paged_attention(query, key_cache, value_cache, block_tables, kv_lens, scale,
+                        out_dtype=None):
+        B, Hq, D = query.shape
+        bs = value_cache.shape[3]
+        width = max(1, max((len(t) for t in block_tables), default=1))
+        bt = torch.zeros(B, width, dtype=torch.int32)
+        for r, t in enumerate(block_tables):
+            if len(t):
+                bt[r, :len(t)] = torch.as_tensor(list(t), dtype=torch.int32)
+        lens = torch.as_tensor(list(kv_lens), dtype=torch.int32)
+        max_len = int(max(kv_lens)) if len(kv_lens) else 0
+        out = torch.empty_like(query)
+        partitions = (max_len + 511) // 512
+        q = query.contiguous()
+        if max_len <= 8192 and (partitions == 1 or B * Hq > 512):
+            paged_attention_v1(out, q, key_cache, value_cache, value_cache.shape[1], scale, bt,
+                               lens, bs, max_len)
+        else:
+            paged_attention_v2(out, q, key_cache, value_cache, value_cache.shape[1], scale, bt,
+                               lens, bs, max_len)
+        return out

@@ -179,9 +179,11 @@ class PagedEvictEngine:
         return md
 
     # -------------------------------------------------------------------------- step
-    def step(self, qkv_fn: QKVFn, keep_outputs: bool = True) -> StepOutput:
+    def step(self, qkv_fn: QKVFn, keep_outputs: bool = True,
+             out_fn: Optional[Callable[[int, torch.Tensor], None]] = None) -> StepOutput:
         """qkv_fn(layer, num_tokens) -> (query [T,Hq*D], key [T,Hkv*D], value [T,Hkv*D])
-        on self.device."""
+        on self.device.  out_fn(layer, out) receives each layer's attention output (the
+        tensor the model's o_proj would consume)."""
         is_prompt, batch = self._schedule()
         md = self.build_metadata(is_prompt, batch)
         n_tok = md.num_prefill_tokens + md.num_decode_tokens
@@ -189,6 +191,8 @@ class PagedEvictEngine:
         for layer, impl in enumerate(self.impls):
             q, k, v = qkv_fn(layer, n_tok)
             o = impl.forward(q, k, v, self.kv_caches[layer], md)
+            if out_fn is not None:
+                out_fn(layer, o)
             if keep_outputs:
                 outs.append(o)
         # model_runner.py:1797-1802: only layer 0's decision reaches the block manager

@@ -18,6 +18,14 @@ from ._lib import PcEvictPolicy, check
 
 PC_BF16 = 0
 
+# kernels launched through this module since import (bench.py reads it for `gpu_launches`)
+launch_count = 0
+
+
+def _launched(n: int = 1) -> None:
+    global launch_count
+    launch_count += n
+
 _DECODE_METHOD = {"streamingLLM": 0, "value_l2": 1}
 
 
@@ -88,6 +96,7 @@ def reshape_and_cache(key: torch.Tensor, value: torch.Tensor, key_cache: torch.T
         key.data_ptr(), value.data_ptr(), key_cache.data_ptr(), value_cache.data_ptr(),
         slot_mapping.data_ptr(), n, Hkv, D, bs, key.stride(0), value.stride(0), blk_stride,
         _dtype_code(key), _stream(key)))
+    _launched()
 
 
 # ----------------------------------------------------------------------- R1+W1+S3
@@ -115,6 +124,7 @@ def prune_prompt_and_cache(key: torch.Tensor, value: torch.Tensor, key_cache: to
         slot_mapping.data_ptr(), req_meta.data_ptr(), tile_offsets.data_ptr(),
         req_meta.shape[0], int(total_tiles), Hkv, D, bs, key.stride(0), value.stride(0),
         blk_stride, _ptr(score_table), _ptr(score_slots), smb, _dtype_code(key), _stream(key)))
+    _launched()
 
 
 # ------------------------------------------------------------------- P3+S4+C1+C2
@@ -141,6 +151,7 @@ def evict_select_compact(block_tables: torch.Tensor, n_blocks: torch.Tensor,
         _ptr(kv_lens), B, C.byref(policy), _ptr(score_table), _ptr(score_slots), smb,
         num_kv_heads, out_tables.data_ptr(), out_tables.stride(0), _ptr(out_kv_lens),
         out_victim.data_ptr(), 1 if kv_lens_pre_adjusted else 0, _stream(block_tables)))
+    _launched()
 
 
 # ------------------------------------------------------------------------ A2 + S2
@@ -193,6 +204,7 @@ def paged_decode_attn_score(out: torch.Tensor, query: torch.Tensor, key_cache: t
         int(max_kv_len), float(scale), query.stride(0), out.stride(0), blk_stride,
         _ptr(seq_lens), _ptr(score_table), _ptr(score_slots), smb, workspace.data_ptr(),
         workspace.numel(), _dtype_code(query), _stream(query)))
+    _launched()
 
 
 def _check_compat(kv_cache_dtype, k_scale, v_scale, alibi_slopes, blocksparse_vert_stride):
@@ -245,6 +257,7 @@ def prefill_attn_topleft_causal(out: torch.Tensor, query: torch.Tensor, key: tor
         out.data_ptr(), query.data_ptr(), key.data_ptr(), value.data_ptr(), req_meta.data_ptr(),
         req_meta.shape[0], int(max_q_len), Hq, Hkv, D, float(scale), query.stride(0), out.stride(0),
         key.stride(0), value.stride(0), _dtype_code(query), _stream(query)))
+    _launched()
 
 
 # ------------------------------------------------------------------- block maintenance
