@@ -121,7 +121,10 @@ int pc_evict_select_compact(const int32_t* block_tables, int64_t table_stride,
  * strides q_stride / out_stride (elements).  kv_lens = physical KV lengths.  If
  * score_table != NULL and seq_lens != NULL, rows with seq_lens[b] % block_size == 0
  * get score_table[score_slots[b]][ceil(kv_len/bs)-1][h] for every kv head h.
- * workspace: pc_paged_decode_workspace_bytes() bytes, 256-byte aligned, reusable. */
+ * workspace: pc_paged_decode_workspace_bytes() bytes, 256-byte aligned.  It must be
+ * ZERO-FILLED by the caller before its first use; every call leaves it ready for the
+ * next one (arrival tickets are reset in-kernel), so one workspace per stream is
+ * allocated once and reused.  A single kernel launch, no memset. */
 size_t pc_paged_decode_workspace_bytes(int32_t batch, int32_t num_heads, int32_t num_kv_heads,
                                        int32_t head_size, int32_t block_size,
                                        int32_t max_kv_len);

@@ -1,0 +1,43 @@
+import sys, json, ctypes, torch, numpy as np
+sys.path.insert(0, '/root/repo')
+from vllm_paged_compression_b200 import _lib, ops, microbench
+lib = _lib.load()
+lib.pc_debug_set_decode_trace.argtypes = [ctypes.c_void_p]
+lib.pc_debug_set_decode_trace.restype = None
+dev = torch.device('cuda', 0)
+B, ctx = int(sys.argv[1]), int(sys.argv[2])
+buf = torch.zeros(148 * 8 * 4, dtype=torch.int64, device=dev)
+# warm without trace
+print(microbench.time_shape(dev, B, ctx, 32, 8, reps=10)['us'])
+lib.pc_debug_set_decode_trace(buf.data_ptr())
+r = microbench.time_shape(dev, B, ctx, 32, 8, reps=1)
+torch.cuda.synchronize()
+lib.pc_debug_set_decode_trace(None)
+t = buf.cpu().numpy().reshape(-1, 4).astype(np.float64)
+act = t[:, 0] > 0
+t = t[act]
+t0 = t[:, 0].min()
+t = (t - t0) / 1e3
+print("workers", len(t))
+for i, n in enumerate(["entry", "sched_ready", "stream_done", "exit"]):
+    print(f"{n:12s} min {t[:, i].min():7.2f} p50 {np.median(t[:, i]):7.2f} p90 {np.percentile(t[:, i], 90):7.2f} max {t[:, i].max():7.2f} us")
+d = t[:, 2] - t[:, 1]
+print("stream dur  min %.2f p50 %.2f max %.2f" % (d.min(), np.median(d), d.max()))
+d = t[:, 3] - t[:, 2]
+print("fixup dur   min %.2f p50 %.2f p90 %.2f max %.2f" % (d.min(), np.median(d), np.percentile(d, 90), d.max()))
+# per-CTA (= per-SM) view: w = warp * grid + block
+full = buf.cpu().numpy().reshape(-1, 4).astype(np.float64)
+grid = 148
+nw = full.shape[0] // grid
+blk_done = np.zeros(grid)
+blk_first = np.zeros(grid)
+for bidx in range(grid):
+    rows = [full[wp * grid + bidx] for wp in range(nw) if full[wp * grid + bidx][0] > 0]
+    if rows:
+        r = (np.array(rows) - t0) / 1e3
+        blk_done[bidx] = r[:, 2].max()
+        blk_first[bidx] = r[:, 2].min()
+print("per-SM last-warp stream_done: min %.2f p50 %.2f max %.2f" % (blk_done.min(), np.median(blk_done), blk_done.max()))
+print("per-SM first-warp stream_done: min %.2f p50 %.2f max %.2f" % (blk_first.min(), np.median(blk_first), blk_first.max()))
+print("within-SM spread (last-first): p50 %.2f max %.2f" % (np.median(blk_done - blk_first), (blk_done - blk_first).max()))
+print("sorted per-SM done:", np.round(np.sort(blk_done), 1).tolist()[::8])

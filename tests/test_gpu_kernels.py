@@ -334,6 +334,33 @@ def test_paged_decode_empty_sequence_and_determinism():
     assert torch.equal(outs[0], outs[1]) and torch.equal(outs[0], outs[2])   # split-KV combine is ordered
 
 
+@pytest.mark.parametrize("B,max_len,zeros", [(130, 300, (5, 31, 32, 129)), (2, 20000, ()), (257, 50, (0, 256)),
+                                             (7, 33, (3,))])
+def test_paged_decode_streamk_schedule(B, max_len, zeros):
+    """Stream-K ranges crossing many row / head boundaries, rows of zero length inside the
+    batch, more rows than one scan chunk, and a group split over > 100 warps; run twice on
+    the same workspace (arrival tickets must come back to zero)."""
+    ops = _ops()
+    Hq, Hkv, D, bs = 32, 8, 128, 16
+    q, kv, tables, kv_lens, scale = _decode_case(B, Hq, Hkv, D, bs, max_len, seed=B + max_len)
+    for z in zeros:
+        kv_lens[z] = 0
+    kc, vc = paged_ops.split_kv_cache(kv, Hkv, D)
+    ref = paged_ops.paged_attention(q, kc, vc, tables.tolist(), kv_lens.tolist(), scale).float()
+    kvd = kv.to(DEV)
+    kcd, vcd = paged_ops.split_kv_cache(kvd, Hkv, D)
+    outs = []
+    for _ in range(2):
+        out = torch.full((B, Hq, D), float("nan"), dtype=torch.bfloat16, device=DEV)
+        ops.paged_decode_attn_score(out, q.to(DEV), kcd, vcd, torch.from_numpy(tables).to(DEV),
+                                    torch.from_numpy(kv_lens).to(DEV), scale, max_len)
+        torch.cuda.synchronize()
+        outs.append(out.float().cpu())
+    assert torch.isfinite(outs[0]).all()
+    np.testing.assert_allclose(outs[0].numpy(), ref.numpy(), atol=8e-3, rtol=0)
+    assert torch.equal(outs[0], outs[1])
+
+
 @pytest.mark.parametrize("Hkv,D,bs", [(8, 128, 16), (8, 64, 16), (2, 128, 32), (4, 64, 32)])
 def test_fused_last_block_score_bit_exact(Hkv, D, bs):
     """Rows with seq_len % bs == 0 get score_table[slot][nblk-1][h] = per-head value_l2 of

@@ -198,4 +198,8 @@ int pc_swap_blocks(const void* src, void* dst, const int64_t* pairs, int32_t num
   return PC_OK;
 }
 
+/* Debug hook (not part of the drop-in surface): per-warp globaltimer stamps of the decode
+ * kernel, [warps][4] = {kernel entry, schedule ready, last page consumed, exit}. */
+void pc_debug_set_decode_trace(void* device_buf) { pc::set_decode_trace(device_buf); }
+
 }  // extern "C"

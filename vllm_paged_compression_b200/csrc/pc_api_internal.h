@@ -34,6 +34,7 @@ struct DecodeArgs {
 };
 size_t decode_workspace_bytes(int B, int Hq, int Hkv, int D, int BS, int max_kv_len, int num_sms);
 int paged_decode_attn_score(const DecodeArgs& a, cudaStream_t stream);
+void set_decode_trace(void* buf);  // debug: per-warp globaltimer stamps, nullptr = off
 
 struct CacheWriteArgs {
   const void* key;

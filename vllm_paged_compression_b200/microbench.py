@@ -95,3 +95,25 @@ def sweep(device, batches=(1, 4, 16, 64, 256), ctxs=(1024, 2048, 4096, 8192, 163
                 print(json.dumps(r), flush=True)
                 torch.cuda.empty_cache()
     return rows
+
+
+def main():
+    """python -m vllm_paged_compression_b200.microbench --B 64 --ctx 592 [--Hq 32 --Hkv 8] : one shape
+    (the target of `ncu -k regex:paged_decode`)."""
+    import argparse
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--B", type=int, default=64)
+    ap.add_argument("--ctx", type=int, default=592)
+    ap.add_argument("--Hq", type=int, default=32)
+    ap.add_argument("--Hkv", type=int, default=8)
+    ap.add_argument("--D", type=int, default=128)
+    ap.add_argument("--block", type=int, default=16)
+    ap.add_argument("--ragged", action="store_true")
+    ap.add_argument("--reps", type=int, default=None)
+    a = ap.parse_args()
+    dev = torch.device("cuda", 0)
+    print(json.dumps(time_shape(dev, a.B, a.ctx, a.Hq, a.Hkv, a.D, a.block, a.ragged, reps=a.reps)), flush=True)
+
+
+if __name__ == "__main__":
+    main()

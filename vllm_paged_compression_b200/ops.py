@@ -165,11 +165,13 @@ _workspaces = {}
 
 
 def _workspace(device: torch.device, nbytes: int) -> torch.Tensor:
-    """Per-(device, stream) scratch for split-KV partials; grown on demand, reused."""
+    """Per-(device, stream) scratch for the decode kernel's stream-K partials and arrival
+    tickets; grown on demand, reused.  Zero-filled once: the kernel leaves its ticket
+    region zero after every launch (include/pagedevict_b200.h)."""
     key = (device.index, torch.cuda.current_stream(device).cuda_stream)
     ws = _workspaces.get(key)
     if ws is None or ws.numel() < nbytes:
-        ws = torch.empty(max(nbytes, 1 << 20), dtype=torch.uint8, device=device)
+        ws = torch.zeros(max(nbytes, 1 << 20), dtype=torch.uint8, device=device)
         _workspaces[key] = ws
     return ws
 
