@@ -33,7 +33,8 @@
 extern "C" {
 #endif
 
-#define PC_ABI_VERSION 1
+#define PC_ABI_VERSION 2
+#define PC_MAX_PEERS 8
 
 typedef enum pc_status {
   PC_OK = 0,
@@ -57,7 +58,30 @@ typedef struct pc_evict_policy {
   int32_t topk_blocks;     /* <0: global window [1, n-1); >0: local window [1, 1+topk) */
 } pc_evict_policy;
 
+/* value_l2 block scores.  Replaces the per-request python lists of BlockL2NormManager
+ * (vllm/attention/block_l2norm_manager.py:8-106).  One fp32 POOL per layer, indexed by
+ * PHYSICAL block id like the KV pool itself: pool[block_id][kv_head] = sum over the
+ * block's tokens of ||V[t, head, :]||_2 (fixed fp32 order, csrc/score_common.cuh).  A
+ * block is scored once, when it fills; evicting a block needs no score bookkeeping (the
+ * table entry goes, the pool row is simply rewritten when the block is reused and fills
+ * again), so there is nothing to compact and nothing keyed by request or batch row.
+ * Tensor parallelism over KV heads: every rank holds a pool with ALL heads
+ * (heads_total columns); a rank computes its own heads [head_offset, head_offset +
+ * num_kv_heads) and the scoring kernels store each partial straight into every rank's
+ * pool through peer memory (pools[0..n_pools), NVLink P2P; n_pools == 1: no peers).
+ * Victim selection then reads the local pool (pools[local]) and sums heads in ascending
+ * global order, so every rank picks the same victim, bit-identical to TP = 1. */
+typedef struct pc_score_pool {
+  float* pools[PC_MAX_PEERS]; /* device pointers, [num_blocks][heads_total] each */
+  int32_t n_pools;            /* pools to store into (>= 1) */
+  int32_t local;              /* index of this rank's own pool in pools[] */
+  int32_t heads_total;        /* kv heads over all ranks */
+  int32_t head_offset;        /* first global kv head computed by this rank */
+} pc_score_pool;
+
 int pc_abi_version(void);
+/* sizeof() of the structs above as this library was compiled (binding self-check). */
+size_t pc_sizeof_struct(int32_t which /* 0 pc_evict_policy, 1 pc_score_pool, 2 pc_decode_step */);
 const char* pc_last_error(void);
 /* SM count of the current device (grid sizing is derived from it). */
 int pc_device_sm_count(void);
@@ -82,17 +106,16 @@ int pc_reshape_and_cache(const void* key, const void* value, void* key_cache, vo
  * req_meta int32 [num_reqs][5] = {src_start, kept, first, pruned, dst_start}: request r
  * keeps source rows src_start + (j < first ? j : j + pruned), j in [0, kept), written
  * at slot_mapping[dst_start + j].  tile_offsets int32 [num_reqs+1] = prefix sum of
- * ceil(kept/block_size).  score_table may be NULL (no scoring); otherwise every FULL
- * kept block j of request r gets score_table[score_slots[r]][j][h] (fp32 per-head
- * value_l2 partial, fixed reduction order, see csrc/score_common.cuh). */
+ * ceil(kept/block_size).  score (HOST struct) may be NULL (no scoring); otherwise every
+ * FULL kept block gets pool[block_id][head_offset + h] (fp32 per-head value_l2 partial,
+ * fixed reduction order, see csrc/score_common.cuh) in every pool of *score. */
 int pc_prune_prompt_and_cache(const void* key, const void* value, void* key_cache,
                               void* value_cache, const int64_t* slot_mapping,
                               const int32_t* req_meta, const int32_t* tile_offsets,
                               int32_t num_reqs, int32_t total_tiles, int32_t num_kv_heads,
                               int32_t head_size, int32_t block_size, int64_t key_stride,
-                              int64_t value_stride, int64_t kv_block_stride, float* score_table,
-                              const int32_t* score_slots, int32_t score_max_blocks,
-                              int32_t dtype, void* stream);
+                              int64_t value_stride, int64_t kv_block_stride,
+                              const pc_score_pool* score /* HOST */, int32_t dtype, void* stream);
 
 /* ---- P3 + S4 + C1 + C2: decode trigger, victim argmin, table/score compaction -------
  * Replaces _prune_decode_reqs_streamingLLM / _prune_decode_reqs_topk /
@@ -100,15 +123,17 @@ int pc_prune_prompt_and_cache(const void* key, const void* value, void* key_cach
  * BlockL2NormManager.get_updated_block_tables (block_l2norm_manager.py:95-106).
  * Row r owns n_blocks[r] table entries.  Triggered rows (policy on seq_lens[r] and
  * n_blocks[r]*block_size) lose entry out_victim[r]: out_tables row = input row with that
- * column deleted, shifted left, 0-padded to out_stride; the score row is compacted the
- * same way in place.  Other rows are copied; out_victim = -1.  out_kv_lens[r] =
- * kv_lens[r] - (triggered && !kv_lens_pre_adjusted ? block_size : 0).  Ties in the
- * argmin go to the lowest index (strict <, torch_cuda_sdpa.py:1536-1541). */
+ * column deleted, shifted left, 0-padded to out_stride.  Other rows are copied;
+ * out_victim = -1.  out_kv_lens[r] = kv_lens[r] - (triggered && !kv_lens_pre_adjusted ?
+ * block_size : 0).  value_l2: score of table entry i = (sum over all heads_total heads,
+ * ascending, of pool[table[i]][h]) / heads_total, read from score->pools[score->local];
+ * ties in the argmin go to the lowest index (strict <, torch_cuda_sdpa.py:1536-1541).
+ * num_kv_heads is unused when score is given (kept for call-site symmetry). */
 int pc_evict_select_compact(const int32_t* block_tables, int64_t table_stride,
                             const int32_t* n_blocks, const int32_t* seq_lens,
                             const int32_t* kv_lens, int32_t batch,
-                            const pc_evict_policy* policy /* HOST */, float* score_table,
-                            const int32_t* score_slots, int32_t score_max_blocks,
+                            const pc_evict_policy* policy /* HOST */,
+                            const pc_score_pool* score /* HOST, NULL for streamingLLM */,
                             int32_t num_kv_heads, int32_t* out_tables, int64_t out_stride,
                             int32_t* out_kv_lens, int32_t* out_victim,
                             int32_t kv_lens_pre_adjusted, void* stream);
@@ -119,8 +144,9 @@ int pc_evict_select_compact(const int32_t* block_tables, int64_t table_stride,
  * vllm/attention/ops/paged_attn.py:87-191) and the last-block scoring read of
  * torch_cuda_sdpa.py:1518-1526.  query/out [batch][num_heads][head_size] with row
  * strides q_stride / out_stride (elements).  kv_lens = physical KV lengths.  If
- * score_table != NULL and seq_lens != NULL, rows with seq_lens[b] % block_size == 0
- * get score_table[score_slots[b]][ceil(kv_len/bs)-1][h] for every kv head h.
+ * score != NULL and seq_lens != NULL, rows with seq_lens[b] % block_size == 0 (and a
+ * full last block) get pool[table[b][ceil(kv_len/bs)-1]][head_offset + h] for every
+ * local kv head h.
  * workspace: pc_paged_decode_workspace_bytes() bytes, 256-byte aligned.  It must be
  * ZERO-FILLED by the caller before its first use; every call leaves it ready for the
  * next one (arrival tickets are reset in-kernel), so one workspace per stream is
@@ -134,10 +160,45 @@ int pc_paged_decode_attn_score(void* out, const void* query, const void* key_cac
                                int32_t num_heads, int32_t num_kv_heads, int32_t head_size,
                                int32_t block_size, int32_t max_kv_len, float scale,
                                int64_t q_stride, int64_t out_stride, int64_t kv_block_stride,
-                               const int32_t* seq_lens, float* score_table,
-                               const int32_t* score_slots, int32_t score_max_blocks,
+                               const int32_t* seq_lens, const pc_score_pool* score /* HOST */,
                                void* workspace, size_t workspace_bytes, int32_t dtype,
                                void* stream);
+
+/* ---- one decode step of one layer in ONE call --------------------------------------
+ * The decode branch of TorchCUDASDPABackendImpl.forward (torch_cuda_sdpa.py:896-1062):
+ * reshape_and_cache of the step's K/V -> [on steps where a row triggers: victim
+ * selection + table compaction into compact_tables] -> paged decode attention over the
+ * (compacted) tables with the fused scoring of freshly filled blocks.  Everything that
+ * is the same for all layers of an engine step lives in struct pc_decode_step, a HOST
+ * struct built once per step; the per-layer call passes only that layer's tensors.
+ * any_trigger: 0 = no row evicts this step (compaction skipped, attention reads
+ * block_tables); != 0 = run selection (out_victim must be non-NULL, int32 [batch]) and
+ * attend over compact_tables unless attend_uncompacted is set (HEAD's streamingLLM
+ * behaviour).  kv_lens are the lengths the host passes (already
+ * reduced by block_size on trigger rows, vllm/worker/model_runner.py:540-543). */
+typedef struct pc_decode_step {
+  const int64_t* slot_mapping;   /* [batch] */
+  const int32_t* block_tables;   /* [batch][table_stride] */
+  int64_t table_stride;
+  const int32_t* kv_lens;        /* [batch] physical KV lengths handed to attention */
+  const int32_t* seq_lens;       /* [batch] logical lengths (trigger / score test) */
+  const int32_t* n_blocks;       /* [batch] table entries each row owns (needed if any_trigger) */
+  int32_t* compact_tables;       /* [batch][compact_stride] scratch (needed if any_trigger) */
+  int64_t compact_stride;
+  int32_t batch, num_heads, num_kv_heads, head_size, block_size, max_kv_len;
+  float scale;
+  int32_t any_trigger, attend_uncompacted;
+  int64_t q_stride, key_stride, value_stride, out_stride, kv_block_stride;
+  pc_evict_policy policy;
+  void* workspace;               /* see pc_paged_decode_workspace_bytes */
+  size_t workspace_bytes;
+  int32_t dtype;
+  void* stream;
+} pc_decode_step;
+int pc_decode_layer(const pc_decode_step* step /* HOST */, void* out, const void* query,
+                    const void* key, const void* value, void* key_cache, void* value_cache,
+                    const pc_score_pool* score /* HOST, NULL = no value_l2 */,
+                    int32_t* out_victim /* [batch] or NULL */);
 
 /* ---- A1: prefill attention, TOP-LEFT aligned causal mask over the pruned prompt -----
  * Replaces _run_sdpa_forward (torch_cuda_sdpa.py:1069-1127): per request

@@ -8,14 +8,20 @@ compaction) with the declared deviations of DESIGN.md:
   D2  a block is scored when it FILLS, after this step's cache write (the reference
       scores before the write, so slot bs-1 is stale) and every full prompt block is
       scored unconditionally
-  D3  the victim's score is deleted with the victim (v1 semantics,
-      torch_cuda_sdpa_v1.py:1541), so score index == table index
+  D3  a score belongs to its PHYSICAL block (dict block id -> per-head partials) instead of
+      living in a per-request python list indexed like the block table.  For layer 0 --
+      the only layer whose victims reach the block manager (model_runner.py:1797-1802) --
+      this equals v1's "delete the victim's score with the victim"
+      (torch_cuda_sdpa_v1.py:1541; HEAD never deletes).  For layers
+      >= 1, v1's list drifts by one position between its own victim and layer 0's after
+      every step on which the layers disagree (the list loses the layer's victim, the
+      table loses layer 0's); here every block keeps its own score.
   D4  compaction is v1 / HEAD-row-0 semantics for every row
   D5  streamingLLM trigger steps attend over the COMPACTED table.  HEAD/v1 compute it
       but never use it (`is_pruned_decode` vs `is_prune_decode` typo,
       torch_cuda_sdpa.py:903,910 vs 858,1046); `head_compat_uncompacted=True`
       reproduces that for the golden traces.
-State is per layer, keyed by request id, like BlockL2NormManager.
+State is per layer (one OracleLayer per attention layer), like BlockL2NormManager.
 """
 from __future__ import annotations
 
@@ -38,8 +44,8 @@ class OracleLayer:
         self.pol = pol
         self.ops = native_ops if native_ops is not None else paged_ops
         self.compat = head_compat_uncompacted
-        # req_id -> list of per-head partial scores [Hkv] fp32, index == table index
-        self.scores: Dict[str, List[np.ndarray]] = {}
+        # physical block id -> per-head partial scores [Hkv] fp32 (D3)
+        self.block_scores: Dict[int, np.ndarray] = {}
         self.last = {}
 
     # -------------------------------------------------------------- prefill
@@ -68,10 +74,10 @@ class OracleLayer:
         self.ops.reshape_and_cache(kp, vp, kc, vc, torch.tensor(slots, dtype=torch.long))
         # scores of every FULL cached prompt block (D2)
         s = 0
-        for L, rid in zip(kept, req_ids) if p.decode_evict_method == "value_l2" else ():
+        for L, tab in zip(kept, block_tables) if p.decode_evict_method == "value_l2" else ():
             vr = vp[s:s + L].float().numpy()
-            self.scores[rid] = [scoring.per_head_block_score(vr[j * bs:(j + 1) * bs])
-                                for j in range(L // bs)]
+            for j in range(L // bs):
+                self.block_scores[int(tab[j])] = scoring.per_head_block_score(vr[j * bs:(j + 1) * bs])
             s += L
         self.last = {"slots": slots, "kept": kept}
         if not compute_attention:
@@ -105,11 +111,9 @@ class OracleLayer:
                 if p.decode_evict_method == "streamingLLM":
                     idx = 1
                 else:
-                    sc = scoring.combine_heads(np.stack(self.scores[req_ids[r]][:n - 1]))
+                    sc = scoring.combine_heads(np.stack([self.block_scores[int(t)] for t in tab[:n - 1]]))
                     idx = policy.argmin_lowest_index(sc, lo, hi)
                 rmv[r] = (req_ids[r], idx)
-                if req_ids[r] in self.scores and len(self.scores[req_ids[r]]) > idx:
-                    del self.scores[req_ids[r]][idx]                      # D3
                 if not (self.compat and p.decode_evict_method == "streamingLLM"):
                     del tab[idx]
             attn_tables.append(tab)
@@ -122,14 +126,12 @@ class OracleLayer:
             if p.decode_evict_method == "value_l2" and policy.score_trigger(seq_lens[r], p):
                 last_blk = block_tables[r][-1]
                 vb = paged_ops.depage_v_block(vc, last_blk).float().numpy()
-                lst = self.scores.setdefault(req_ids[r], [])
-                n_after = len(block_tables[r]) - (1 if r in rmv else 0)
-                assert len(lst) == n_after - 1, (len(lst), n_after)
-                lst.append(scoring.per_head_block_score(vb))
+                self.block_scores[int(last_blk)] = scoring.per_head_block_score(vb)
         self.last = {"slots": slots}
         return out.view(-1, self.Hq * self.D), rmv, attn_tables
 
-    def drop_finished(self, live_req_ids):
-        for rid in list(self.scores):
-            if rid not in live_req_ids:
-                del self.scores[rid]
+    def scores_of(self, table: Sequence[int], n_full: int) -> np.ndarray:
+        """[n_full, Hkv] per-head partials of the first n_full (full) blocks of a table."""
+        if n_full == 0:
+            return np.zeros((0, self.Hkv), np.float32)
+        return np.stack([self.block_scores[int(t)] for t in table[:n_full]])

@@ -48,7 +48,6 @@ def layer_inputs(seed, layer, step, n_tok, Hq, Hkv, D):
 
 
 def run_case(c: Dict, device="cuda:0", num_layers=2, num_blocks=256, check_outputs=True) -> Dict:
-    from vllm_paged_compression_b200.backend import ScoreSlotMap
     from vllm_paged_compression_b200.engine import PagedEvictEngine
     Hq, Hkv, D, bs = c["Hq"], c["Hkv"], c["D"], c["bs"]
     cache_config, pol = make_configs(c)
@@ -103,16 +102,16 @@ def run_case(c: Dict, device="cuda:0", num_layers=2, num_blocks=256, check_outpu
         step += 1
     torch.cuda.synchronize()
     # end state: cache bytes and every live score, per layer
-    slot_map = cache_config._pc_score_slots.slot_of if pol.decode_evict_method == "value_l2" else {}
     for layer in range(num_layers):
         assert np.array_equal(eng.kv_caches[layer].cpu().view(torch.int16).numpy(),
                               kv_ref[layer].view(torch.int16).numpy()), f"layer {layer}: KV cache bytes differ"
         if pol.decode_evict_method == "value_l2":
-            table = eng.impls[layer]._score_table.cpu().numpy()
+            pool = eng.impls[layer]._score_pool.cpu().numpy()          # [num_blocks, Hkv]
             for s in eng.running:
-                lst = layers[layer].scores[s.request_id]
-                want = np.stack(lst) if lst else np.zeros((0, Hkv), np.float32)
-                got = table[slot_map[(s.request_id, s.seq_id)], :len(lst)]
+                ids = list(eng.block_manager.get_block_table(s.seq_id))
+                n_full = eng.block_manager.get_seq_kv_len(s.seq_id) // bs     # every full block is scored
+                want = layers[layer].scores_of(ids, n_full)
+                got = pool[ids[:n_full]]
                 assert np.array_equal(got.view(np.int32), want.view(np.int32)), \
                     f"layer {layer} req {s.request_id}: block scores differ"
     return stats

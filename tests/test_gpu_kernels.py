@@ -149,21 +149,24 @@ def test_prune_prompt_and_cache(D, bs, mode):
         s += L
     gidx = torch.cat(gidx)
     paged_ops.reshape_and_cache(key[gidx], value[gidx], kc, vc, torch.tensor(slots))
-    max_blocks = 32
-    ref_scores = np.zeros((len(prompt_lens), max_blocks, Hkv), dtype=np.float32)
+    # score pool: one row per PHYSICAL block, two extra head columns on each side to check that a
+    # TP rank only touches its own columns [head_offset, head_offset + Hkv)
+    HT, hoff = Hkv + 4, 2
+    ref_scores = np.full((nb, HT), -1.0, dtype=np.float32)
     vp = value[gidx].float().numpy()
     for r, m in enumerate(meta):
         for j in range(m[1] // bs):
-            ref_scores[r, j] = scoring.per_head_block_score(vp[m[4] + j * bs: m[4] + (j + 1) * bs])
+            blk = slots[m[4] + j * bs] // bs
+            ref_scores[blk, hoff:hoff + Hkv] = scoring.per_head_block_score(vp[m[4] + j * bs: m[4] + (j + 1) * bs])
     # device
     kv_dev = torch.zeros_like(kv_ref, device=DEV)
     kcd, vcd = paged_ops.split_kv_cache(kv_dev, Hkv, D)
-    score = torch.zeros(len(prompt_lens), max_blocks, Hkv, dtype=torch.float32, device=DEV)
+    score = torch.full((nb, HT), -1.0, dtype=torch.float32, device=DEV)
     ops.prune_prompt_and_cache(
         key.to(DEV), value.to(DEV), kcd, vcd, torch.tensor(slots, dtype=torch.int64, device=DEV),
         torch.tensor(meta, dtype=torch.int32, device=DEV),
-        torch.tensor(tile_off, dtype=torch.int32, device=DEV), tile_off[-1], score,
-        torch.arange(len(prompt_lens), dtype=torch.int32, device=DEV))
+        torch.tensor(tile_off, dtype=torch.int32, device=DEV), tile_off[-1],
+        ops.make_score_pool(score, head_offset=hoff))
     torch.cuda.synchronize()
     assert np.array_equal(_bits(kv_dev), _bits(kv_ref))
     assert np.array_equal(score.cpu().numpy().view(np.int32), ref_scores.view(np.int32))   # bit-exact
@@ -175,8 +178,10 @@ def _evict_case(B, M, pol, rs, tie=False):
     n_blocks = rs.randint(1, M + 1, size=B).astype(np.int32)
     n_blocks[0] = M
     tables = np.zeros((B, M), dtype=np.int32)
+    ids, o = rs.permutation(100000), 0
     for r in range(B):
-        tables[r, :n_blocks[r]] = rs.permutation(100000)[:n_blocks[r]] + 1
+        tables[r, :n_blocks[r]] = ids[o:o + n_blocks[r]] + 1          # block ids unique over the batch
+        o += int(n_blocks[r])
     # logical lengths: mix of trigger / non-trigger steps
     seq_lens = np.zeros(B, dtype=np.int32)
     for r in range(B):
@@ -186,7 +191,11 @@ def _evict_case(B, M, pol, rs, tie=False):
     scores = rs.rand(B, M, Hkv).astype(np.float32) * 50
     if tie:
         scores[:, 2:, :] = scores[:, 2:3, :]           # all candidates >= 2 tie; lowest index must win
-    return tables, n_blocks, seq_lens, scores, Hkv
+    # the device keeps scores with the physical block: pool[block_id][head]
+    pool = np.zeros((100002, Hkv), dtype=np.float32)
+    for r in range(B):
+        pool[tables[r, :n_blocks[r]]] = scores[r, :n_blocks[r]]
+    return tables, n_blocks, seq_lens, scores, Hkv, pool
 
 
 @pytest.mark.parametrize("method,topk", [("streamingLLM", -1), ("value_l2", -1), ("value_l2", 3)])
@@ -199,11 +208,10 @@ def test_evict_select_compact_bit_exact(method, topk, mode, tie):
     pol = Policy(block_size=bs, cache_prune_type=mode, cache_budget=128, evict_freq=2,
                  decode_evict_method=method, topk_blocks=topk)
     rs = np.random.RandomState(5 + (13 if tie else 0))
-    tables, n_blocks, seq_lens, scores, Hkv = _evict_case(B, M, pol, rs, tie)
+    tables, n_blocks, seq_lens, scores, Hkv, pool = _evict_case(B, M, pol, rs, tie)
     kv_lens = (n_blocks * bs - rs.randint(0, bs, size=B)).astype(np.int32)
     # oracle
     victims = {}
-    ref_scores = scores.copy()
     for r in range(B):
         n = int(n_blocks[r])
         if n >= 3 and policy.decode_trigger(int(seq_lens[r]), n * bs, pol):
@@ -212,8 +220,6 @@ def test_evict_select_compact_bit_exact(method, topk, mode, tie):
                 victims[r] = 1
             else:
                 victims[r] = policy.argmin_lowest_index(scoring.combine_heads(scores[r, :n - 1]), lo, hi)
-                v = victims[r]
-                ref_scores[r, v:n - 2] = scores[r, v + 1:n - 1]
     ref_tables = policy.compact_block_tables(tables, n_blocks, victims)
     ref_victim = np.array([victims.get(r, -1) for r in range(B)], dtype=np.int32)
     ref_kv = np.array([kv_lens[r] - (bs if r in victims else 0) for r in range(B)], dtype=np.int32)
@@ -224,19 +230,15 @@ def test_evict_select_compact_bit_exact(method, topk, mode, tie):
     out_t = torch.full((B, M), -7, dtype=torch.int32, device=DEV)
     out_kv = torch.zeros(B, dtype=torch.int32, device=DEV)
     out_v = torch.zeros(B, dtype=torch.int32, device=DEV)
-    sc = d(scores.copy())
+    sc = d(pool.copy())
     ops.evict_select_compact(d(tables), d(n_blocks), d(seq_lens), d(kv_lens), cpol, Hkv, out_t, out_kv,
-                             out_v, sc, torch.arange(B, dtype=torch.int32, device=DEV),
+                             out_v, ops.make_score_pool(sc) if method == "value_l2" else None,
                              kv_lens_pre_adjusted=False)
     torch.cuda.synchronize()
     assert np.array_equal(out_v.cpu().numpy(), ref_victim)
     assert np.array_equal(out_t.cpu().numpy(), ref_tables)
     assert np.array_equal(out_kv.cpu().numpy(), ref_kv)
-    if method == "value_l2":
-        got = sc.cpu().numpy()
-        for r in range(B):   # live score entries [0, n_after - 1) must equal the compacted oracle row
-            n_after = int(n_blocks[r]) - (1 if r in victims else 0)
-            assert np.array_equal(got[r, :max(n_after - 1, 0)], ref_scores[r, :max(n_after - 1, 0)])
+    assert np.array_equal(sc.cpu().numpy(), pool)      # scores stay with their blocks: nothing to compact
     assert len(victims) > 3
 
 
@@ -363,8 +365,9 @@ def test_paged_decode_streamk_schedule(B, max_len, zeros):
 
 @pytest.mark.parametrize("Hkv,D,bs", [(8, 128, 16), (8, 64, 16), (2, 128, 32), (4, 64, 32)])
 def test_fused_last_block_score_bit_exact(Hkv, D, bs):
-    """Rows with seq_len % bs == 0 get score_table[slot][nblk-1][h] = per-head value_l2 of
-    their last (just filled) block, bit-identical to oracle/scoring.py."""
+    """Rows with seq_len % bs == 0 get pool[last block id][head_offset + h] = per-head value_l2 of
+    their last (just filled) block, bit-identical to oracle/scoring.py; written to every pool
+    listed in the pc_score_pool (the TP peer stores, emulated here with two local pools)."""
     ops = _ops()
     B, Hq, M = 9, Hkv * 4, 40
     rs = np.random.RandomState(D + bs)
@@ -385,21 +388,25 @@ def test_fused_last_block_score_bit_exact(Hkv, D, bs):
     kv = rnd(9, 2, nb, bs * Hkv * D)
     q = rnd(10, B, Hq, D)
     kc, vc = paged_ops.split_kv_cache(kv, Hkv, D)
-    slots = rs.permutation(B).astype(np.int32)
-    ref = np.full((B, M, Hkv), -1.0, dtype=np.float32)
+    HT, hoff = 2 * Hkv, Hkv          # this rank computes the upper half of the heads
+    ref = np.full((nb, HT), -1.0, dtype=np.float32)
     for r in range(B):
-        if seq_lens[r] % bs == 0:
-            vb = paged_ops.depage_v_block(vc, int(tables[r, nblk[r] - 1])).float().numpy()
-            ref[slots[r], nblk[r] - 1] = scoring.per_head_block_score(vb)
+        if seq_lens[r] % bs == 0 and kv_lens[r] % bs == 0:
+            blk = int(tables[r, nblk[r] - 1])
+            vb = paged_ops.depage_v_block(vc, blk).float().numpy()
+            ref[blk, hoff:hoff + Hkv] = scoring.per_head_block_score(vb)
     kvd = kv.to(DEV)
     kcd, vcd = paged_ops.split_kv_cache(kvd, Hkv, D)
-    score = torch.full((B, M, Hkv), -1.0, dtype=torch.float32, device=DEV)
+    score = torch.full((nb, HT), -1.0, dtype=torch.float32, device=DEV)
+    peer = torch.full((nb, HT), -1.0, dtype=torch.float32, device=DEV)
+    sp = ops.make_score_pool(score, head_offset=hoff, peer_ptrs=[peer.data_ptr(), score.data_ptr()], local=1)
     out = torch.empty(B, Hq, D, dtype=torch.bfloat16, device=DEV)
     ops.paged_decode_attn_score(out, q.to(DEV), kcd, vcd, torch.from_numpy(tables).to(DEV),
                                 torch.from_numpy(kv_lens).to(DEV), D ** -0.5, M * bs,
-                                torch.from_numpy(seq_lens).to(DEV), score, torch.from_numpy(slots).to(DEV))
+                                torch.from_numpy(seq_lens).to(DEV), sp)
     torch.cuda.synchronize()
     assert np.array_equal(score.cpu().numpy().view(np.int32), ref.view(np.int32))
+    assert torch.equal(score, peer)
 
 
 # ------------------------------------------------------------------------------ A1

@@ -130,22 +130,6 @@ def test_cli_flag_sets():
         CacheConfig(block_size=16, paged_evict_config=_budget(200))       # budget % block_size != 0
 
 
-def test_score_slot_map():
-    from vllm_paged_compression_b200.backend import ScoreSlotMap
-    m = ScoreSlotMap(4)
-    s1, fresh = m.assign([("a", 0), ("b", 1)])
-    assert sorted(fresh) == sorted(s1) and len(set(s1)) == 2
-    s2, fresh = m.assign([("c", 2)])                      # a, b absent from this batch keep their rows
-    assert fresh == s2 and m.assign([("a", 0), ("b", 1)])[0] == s1
-    m.assign([("d", 3)])
-    s5, fresh = m.assign([("e", 4)])                      # full: least recently seen ("c") is recycled
-    assert fresh == s5 == s2
-    m.release("a")
-    assert ("a", 0) not in m.slot_of
-    with pytest.raises(RuntimeError):
-        m.assign([(str(i), i) for i in range(10)])
-
-
 def test_backend_surface_names():
     from vllm_paged_compression_b200.backend import (PagedAttention, TorchCUDASDPABackend,
                                                      TorchCUDASDPABackendImpl, TorchCUDASDPAMetadata,

@@ -328,64 +328,6 @@ class TorchCUDASDPAMetadataBuilder(AttentionMetadataBuilder[TorchCUDASDPAMetadat
 
 
 # ==================================================================== per-device state
-class ScoreSlotMap:
-    """request -> row of the per-layer score tables.  Replaces the request diffing of
-    BlockL2NormManager.update_reqs / flat_sequence_map (block_l2norm_manager.py:16-88), with
-    one difference (declared): a request keeps its row while it is alive even when a batch
-    does not contain it (the reference drops every request that is absent from the current
-    batch, so interleaved prefill batches wipe the scores of running requests).  Rows are
-    recycled least-recently-seen first when the table is full."""
-
-    @classmethod
-    def for_config(cls, cache_config, capacity: int) -> "ScoreSlotMap":
-        """One map per engine: every layer's impl receives the same CacheConfig object
-        (vllm/attention/layer.py:102-105), so the map rides on it."""
-        inst = getattr(cache_config, "_pc_score_slots", None)
-        if inst is None or inst.capacity < capacity:
-            inst = cls(capacity)
-            cache_config._pc_score_slots = inst
-        return inst
-
-    def __init__(self, capacity: int) -> None:
-        self.capacity = capacity
-        self.slot_of: Dict[Tuple[str, int], int] = {}
-        self.last_seen: Dict[Tuple[str, int], int] = {}
-        self.free: List[int] = list(range(capacity - 1, -1, -1))
-        self.tick = 0
-
-    def assign(self, keys: List[Tuple[str, int]]) -> Tuple[List[int], List[int]]:
-        """-> (slot per key, slots that were newly handed out and must be zeroed)."""
-        self.tick += 1
-        fresh: List[int] = []
-        out: List[int] = []
-        for k in keys:
-            s = self.slot_of.get(k)
-            if s is None:
-                if not self.free:
-                    self._reclaim(set(keys))
-                s = self.free.pop()
-                self.slot_of[k] = s
-                fresh.append(s)
-            self.last_seen[k] = self.tick
-            out.append(s)
-        return out, fresh
-
-    def _reclaim(self, keep) -> None:
-        victims = sorted((k for k in self.slot_of if k not in keep), key=lambda k: self.last_seen[k])
-        if not victims:
-            raise RuntimeError(f"score table has {self.capacity} rows but the batch needs more; "
-                               "raise cache_config.max_num_seqs")
-        for k in victims[:max(1, len(victims) // 4)]:
-            self.free.append(self.slot_of.pop(k))
-            del self.last_seen[k]
-
-    def release(self, request_id: str) -> None:
-        """Optional engine hook: a finished request frees its rows immediately."""
-        for k in [k for k in self.slot_of if k[0] == request_id]:
-            self.free.append(self.slot_of.pop(k))
-            del self.last_seen[k]
-
-
 def _flat_rows(reqid_mapping_blocktables) -> List[Tuple[str, int]]:
     """Batch row -> (request_id, seq_id), the order the builder appended them in
     (= BlockL2NormManager.flat_sequence_map, block_l2norm_manager.py:56-62)."""
@@ -394,7 +336,15 @@ def _flat_rows(reqid_mapping_blocktables) -> List[Tuple[str, int]]:
 
 # ============================================================================== impl
 class TorchCUDASDPABackendImpl(AttentionImpl[TorchCUDASDPAMetadata]):
-    """torch_cuda_sdpa.py:728-1586."""
+    """torch_cuda_sdpa.py:728-1586.
+
+    Extra keyword arguments (all optional; the reference passes cache_config / prefix,
+    vllm/attention/layer.py:102-105):
+      tp_rank, tp_size   tensor-parallel position; num_kv_heads is the LOCAL head count
+                         (vllm/model_executor/models/llama.py:117-130)
+      score_exchange     parallel.ScoreExchange: allocates the per-layer score pools so that
+                         every rank can store into every rank's pool (None = single GPU)
+    """
 
     def __init__(self, num_heads: int, head_size: int, scale: float, num_kv_heads: Optional[int] = None,
                  alibi_slopes: Optional[List[float]] = None, sliding_window: Optional[int] = None,
@@ -429,6 +379,12 @@ class TorchCUDASDPABackendImpl(AttentionImpl[TorchCUDASDPAMetadata]):
             self.paged_evict_config = self.cache_config.paged_evict_config
         self.prefix: str = kwargs.get("prefix", "")
         self.layer_idx = _extract_layer_index(self.prefix)
+        self.tp_rank = int(kwargs.get("tp_rank", 0))
+        self.tp_size = int(kwargs.get("tp_size", 1))
+        self.score_exchange = kwargs.get("score_exchange", None)
+        if self.tp_size > 1 and self._value_l2 and self.score_exchange is None:
+            raise ValueError("value_l2 eviction under tensor parallelism needs a score_exchange "
+                             "(every rank must see every head's block scores)")
         # HEAD/v1 compute the compacted table on streamingLLM trigger steps but hand the
         # un-compacted one to the kernel (is_pruned_decode vs is_prune_decode,
         # torch_cuda_sdpa.py:903,910 vs 858,1046).  Default = the intended behaviour;
@@ -437,8 +393,10 @@ class TorchCUDASDPABackendImpl(AttentionImpl[TorchCUDASDPAMetadata]):
             "head_compat_uncompacted", os.environ.get("PC_HEAD_COMPAT_UNCOMPACTED", "0") == "1"))
         self.reqids_mapping_rmv_blockIdx: Dict[int, Tuple[str, int]] = {}
         self._pending_victims = None      # (device int32 [B], rows) of the last value_l2 step
-        self._score_table: Optional[torch.Tensor] = None   # fp32 [slots, max_blocks, Hkv]
+        self._score_pool: Optional[torch.Tensor] = None   # fp32 [num_blocks, Hkv * tp_size]
+        self._score = None                                 # ops.PcScorePool over it
         self._c_policy = None
+        self._cache_ptrs = None           # (kv_cache data_ptr, key ptr, value ptr, views)
 
     # ------------------------------------------------------------------ state helpers
     @property
@@ -450,38 +408,43 @@ class TorchCUDASDPABackendImpl(AttentionImpl[TorchCUDASDPAMetadata]):
             self._c_policy = ops.make_policy(self.paged_evict_config, self.cache_config.block_size)
         return self._c_policy
 
-    def _scores(self, device, need_blocks: int) -> torch.Tensor:
-        """Score table of this layer, allocated on first use, widened on demand."""
-        slots = int(getattr(self.cache_config, "max_num_seqs", 256))
-        want = max(need_blocks + 1, int(getattr(self.cache_config, "max_model_len", 0) or 0)
-                   // self.cache_config.block_size + 2, 64)
-        t = self._score_table
-        if t is None or t.device != device:
-            self._score_table = torch.zeros(slots, want, self.num_kv_heads, dtype=torch.float32,
-                                            device=device)
-        elif t.shape[1] <= need_blocks or t.shape[0] < slots:
-            new = torch.zeros(max(slots, t.shape[0]), max(want, 2 * t.shape[1]), self.num_kv_heads,
-                              dtype=torch.float32, device=device)
-            new[:t.shape[0], :t.shape[1]] = t
-            self._score_table = new
-        return self._score_table
+    def _scores(self, device, num_blocks: int):
+        """Score pool of this layer (one fp32 row per physical block, every TP rank's
+        heads), allocated on first use next to the KV pool it shadows."""
+        t = self._score_pool
+        if t is None or t.device != device or t.shape[0] < num_blocks:
+            heads_total = self.num_kv_heads * self.tp_size
+            if self.score_exchange is not None:
+                t, peers = self.score_exchange.alloc_pool(num_blocks, heads_total, device)
+                self._score = ops.make_score_pool(t, self.tp_rank * self.num_kv_heads, peers, self.tp_rank)
+            else:
+                t = torch.zeros(num_blocks, heads_total, dtype=torch.float32, device=device)
+                self._score = ops.make_score_pool(t, 0)
+            self._score_pool = t
+        return self._score
+
+    def _caches(self, kv_cache: torch.Tensor):
+        """key/value cache views + raw pointers, cached per kv_cache tensor."""
+        c = self._cache_ptrs
+        if c is None or c[0] != kv_cache.data_ptr() or c[4] != kv_cache.shape[1]:
+            kc, vc = PagedAttention.split_kv_cache(kv_cache, self.num_kv_heads, self.head_size)
+            ops._cache_dims(kc, vc)       # layout check once
+            c = (kv_cache.data_ptr(), kc, vc, (kc.data_ptr(), vc.data_ptr(), vc.stride(0)), kv_cache.shape[1])
+            self._cache_ptrs = c
+        return c[1], c[2], c[3]
 
     def _prepare_step(self, md: TorchCUDASDPAMetadata, device, bs: int) -> Dict[str, Any]:
         """Host work done ONCE per engine step (by the first layer that sees `md`): policy
-        arithmetic, request -> score row assignment and one packed H2D of the int32 side
-        tables.  The reference repeats its equivalent loops in every layer."""
+        arithmetic and one packed H2D of the int32 side tables.  The reference repeats its
+        equivalent loops in every layer."""
         if md._pc_step is not None:
             return md._pc_step
         cfg = self.paged_evict_config
         st: Dict[str, Any] = {}
         rows = _flat_rows(md.reqid_mapping_blocktables) if md.reqid_mapping_blocktables else []
         st["rows"] = rows
-        slots, fresh = [], []
-        if self._value_l2 and rows:
-            cap = int(getattr(self.cache_config, "max_num_seqs", 256))
-            slots, fresh = ScoreSlotMap.for_config(self.cache_config, cap).assign(rows)
-        st["fresh_slots"] = fresh
         pack: List[np.ndarray] = []
+        names: List[str] = []
         if md.num_prefills > 0:
             seq_lens = md.seq_lens[:md.num_prefills]
             m5, m6, m6_full, toff = [], [], [], [0]
@@ -495,12 +458,11 @@ class TorchCUDASDPABackendImpl(AttentionImpl[TorchCUDASDPAMetadata]):
                 src += L
                 dst += kept
             st["total_tiles"] = toff[-1]
-            st["max_blocks"] = max((b - a for a, b in zip(toff[:-1], toff[1:])), default=0)
             st["kept_tokens"] = dst
             use = m6_full if (cfg is None or cfg.disable_evict_prefill) else m6
             pack = [np.asarray(m5, np.int32).reshape(-1), np.asarray(toff, np.int32),
-                    np.asarray(use, np.int32).reshape(-1), np.asarray(slots, np.int32)]
-            names = ["m5", "toff", "m6", "slots"]
+                    np.asarray(use, np.int32).reshape(-1)]
+            names = ["m5", "toff", "m6"]
         else:
             kv = md.seq_kv_lens if md.seq_kv_lens else md.seq_lens
             if md.reqid_mapping_blocktables:
@@ -512,9 +474,8 @@ class TorchCUDASDPABackendImpl(AttentionImpl[TorchCUDASDPAMetadata]):
             # on trigger rows kv lens arrive already reduced by block_size (model_runner.py:540-543)
             st["trigger_rows"] = [i for i, t in enumerate(trig) if t]
             st["max_kv_len"] = max(kv, default=0)
-            st["max_blocks"] = max(nblk, default=0)
-            pack = [np.asarray(nblk, np.int32), np.asarray(slots, np.int32)]
-            names = ["nblk", "slots"]
+            pack = [np.asarray(nblk, np.int32)]
+            names = ["nblk"]
         flat = np.concatenate(pack) if pack else np.empty(0, np.int32)
         dev = _h2d(flat, device, True)
         o = 0
@@ -524,8 +485,6 @@ class TorchCUDASDPABackendImpl(AttentionImpl[TorchCUDASDPAMetadata]):
         if "m5" in st:
             st["m5"] = st["m5"].view(-1, 5)
             st["m6"] = st["m6"].view(-1, 6)
-        if fresh:
-            st["fresh_idx"] = torch.as_tensor(fresh, dtype=torch.long, device=device)
         md._pc_step = st
         return st
 
@@ -547,7 +506,7 @@ class TorchCUDASDPABackendImpl(AttentionImpl[TorchCUDASDPAMetadata]):
         v = value.view(-1, self.num_kv_heads, self.head_size)
         out = output.view(-1, self.num_heads, self.head_size) if output is not None else torch.empty_like(q)
         is_profile_run = kv_cache.numel() == 0
-        assert md.prefill_metadata is None or md.decode_metadata is None, \
+        assert md.num_prefills == 0 or md.num_decode_tokens == 0, \
             "paged eviction does not support chunked prefill"
         dev = query.device
         if self.cache_config is not None:
@@ -555,62 +514,72 @@ class TorchCUDASDPABackendImpl(AttentionImpl[TorchCUDASDPAMetadata]):
         else:
             bs = 16 if is_profile_run else kv_cache.shape[2] // (self.num_kv_heads * self.head_size)
         st = self._prepare_step(md, dev, bs)
-        if not is_profile_run:
-            key_cache, value_cache = PagedAttention.split_kv_cache(kv_cache, self.num_kv_heads,
-                                                                   self.head_size)
         if md.num_prefills > 0:
-            self._forward_prefill(q, k, v, out, md, st, None if is_profile_run else (key_cache, value_cache))
+            self._forward_prefill(q, k, v, out, md, st, None if is_profile_run else kv_cache)
         elif md.num_decode_tokens > 0:
-            self._forward_decode(q, k, v, out, md, st, key_cache, value_cache)
+            self._forward_decode(q, k, v, out, md, st, kv_cache, bs)
         return out.view(-1, self.num_heads * self.head_size)
 
-    def _forward_prefill(self, q, k, v, out, md, st, caches) -> None:
-        if caches is not None:
-            score = slots = None
-            if self._value_l2:
-                score = self._scores(q.device, st["max_blocks"])
-                slots = st["slots"]
-                if st["fresh_slots"]:
-                    score[st["fresh_idx"]] = 0
+    def _forward_prefill(self, q, k, v, out, md, st, kv_cache) -> None:
+        if kv_cache is not None:
+            key_cache, value_cache, _ = self._caches(kv_cache)
+            score = self._scores(q.device, kv_cache.shape[1]) if self._value_l2 else None
             if self.enabled_paged_eviction:
                 # R1 + W1 + S3 in one pass; slot_mapping has exactly `kept` entries per request
-                ops.prune_prompt_and_cache(k, v, caches[0], caches[1], md.slot_mapping, st["m5"],
-                                           st["toff"], st["total_tiles"], score, slots)
+                ops.prune_prompt_and_cache(k, v, key_cache, value_cache, md.slot_mapping, st["m5"],
+                                           st["toff"], st["total_tiles"], score)
             else:
-                ops.reshape_and_cache(k, v, caches[0], caches[1], md.slot_mapping)
+                ops.reshape_and_cache(k, v, key_cache, value_cache, md.slot_mapping)
         # A1: top-left aligned causal mask over the kept rows (or all rows when
         # disable_evict_prefill / eviction off) -- torch_cuda_sdpa.py:1069-1127
         ops.prefill_attn_topleft_causal(out, q, k, v, st["m6"], md.max_query_len, self.scale)
 
-    def _forward_decode(self, q, k, v, out, md, st, key_cache, value_cache) -> None:
-        ops.reshape_and_cache(k, v, key_cache, value_cache, md.slot_mapping)
+    def _decode_step_struct(self, q, k, v, out, md, st, blk_stride: int, bs: int):
+        """struct pc_decode_step shared by every layer of this engine step."""
+        ds = st.get("c_step")
+        if ds is not None and (ds.q_stride, ds.key_stride, ds.value_stride, ds.out_stride,
+                               ds.kv_block_stride) == (q.stride(0), k.stride(0), v.stride(0),
+                                                       out.stride(0), blk_stride):
+            return ds
+        for t in (q, k, v, out):
+            if t.stride()[1:] != (self.head_size, 1) or t.dtype != torch.bfloat16:
+                raise RuntimeError("query/key/value/out rows must be dense bf16 [heads, head_size]")
         tables = md.block_tables
         kv_lens = md.seq_kv_lens_tensor if self.enabled_paged_eviction else md.seq_lens_tensor
-        score = slots = seq_lens_t = None
-        if self._value_l2:
-            score = self._scores(q.device, st["max_blocks"])
-            slots, seq_lens_t = st["slots"], md.seq_lens_tensor
-            if st["fresh_slots"]:          # decode row without a scored prefill (e.g. swapped in)
-                score[st["fresh_idx"]] = 0
         trig = st.get("trigger_rows", [])
+        compact = None
         if trig:
-            B, M = tables.shape
-            out_tables = torch.empty(B, M, dtype=torch.int32, device=q.device)
-            victims = torch.empty(B, dtype=torch.int32, device=q.device)
-            ops.evict_select_compact(tables, st["nblk"], md.seq_lens_tensor, None, self._policy_struct(),
-                                     self.num_kv_heads, out_tables, None, victims, score, slots,
-                                     kv_lens_pre_adjusted=True)
+            compact = st.get("compact")
+            if compact is None:
+                compact = torch.empty_like(tables)
+                st["compact"] = compact
+        attend_unc = bool(trig) and (not self._value_l2) and self.head_compat_uncompacted
+        ds = ops.make_decode_step(
+            md.slot_mapping, tables, kv_lens, md.seq_lens_tensor, q.shape[0], self.num_heads,
+            self.num_kv_heads, self.head_size, bs, st["max_kv_len"], self.scale, q.stride(0),
+            k.stride(0), v.stride(0), out.stride(0), blk_stride,
+            policy=self._policy_struct() if self.enabled_paged_eviction else None,
+            n_blocks=st["nblk"], compact_tables=compact, any_trigger=bool(trig),
+            attend_uncompacted=attend_unc)
+        st["c_step"] = ds
+        return ds
+
+    def _forward_decode(self, q, k, v, out, md, st, kv_cache, bs: int) -> None:
+        """W1 -> [P3 + S4 + C1 on trigger steps] -> A2 + S2, one native call."""
+        _, _, (kptr, vptr, blk_stride) = self._caches(kv_cache)
+        ds = self._decode_step_struct(q, k, v, out, md, st, blk_stride, bs)
+        score = self._scores(q.device, kv_cache.shape[1]) if self._value_l2 else None
+        trig = st.get("trigger_rows", [])
+        victims = None
+        if trig:
+            victims = torch.empty(q.shape[0], dtype=torch.int32, device=q.device)
+        ops.decode_layer(ds, out, q, k, v, kptr, vptr, score, victims)
+        if trig:
             rows = st["rows"]
             if self._value_l2:
                 self._pending_victims = (victims, trig, rows)
             else:                          # streamingLLM: the victim is always table index 1
                 self.reqids_mapping_rmv_blockIdx = {r: (rows[r][0], 1) for r in trig}
-                if not self.head_compat_uncompacted:
-                    tables = out_tables
-            if self._value_l2:
-                tables = out_tables
-        ops.paged_decode_attn_score(out, q, key_cache, value_cache, tables, kv_lens, self.scale,
-                                    st["max_kv_len"], seq_lens_t, score, slots)
 
     def get_rmv_block_idx(self) -> Dict[int, Tuple[str, int]]:
         """{batch_row: (request_id, table_index)} of THIS step (torch_cuda_sdpa.py:1066-1067).

@@ -29,9 +29,7 @@ struct CacheWriteParams {
   const int* __restrict__ tile_offsets;  // [R+1]
   int num_reqs, num_tokens, Hkv;
   long long key_stride, value_stride, kv_block_stride;
-  float* score_table;
-  const int* __restrict__ score_slots;
-  int score_max_blocks;
+  ScorePool score;
 };
 
 template <int D, int BS>
@@ -136,11 +134,10 @@ __global__ void __launch_bounds__(128) cache_write_kernel(const CacheWriteParams
   }
 
   // ---- prompt block score (full kept blocks only), per kv head, fixed fp32 order
-  if (p.score_table != nullptr && ntok == BS && tid < 32) {
+  if (p.score.n_pools > 0 && whole && tid < 32) {
     const float sc = warp_value_l2_head_score<D, BS>(
         [&](int tok, int d) { return __bfloat162float(vs[tok * VROW + d]); });
-    if (tid == 0)
-      p.score_table[((size_t)p.score_slots[r] * p.score_max_blocks + j) * p.Hkv + h] = sc;
+    if (tid == 0) score_store(p.score, slot_s[0] / BS, h, sc);
   }
 }
 
@@ -171,9 +168,7 @@ int cache_write(const CacheWriteArgs& a, cudaStream_t stream) {
   p.key_stride = a.key_stride;
   p.value_stride = a.value_stride;
   p.kv_block_stride = a.kv_block_stride;
-  p.score_table = a.score_table;
-  p.score_slots = a.score_slots;
-  p.score_max_blocks = a.score_max_blocks;
+  p.score = a.score;
   const int tiles = a.req_meta ? a.total_tiles : (a.num_tokens + a.BS - 1) / a.BS;
   if (tiles <= 0) return 0;
   if (a.D == 128 && a.BS == 16) return launch_cache_write<128, 16>(p, tiles, stream);

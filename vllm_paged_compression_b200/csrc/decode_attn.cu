@@ -38,7 +38,7 @@
 //   * scoring: when seq_lens[b] % BS == 0 the row's last block just filled; the warp
 //     that owns that page computes the per-head value_l2 partial from the V page it
 //     already has in shared memory (zero extra HBM bytes) and stores it at
-//     score_table[slot][nblk-1][h].
+//     pool[physical block][head] of every rank's score pool (peer stores under TP).
 #include "pc_common.cuh"
 #include "score_common.cuh"
 #include <stdlib.h>
@@ -59,9 +59,7 @@ struct DecodeParams {
   int* counters;    // [0] next chunk id - launched warps, [1] warps that have exited; zero between launches
   int* tickets;     // [B * GH] arrival counters, zero between launches
   const int* __restrict__ seq_lens;     // nullptr: no scoring
-  const int* __restrict__ score_slots;  // [B]
-  float* score_table;                   // [slots][score_max_blocks][Hkv]
-  int score_max_blocks;
+  ScorePool score;                      // per-block value_l2 partials, indexed by physical block
   int B, Hq, Hkv, G, HG, GH;  // G = Hq/Hkv, HG = ceil(G/8), GH = Hkv*HG groups per row
   long long q_stride;         // elements between sequences in q
   long long out_stride;       // elements between sequences in out
@@ -376,7 +374,7 @@ paged_decode_attn_score_kernel(const DecodeParams p) {
         const float sc = warp_value_l2_head_score<D, BS>(
             [&](int tok, int dd) { return __bfloat162float(vp[dd * BS + tok]); });
         if (lane == 0)
-          p.score_table[((size_t)__ldg(p.score_slots + b) * p.score_max_blocks + (nblk - 1)) * p.Hkv + h] = sc;
+          score_store(p.score, __ldg(p.block_tables + (size_t)b * p.table_stride + blk), h, sc);
       }
 
       // ---------------- refill this slot (the issue side may open the next chunk here)
@@ -634,10 +632,8 @@ int paged_decode_attn_score(const DecodeArgs& a, cudaStream_t stream) {
   p.tickets = reinterpret_cast<int*>(ws + kOffTickets);
   p.part_ml = reinterpret_cast<float*>(ws + kOffPartials);
   p.part_o = reinterpret_cast<float*>(ws + pl.off_part_o);
-  p.seq_lens = a.score_table ? a.seq_lens : nullptr;
-  p.score_slots = a.score_slots;
-  p.score_table = a.score_table;
-  p.score_max_blocks = a.score_max_blocks;
+  p.seq_lens = a.score.n_pools > 0 ? a.seq_lens : nullptr;
+  p.score = a.score;
   p.B = a.B; p.Hq = a.Hq; p.Hkv = a.Hkv; p.G = a.Hq / a.Hkv; p.HG = (p.G + 7) / 8; p.GH = a.Hkv * p.HG;
   if ((long long)p.B * p.GH > kMaxGroups)
     return set_error(PC_ERR_INVALID, "decode: batch x kv heads exceeds the ticket table (1M groups)");

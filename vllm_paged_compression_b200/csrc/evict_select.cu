@@ -25,9 +25,7 @@ struct EvictParams {
   const int* __restrict__ seq_lens;
   const int* __restrict__ kv_lens;
   pc_evict_policy pol;
-  float* score_table;
-  const int* __restrict__ score_slots;
-  int score_max_blocks, Hkv;
+  ScorePool score;
   int* out_tables;
   long long out_stride;
   int* out_kv_lens;
@@ -67,13 +65,15 @@ __global__ void __launch_bounds__(kEvictThreads) evict_select_compact_kernel(con
       const int lo = 1;
       int hi = n - 1;
       if (p.pol.topk_blocks > 0) hi = min(hi, 1 + p.pol.topk_blocks);
-      const float* srow = p.score_table + (size_t)p.score_slots[b] * p.score_max_blocks * p.Hkv;
+      const float* pool = p.score.pools[p.score.local];
+      const int HT = p.score.heads_total;
       float bv = FLT_MAX;
       int bi = 0x7fffffff;
       for (int i = lo + tid; i < hi; i += kEvictThreads) {
+        const float* srow = pool + (size_t)row[i] * HT;  // scores live with the physical block
         float acc = 0.f;  // heads ascending, then / Hkv: oracle/scoring.py combine_heads
-        for (int hh = 0; hh < p.Hkv; ++hh) acc = __fadd_rn(acc, srow[(size_t)i * p.Hkv + hh]);
-        const float sc = __fdiv_rn(acc, (float)p.Hkv);
+        for (int hh = 0; hh < HT; ++hh) acc = __fadd_rn(acc, __ldcg(srow + hh));
+        const float sc = __fdiv_rn(acc, (float)HT);
         if (bi == 0x7fffffff || sc < bv) { bv = sc; bi = i; }  // strict <: lowest index wins
       }
       // (value, index) min-reduction; ties -> lower index
@@ -111,28 +111,13 @@ __global__ void __launch_bounds__(kEvictThreads) evict_select_compact_kernel(con
       p.out_kv_lens[b] = p.kv_lens[b] - ((victim >= 0 && !p.pre_adjusted) ? p.pol.block_size : 0);
   }
 
-  // ---- score-row compaction (value_l2 only): entries [victim+1, n-1) move down one block.
-  // In-place shift done in ascending chunks: read chunk (from +Hkv ahead), sync, write.
-  if (victim >= 0 && p.pol.decode_method != 0 && p.score_table != nullptr) {
-    float* srow = p.score_table + (size_t)p.score_slots[b] * p.score_max_blocks * p.Hkv;
-    const int e0 = victim * p.Hkv;
-    const int e1 = (n - 2) * p.Hkv;  // scored entries are [0, n-1); after shift [0, n-2)
-    for (int base = e0; base < e1; base += kEvictThreads) {
-      const int e = base + tid;
-      float v = 0.f;
-      if (e < e1) v = srow[e + p.Hkv];
-      __syncthreads();
-      if (e < e1) srow[e] = v;
-      __syncthreads();
-    }
-  }
 }
 
 int evict_select_compact(const EvictSelectArgs& a, cudaStream_t stream) {
   if (a.B <= 0) return 0;
   if (a.pol.block_size <= 0) return set_error(PC_ERR_INVALID, "policy.block_size must be > 0");
-  if (a.pol.decode_method != 0 && (a.score_table == nullptr || a.score_slots == nullptr))
-    return set_error(PC_ERR_INVALID, "value_l2 eviction needs score_table and score_slots");
+  if (a.pol.decode_method != 0 && a.score.n_pools <= 0)
+    return set_error(PC_ERR_INVALID, "value_l2 eviction needs a score pool");
   EvictParams p;
   p.block_tables = a.block_tables;
   p.table_stride = a.table_stride;
@@ -140,10 +125,7 @@ int evict_select_compact(const EvictSelectArgs& a, cudaStream_t stream) {
   p.seq_lens = a.seq_lens;
   p.kv_lens = a.kv_lens;
   p.pol = a.pol;
-  p.score_table = a.score_table;
-  p.score_slots = a.score_slots;
-  p.score_max_blocks = a.score_max_blocks;
-  p.Hkv = a.Hkv;
+  p.score = a.score;
   p.out_tables = a.out_tables;
   p.out_stride = a.out_stride;
   p.out_kv_lens = a.out_kv_lens;

@@ -9,6 +9,27 @@
 
 namespace pc {
 
+// Device-side view of pc_score_pool (passed by value in kernel params).
+struct ScorePool {
+  float* pools[PC_MAX_PEERS];
+  int n_pools;      // 0 = scoring off
+  int local;
+  int heads_total;
+  int head_offset;
+};
+inline ScorePool make_score_pool(const pc_score_pool* s) {
+  ScorePool sp;
+  for (int i = 0; i < PC_MAX_PEERS; ++i) sp.pools[i] = nullptr;
+  sp.n_pools = 0; sp.local = 0; sp.heads_total = 0; sp.head_offset = 0;
+  if (s != nullptr) {
+    for (int i = 0; i < s->n_pools && i < PC_MAX_PEERS; ++i) sp.pools[i] = s->pools[i];
+    sp.n_pools = s->n_pools; sp.local = s->local; sp.heads_total = s->heads_total;
+    sp.head_offset = s->head_offset;
+  }
+  return sp;
+}
+int check_score_pool(const pc_score_pool* s, int num_kv_heads, const char* who);
+
 int set_error(int code, const char* msg);
 int set_cuda_error(const char* what, cudaError_t e);
 int check_launch(const char* kernel_name);
@@ -26,9 +47,7 @@ struct DecodeArgs {
   float scale;
   long long q_stride, out_stride, kv_block_stride;
   const int* seq_lens;
-  float* score_table;
-  const int* score_slots;
-  int score_max_blocks;
+  ScorePool score;
   void* workspace;
   size_t workspace_bytes;
 };
@@ -47,9 +66,7 @@ struct CacheWriteArgs {
   int num_reqs, total_tiles, num_tokens;
   int Hkv, D, BS;
   long long key_stride, value_stride, kv_block_stride;
-  float* score_table;
-  const int* score_slots;
-  int score_max_blocks;
+  ScorePool score;
 };
 int cache_write(const CacheWriteArgs& a, cudaStream_t stream);
 
@@ -61,9 +78,7 @@ struct EvictSelectArgs {
   const int* kv_lens;
   int B;
   pc_evict_policy pol;
-  float* score_table;
-  const int* score_slots;
-  int score_max_blocks, Hkv;
+  ScorePool score;
   int* out_tables;
   long long out_stride;
   int* out_kv_lens;

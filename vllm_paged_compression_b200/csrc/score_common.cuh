@@ -13,6 +13,7 @@
 // One warp computes one (block, head).  `get(t, d)` returns V[t, d] as float.
 #pragma once
 #include "pc_common.cuh"
+#include "pc_api_internal.h"
 
 namespace pc {
 
@@ -44,6 +45,15 @@ __device__ __forceinline__ float warp_value_l2_head_score(Get get) {
     head = __fadd_rn(head, nt);
   }
   return head;  // identical in every lane
+}
+
+// Publish one per-head partial to every rank's pool (peer stores over NVLink when
+// n_pools > 1; they become visible to the peers at the next inter-rank barrier).
+__device__ __forceinline__ void score_store(const ScorePool& sp, long long block_id, int h_local, float v) {
+  const size_t idx = (size_t)block_id * sp.heads_total + sp.head_offset + h_local;
+#pragma unroll
+  for (int i = 0; i < PC_MAX_PEERS; ++i)
+    if (i < sp.n_pools) sp.pools[i][idx] = v;
 }
 
 }  // namespace pc

@@ -14,7 +14,7 @@ from typing import Optional, Sequence, Tuple
 import torch
 
 from . import _lib
-from ._lib import PcEvictPolicy, check
+from ._lib import MAX_PEERS, PcDecodeStep, PcEvictPolicy, PcScorePool, check
 
 PC_BF16 = 0
 
@@ -62,6 +62,31 @@ def make_policy(pol, block_size: int) -> PcEvictPolicy:
         topk_blocks=int(pol.topk_blocks) if pol.topk_blocks is not None else -1)
 
 
+def make_score_pool(pool: torch.Tensor, head_offset: int = 0,
+                    peer_ptrs: Optional[Sequence[int]] = None, local: int = 0) -> PcScorePool:
+    """struct pc_score_pool for one layer.  pool fp32 [num_blocks, heads_total] on the device
+    (this rank's copy); peer_ptrs = data pointers of EVERY rank's pool in rank order (symmetric
+    memory, this rank's own at index `local`) or None for a single GPU."""
+    if not pool.is_cuda or pool.dtype != torch.float32 or pool.dim() != 2 or not pool.is_contiguous():
+        raise RuntimeError("score pool must be a contiguous fp32 CUDA tensor [num_blocks, heads_total]")
+    sp = PcScorePool()
+    ptrs = list(peer_ptrs) if peer_ptrs else [pool.data_ptr()]
+    if len(ptrs) > MAX_PEERS:
+        raise RuntimeError(f"at most {MAX_PEERS} score pools (tensor-parallel ranks) are supported")
+    if peer_ptrs and ptrs[local] != pool.data_ptr():
+        raise RuntimeError("peer_ptrs[local] must be this rank's own pool")
+    for i, a in enumerate(ptrs):
+        sp.pools[i] = a
+    sp.n_pools, sp.local = len(ptrs), (local if peer_ptrs else 0)
+    sp.heads_total, sp.head_offset = pool.shape[1], int(head_offset)
+    sp._keepalive = pool
+    return sp
+
+
+def _sp(score: Optional[PcScorePool]):
+    return None if score is None else C.byref(score)
+
+
 def _cache_dims(key_cache: torch.Tensor, value_cache: torch.Tensor) -> Tuple[int, int, int, int]:
     """key_cache [nb, Hkv, D/8, bs, 8], value_cache [nb, Hkv, D, bs] (paged_attn.py:49-62)."""
     nb, Hkv, D, bs = value_cache.shape
@@ -103,27 +128,19 @@ def reshape_and_cache(key: torch.Tensor, value: torch.Tensor, key_cache: torch.T
 def prune_prompt_and_cache(key: torch.Tensor, value: torch.Tensor, key_cache: torch.Tensor,
                            value_cache: torch.Tensor, slot_mapping: torch.Tensor,
                            req_meta: torch.Tensor, tile_offsets: torch.Tensor, total_tiles: int,
-                           score_table: Optional[torch.Tensor] = None,
-                           score_slots: Optional[torch.Tensor] = None) -> None:
+                           score: Optional[PcScorePool] = None) -> None:
     """Fused streamingLLM prompt prune + cache write + prompt block scoring.
     req_meta int32 [R,5] = {src_start, kept, first, pruned, dst_start}; tile_offsets int32
-    [R+1]; score_table fp32 [slots, max_blocks, Hkv] (optional)."""
-    _req_cuda(key, value, key_cache, value_cache, slot_mapping, req_meta, tile_offsets,
-              score_table, score_slots)
+    [R+1]; score = the layer's score pool (optional)."""
+    _req_cuda(key, value, key_cache, value_cache, slot_mapping, req_meta, tile_offsets)
     Hkv, D, bs, blk_stride = _cache_dims(key_cache, value_cache)
     if req_meta.dtype != torch.int32 or tile_offsets.dtype != torch.int32:
         raise RuntimeError("req_meta / tile_offsets must be int32")
-    smb = 0
-    if score_table is not None:
-        if score_table.dtype != torch.float32 or not score_table.is_contiguous() \
-                or score_table.shape[-1] != Hkv:
-            raise RuntimeError("score_table must be contiguous fp32 [slots, max_blocks, Hkv]")
-        smb = score_table.shape[1]
     check(_lib.load().pc_prune_prompt_and_cache(
         key.data_ptr(), value.data_ptr(), key_cache.data_ptr(), value_cache.data_ptr(),
         slot_mapping.data_ptr(), req_meta.data_ptr(), tile_offsets.data_ptr(),
         req_meta.shape[0], int(total_tiles), Hkv, D, bs, key.stride(0), value.stride(0),
-        blk_stride, _ptr(score_table), _ptr(score_slots), smb, _dtype_code(key), _stream(key)))
+        blk_stride, _sp(score), _dtype_code(key), _stream(key)))
     _launched()
 
 
@@ -132,25 +149,21 @@ def evict_select_compact(block_tables: torch.Tensor, n_blocks: torch.Tensor,
                          seq_lens: torch.Tensor, kv_lens: Optional[torch.Tensor],
                          policy: PcEvictPolicy, num_kv_heads: int,
                          out_tables: torch.Tensor, out_kv_lens: Optional[torch.Tensor],
-                         out_victim: torch.Tensor,
-                         score_table: Optional[torch.Tensor] = None,
-                         score_slots: Optional[torch.Tensor] = None,
+                         out_victim: torch.Tensor, score: Optional[PcScorePool] = None,
                          kv_lens_pre_adjusted: bool = True) -> None:
-    """On-device decode trigger + victim argmin + table/score compaction (one launch)."""
-    _req_cuda(block_tables, n_blocks, seq_lens, kv_lens, out_tables, out_kv_lens, out_victim,
-              score_table, score_slots)
+    """On-device decode trigger + victim argmin + table compaction (one launch)."""
+    _req_cuda(block_tables, n_blocks, seq_lens, kv_lens, out_tables, out_kv_lens, out_victim)
     for t in (block_tables, n_blocks, seq_lens, out_tables, out_victim):
         if t.dtype != torch.int32:
             raise RuntimeError("block tables / lengths / victims must be int32")
     if block_tables.stride(-1) != 1 or out_tables.stride(-1) != 1:
         raise RuntimeError("block table rows must be contiguous")
     B = block_tables.shape[0]
-    smb = score_table.shape[1] if score_table is not None else 0
     check(_lib.load().pc_evict_select_compact(
         block_tables.data_ptr(), block_tables.stride(0), n_blocks.data_ptr(), seq_lens.data_ptr(),
-        _ptr(kv_lens), B, C.byref(policy), _ptr(score_table), _ptr(score_slots), smb,
-        num_kv_heads, out_tables.data_ptr(), out_tables.stride(0), _ptr(out_kv_lens),
-        out_victim.data_ptr(), 1 if kv_lens_pre_adjusted else 0, _stream(block_tables)))
+        _ptr(kv_lens), B, C.byref(policy), _sp(score), num_kv_heads, out_tables.data_ptr(),
+        out_tables.stride(0), _ptr(out_kv_lens), out_victim.data_ptr(),
+        1 if kv_lens_pre_adjusted else 0, _stream(block_tables)))
     _launched()
 
 
@@ -180,14 +193,12 @@ def paged_decode_attn_score(out: torch.Tensor, query: torch.Tensor, key_cache: t
                             value_cache: torch.Tensor, block_tables: torch.Tensor,
                             kv_lens: torch.Tensor, scale: float, max_kv_len: int,
                             seq_lens: Optional[torch.Tensor] = None,
-                            score_table: Optional[torch.Tensor] = None,
-                            score_slots: Optional[torch.Tensor] = None,
+                            score: Optional[PcScorePool] = None,
                             workspace: Optional[torch.Tensor] = None) -> None:
     """Paged decode attention over (compacted) tables; rows whose last block fills this
-    step (seq_lens % bs == 0) get that block's per-head value_l2 partial written to
-    score_table in the same pass.  query/out [B, Hq, D]."""
-    _req_cuda(out, query, key_cache, value_cache, block_tables, kv_lens, seq_lens, score_table,
-              score_slots)
+    step (seq_lens % bs == 0) get that block's per-head value_l2 partial written to the
+    score pool in the same pass.  query/out [B, Hq, D]."""
+    _req_cuda(out, query, key_cache, value_cache, block_tables, kv_lens, seq_lens)
     Hkv, D, bs, blk_stride = _cache_dims(key_cache, value_cache)
     B, Hq, Dq = query.shape
     if Dq != D or out.shape != query.shape:
@@ -199,14 +210,62 @@ def paged_decode_attn_score(out: torch.Tensor, query: torch.Tensor, key_cache: t
     need = paged_decode_workspace_bytes(B, Hq, Hkv, D, bs, max_kv_len)
     if workspace is None:
         workspace = _workspace(query.device, need)
-    smb = score_table.shape[1] if score_table is not None else 0
     check(_lib.load().pc_paged_decode_attn_score(
         out.data_ptr(), query.data_ptr(), key_cache.data_ptr(), value_cache.data_ptr(),
         block_tables.data_ptr(), block_tables.stride(0), kv_lens.data_ptr(), B, Hq, Hkv, D, bs,
         int(max_kv_len), float(scale), query.stride(0), out.stride(0), blk_stride,
-        _ptr(seq_lens), _ptr(score_table), _ptr(score_slots), smb, workspace.data_ptr(),
+        _ptr(seq_lens) if score is not None else None, _sp(score), workspace.data_ptr(),
         workspace.numel(), _dtype_code(query), _stream(query)))
     _launched()
+
+
+# ------------------------------------------------------- fused decode step of one layer
+def make_decode_step(slot_mapping: torch.Tensor, block_tables: torch.Tensor, kv_lens: torch.Tensor,
+                     seq_lens: torch.Tensor, batch: int, num_heads: int, num_kv_heads: int,
+                     head_size: int, block_size: int, max_kv_len: int, scale: float,
+                     q_stride: int, key_stride: int, value_stride: int, out_stride: int,
+                     kv_block_stride: int, policy: Optional[PcEvictPolicy] = None,
+                     n_blocks: Optional[torch.Tensor] = None,
+                     compact_tables: Optional[torch.Tensor] = None, any_trigger: bool = False,
+                     attend_uncompacted: bool = False) -> PcDecodeStep:
+    """struct pc_decode_step: everything that is the same for every layer of one engine
+    step (built once per step, passed by pointer to `decode_layer`)."""
+    _req_cuda(slot_mapping, block_tables, kv_lens, seq_lens, n_blocks, compact_tables)
+    dev = block_tables.device
+    st = PcDecodeStep()
+    st.slot_mapping, st.block_tables = slot_mapping.data_ptr(), block_tables.data_ptr()
+    st.table_stride = block_tables.stride(0)
+    st.kv_lens, st.seq_lens = kv_lens.data_ptr(), seq_lens.data_ptr()
+    st.n_blocks = _ptr(n_blocks)
+    st.compact_tables = _ptr(compact_tables)
+    st.compact_stride = compact_tables.stride(0) if compact_tables is not None else 0
+    st.batch, st.num_heads, st.num_kv_heads = batch, num_heads, num_kv_heads
+    st.head_size, st.block_size, st.max_kv_len = head_size, block_size, int(max_kv_len)
+    st.scale = float(scale)
+    st.any_trigger, st.attend_uncompacted = int(any_trigger), int(attend_uncompacted)
+    st.q_stride, st.key_stride, st.value_stride = q_stride, key_stride, value_stride
+    st.out_stride, st.kv_block_stride = out_stride, kv_block_stride
+    if policy is not None:
+        st.policy = policy
+    need = paged_decode_workspace_bytes(batch, num_heads, num_kv_heads, head_size, block_size, max_kv_len)
+    ws = _workspace(dev, need)
+    st.workspace, st.workspace_bytes = ws.data_ptr(), ws.numel()
+    st.dtype = PC_BF16
+    st.stream = torch.cuda.current_stream(dev).cuda_stream
+    st._keepalive = (slot_mapping, block_tables, kv_lens, seq_lens, n_blocks, compact_tables, ws)
+    st._launches = 2 + (1 if any_trigger else 0)
+    return st
+
+
+def decode_layer(step: PcDecodeStep, out: torch.Tensor, query: torch.Tensor, key: torch.Tensor,
+                 value: torch.Tensor, key_cache_ptr: int, value_cache_ptr: int,
+                 score: Optional[PcScorePool] = None, out_victim: Optional[torch.Tensor] = None) -> None:
+    """One layer's decode step in one native call (cache write -> [select + compact] ->
+    attention + scoring).  Shapes / strides were validated when `step` was built."""
+    check(_lib.load().pc_decode_layer(C.byref(step), out.data_ptr(), query.data_ptr(), key.data_ptr(),
+                                      value.data_ptr(), key_cache_ptr, value_cache_ptr, _sp(score),
+                                      _ptr(out_victim)))
+    _launched(step._launches)
 
 
 def _check_compat(kv_cache_dtype, k_scale, v_scale, alibi_slopes, blocksparse_vert_stride):
