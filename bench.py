@@ -69,6 +69,8 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-graph", action="store_true", help="disable CUDA-graph replay of the step")
+    ap.add_argument("--score-exchange", default="p2p", choices=["p2p", "nccl"],
+                    help="N > 1: how per-head block scores reach the other ranks (parallel.py)")
     ap.add_argument("--sweep", action="store_true",
                     help="kernel microbench (BASELINE.json configs[1]) -> table on stdout")
     return ap.parse_args()
@@ -157,8 +159,12 @@ class Arm:
         bs = args.block_size
         cc = make_cache_config(args, self.B)
         blocks_per_seq = -(-(args.prompt_len + args.steps + args.warmup + 2 * bs) // bs) + 2
+        ex = None
+        if world > 1 and args.evict_freq > 0:
+            from vllm_paged_compression_b200.parallel import ScoreExchange
+            ex = ScoreExchange(self.L, self.Hkv, mode=args.score_exchange)
         self.eng = PagedEvictEngine(self.L, self.Hq, self.Hkv, self.D, cc, self.B * blocks_per_seq + 8,
-                                    device=device, tp_rank=rank, tp_size=world)
+                                    device=device, score_exchange=ex, tp_rank=rank, tp_size=world)
         for i in range(self.B):
             self.eng.add_request(f"r{i}", args.prompt_len)
         g = torch.Generator(device=device)
@@ -478,7 +484,8 @@ def main():
         "ms_per_step": sec / K * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "bf16", "data": "synthetic",
         "config": {"workload": workload_name(args, world), "global_batch": B,
-                   "parallelism": f"tp{world}" if world > 1 else "single GPU",
+                   "parallelism": (f"tp{world} over kv heads, batch x{world}, score exchange "
+                                   f"{args.score_exchange}") if world > 1 else "single GPU",
                    "l2": "inputs larger than L2 (per-layer KV pools, {:.1f} GB touched per step)".format(
                        alg_bytes * args.layers / 1e9),
                    "prompt_tokens_kept": kept_prompt, "evictions_in_timed_region": evictions,

@@ -88,16 +88,22 @@ QKVFn = Callable[[int, int], Tuple[torch.Tensor, torch.Tensor, torch.Tensor]]
 class PagedEvictEngine:
     def __init__(self, num_layers: int, num_heads: int, num_kv_heads: int, head_size: int,
                  cache_config: CacheConfig, num_gpu_blocks: int, device="cuda:0",
-                 dtype=torch.bfloat16, max_num_batched_tokens: int = 1 << 30, **impl_kwargs) -> None:
+                 dtype=torch.bfloat16, max_num_batched_tokens: int = 1 << 30, score_exchange=None,
+                 **impl_kwargs) -> None:
+        """num_heads / num_kv_heads are the LOCAL (per tensor-parallel rank) head counts;
+        tp_rank / tp_size go to the impls through impl_kwargs; score_exchange
+        (parallel.ScoreExchange) is required for value_l2 eviction when tp_size > 1."""
         self.device = torch.device(device)
         self.cache_config = cache_config
         self.block_size = cache_config.block_size
         self.num_layers, self.num_heads = num_layers, num_heads
         self.num_kv_heads, self.head_size = num_kv_heads, head_size
         scale = head_size ** -0.5
+        self.score_exchange = score_exchange
         self.impls = [TorchCUDASDPABackendImpl(num_heads, head_size, scale, num_kv_heads, None, None,
                                                "auto", cache_config=cache_config,
-                                               prefix=f"model.layers.{i}.self_attn.attn", **impl_kwargs)
+                                               prefix=f"model.layers.{i}.self_attn.attn",
+                                               score_exchange=score_exchange, **impl_kwargs)
                       for i in range(num_layers)]
         shape = TorchCUDASDPABackend.get_kv_cache_shape(num_gpu_blocks, self.block_size, num_kv_heads,
                                                         head_size)
@@ -178,6 +184,21 @@ class PagedEvictEngine:
             md.seq_kv_lens, md.seq_kv_lens_tensor = None, None
         return md
 
+    def _scored_blocks(self, is_prompt: bool, batch: List[_Seq]) -> List[int]:
+        """Physical ids of the blocks the layers scored during this step: every full kept
+        block of a prefilled prompt, or the last block of each row that just filled."""
+        cfg, bs = self.cache_config.paged_evict_config, self.block_size
+        if cfg is None or cfg.decode_evict_method != "value_l2":
+            return []
+        ids: List[int] = []
+        for s in batch:
+            table = self.block_manager.get_block_table(s.seq_id)
+            if is_prompt:
+                ids.extend(table[:self.block_manager.get_seq_kv_len(s.seq_id) // bs])
+            elif s.seq_len % bs == 0:
+                ids.append(table[-1])
+        return ids
+
     # -------------------------------------------------------------------------- step
     def step(self, qkv_fn: QKVFn, keep_outputs: bool = True,
              out_fn: Optional[Callable[[int, torch.Tensor], None]] = None) -> StepOutput:
@@ -195,6 +216,8 @@ class PagedEvictEngine:
                 out_fn(layer, o)
             if keep_outputs:
                 outs.append(o)
+        if self.score_exchange is not None:
+            self.score_exchange.publish(self._scored_blocks(is_prompt, batch))
         # model_runner.py:1797-1802: only layer 0's decision reaches the block manager
         rmv = dict(self.impls[0].get_rmv_block_idx())
         out = StepOutput(is_prompt, [s.request_id for s in batch], list(md.seq_lens),
