@@ -68,7 +68,8 @@ def parse_args():
     ap.add_argument("--cpu-steps", type=int, default=0, help="0 = derive from a ~15 s budget")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--no-graph", action="store_true", help="disable CUDA-graph replay of the step")
+    ap.add_argument("--no-graph", action="store_true",
+                    help="eager PagedEvictEngine.step (one forward() per layer) instead of CUDA-graph replay")
     ap.add_argument("--score-exchange", default="p2p", choices=["p2p", "nccl"],
                     help="N > 1: how per-head block scores reach the other ranks (parallel.py)")
     ap.add_argument("--sweep", action="store_true",
@@ -182,13 +183,15 @@ class Arm:
         self.v = [(u(self.B, self.Hkv * self.D).float() * row * (1 + 0.1 * l)).to(torch.bfloat16)
                   for l in range(self.L)]
         self.h2d = self.d2h = 0
+        self.runner = None
         if host_io:
-            pin = lambda t: t.cpu().pin_memory()
-            self.qh, self.kh, self.vh = [[pin(t) for t in x] for x in (self.q, self.k, self.v)]
-            self.oh = [torch.empty(self.B, self.Hq * self.D, dtype=torch.bfloat16).pin_memory()
-                       for _ in range(self.L)]
-            self.h2d = sum(t.numel() * 2 for x in (self.qh, self.kh, self.vh) for t in x)
-            self.d2h = sum(t.numel() * 2 for t in self.oh)
+            from vllm_paged_compression_b200.engine import PinnedLayerIO
+            # fused [B, (Hq + 2 Hkv) D] rows per layer in pinned host memory (what qkv_proj emits)
+            self.io = PinnedLayerIO(self.L, self.B, self.Hq, self.Hkv, self.D, device)
+            for l in range(self.L):
+                self.io.qkv_host[l].copy_(torch.cat([self.q[l], self.k[l], self.v[l]], dim=1).cpu())
+            self.h2d, self.d2h = self.io.h2d_bytes, self.io.d2h_bytes
+            self.q = self.k = self.v = None
 
     def prefill(self):
         """One untimed prefill batch (chunked by request so activations stay small)."""
@@ -206,20 +209,34 @@ class Arm:
             assert so.is_prompt
         torch.cuda.synchronize()
 
-    def step(self):
+    def make_runner(self):
+        """Decode steps as CUDA-graph replays (graph_runner.py) unless --no-graph."""
+        if self.args.no_graph:
+            self.runner = None
+            return
+        from vllm_paged_compression_b200.graph_runner import DecodeGraphRunner
+        a = self.args
+        kv_now = max(self.eng.block_manager.get_seq_kv_len(s.seq_id) for s in self.eng.running)
+        bound = kv_now + a.steps + a.warmup + 2 * a.block_size + 64
+        if self.host_io:
+            self.runner = DecodeGraphRunner(self.eng, None, io=self.io, max_kv_len=bound)
+        else:
+            self.runner = DecodeGraphRunner(self.eng, list(zip(self.q, self.k, self.v)), max_kv_len=bound)
+
+    def step(self) -> int:
+        """One decode step of the whole batch; -> blocks evicted (layer-0 feedback)."""
+        if self.runner is not None:
+            # host_io: H2D of every layer's fused qkv rows and D2H of every layer's attention
+            # output are nodes of the replayed graph; step() returns once out_host is valid
+            return len(self.runner.step())
         if not self.host_io:
-            return self.eng.step(lambda l, n: (self.q[l], self.k[l], self.v[l]), keep_outputs=False)
-
-        def qkv(l, n):
-            return (self.qh[l].to(self.device, non_blocking=True),
-                    self.kh[l].to(self.device, non_blocking=True),
-                    self.vh[l].to(self.device, non_blocking=True))
-
-        def out(l, o):
-            self.oh[l].copy_(o, non_blocking=True)
-        so = self.eng.step(qkv, keep_outputs=False, out_fn=out)
-        self.torch.cuda.current_stream().synchronize()     # the caller owns the host result now
-        return so
+            so = self.eng.step(lambda l, n: (self.q[l], self.k[l], self.v[l]), keep_outputs=False)
+            return len(so.rmv)
+        self.io.begin_step()
+        so = self.eng.step(self.io.qkv, keep_outputs=False, out_fn=self.io.put_out,
+                           out_buf_fn=self.io.out_buf)
+        self.io.end_step()                                  # the caller owns the host result now
+        return len(so.rmv)
 
 
 def timed_steps(torch, dist, arm, K, W, world):
@@ -235,12 +252,13 @@ def timed_steps(torch, dist, arm, K, W, world):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     n0 = ops.launch_count
     evictions = 0
+    torch.cuda.profiler.start()          # ncu --profile-from-start off sees the timed region only
     e0.record()
     for _ in range(K):
-        so = arm.step()
-        evictions += len(so.rmv)
+        evictions += arm.step()
     e1.record()
     torch.cuda.synchronize()
+    torch.cuda.profiler.stop()
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
@@ -449,6 +467,7 @@ def main():
     # ---- value: inputs resident in HBM
     arm = Arm(args, device, rank, world, host_io=False)
     arm.prefill()
+    arm.make_runner()
     sampler = ClockSampler(local_rank) if rank == 0 else None
     sec, evictions, launches = timed_steps(torch, dist, arm, K, W, world)
     clocks = sampler.stop() if sampler else None
@@ -471,6 +490,7 @@ def main():
     if not args.no_e2e:
         arm = Arm(args, device, rank, world, host_io=True)
         arm.prefill()
+        arm.make_runner()
         sec_e, _, _ = timed_steps(torch, dist, arm, K, W, world)
         e2e = {"value": B * K / sec_e, "unit": "tok/s", "h2d_bytes_per_step": arm.h2d,
                "d2h_bytes_per_step": arm.d2h, "ms_per_step": sec_e / K * 1e3}
@@ -488,6 +508,8 @@ def main():
                                    f"{args.score_exchange}") if world > 1 else "single GPU",
                    "l2": "inputs larger than L2 (per-layer KV pools, {:.1f} GB touched per step)".format(
                        alg_bytes * args.layers / 1e9),
+                   "step_mode": "eager per-layer forward()" if args.no_graph else
+                   "CUDA-graph replay of the 32-layer step (graph_runner.py)",
                    "prompt_tokens_kept": kept_prompt, "evictions_in_timed_region": evictions,
                    "mean_kv_len": sum(kv_lens_host) / len(kv_lens_host)},
         "clocks": clocks,

@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define PC_ABI_VERSION 2
+#define PC_ABI_VERSION 3
 #define PC_MAX_PEERS 8
 
 typedef enum pc_status {
@@ -194,7 +194,23 @@ typedef struct pc_decode_step {
   size_t workspace_bytes;
   int32_t dtype;
   void* stream;
+  /* ABI 3 */
+  int32_t fuse_cache_write;      /* != 0: the attention kernel writes this step's K/V rows itself
+                                  * (no separate reshape_and_cache launch).  The caller guarantees
+                                  * what the reference's builder produces for a decode row
+                                  * (torch_cuda_sdpa.py:565-598): slot_mapping[r] ==
+                                  * last_table_entry(r) * block_size + (kv_lens[r] - 1) % block_size.
+                                  * Ignored (separate write) when attend_uncompacted is set. */
+  const int32_t* plan;           /* DEVICE int32[1] = {chunk_pages} from pc_paged_decode_plan, read by
+                                  * the kernel at run time instead of being planned from max_kv_len at
+                                  * launch time -- lets a captured (CUDA graph) launch be replayed while
+                                  * kv lengths move; NULL = plan on the host.  workspace must then hold
+                                  * pc_paged_decode_workspace_bytes of every max_kv_len it is replayed
+                                  * with. */
 } pc_decode_step;
+/* chunk_pages the host planner picks for this launch shape (to fill pc_decode_step.plan). */
+int32_t pc_paged_decode_plan(int32_t batch, int32_t num_heads, int32_t num_kv_heads,
+                             int32_t head_size, int32_t block_size, int32_t max_kv_len);
 int pc_decode_layer(const pc_decode_step* step /* HOST */, void* out, const void* query,
                     const void* key, const void* value, void* key_cache, void* value_cache,
                     const pc_score_pool* score /* HOST, NULL = no value_l2 */,

@@ -457,3 +457,53 @@ def test_copy_and_swap_blocks():
     ops.swap_blocks(kv[0], host, torch.tensor([[3, 7], [4, 0]]))
     torch.cuda.synchronize()
     assert torch.equal(host[7], kv[0, 3].cpu()) and torch.equal(host[0], kv[0, 4].cpu())
+
+
+# --------------------------------------------------------------------------- W1 fused into A2
+@pytest.mark.parametrize("Hq,Hkv,D,bs", [(32, 8, 128, 16), (8, 2, 64, 16), (16, 2, 128, 32), (32, 2, 64, 32)])
+@pytest.mark.parametrize("B,max_len", [(5, 90), (33, 1300)])
+def test_decode_layer_fused_cache_write(Hq, Hkv, D, bs, B, max_len):
+    """pc_decode_layer with fuse_cache_write: the attention kernel itself stores the step's
+    K/V rows.  Cache bytes must equal the oracle's reshape_and_cache (and the un-fused
+    path's) bit for bit, outputs must equal the un-fused path's bit for bit (same arithmetic
+    on the same bytes), scores of blocks that fill this step likewise.  kv lengths are
+    chosen so that new tokens land at every offset, including 0 (fresh block) and bs-1."""
+    ops = _ops()
+    seed = B * 7 + D + bs + Hq
+    q, kv, tables, kv_lens, scale = _decode_case(B, Hq, Hkv, D, bs, max_len, seed=seed)
+    for r in range(min(B, bs)):                 # force every in-block offset to occur
+        kv_lens[r] = max(1, (int(kv_lens[r]) // bs) * bs - r) if kv_lens[r] >= bs else r + 1
+    n = [policy.cdiv(int(x), bs) for x in kv_lens]
+    slots = np.array([int(tables[r, n[r] - 1]) * bs + (int(kv_lens[r]) - 1) % bs for r in range(B)], np.int64)
+    key = (rnd(seed + 5, B, Hkv, D).float() * 0.5).to(torch.bfloat16)
+    val = rnd(seed + 6, B, Hkv, D)
+    # oracle: write, then attend
+    kv_ref = kv.clone()
+    kc, vc = paged_ops.split_kv_cache(kv_ref, Hkv, D)
+    paged_ops.reshape_and_cache(key, val, kc, vc, torch.from_numpy(slots))
+    ref = paged_ops.paged_attention(q, kc, vc, tables.tolist(), kv_lens.tolist(), scale).float()
+    seq_lens = kv_lens.copy()                   # rows with seq_len % bs == 0 are scored
+    results = []
+    for fused in (False, True):
+        kvd = kv.clone().to(DEV)
+        kcd, vcd = paged_ops.split_kv_cache(kvd, Hkv, D)
+        nb = kvd.shape[1]
+        pool = torch.zeros(nb, Hkv, dtype=torch.float32, device=DEV)
+        sp = ops.make_score_pool(pool, 0)
+        out = torch.full((B, Hq, D), float("nan"), dtype=torch.bfloat16, device=DEV)
+        qd, kd, vd = q.to(DEV), key.to(DEV), val.to(DEV)
+        st = ops.make_decode_step(torch.from_numpy(slots).to(DEV), torch.from_numpy(tables).to(DEV),
+                                  torch.from_numpy(kv_lens).to(DEV), torch.from_numpy(seq_lens).to(DEV),
+                                  B, Hq, Hkv, D, bs, int(kv_lens.max()), scale, qd.stride(0), kd.stride(0),
+                                  vd.stride(0), out.stride(0), vcd.stride(0), fuse_cache_write=fused)
+        assert st.fuse_cache_write == int(fused)
+        ops.decode_layer(st, out, qd, kd, vd, kcd.data_ptr(), vcd.data_ptr(), sp, None)
+        torch.cuda.synchronize()
+        results.append((out.cpu(), kvd.cpu(), pool.cpu()))
+    (o0, c0, s0), (o1, c1, s1) = results
+    assert np.array_equal(_bits(c0), _bits(kv_ref)), "un-fused cache bytes differ from the oracle"
+    assert np.array_equal(_bits(c1), _bits(kv_ref)), "fused cache bytes differ from the oracle"
+    assert torch.equal(o0, o1)
+    assert torch.equal(s0, s1)
+    assert any(int(x) % bs == 0 for x in kv_lens) and s1.abs().sum() > 0
+    np.testing.assert_allclose(o1.float().numpy(), ref.numpy(), atol=8e-3, rtol=0)

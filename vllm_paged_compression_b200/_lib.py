@@ -10,7 +10,7 @@ import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libpagedevict_b200.so")
-ABI_VERSION = 2
+ABI_VERSION = 3
 MAX_PEERS = 8
 
 
@@ -39,7 +39,8 @@ class PcDecodeStep(C.Structure):
                 ("q_stride", C.c_int64), ("key_stride", C.c_int64), ("value_stride", C.c_int64),
                 ("out_stride", C.c_int64), ("kv_block_stride", C.c_int64),
                 ("policy", PcEvictPolicy), ("workspace", C.c_void_p), ("workspace_bytes", C.c_size_t),
-                ("dtype", C.c_int32), ("stream", C.c_void_p)]
+                ("dtype", C.c_int32), ("stream", C.c_void_p),
+                ("fuse_cache_write", C.c_int32), ("plan", C.c_void_p)]
 
 
 _P, _I32, _I64, _F, _SZ = C.c_void_p, C.c_int32, C.c_int64, C.c_float, C.c_size_t
@@ -58,6 +59,7 @@ PROTOTYPES = {
     "pc_evict_select_compact": (C.c_int, [_P, _I64, _P, _P, _P, _I32, C.POINTER(PcEvictPolicy), _SP,
                                           _I32, _P, _I64, _P, _P, _I32, _P]),
     "pc_paged_decode_workspace_bytes": (_SZ, [_I32, _I32, _I32, _I32, _I32, _I32]),
+    "pc_paged_decode_plan": (_I32, [_I32, _I32, _I32, _I32, _I32, _I32]),
     "pc_paged_decode_attn_score": (C.c_int, [_P, _P, _P, _P, _P, _I64, _P, _I32, _I32, _I32, _I32, _I32,
                                              _I32, _F, _I64, _I64, _I64, _P, _SP, _P, _SZ,
                                              _I32, _P]),

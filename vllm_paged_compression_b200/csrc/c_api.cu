@@ -63,6 +63,20 @@ static int check_dtype(int dtype) {
 
 using namespace pc;
 
+// extras pc_decode_layer adds to the attention launch: the fused cache write of the step's
+// token and the device-side plan
+struct FuseExtras {
+  const void* key; const void* value; const long long* slot_mapping;
+  long long key_stride, value_stride; const int* plan;
+};
+static int decode_attn_impl(void* out, const void* query, const void* key_cache, const void* value_cache,
+                            const int32_t* block_tables, int64_t table_stride, const int32_t* kv_lens,
+                            int32_t batch, int32_t num_heads, int32_t num_kv_heads, int32_t head_size,
+                            int32_t block_size, int32_t max_kv_len, float scale, int64_t q_stride,
+                            int64_t out_stride, int64_t kv_block_stride, const int32_t* seq_lens,
+                            const pc_score_pool* score, void* workspace, size_t workspace_bytes,
+                            int32_t dtype, void* stream, const FuseExtras& g_fuse);
+
 extern "C" {
 
 int pc_abi_version(void) { return PC_ABI_VERSION; }
@@ -149,6 +163,13 @@ size_t pc_paged_decode_workspace_bytes(int32_t batch, int32_t num_heads, int32_t
   return decode_workspace_bytes(batch, num_heads, num_kv_heads, head_size, block_size, max_kv_len, sms);
 }
 
+int32_t pc_paged_decode_plan(int32_t batch, int32_t num_heads, int32_t num_kv_heads,
+                             int32_t head_size, int32_t block_size, int32_t max_kv_len) {
+  const int sms = device_sm_count();
+  if (sms <= 0 || batch <= 0 || num_kv_heads <= 0 || num_heads % num_kv_heads) return 0;
+  return decode_plan_chunk_pages(batch, num_heads, num_kv_heads, head_size, block_size, max_kv_len, sms);
+}
+
 int pc_paged_decode_attn_score(void* out, const void* query, const void* key_cache,
                                const void* value_cache, const int32_t* block_tables,
                                int64_t table_stride, const int32_t* kv_lens, int32_t batch,
@@ -158,6 +179,21 @@ int pc_paged_decode_attn_score(void* out, const void* query, const void* key_cac
                                const int32_t* seq_lens, const pc_score_pool* score,
                                void* workspace, size_t workspace_bytes, int32_t dtype,
                                void* stream) {
+  const FuseExtras none = {nullptr, nullptr, nullptr, 0, 0, nullptr};
+  return decode_attn_impl(out, query, key_cache, value_cache, block_tables, table_stride, kv_lens, batch,
+                          num_heads, num_kv_heads, head_size, block_size, max_kv_len, scale, q_stride,
+                          out_stride, kv_block_stride, seq_lens, score, workspace, workspace_bytes, dtype,
+                          stream, none);
+}
+}  // extern "C"
+
+static int decode_attn_impl(void* out, const void* query, const void* key_cache, const void* value_cache,
+                            const int32_t* block_tables, int64_t table_stride, const int32_t* kv_lens,
+                            int32_t batch, int32_t num_heads, int32_t num_kv_heads, int32_t head_size,
+                            int32_t block_size, int32_t max_kv_len, float scale, int64_t q_stride,
+                            int64_t out_stride, int64_t kv_block_stride, const int32_t* seq_lens,
+                            const pc_score_pool* score, void* workspace, size_t workspace_bytes,
+                            int32_t dtype, void* stream, const FuseExtras& g_fuse) {
   if (int rc = check_dtype(dtype)) return rc;
   if (batch == 0) return PC_OK;
   if (!out || !query || !key_cache || !value_cache || !block_tables || !kv_lens || !workspace)
@@ -179,19 +215,25 @@ int pc_paged_decode_attn_score(void* out, const void* query, const void* key_cac
   a.q_stride = q_stride; a.out_stride = out_stride; a.kv_block_stride = kv_block_stride;
   a.seq_lens = seq_lens; a.score = make_score_pool(score);
   a.workspace = workspace; a.workspace_bytes = workspace_bytes;
+  a.new_k = g_fuse.key; a.new_v = g_fuse.value; a.slot_mapping = g_fuse.slot_mapping;
+  a.new_k_stride = g_fuse.key_stride; a.new_v_stride = g_fuse.value_stride; a.plan = g_fuse.plan;
   return paged_decode_attn_score(a, static_cast<cudaStream_t>(stream));
 }
+
+extern "C" {
 
 int pc_decode_layer(const pc_decode_step* st, void* out, const void* query, const void* key,
                     const void* value, void* key_cache, void* value_cache,
                     const pc_score_pool* score, int32_t* out_victim) {
   if (!st) return set_error(PC_ERR_INVALID, "pc_decode_layer: null step");
   if (st->batch == 0) return PC_OK;
-  // W1: this step's K/V rows into the pool
-  if (int rc = pc_reshape_and_cache(key, value, key_cache, value_cache, st->slot_mapping, st->batch,
-                                    st->num_kv_heads, st->head_size, st->block_size, st->key_stride,
-                                    st->value_stride, st->kv_block_stride, st->dtype, st->stream))
-    return rc;
+  // W1: this step's K/V rows into the pool -- inside the attention kernel when fused
+  const bool fuse = st->fuse_cache_write && !(st->any_trigger && st->attend_uncompacted);
+  if (!fuse)
+    if (int rc = pc_reshape_and_cache(key, value, key_cache, value_cache, st->slot_mapping, st->batch,
+                                      st->num_kv_heads, st->head_size, st->block_size, st->key_stride,
+                                      st->value_stride, st->kv_block_stride, st->dtype, st->stream))
+      return rc;
   const int32_t* tables = st->block_tables;
   int64_t stride = st->table_stride;
   if (st->any_trigger) {
@@ -206,12 +248,20 @@ int pc_decode_layer(const pc_decode_step* st, void* out, const void* query, cons
     if (!st->attend_uncompacted) { tables = st->compact_tables; stride = st->compact_stride; }
   }
   // A2 + S2: attention over the (compacted) tables, scoring the blocks that fill this step
-  return pc_paged_decode_attn_score(out, query, key_cache, value_cache, tables, stride, st->kv_lens,
-                                    st->batch, st->num_heads, st->num_kv_heads, st->head_size,
-                                    st->block_size, st->max_kv_len, st->scale, st->q_stride,
-                                    st->out_stride, st->kv_block_stride,
-                                    score ? st->seq_lens : nullptr, score, st->workspace,
-                                    st->workspace_bytes, st->dtype, st->stream);
+  FuseExtras g_fuse = {nullptr, nullptr, nullptr, 0, 0, st->plan};
+  if (fuse) {
+    if (!key || !value || !st->slot_mapping)
+      return set_error(PC_ERR_INVALID, "pc_decode_layer: fused cache write needs key, value, slot_mapping");
+    g_fuse.key = key; g_fuse.value = value;
+    g_fuse.slot_mapping = reinterpret_cast<const long long*>(st->slot_mapping);
+    g_fuse.key_stride = st->key_stride; g_fuse.value_stride = st->value_stride;
+  }
+  return decode_attn_impl(out, query, key_cache, value_cache, tables, stride, st->kv_lens,
+                                            st->batch, st->num_heads, st->num_kv_heads, st->head_size,
+                                            st->block_size, st->max_kv_len, st->scale, st->q_stride,
+                                            st->out_stride, st->kv_block_stride,
+                          score ? st->seq_lens : nullptr, score, st->workspace,
+                          st->workspace_bytes, st->dtype, st->stream, g_fuse);
 }
 
 int pc_prefill_attn_topleft_causal(void* out, const void* query, const void* key,

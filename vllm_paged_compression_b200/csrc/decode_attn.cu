@@ -67,6 +67,16 @@ struct DecodeParams {
   long long kv_block_stride;  // elements between blocks in k/v cache
   float scale_log2;
   int chunk_pages;            // pages per chunk (the last chunk of a group may be shorter)
+  const int* __restrict__ plan;  // device-side {chunk_pages} overriding the field above (CUDA-graph replay), or nullptr
+  // fused reshape_and_cache of this step's token (nullptr = the caller wrote the cache):
+  // the warp that owns a row's LAST page patches the new token's K/V into the page it has
+  // in shared memory and stores it to the pool at slot_mapping[b]
+  const __nv_bfloat16* __restrict__ new_k;
+  const __nv_bfloat16* __restrict__ new_v;
+  const long long* __restrict__ slot_mapping;
+  __nv_bfloat16* k_cache_w;
+  __nv_bfloat16* v_cache_w;
+  long long new_k_stride, new_v_stride;
   unsigned long long* trace;  // debug: [warps][8]: 4 globaltimer stamps, chunks, combines, smid, membar ns (nullptr = off)
 };
 
@@ -119,6 +129,7 @@ paged_decode_attn_score_kernel(const DecodeParams p) {
   const int w = warp * gridDim.x + blockIdx.x;  // interleaved over SMs
 
   const unsigned long long t_start = p.trace ? gtimer() : 0ull;
+  const int chunk_pages = (p.plan != nullptr) ? max(1, __ldg(p.plan)) : p.chunk_pages;
   uint8_t* my_stages = smem + (size_t)warp * kStages * T::kStageBytes;
   uint64_t* my_bars = reinterpret_cast<uint64_t*>(smem + T::kRingBytes) + warp * kStages;
   ChunkDesc* my_fifo = reinterpret_cast<ChunkDesc*>(smem + T::kRingBytes + T::kBarBytes) + warp * kFifo;
@@ -134,7 +145,7 @@ paged_decode_attn_score_kernel(const DecodeParams p) {
   // ---- schedule: chunks per (row, group) -> exclusive prefix sum (same in every CTA)
   for (int r = threadIdx.x; r < p.B; r += T::kThreads) {
     const int len = p.kv_lens[r];
-    cpre[r + 1] = ((len + BS - 1) / BS + p.chunk_pages - 1) / p.chunk_pages;
+    cpre[r + 1] = ((len + BS - 1) / BS + chunk_pages - 1) / chunk_pages;
     if (len == 0 && blockIdx.x == 0) {  // empty sequence: defined output (zeros)
       __nv_bfloat16* o = p.out + (size_t)r * p.out_stride;
       for (int i = 0; i < p.Hq * D; ++i) o[i] = __float2bfloat16(0.f);
@@ -190,8 +201,8 @@ paged_decode_attn_score_kernel(const DecodeParams p) {
     const int nblk = (kv_len + BS - 1) / BS;
     if (lane == 0) {
       ChunkDesc d;
-      d.id = id; d.b = lo; d.gh = gh; d.blk_begin = c * p.chunk_pages;
-      d.blk_end = min(nblk, d.blk_begin + p.chunk_pages); d.nblk = nblk; d.kv_len = kv_len; d.pad = 0;
+      d.id = id; d.b = lo; d.gh = gh; d.blk_begin = c * chunk_pages;
+      d.blk_end = min(nblk, d.blk_begin + chunk_pages); d.nblk = nblk; d.kv_len = kv_len; d.pad = 0;
       my_fifo[fifo_head % kFifo] = d;
     }
     ++fifo_head;
@@ -288,14 +299,57 @@ paged_decode_attn_score_kernel(const DecodeParams p) {
       const uint32_t slot = (uint32_t)pages_consumed % kStages;
       const uint32_t parity = ((uint32_t)pages_consumed / kStages) & 1u;
       ++pages_consumed;
+      const int page_tok0 = blk * BS;
+      const bool last_partial = (page_tok0 + BS > kv_len);
+      const bool write_new = (p.new_k != nullptr) && (blk == nblk - 1);
+      // this step's token (W1 fused): its loads overlap the wait for the page
+      constexpr int VPL = D / 32;  // V dims per lane
+      uint4 nk = make_uint4(0u, 0u, 0u, 0u);
+      __nv_bfloat16 nv[VPL];
+      long long nslot = -1;
+      if (write_new) {
+        nslot = __ldg(p.slot_mapping + b);
+        if (lane < D / 8)
+          nk = __ldg(reinterpret_cast<const uint4*>(p.new_k + (size_t)b * p.new_k_stride + (size_t)h * D + lane * 8));
+        const __nv_bfloat16* vsrc = p.new_v + (size_t)b * p.new_v_stride + (size_t)h * D + lane * VPL;
+        if constexpr (VPL == 4) {
+          const uint2 w2 = __ldg(reinterpret_cast<const uint2*>(vsrc));
+          *reinterpret_cast<uint2*>(nv) = w2;
+        } else {
+          const unsigned int w1 = __ldg(reinterpret_cast<const unsigned int*>(vsrc));
+          *reinterpret_cast<unsigned int*>(nv) = w1;
+        }
+      }
       mbar_wait(&my_bars[slot], parity);
 
       const uint8_t* kpage = my_stages + (size_t)slot * T::kStageBytes;
       const uint8_t* vpage = kpage + T::kPageBytes;
       const uint32_t kaddr = smem_u32(kpage);
       const uint32_t vaddr = smem_u32(vpage);
-      const int page_tok0 = blk * BS;
-      const bool last_partial = (page_tok0 + BS > kv_len);
+
+      if (write_new) {
+        const int off = kv_len - 1 - page_tok0;  // position of the new token in this page
+        const int phys = __ldg(p.block_tables + (size_t)b * p.table_stride + blk);
+        // the page under attention holds the token iff the slot is where the table says
+        const bool here = (nslot == (long long)phys * BS + off);
+        const bool store = (hg == 0) && (nslot >= 0);
+        const long long wblk = nslot / BS;
+        const int woff = (int)(nslot - wblk * BS);
+        const size_t wbase = (size_t)wblk * p.kv_block_stride + (size_t)h * (D * BS);
+        if (lane < D / 8) {
+          if (here) *reinterpret_cast<uint4*>(const_cast<uint8_t*>(kpage) + (size_t)(lane * BS + off) * 16) = nk;
+          if (store) *reinterpret_cast<uint4*>(p.k_cache_w + wbase + (size_t)(lane * BS + woff) * 8) = nk;
+        }
+        __nv_bfloat16* vp = reinterpret_cast<__nv_bfloat16*>(const_cast<uint8_t*>(vpage));
+#pragma unroll
+        for (int i = 0; i < VPL; ++i) {
+          const int dd = lane * VPL + i;
+          if (here) vp[dd * BS + off] = nv[i];
+          if (store) p.v_cache_w[wbase + (size_t)dd * BS + woff] = nv[i];
+        }
+        fence_proxy_async();  // generic-proxy writes before a later TMA refill of this slot
+        __syncwarp();
+      }
 
       if (last_partial) {
         // zero V columns of tokens >= kv_len so 0 * garbage cannot produce NaN
@@ -401,7 +455,7 @@ paged_decode_attn_score_kernel(const DecodeParams p) {
       l_run[0] += __shfl_xor_sync(kFull, l_run[0], sh);
       l_run[1] += __shfl_xor_sync(kFull, l_run[1], sh);
     }
-    const int n_chunks = (nblk + p.chunk_pages - 1) / p.chunk_pages;  // chunks of this group
+    const int n_chunks = (nblk + chunk_pages - 1) / chunk_pages;  // chunks of this group
     // o[m][0]=(dim 16m+g, head 2t) [1]=(dim 16m+g, head 2t+1) [2]=(dim 16m+g+8, 2t) [3]=(.., 2t+1)
     if (n_chunks == 1) {  // the whole group was this chunk: final result
       const float inv0 = 1.f / (l_run[0] + 1e-6f), inv1 = 1.f / (l_run[1] + 1e-6f);
@@ -448,7 +502,7 @@ paged_decode_attn_score_kernel(const DecodeParams p) {
     ++tr_combines;
     if (lane == 0) *tk = 0;  // leave the workspace clean for the next launch
     {
-      const int id0 = d.id - d.blk_begin / p.chunk_pages;  // first chunk of the group
+      const int id0 = d.id - d.blk_begin / chunk_pages;  // first chunk of the group
       const int hh = lane >> 2;             // head of the group this lane combines
       const int d0 = (lane & 3) * (D / 4);  // its D/4 contiguous dims
       // pass 1: group max per head (lanes sharing a head read the same words: broadcast)
@@ -587,6 +641,10 @@ size_t decode_workspace_bytes(int B, int Hq, int Hkv, int D, int BS, int max_kv_
   if (Hkv <= 0 || Hq < Hkv) return 0;
   return plan_decode(B, Hq, Hkv, D, BS, max_kv_len, num_sms, decode_warps(D, BS)).bytes;
 }
+int decode_plan_chunk_pages(int B, int Hq, int Hkv, int D, int BS, int max_kv_len, int num_sms) {
+  if (Hkv <= 0 || Hq < Hkv) return 0;
+  return plan_decode(B, Hq, Hkv, D, BS, max_kv_len, num_sms, decode_warps(D, BS)).chunk_pages;
+}
 
 template <int D, int BS, int kWarps, int kStages>
 static int launch_decode(const DecodeParams& p, int num_sms, long long max_chunks, cudaStream_t stream) {
@@ -641,12 +699,28 @@ int paged_decode_attn_score(const DecodeArgs& a, cudaStream_t stream) {
   p.table_stride = a.table_stride; p.kv_block_stride = a.kv_block_stride;
   p.scale_log2 = a.scale * 1.4426950408889634f;
   p.chunk_pages = pl.chunk_pages;
+  p.plan = a.plan;
   p.trace = g_decode_trace;
+  p.new_k = static_cast<const __nv_bfloat16*>(a.new_k);
+  p.new_v = static_cast<const __nv_bfloat16*>(a.new_v);
+  p.slot_mapping = a.slot_mapping;
+  p.k_cache_w = static_cast<__nv_bfloat16*>(const_cast<void*>(a.k_cache));
+  p.v_cache_w = static_cast<__nv_bfloat16*>(const_cast<void*>(a.v_cache));
+  p.new_k_stride = a.new_k_stride; p.new_v_stride = a.new_v_stride;
+  if (p.new_k != nullptr) {
+    if (!p.new_v || !p.slot_mapping)
+      return set_error(PC_ERR_INVALID, "decode: fused cache write needs key, value and slot_mapping");
+    if ((a.new_k_stride % 8) || (a.new_v_stride % 4) || (reinterpret_cast<uintptr_t>(a.new_k) & 15) ||
+        (reinterpret_cast<uintptr_t>(a.new_v) & 7))
+      return set_error(PC_ERR_INVALID, "decode: fused cache write needs 16-byte aligned key rows, 8-byte aligned value rows");
+  }
 
-  if (a.D == 128 && a.BS == 16) return launch_decode<128, 16, 8, 3>(p, num_sms, pl.max_chunks, stream);
-  if (a.D == 128 && a.BS == 32) return launch_decode<128, 32, 4, 3>(p, num_sms, pl.max_chunks, stream);
-  if (a.D == 64 && a.BS == 16) return launch_decode<64, 16, 8, 6>(p, num_sms, pl.max_chunks, stream);
-  if (a.D == 64 && a.BS == 32) return launch_decode<64, 32, 8, 3>(p, num_sms, pl.max_chunks, stream);
+  // a device-side plan may change between replays of a captured launch: full grid
+  const long long grid_chunks = a.plan ? (long long)num_sms : pl.max_chunks;
+  if (a.D == 128 && a.BS == 16) return launch_decode<128, 16, 8, 3>(p, num_sms, grid_chunks, stream);
+  if (a.D == 128 && a.BS == 32) return launch_decode<128, 32, 4, 3>(p, num_sms, grid_chunks, stream);
+  if (a.D == 64 && a.BS == 16) return launch_decode<64, 16, 8, 6>(p, num_sms, grid_chunks, stream);
+  if (a.D == 64 && a.BS == 32) return launch_decode<64, 32, 8, 3>(p, num_sms, grid_chunks, stream);
   // mirrors TORCH_CHECK(false, "Unsupported head size / block size") in
   // csrc/attention/paged_attention_v1.cu:108-110,160-162
   return set_error(PC_ERR_UNSUPPORTED, "Unsupported head size / block size (supported: head 64|128, block 16|32)");

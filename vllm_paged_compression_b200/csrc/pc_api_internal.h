@@ -50,8 +50,15 @@ struct DecodeArgs {
   ScorePool score;
   void* workspace;
   size_t workspace_bytes;
+  // fused reshape_and_cache of the step's token (nullptr = off)
+  const void* new_k;
+  const void* new_v;
+  const long long* slot_mapping;
+  long long new_k_stride, new_v_stride;
+  const int* plan;  // device {chunk_pages} or nullptr (host plans from max_kv_len)
 };
 size_t decode_workspace_bytes(int B, int Hq, int Hkv, int D, int BS, int max_kv_len, int num_sms);
+int decode_plan_chunk_pages(int B, int Hq, int Hkv, int D, int BS, int max_kv_len, int num_sms);
 int paged_decode_attn_score(const DecodeArgs& a, cudaStream_t stream);
 void set_decode_trace(void* buf);  // debug: per-warp globaltimer stamps, nullptr = off
 

@@ -201,17 +201,20 @@ class PagedEvictEngine:
 
     # -------------------------------------------------------------------------- step
     def step(self, qkv_fn: QKVFn, keep_outputs: bool = True,
-             out_fn: Optional[Callable[[int, torch.Tensor], None]] = None) -> StepOutput:
+             out_fn: Optional[Callable[[int, torch.Tensor], None]] = None,
+             out_buf_fn: Optional[Callable[[int, int], torch.Tensor]] = None) -> StepOutput:
         """qkv_fn(layer, num_tokens) -> (query [T,Hq*D], key [T,Hkv*D], value [T,Hkv*D])
         on self.device.  out_fn(layer, out) receives each layer's attention output (the
-        tensor the model's o_proj would consume)."""
+        tensor the model's o_proj would consume); out_buf_fn(layer, num_tokens) supplies
+        the tensor `forward(..., output=)` writes into."""
         is_prompt, batch = self._schedule()
         md = self.build_metadata(is_prompt, batch)
         n_tok = md.num_prefill_tokens + md.num_decode_tokens
         outs = []
         for layer, impl in enumerate(self.impls):
             q, k, v = qkv_fn(layer, n_tok)
-            o = impl.forward(q, k, v, self.kv_caches[layer], md)
+            ob = out_buf_fn(layer, n_tok) if out_buf_fn is not None else None
+            o = impl.forward(q, k, v, self.kv_caches[layer], md, output=ob)
             if out_fn is not None:
                 out_fn(layer, o)
             if keep_outputs:
@@ -232,3 +235,75 @@ class PagedEvictEngine:
                 s.prefilled = True
                 self.running.append(s)
         return out
+
+
+class PinnedLayerIO:
+    """Host <-> device staging for a caller whose per-layer activations live in HOST memory.
+
+    The reference's model runner hands `forward` device tensors; a caller that keeps q/k/v
+    on the host (bench.py's e2e leg, an offloaded model) would otherwise pay one blocking
+    copy per tensor per layer on the compute stream.  Here the step's inputs travel as one
+    fused `[B, (Hq + 2 Hkv) D]` row block per layer (the layout `qkv_proj` produces,
+    vllm/model_executor/models/llama.py:195-199) on a copy stream that runs ahead of the
+    compute stream in groups of `group` layers, and every group's attention output is
+    drained on a third stream while later layers compute.  PCIe is full duplex, so the
+    step costs max(compute, H2D, D2H) plus the first group's H2D and the last group's D2H.
+
+    Use:  io.begin_step(); engine.step(io.qkv, out_fn=io.put_out, out_buf_fn=io.out_buf); io.end_step()
+    """
+
+    def __init__(self, num_layers: int, batch: int, num_heads: int, num_kv_heads: int, head_size: int,
+                 device, group: int = 4, dtype=torch.bfloat16) -> None:
+        self.L, self.B, self.group = num_layers, batch, max(1, group)
+        self.qw, self.kw = num_heads * head_size, num_kv_heads * head_size
+        w = self.qw + 2 * self.kw
+        self.device = torch.device(device)
+        self.qkv_host = torch.empty(num_layers, batch, w, dtype=dtype).pin_memory()
+        self.out_host = torch.empty(num_layers, batch, self.qw, dtype=dtype).pin_memory()
+        self.qkv_dev = torch.empty(num_layers, batch, w, dtype=dtype, device=self.device)
+        self.out_dev = torch.empty(num_layers, batch, self.qw, dtype=dtype, device=self.device)
+        self.h2d_stream = torch.cuda.Stream(self.device)
+        self.d2h_stream = torch.cuda.Stream(self.device)
+        n_groups = -(-num_layers // self.group)
+        self.h2d_done = [torch.cuda.Event() for _ in range(n_groups)]
+        self.grp_done = [torch.cuda.Event() for _ in range(n_groups)]
+        self.step_done = torch.cuda.Event()
+        self.h2d_bytes = self.qkv_host.numel() * self.qkv_host.element_size()
+        self.d2h_bytes = self.out_host.numel() * self.out_host.element_size()
+
+    def begin_step(self) -> None:
+        """Queue every layer group's H2D on the copy stream (after the previous step's
+        compute has consumed the staging buffers)."""
+        cur = torch.cuda.current_stream(self.device)
+        self.h2d_stream.wait_stream(cur)
+        with torch.cuda.stream(self.h2d_stream):
+            for gi in range(len(self.h2d_done)):
+                lo, hi = gi * self.group, min(self.L, (gi + 1) * self.group)
+                self.qkv_dev[lo:hi].copy_(self.qkv_host[lo:hi], non_blocking=True)
+                self.h2d_done[gi].record(self.h2d_stream)
+
+    def qkv(self, layer: int, n_tok: int, wait: bool = True):
+        if wait and layer % self.group == 0:
+            torch.cuda.current_stream(self.device).wait_event(self.h2d_done[layer // self.group])
+        row = self.qkv_dev[layer]
+        return row[:, :self.qw], row[:, self.qw:self.qw + self.kw], row[:, self.qw + self.kw:]
+
+    def out_buf(self, layer: int, n_tok: int) -> torch.Tensor:
+        return self.out_dev[layer]
+
+    def put_out(self, layer: int, out: torch.Tensor) -> None:
+        if out.data_ptr() != self.out_dev[layer].data_ptr():
+            self.out_dev[layer].copy_(out.view(self.B, self.qw))
+        if (layer + 1) % self.group == 0 or layer == self.L - 1:
+            gi = layer // self.group
+            cur = torch.cuda.current_stream(self.device)
+            self.grp_done[gi].record(cur)
+            self.d2h_stream.wait_event(self.grp_done[gi])
+            lo = gi * self.group
+            with torch.cuda.stream(self.d2h_stream):
+                self.out_host[lo:layer + 1].copy_(self.out_dev[lo:layer + 1], non_blocking=True)
+
+    def end_step(self) -> None:
+        """Block until the step's outputs are in `out_host` (the caller owns them now)."""
+        self.step_done.record(self.d2h_stream)
+        self.step_done.synchronize()

@@ -1,0 +1,264 @@
+"""Decode steps of a fixed set of running sequences, replayed as CUDA graphs.
+
+The reference runs the eviction path with `--enforce-eager` (every documented command;
+`TorchCUDASDPAMetadataBuilder.build` has a graph branch, torch_cuda_sdpa.py:626-640, but the
+compacted tables change width so it is unusable).  Measured on B200 the eager path of this
+package is HOST-bound for the 8B shape (1.28 ms of Python + ctypes per 32-layer step against
+1.23 ms of kernels, profiles/r01_e2e_breakdown.txt), so the B200-native step is:
+
+  * all per-step integer state (slot mapping, block tables, kv / seq lengths, blocks per row,
+    the decode kernel's chunk plan) lives in ONE fixed device buffer, refreshed by ONE
+    pinned H2D copy per step; the host keeps a numpy mirror that it updates incrementally
+    (a new block = one element, an eviction = one row shift) instead of rebuilding
+    `TorchCUDASDPAMetadata` from Python lists;
+  * the per-layer launches (`pc_decode_layer`: [select + compact] -> attention with the
+    fused cache write and block scoring) of all layers are captured once per variant
+    (trigger step / plain step) and replayed; table width, kv lengths and the chunk plan are
+    read from device memory by the kernels, so one capture serves every step;
+  * with host-resident activations (`PinnedLayerIO`) the H2D / D2H copies and their stream
+    fork / join are part of the same graph.
+
+Semantics are those of `PagedEvictEngine.step` (engine.py): same scheduler arithmetic, same
+kernels, same layer-0 feedback; tests/test_gpu_layer.py checks both paths bit for bit.
+"""
+from __future__ import annotations
+
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+
+from . import ops
+from .policy import cdiv
+
+
+class DecodeGraphRunner:
+    def __init__(self, engine, qkv: Optional[Sequence[Tuple[torch.Tensor, torch.Tensor, torch.Tensor]]],
+                 outs: Optional[Sequence[torch.Tensor]] = None, io=None, max_kv_len: Optional[int] = None,
+                 use_graph: bool = True) -> None:
+        """engine: PagedEvictEngine whose `running` sequences are all prefilled.
+        qkv[l] = (query [B,Hq*D], key [B,Hkv*D], value [B,Hkv*D]) STATIC device tensors the
+        caller refills before every step (ignored when `io` is given: PinnedLayerIO supplies
+        its device staging buffers and moves host data in-graph).  outs[l] [B, Hq*D] static.
+        max_kv_len bounds the physical KV length of any row while this runner lives."""
+        eng = self.eng = engine
+        self.device = eng.device
+        self.io = io
+        self.use_graph = use_graph
+        self.seqs = list(eng.running)
+        if not self.seqs:
+            raise RuntimeError("DecodeGraphRunner needs running (prefilled) sequences")
+        B = self.B = len(self.seqs)
+        bs = self.bs = eng.block_size
+        L = self.L = eng.num_layers
+        self.cfg = eng.cache_config.paged_evict_config
+        impl0 = eng.impls[0]
+        self.value_l2 = impl0._value_l2
+        self.attend_unc = (self.cfg is not None) and (not self.value_l2) and impl0.head_compat_uncompacted
+        bm = eng.block_manager
+        self.bts = [bm.block_tables[s.seq_id] for s in self.seqs]
+        cur_max = max(bt.get_seq_kv_len() for bt in self.bts)
+        if max_kv_len is None:
+            # eviction bounds the physical length near where it is now; otherwise leave room
+            max_kv_len = cur_max + (8 * bs * max(getattr(self.cfg, "evict_freq", 1) or 1, 1)
+                                    if self.cfg is not None else 4096)
+        self.max_kv_len = int(max_kv_len)
+        M = self.M = cdiv(self.max_kv_len, bs) + 1
+
+        if io is not None:
+            qkv = [io.qkv(l, B, wait=False) for l in range(L)]
+            outs = [io.out_dev[l] for l in range(L)]
+        if outs is None:
+            outs = [torch.empty(B, eng.num_heads * eng.head_size, dtype=torch.bfloat16, device=self.device)
+                    for _ in range(L)]
+        self.qkv = [tuple(t.view(B, -1, eng.head_size) for t in x) for x in qkv]
+        self.outs = [o.view(B, eng.num_heads, eng.head_size) for o in outs]
+        self.out_flat = list(outs)
+
+        # ---- packed int32 state: device buffer + ring of pinned host copies
+        o_slot, o_kv, o_seq, o_nblk, o_plan, o_tab = 0, 2 * B, 3 * B, 4 * B, 5 * B, 5 * B + 4
+        self.n_meta = o_tab + B * M
+        self.meta = torch.zeros(self.n_meta, dtype=torch.int32, device=self.device)
+        self._ring = [torch.zeros(self.n_meta, dtype=torch.int32).pin_memory() for _ in range(4)]
+        self._ring_ev = [None] * len(self._ring)
+        self._ring_i = 0
+        m = self.meta
+        self.d_slot = m[o_slot:o_kv].view(torch.int64)
+        self.d_kv, self.d_seq, self.d_nblk = m[o_kv:o_seq], m[o_seq:o_nblk], m[o_nblk:o_plan]
+        self.d_plan = m[o_plan:o_tab]
+        self.d_tab = m[o_tab:].view(B, M)
+        self._off = (o_slot, o_kv, o_seq, o_nblk, o_plan, o_tab)
+        self.d_compact = torch.zeros(B, M, dtype=torch.int32, device=self.device)
+        self.d_victims = torch.full((L, B), -1, dtype=torch.int32, device=self.device)
+
+        # ---- host mirror
+        self.tab = np.zeros((B, M), dtype=np.int32)
+        self.nblk = np.zeros(B, dtype=np.int32)
+        for r, bt in enumerate(self.bts):
+            ids = bt.physical_block_ids
+            if len(ids) > M:
+                raise RuntimeError("max_kv_len is smaller than a sequence already is")
+            self.tab[r, :len(ids)] = ids
+            self.nblk[r] = len(ids)
+        self.seq = np.asarray([s.seq_len for s in self.seqs], dtype=np.int64)
+        self.kv = np.asarray([bt.get_seq_kv_len() for bt in self.bts], dtype=np.int64)
+        self.rows = np.arange(B)
+
+        # ---- decode workspace large enough for every plan up to max_kv_len
+        Hq, Hkv, D = eng.num_heads, eng.num_kv_heads, eng.head_size
+        need = max(ops.paged_decode_workspace_bytes(B, Hq, Hkv, D, bs, n * bs) for n in range(1, M + 1))
+        self.ws = torch.zeros(need, dtype=torch.uint8, device=self.device)
+        self._plan_cache: Dict[int, int] = {}
+
+        # ---- per-layer pointers
+        self.layers = []
+        for l, impl in enumerate(eng.impls):
+            kc, vc, (kptr, vptr, blk_stride) = impl._caches(eng.kv_caches[l])
+            score = impl._scores(self.device, eng.kv_caches[l].shape[1]) if self.value_l2 else None
+            self.layers.append((kptr, vptr, score))
+        self.blk_stride = blk_stride
+        self._graphs: Dict[bool, object] = {}
+        self._launches: Dict[bool, int] = {}
+        self._warm()
+
+    # ------------------------------------------------------------------ launches
+    def _make_step(self, trig: bool):
+        eng = self.eng
+        q, k, v = self.qkv[0]
+        return ops.make_decode_step(
+            self.d_slot, self.d_tab, self.d_kv, self.d_seq, self.B, eng.num_heads, eng.num_kv_heads,
+            eng.head_size, self.bs, self.max_kv_len, eng.impls[0].scale, q.stride(0), k.stride(0),
+            v.stride(0), self.outs[0].stride(0), self.blk_stride,
+            policy=eng.impls[0]._policy_struct() if self.cfg is not None else None,
+            n_blocks=self.d_nblk, compact_tables=self.d_compact if trig else None, any_trigger=trig,
+            attend_uncompacted=trig and self.attend_unc, plan=self.d_plan, workspace=self.ws)
+
+    def _launch_layers(self, trig: bool, count: bool = False) -> None:
+        """All layers of one decode step on the current stream (captured or eager)."""
+        ds = self._make_step(trig)
+        self._launches[trig] = ds._launches * self.L
+        io = self.io
+        cur = torch.cuda.current_stream(self.device)
+        if io is not None:
+            io.begin_step()
+        for l in range(self.L):
+            if io is not None and l % io.group == 0:
+                cur.wait_event(io.h2d_done[l // io.group])
+            q, k, v = self.qkv[l]
+            kptr, vptr, score = self.layers[l]
+            ops.decode_layer(ds, self.outs[l], q, k, v, kptr, vptr, score,
+                             self.d_victims[l] if trig else None)
+            if io is not None:
+                io.put_out(l, self.out_flat[l])
+        if io is not None:
+            cur.wait_stream(io.d2h_stream)
+            cur.wait_stream(io.h2d_stream)
+
+    def _warm(self) -> None:
+        """Load every kernel (lazy module loading must not happen under capture): one eager
+        pass of both variants over rows of length zero -- no page is read or written."""
+        self.meta.zero_()
+        io, self.io = self.io, None
+        try:
+            for trig in ((False, True) if self.cfg is not None else (False,)):
+                self._launch_layers(trig)
+        finally:
+            self.io = io
+        torch.cuda.current_stream(self.device).synchronize()
+
+    def _graph(self, trig: bool):
+        g = self._graphs.get(trig)
+        if g is None:
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                self._launch_layers(trig)
+            self._graphs[trig] = g
+        return g
+
+    # ---------------------------------------------------------------------- step
+    def _trigger(self) -> np.ndarray:
+        cfg, bs = self.cfg, self.bs
+        if cfg is None:
+            return np.zeros(self.B, dtype=bool)
+        ok = self.nblk >= 3
+        if cfg.cache_prune_type == "budget":
+            return ok & (self.seq > cfg.cache_budget) & (self.seq % bs == 0)
+        return (ok & (self.seq % (bs * cfg.evict_freq) == 0)
+                & (self.nblk.astype(np.int64) * bs > (cfg.initial_blocks + cfg.num_block_merge) * bs))
+
+    def step(self) -> Dict[int, Tuple[str, int]]:
+        """One decode step of every sequence.  The caller has refilled the static q/k/v
+        buffers (or `io.qkv_host`).  Returns layer 0's {row: (request_id, table index)}
+        after applying it to the block manager (llm_engine.py:1179-1193)."""
+        eng, bs, B = self.eng, self.bs, self.B
+        bm = eng.block_manager
+        if not bm.can_append_slots(B):
+            raise RuntimeError("out of KV blocks (preemption is outside the hot path)")
+        tab, nblk = self.tab, self.nblk
+        for r, (s, bt) in enumerate(zip(self.seqs, self.bts)):      # scheduler.py _schedule_default
+            s.seq_len += 1
+            n0 = int(nblk[r])
+            bt.append_slots(1)
+            ids = bt.physical_block_ids
+            if len(ids) != n0:
+                if len(ids) > self.M:
+                    raise RuntimeError("sequence outgrew the runner's max_kv_len")
+                tab[r, n0] = ids[-1]
+                nblk[r] = n0 + 1
+        self.seq += 1
+        self.kv += 1
+        trig = self._trigger()
+        any_trig = bool(trig.any())
+        kv_pass = self.kv - bs * trig if self.cfg is not None else self.seq     # model_runner.py:540-543
+        slot = tab[self.rows, nblk - 1].astype(np.int64) * bs + (self.seq - 1) % bs
+        mx = int(kv_pass.max())
+        plan = self._plan_cache.get(mx)
+        if plan is None:
+            plan = self._plan_cache[mx] = ops.paged_decode_plan(B, eng.num_heads, eng.num_kv_heads,
+                                                                eng.head_size, bs, mx)
+        # ---- one packed H2D
+        i = self._ring_i
+        self._ring_i = (i + 1) % len(self._ring)
+        if self._ring_ev[i] is not None:
+            self._ring_ev[i].synchronize()
+        host = self._ring[i].numpy()
+        o_slot, o_kv, o_seq, o_nblk, o_plan, o_tab = self._off
+        host[o_slot:o_kv].view(np.int64)[:] = slot
+        host[o_kv:o_seq] = kv_pass
+        host[o_seq:o_nblk] = self.seq
+        host[o_nblk:o_plan] = nblk
+        host[o_plan] = plan
+        host[o_tab:] = tab.reshape(-1)
+        self.meta.copy_(self._ring[i], non_blocking=True)
+        ev = self._ring_ev[i] or torch.cuda.Event()
+        ev.record(torch.cuda.current_stream(self.device))
+        self._ring_ev[i] = ev
+        # ---- all layers
+        if self.use_graph:
+            self._graph(any_trig).replay()
+            ops._launched(self._launches[any_trig])      # kernel nodes of the replayed graph
+        else:
+            self._launch_layers(any_trig)                # ops.decode_layer counts its own
+        if eng.score_exchange is not None:
+            scored = [int(tab[r, nblk[r] - 1]) for r in range(B) if self.seq[r] % bs == 0] \
+                if self.value_l2 else []
+            eng.score_exchange.publish(scored)
+        # ---- layer-0 feedback (model_runner.py:1797-1802)
+        rmv: Dict[int, Tuple[str, int]] = {}
+        if any_trig:
+            rows = np.nonzero(trig)[0]
+            if self.value_l2:
+                vict = self.d_victims[0].cpu().numpy()
+                rmv = {int(r): (self.seqs[r].request_id, int(vict[r])) for r in rows if vict[r] >= 0}
+            else:
+                rmv = {int(r): (self.seqs[r].request_id, 1) for r in rows}
+            for r, (_, idx) in rmv.items():
+                self.bts[r].free_prunned_blocks(idx)
+                n = int(nblk[r])
+                tab[r, idx:n - 1] = tab[r, idx + 1:n]
+                tab[r, n - 1] = 0
+                nblk[r] = n - 1
+                self.kv[r] -= bs
+        if self.io is not None:
+            torch.cuda.current_stream(self.device).synchronize()    # the caller owns out_host now
+        return rmv

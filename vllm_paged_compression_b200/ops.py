@@ -227,7 +227,9 @@ def make_decode_step(slot_mapping: torch.Tensor, block_tables: torch.Tensor, kv_
                      kv_block_stride: int, policy: Optional[PcEvictPolicy] = None,
                      n_blocks: Optional[torch.Tensor] = None,
                      compact_tables: Optional[torch.Tensor] = None, any_trigger: bool = False,
-                     attend_uncompacted: bool = False) -> PcDecodeStep:
+                     attend_uncompacted: bool = False, fuse_cache_write: bool = True,
+                     plan: Optional[torch.Tensor] = None,
+                     workspace: Optional[torch.Tensor] = None) -> PcDecodeStep:
     """struct pc_decode_step: everything that is the same for every layer of one engine
     step (built once per step, passed by pointer to `decode_layer`)."""
     _req_cuda(slot_mapping, block_tables, kv_lens, seq_lens, n_blocks, compact_tables)
@@ -248,13 +250,26 @@ def make_decode_step(slot_mapping: torch.Tensor, block_tables: torch.Tensor, kv_
     if policy is not None:
         st.policy = policy
     need = paged_decode_workspace_bytes(batch, num_heads, num_kv_heads, head_size, block_size, max_kv_len)
-    ws = _workspace(dev, need)
+    ws = workspace if workspace is not None else _workspace(dev, need)
+    if ws.numel() < need:
+        raise RuntimeError(f"decode workspace too small: {ws.numel()} < {need} bytes")
     st.workspace, st.workspace_bytes = ws.data_ptr(), ws.numel()
     st.dtype = PC_BF16
     st.stream = torch.cuda.current_stream(dev).cuda_stream
-    st._keepalive = (slot_mapping, block_tables, kv_lens, seq_lens, n_blocks, compact_tables, ws)
-    st._launches = 2 + (1 if any_trigger else 0)
+    fused = bool(fuse_cache_write) and not (any_trigger and attend_uncompacted)
+    st.fuse_cache_write = int(fused)
+    _req_cuda(plan)
+    st.plan = _ptr(plan)
+    st._keepalive = (slot_mapping, block_tables, kv_lens, seq_lens, n_blocks, compact_tables, ws, plan)
+    st._launches = (1 if fused else 2) + (1 if any_trigger else 0)
     return st
+
+
+def paged_decode_plan(batch: int, num_heads: int, num_kv_heads: int, head_size: int, block_size: int,
+                      max_kv_len: int) -> int:
+    """chunk_pages the host planner picks for this launch shape (pc_decode_step.plan)."""
+    return int(_lib.load().pc_paged_decode_plan(batch, num_heads, num_kv_heads, head_size, block_size,
+                                                max_kv_len))
 
 
 def decode_layer(step: PcDecodeStep, out: torch.Tensor, query: torch.Tensor, key: torch.Tensor,
