@@ -70,6 +70,8 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-graph", action="store_true",
                     help="eager PagedEvictEngine.step (one forward() per layer) instead of CUDA-graph replay")
+    ap.add_argument("--no-pdl", action="store_true",
+                    help="no programmatic dependent launch between consecutive layers' decode kernels")
     ap.add_argument("--score-exchange", default="p2p", choices=["p2p", "nccl"],
                     help="N > 1: how per-head block scores reach the other ranks (parallel.py)")
     ap.add_argument("--sweep", action="store_true",
@@ -219,9 +221,10 @@ class Arm:
         kv_now = max(self.eng.block_manager.get_seq_kv_len(s.seq_id) for s in self.eng.running)
         bound = kv_now + a.steps + a.warmup + 2 * a.block_size + 64
         if self.host_io:
-            self.runner = DecodeGraphRunner(self.eng, None, io=self.io, max_kv_len=bound)
+            self.runner = DecodeGraphRunner(self.eng, None, io=self.io, max_kv_len=bound, pdl=not a.no_pdl)
         else:
-            self.runner = DecodeGraphRunner(self.eng, list(zip(self.q, self.k, self.v)), max_kv_len=bound)
+            self.runner = DecodeGraphRunner(self.eng, list(zip(self.q, self.k, self.v)), max_kv_len=bound,
+                                            pdl=not a.no_pdl)
 
     def step(self) -> int:
         """One decode step of the whole batch; -> blocks evicted (layer-0 feedback)."""

@@ -207,6 +207,14 @@ typedef struct pc_decode_step {
                                   * kv lengths move; NULL = plan on the host.  workspace must then hold
                                   * pc_paged_decode_workspace_bytes of every max_kv_len it is replayed
                                   * with. */
+  int32_t pdl;                   /* != 0: launch the attention kernel with programmatic stream
+                                  * serialization (PDL): its prologue and first ring of KV-page loads
+                                  * overlap the tail of the PRECEDING kernel of the stream.  The caller
+                                  * promises that that kernel does not write this layer's KV pool, the
+                                  * block tables or the length arrays (true for the preceding layer's
+                                  * call and for the model's projection kernels).  Q and the step's
+                                  * K/V rows are read after the dependency wait.  Only honoured with
+                                  * fuse_cache_write on non-trigger steps. */
 } pc_decode_step;
 /* chunk_pages the host planner picks for this launch shape (to fill pc_decode_step.plan). */
 int32_t pc_paged_decode_plan(int32_t batch, int32_t num_heads, int32_t num_kv_heads,

@@ -1,0 +1,263 @@
+// extern "C" entry points of libpagedevict_b200.so (see include/pagedevict_b200.h).
+#include <stdio.h>
+#include <string.h>
+
+#include "pc_api_internal.h"
+
+namespace pc {
+
+static thread_local char g_err[512] = "";
+
+int set_error(int code, const char* msg) {
+  snprintf(g_err, sizeof(g_err), "%s", msg);
+  return code;
+}
+int set_cuda_error(const char* what, cudaError_t e) {
+  snprintf(g_err, sizeof(g_err), "%s: %s", what, cudaGetErrorString(e));
+  return PC_ERR_CUDA;
+}
+int check_launch(const char* kernel_name) {
+  const cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return set_cuda_error(kernel_name, e);
+  return PC_OK;
+}
+int device_sm_count() {
+  static thread_local int cached_dev = -1, cached = 0;
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) { set_cuda_error("cudaGetDevice", e); return -1; }
+  if (dev != cached_dev) {
+    e = cudaDeviceGetAttribute(&cached, cudaDevAttrMultiProcessorCount, dev);
+    if (e != cudaSuccess) { set_cuda_error("cudaDeviceGetAttribute", e); return -1; }
+    cached_dev = dev;
+  }
+  return cached;
+}
+
+int check_score_pool(const pc_score_pool* s, int num_kv_heads, const char* who) {
+  if (s == nullptr) return PC_OK;
+  char msg[160];
+  if (s->n_pools < 1 || s->n_pools > PC_MAX_PEERS || s->local < 0 || s->local >= s->n_pools) {
+    snprintf(msg, sizeof(msg), "%s: score pool needs 1 <= n_pools <= %d and 0 <= local < n_pools", who, PC_MAX_PEERS);
+    return set_error(PC_ERR_INVALID, msg);
+  }
+  for (int i = 0; i < s->n_pools; ++i)
+    if (s->pools[i] == nullptr) {
+      snprintf(msg, sizeof(msg), "%s: score pool %d is a null pointer", who, i);
+      return set_error(PC_ERR_INVALID, msg);
+    }
+  if (s->heads_total < 1 || s->head_offset < 0 || s->head_offset + num_kv_heads > s->heads_total) {
+    snprintf(msg, sizeof(msg), "%s: score pool heads [%d, %d) do not fit heads_total %d", who, s->head_offset,
+             s->head_offset + num_kv_heads, s->heads_total);
+    return set_error(PC_ERR_INVALID, msg);
+  }
+  return PC_OK;
+}
+
+static int check_dtype(int dtype) {
+  if (dtype != PC_BF16) return set_error(PC_ERR_UNSUPPORTED, "only bf16 KV cache / activations are built");
+  return PC_OK;
+}
+
+}  // namespace pc
+
+using namespace pc;
+
+extern "C" {
+
+int pc_abi_version(void) { return PC_ABI_VERSION; }
+size_t pc_sizeof_struct(int32_t which) {
+  switch (which) {
+    case 0: return sizeof(pc_evict_policy);
+    case 1: return sizeof(pc_score_pool);
+    case 2: return sizeof(pc_decode_step);
+    default: return 0;
+  }
+}
+const char* pc_last_error(void) { return g_err; }
+int pc_device_sm_count(void) { return device_sm_count(); }
+
+int pc_reshape_and_cache(const void* key, const void* value, void* key_cache, void* value_cache,
+                         const int64_t* slot_mapping, int32_t num_tokens, int32_t num_kv_heads,
+                         int32_t head_size, int32_t block_size, int64_t key_stride,
+                         int64_t value_stride, int64_t kv_block_stride, int32_t dtype,
+                         void* stream) {
+  if (int rc = check_dtype(dtype)) return rc;
+  if (num_tokens == 0) return PC_OK;
+  if (!key || !value || !key_cache || !value_cache || !slot_mapping)
+    return set_error(PC_ERR_INVALID, "pc_reshape_and_cache: null pointer");
+  CacheWriteArgs a{};
+  a.key = key; a.value = value; a.k_cache = key_cache; a.v_cache = value_cache;
+  a.slot_mapping = reinterpret_cast<const long long*>(slot_mapping);
+  a.req_meta = nullptr; a.tile_offsets = nullptr; a.num_reqs = 1; a.total_tiles = 0;
+  a.num_tokens = num_tokens; a.Hkv = num_kv_heads; a.D = head_size; a.BS = block_size;
+  a.key_stride = key_stride; a.value_stride = value_stride; a.kv_block_stride = kv_block_stride;
+  a.score = make_score_pool(nullptr);
+  return cache_write(a, static_cast<cudaStream_t>(stream));
+}
+
+int pc_prune_prompt_and_cache(const void* key, const void* value, void* key_cache,
+                              void* value_cache, const int64_t* slot_mapping,
+                              const int32_t* req_meta, const int32_t* tile_offsets,
+                              int32_t num_reqs, int32_t total_tiles, int32_t num_kv_heads,
+                              int32_t head_size, int32_t block_size, int64_t key_stride,
+                              int64_t value_stride, int64_t kv_block_stride,
+                              const pc_score_pool* score, int32_t dtype, void* stream) {
+  if (int rc = check_dtype(dtype)) return rc;
+  if (num_reqs == 0 || total_tiles == 0) return PC_OK;
+  if (!key || !value || !key_cache || !value_cache || !slot_mapping || !req_meta || !tile_offsets)
+    return set_error(PC_ERR_INVALID, "pc_prune_prompt_and_cache: null pointer");
+  if (int rc = check_score_pool(score, num_kv_heads, "pc_prune_prompt_and_cache")) return rc;
+  CacheWriteArgs a{};
+  a.key = key; a.value = value; a.k_cache = key_cache; a.v_cache = value_cache;
+  a.slot_mapping = reinterpret_cast<const long long*>(slot_mapping);
+  a.req_meta = req_meta; a.tile_offsets = tile_offsets; a.num_reqs = num_reqs;
+  a.total_tiles = total_tiles; a.num_tokens = 0;
+  a.Hkv = num_kv_heads; a.D = head_size; a.BS = block_size;
+  a.key_stride = key_stride; a.value_stride = value_stride; a.kv_block_stride = kv_block_stride;
+  a.score = make_score_pool(score);
+  return cache_write(a, static_cast<cudaStream_t>(stream));
+}
+
+int pc_evict_select_compact(const int32_t* block_tables, int64_t table_stride,
+                            const int32_t* n_blocks, const int32_t* seq_lens,
+                            const int32_t* kv_lens, int32_t batch, const pc_evict_policy* policy,
+                            const pc_score_pool* score, int32_t num_kv_heads, int32_t* out_tables,
+                            int64_t out_stride, int32_t* out_kv_lens, int32_t* out_victim,
+                            int32_t kv_lens_pre_adjusted, void* stream) {
+  if (batch == 0) return PC_OK;
+  if (!block_tables || !n_blocks || !seq_lens || !policy || !out_tables || !out_victim)
+    return set_error(PC_ERR_INVALID, "pc_evict_select_compact: null pointer");
+  if (out_kv_lens && !kv_lens)
+    return set_error(PC_ERR_INVALID, "pc_evict_select_compact: out_kv_lens needs kv_lens");
+  (void)num_kv_heads;
+  if (int rc = check_score_pool(score, 0, "pc_evict_select_compact")) return rc;
+  EvictSelectArgs a{};
+  a.block_tables = block_tables; a.table_stride = table_stride; a.n_blocks = n_blocks;
+  a.seq_lens = seq_lens; a.kv_lens = kv_lens; a.B = batch; a.pol = *policy;
+  a.score = make_score_pool(score);
+  a.out_tables = out_tables; a.out_stride = out_stride; a.out_kv_lens = out_kv_lens;
+  a.out_victim = out_victim; a.pre_adjusted = kv_lens_pre_adjusted;
+  return evict_select_compact(a, static_cast<cudaStream_t>(stream));
+}
+
+size_t pc_paged_decode_workspace_bytes(int32_t batch, int32_t num_heads, int32_t num_kv_heads,
+                                       int32_t head_size, int32_t block_size,
+                                       int32_t max_kv_len) {
+  const int sms = device_sm_count();
+  if (sms <= 0 || batch <= 0 || num_kv_heads <= 0 || num_heads % num_kv_heads) return 0;
+  return decode_workspace_bytes(batch, num_heads, num_kv_heads, head_size, block_size, max_kv_len, sms);
+}
+
+int pc_paged_decode_attn_score(void* out, const void* query, const void* key_cache,
+                               const void* value_cache, const int32_t* block_tables,
+                               int64_t table_stride, const int32_t* kv_lens, int32_t batch,
+                               int32_t num_heads, int32_t num_kv_heads, int32_t head_size,
+                               int32_t block_size, int32_t max_kv_len, float scale,
+                               int64_t q_stride, int64_t out_stride, int64_t kv_block_stride,
+                               const int32_t* seq_lens, const pc_score_pool* score,
+                               void* workspace, size_t workspace_bytes, int32_t dtype,
+                               void* stream) {
+  if (int rc = check_dtype(dtype)) return rc;
+  if (batch == 0) return PC_OK;
+  if (!out || !query || !key_cache || !value_cache || !block_tables || !kv_lens || !workspace)
+    return set_error(PC_ERR_INVALID, "pc_paged_decode_attn_score: null pointer");
+  if (score && !seq_lens)
+    return set_error(PC_ERR_INVALID, "pc_paged_decode_attn_score: scoring needs seq_lens");
+  if (int rc = check_score_pool(score, num_kv_heads, "pc_paged_decode_attn_score")) return rc;
+  if ((reinterpret_cast<uintptr_t>(key_cache) | reinterpret_cast<uintptr_t>(value_cache)) & 15)
+    return set_error(PC_ERR_INVALID, "key/value cache must be 16-byte aligned (TMA bulk copy)");
+  if ((kv_block_stride % 8) || (q_stride % 2) || (reinterpret_cast<uintptr_t>(query) & 3))
+    return set_error(PC_ERR_INVALID, "kv_block_stride % 8 == 0, q_stride even, query 4-byte aligned required");
+  if (reinterpret_cast<uintptr_t>(workspace) & 255)
+    return set_error(PC_ERR_INVALID, "workspace must be 256-byte aligned");
+  DecodeArgs a{};
+  a.out = out; a.q = query; a.k_cache = key_cache; a.v_cache = value_cache;
+  a.block_tables = block_tables; a.table_stride = table_stride; a.kv_lens = kv_lens;
+  a.B = batch; a.Hq = num_heads; a.Hkv = num_kv_heads; a.D = head_size; a.BS = block_size;
+  a.max_kv_len = max_kv_len; a.scale = scale;
+  a.q_stride = q_stride; a.out_stride = out_stride; a.kv_block_stride = kv_block_stride;
+  a.seq_lens = seq_lens; a.score = make_score_pool(score);
+  a.workspace = workspace; a.workspace_bytes = workspace_bytes;
+  return paged_decode_attn_score(a, static_cast<cudaStream_t>(stream));
+}
+
+int pc_decode_layer(const pc_decode_step* st, void* out, const void* query, const void* key,
+                    const void* value, void* key_cache, void* value_cache,
+                    const pc_score_pool* score, int32_t* out_victim) {
+  if (!st) return set_error(PC_ERR_INVALID, "pc_decode_layer: null step");
+  if (st->batch == 0) return PC_OK;
+  // W1: this step's K/V rows into the pool
+  if (int rc = pc_reshape_and_cache(key, value, key_cache, value_cache, st->slot_mapping, st->batch,
+                                    st->num_kv_heads, st->head_size, st->block_size, st->key_stride,
+                                    st->value_stride, st->kv_block_stride, st->dtype, st->stream))
+    return rc;
+  const int32_t* tables = st->block_tables;
+  int64_t stride = st->table_stride;
+  if (st->any_trigger) {
+    // P3 + S4 + C1: victims from the scores of blocks filled on EARLIER steps, compacted tables
+    if (!out_victim || !st->compact_tables || !st->n_blocks)
+      return set_error(PC_ERR_INVALID, "pc_decode_layer: trigger step needs out_victim, compact_tables, n_blocks");
+    if (int rc = pc_evict_select_compact(st->block_tables, st->table_stride, st->n_blocks, st->seq_lens,
+                                         nullptr, st->batch, &st->policy, score, st->num_kv_heads,
+                                         st->compact_tables, st->compact_stride, nullptr, out_victim, 1,
+                                         st->stream))
+      return rc;
+    if (!st->attend_uncompacted) { tables = st->compact_tables; stride = st->compact_stride; }
+  }
+  // A2 + S2: attention over the (compacted) tables, scoring the blocks that fill this step
+  return pc_paged_decode_attn_score(out, query, key_cache, value_cache, tables, stride, st->kv_lens,
+                                    st->batch, st->num_heads, st->num_kv_heads, st->head_size,
+                                    st->block_size, st->max_kv_len, st->scale, st->q_stride,
+                                    st->out_stride, st->kv_block_stride,
+                                    score ? st->seq_lens : nullptr, score, st->workspace,
+                                    st->workspace_bytes, st->dtype, st->stream);
+}
+
+int pc_prefill_attn_topleft_causal(void* out, const void* query, const void* key,
+                                   const void* value, const int32_t* req_meta,
+                                   int32_t num_reqs, int32_t max_q_len, int32_t num_heads,
+                                   int32_t num_kv_heads, int32_t head_size, float scale,
+                                   int64_t q_stride, int64_t out_stride, int64_t key_stride,
+                                   int64_t value_stride, int32_t dtype, void* stream) {
+  if (int rc = check_dtype(dtype)) return rc;
+  if (num_reqs == 0) return PC_OK;
+  if (!out || !query || !key || !value || !req_meta)
+    return set_error(PC_ERR_INVALID, "pc_prefill_attn_topleft_causal: null pointer");
+  PrefillArgs a{};
+  a.out = out; a.q = query; a.k = key; a.v = value; a.req_meta = req_meta;
+  a.num_reqs = num_reqs; a.max_q_len = max_q_len; a.Hq = num_heads; a.Hkv = num_kv_heads;
+  a.D = head_size; a.scale = scale; a.q_stride = q_stride; a.out_stride = out_stride;
+  a.key_stride = key_stride; a.value_stride = value_stride;
+  return prefill_attn(a, static_cast<cudaStream_t>(stream));
+}
+
+int pc_copy_blocks(void* key_cache, void* value_cache, const int64_t* pairs, int32_t num_pairs,
+                   int64_t block_bytes, void* stream) {
+  if (num_pairs == 0) return PC_OK;
+  if (!key_cache || !value_cache || !pairs)
+    return set_error(PC_ERR_INVALID, "pc_copy_blocks: null pointer");
+  return copy_blocks(key_cache, value_cache, reinterpret_cast<const long long*>(pairs), num_pairs,
+                     block_bytes, static_cast<cudaStream_t>(stream));
+}
+
+int pc_swap_blocks(const void* src, void* dst, const int64_t* pairs, int32_t num_pairs,
+                   int64_t block_bytes, void* stream) {
+  if (num_pairs == 0) return PC_OK;
+  if (!src || !dst || !pairs) return set_error(PC_ERR_INVALID, "pc_swap_blocks: null pointer");
+  // one cudaMemcpyAsync per pair, like csrc/cache_kernels.cu:24-66 (direction inferred by UVA)
+  for (int i = 0; i < num_pairs; ++i) {
+    const char* s = static_cast<const char*>(src) + pairs[2 * i] * block_bytes;
+    char* d = static_cast<char*>(dst) + pairs[2 * i + 1] * block_bytes;
+    const cudaError_t e = cudaMemcpyAsync(d, s, (size_t)block_bytes, cudaMemcpyDefault,
+                                          static_cast<cudaStream_t>(stream));
+    if (e != cudaSuccess) return set_cuda_error("pc_swap_blocks cudaMemcpyAsync", e);
+  }
+  return PC_OK;
+}
+
+/* Debug hook (not part of the drop-in surface): per-warp globaltimer stamps of the decode
+ * kernel, [warps][4] = {kernel entry, schedule ready, last page consumed, exit}. */
+void pc_debug_set_decode_trace(void* device_buf) { pc::set_decode_trace(device_buf); }
+
+}  // extern "C"

@@ -1,0 +1,655 @@
+// Paged decode attention over (compacted) block tables with value_l2 block scoring
+// fused into the same KV read.  sm_100a.
+//
+// Replaces csrc/attention/attention_kernels.cuh:86-668 (paged_attention_v1/v2 + reduce)
+// and the extra V read of torch_cuda_sdpa.py:1518-1526 (last-block scoring).
+//
+// Design (HBM-bound; see DESIGN.md "decode kernel"):
+//   * unit of work = one PAGE = (sequence b, kv head h [, 8-q-head group hg], block):
+//     two contiguous chunks of the reference cache layout (K [D/8][BS][8], V [D][BS],
+//     vllm/attention/ops/paged_attn.py:49-62), fetched with two TMA 1-D bulk copies
+//     (cp.async.bulk -> UBLKCP) that complete on one mbarrier.
+//   * schedule: every (row, group) is cut into CHUNKS of `chunk_pages` consecutive pages
+//     (a fixed, deterministic partition); chunks are numbered in (b, h, hg, chunk) order.
+//     A WARP is a worker: its first chunk is static (id = warp x grid + cta, so
+//     neighbouring chunks land on different SMs), further chunks come from a global
+//     atomic counter.  The hand-out must be dynamic: per-SM HBM bandwidth differs by
+//     ~+-15 % across the chip (measured with the trace hook, profiles/), a static equal
+//     split loses that much at the tail.  Everything on the hand-out path is prefetched
+//     one chunk ahead -- the counter atomic, the chunk descriptor (binary search of a
+//     per-row prefix sum that every CTA derives from the device-side kv_lens), the block
+//     table entries and Q -- and the kStages-deep page ring keeps running ACROSS chunk
+//     boundaries, so a warp never drains its loads in flight.  No __syncthreads after
+//     the prologue.
+//   * the whole GQA group (<= 8 q heads) is served from ONE read of the page:
+//     S^T[16 tok x 8 heads] = K_tile(A, ldmatrix straight from the cache layout)
+//     x Q^T(B, registers) with mma.sync m16n8k16 bf16/fp32; online softmax with warp
+//     shuffles in the exp2 domain; P^T is transposed in registers (movmatrix) and
+//     O^T[D x 8 heads] += V^T_tile(A, ldmatrix straight from the cache layout) x P^T.
+//     Tensor cores are used because 2*G FMAs per KV byte exceed the SIMT fp32 budget
+//     at HBM speed for G >= 4; the legacy HMMA path is far from saturated (HBM-bound).
+//   * numerics follow attention_kernels.cuh: fp32 logits, probabilities rounded to
+//     bf16 before P.V, fp32 accumulation, final 1/(sum + 1e-6).
+//   * a group with more than one chunk is finished split-KV style: every chunk publishes
+//     (m, l, O) fp32 to its own workspace slot and the LAST one to arrive (acq_rel
+//     ticket) combines them in chunk order (deterministic), warp-parallel over heads x
+//     dims, while the warp's ring already holds the next chunk's pages.  Tickets and the
+//     chunk counter are reset in-kernel, so the op is a single launch with no memset.
+//   * scoring: when seq_lens[b] % BS == 0 the row's last block just filled; the warp
+//     that owns that page computes the per-head value_l2 partial from the V page it
+//     already has in shared memory (zero extra HBM bytes) and stores it at
+//     pool[physical block][head] of every rank's score pool (peer stores under TP).
+#include "pc_common.cuh"
+#include "score_common.cuh"
+#include <stdlib.h>
+
+#include "pc_api_internal.h"
+
+namespace pc {
+
+struct DecodeParams {
+  const __nv_bfloat16* __restrict__ q;
+  const __nv_bfloat16* __restrict__ k_cache;
+  const __nv_bfloat16* __restrict__ v_cache;
+  const int* __restrict__ block_tables;
+  const int* __restrict__ kv_lens;
+  __nv_bfloat16* __restrict__ out;
+  float* part_o;    // [chunks][8][D]
+  float* part_ml;   // [chunks][8][2]
+  int* counters;    // [0] next chunk id - launched warps, [1] warps that have exited; zero between launches
+  int* tickets;     // [B * GH] arrival counters, zero between launches
+  const int* __restrict__ seq_lens;     // nullptr: no scoring
+  ScorePool score;                      // per-block value_l2 partials, indexed by physical block
+  int B, Hq, Hkv, G, HG, GH;  // G = Hq/Hkv, HG = ceil(G/8), GH = Hkv*HG groups per row
+  long long q_stride;         // elements between sequences in q
+  long long out_stride;       // elements between sequences in out
+  long long table_stride;     // ints between rows
+  long long kv_block_stride;  // elements between blocks in k/v cache
+  float scale_log2;
+  int chunk_pages;            // pages per chunk (the last chunk of a group may be shorter)
+  unsigned long long* trace;  // debug: [warps][8]: 4 globaltimer stamps, chunks, combines, smid, membar ns (nullptr = off)
+};
+
+__device__ __forceinline__ unsigned long long gtimer() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+// ticket arrival: releases this warp's partial (after __syncwarp) and acquires the others'
+__device__ __forceinline__ int atom_add_acq_rel(int* p, int v) {
+  int old;
+  asm volatile("atom.acq_rel.gpu.global.add.s32 %0, [%1], %2;" : "=r"(old) : "l"(p), "r"(v) : "memory");
+  return old;
+}
+
+constexpr int kFifo = 8;  // chunk descriptors in flight per warp (> kStages)
+
+struct ChunkDesc {  // 32 bytes
+  int id, b, gh, blk_begin, blk_end, nblk, kv_len, pad;
+};
+
+template <int D, int BS, int kWarps, int kStages>
+struct DecodeTraits {
+  static constexpr int kPageBytes = BS * D * 2;        // K or V page of one (block, head)
+  static constexpr int kStageBytes = 2 * kPageBytes;   // K + V
+  static constexpr int kRingBytes = kWarps * kStages * kStageBytes;
+  static constexpr int kBarBytes = kWarps * kStages * 8;
+  static constexpr int kFifoBytes = kWarps * kFifo * (int)sizeof(ChunkDesc);
+  static constexpr int kThreads = kWarps * 32;
+  static size_t smem_bytes(int B) {
+    return (size_t)kRingBytes + kBarBytes + kFifoBytes + ((size_t)B + 1) * 4;
+  }
+};
+
+template <int D, int BS, int kWarps, int kStages>
+__global__ void __launch_bounds__(kWarps * 32, 1)
+paged_decode_attn_score_kernel(const DecodeParams p) {
+  using T = DecodeTraits<D, BS, kWarps, kStages>;
+  static_assert(kStages < kFifo, "descriptor fifo must outrun the page ring");
+  constexpr int KSTEPS = D / 16;   // k-steps of the QK^T contraction
+  constexpr int MT = D / 16;       // m-tiles (16 dims) of O^T
+  constexpr int TT = BS / 16;      // 16-token tiles per page
+
+  extern __shared__ __align__(1024) uint8_t smem[];
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int g = lane >> 2;  // fragment row group
+  const int t = lane & 3;   // fragment column pair
+  const int n_launched = gridDim.x * kWarps;
+  const int w = warp * gridDim.x + blockIdx.x;  // interleaved over SMs
+
+  const unsigned long long t_start = p.trace ? gtimer() : 0ull;
+  uint8_t* my_stages = smem + (size_t)warp * kStages * T::kStageBytes;
+  uint64_t* my_bars = reinterpret_cast<uint64_t*>(smem + T::kRingBytes) + warp * kStages;
+  ChunkDesc* my_fifo = reinterpret_cast<ChunkDesc*>(smem + T::kRingBytes + T::kBarBytes) + warp * kFifo;
+  int* cpre = reinterpret_cast<int*>(smem + T::kRingBytes + T::kBarBytes + T::kFifoBytes);  // [B + 1]
+
+  // chunk ids of this warp: the first one is static (= w), the rest come from a global
+  // counter, fetched only when the issue side runs out of pages (kStages pages before the
+  // consumer does), so a slow SM never commits to work ahead of time.
+  if (lane == 0) {
+#pragma unroll
+    for (int s = 0; s < kStages; ++s) mbar_init(&my_bars[s], 1);
+  }
+  // ---- schedule: chunks per (row, group) -> exclusive prefix sum (same in every CTA)
+  for (int r = threadIdx.x; r < p.B; r += T::kThreads) {
+    const int len = p.kv_lens[r];
+    cpre[r + 1] = ((len + BS - 1) / BS + p.chunk_pages - 1) / p.chunk_pages;
+    if (len == 0 && blockIdx.x == 0) {  // empty sequence: defined output (zeros)
+      __nv_bfloat16* o = p.out + (size_t)r * p.out_stride;
+      for (int i = 0; i < p.Hq * D; ++i) o[i] = __float2bfloat16(0.f);
+    }
+  }
+  __syncthreads();
+  if (warp == 0) {
+    int carry = 0;
+    for (int base = 0; base < p.B; base += 32) {
+      const int r = base + lane;
+      int n = (r < p.B) ? cpre[r + 1] : 0;
+#pragma unroll
+      for (int sh = 1; sh < 32; sh <<= 1) {
+        const int v = __shfl_up_sync(kFull, n, sh);
+        if (lane >= sh) n += v;
+      }
+      if (r < p.B) cpre[r + 1] = carry + n;
+      carry += __shfl_sync(kFull, n, 31);
+    }
+    if (lane == 0) cpre[0] = 0;
+  }
+  mbar_fence_init();
+  __syncthreads();
+
+  const int C = cpre[p.B] * p.GH;  // chunks in this launch
+
+  // ---- chunk stream: ids -> descriptors (fifo in shared memory, written by the issue side)
+  int fifo_head = 0;   // descriptors opened (issue side)
+  int fifo_tail = 0;   // descriptors retired (consume side)
+  int next_id = w;     // id the next open_chunk() will decode
+  bool first_open = true;
+  auto open_chunk = [&]() -> bool {  // all lanes, uniform
+    if (!first_open) {
+      int nid = 0;
+      if (lane == 0) nid = atomicAdd(&p.counters[0], 1);
+      next_id = __shfl_sync(kFull, nid, 0) + n_launched;
+    }
+    first_open = false;
+    if (next_id >= C) return false;
+    const int id = next_id;
+    next_id = C;  // the following id is fetched on demand (fetch_next)
+    const int key = id / p.GH;
+    int lo = 0, hi = p.B;  // largest b with cpre[b] <= key (cpre[B] > key)
+    while (hi - lo > 1) {
+      const int mid = (lo + hi) >> 1;
+      if (cpre[mid] <= key) lo = mid; else hi = mid;
+    }
+    const int cpr = cpre[lo + 1] - cpre[lo];  // chunks per group in this row
+    const int rem = id - p.GH * cpre[lo];
+    const int gh = rem / cpr;
+    const int c = rem - gh * cpr;
+    const int kv_len = __ldg(p.kv_lens + lo);
+    const int nblk = (kv_len + BS - 1) / BS;
+    if (lane == 0) {
+      ChunkDesc d;
+      d.id = id; d.b = lo; d.gh = gh; d.blk_begin = c * p.chunk_pages;
+      d.blk_end = min(nblk, d.blk_begin + p.chunk_pages); d.nblk = nblk; d.kv_len = kv_len; d.pad = 0;
+      my_fifo[fifo_head % kFifo] = d;
+    }
+    ++fifo_head;
+    __syncwarp();
+    return true;
+  };
+
+  // ---- issue side: walks pages of successive chunks, kStages ahead of the consumer
+  int is_b = 0, is_h = 0, is_blk = 0, is_end = 0;  // current issue chunk (is_blk == is_end: exhausted)
+  bool is_open = false;
+  int phys_next = 0;   // table entry of the next page to issue, loaded one page ahead
+  int pages_issued = 0, pages_consumed = 0;
+
+  auto issue_advance = [&]() {  // make (is_b, is_h, is_blk) point at the next page, if any
+    if (is_open && is_blk < is_end) {
+      phys_next = __ldg(p.block_tables + (size_t)is_b * p.table_stride + is_blk);
+      return;
+    }
+    is_open = open_chunk();
+    if (!is_open) return;
+    const ChunkDesc& d = my_fifo[(fifo_head - 1) % kFifo];
+    is_b = d.b; is_h = d.gh / p.HG; is_blk = d.blk_begin; is_end = d.blk_end;
+    phys_next = __ldg(p.block_tables + (size_t)is_b * p.table_stride + is_blk);
+  };
+  auto issue_page = [&]() {  // issue the page under the cursor into the next ring slot
+    const int slot = pages_issued % kStages;
+    if (lane == 0) {
+      uint8_t* dst = my_stages + (size_t)slot * T::kStageBytes;
+      const size_t off = ((size_t)phys_next * p.kv_block_stride) + (size_t)is_h * (D * BS);
+      mbar_expect_tx(&my_bars[slot], T::kStageBytes);
+      tma_load_1d(dst, p.k_cache + off, T::kPageBytes, &my_bars[slot]);
+      tma_load_1d(dst + T::kPageBytes, p.v_cache + off, T::kPageBytes, &my_bars[slot]);
+    }
+    ++pages_issued;
+    ++is_blk;
+  };
+
+  // Q^T as the mma B operand: b0 = Q[head g][16j + 2t..], b1 = Q[head g][16j + 8 + 2t..]
+  auto load_q = [&](uint32_t (&qf)[KSTEPS][2], int b, int gh) {
+    const int h = gh / p.HG, hg = gh - h * p.HG;
+    const int head0 = h * p.G + hg * 8;
+    const int nheads = min(8, p.G - hg * 8);
+    const bool valid = g < nheads;
+    const __nv_bfloat16* qrow = p.q + (size_t)b * p.q_stride + (size_t)(head0 + (valid ? g : 0)) * D;
+#pragma unroll
+    for (int j = 0; j < KSTEPS; ++j) {
+      qf[j][0] = valid ? __ldg(reinterpret_cast<const unsigned int*>(qrow + 16 * j + 2 * t)) : 0u;
+      qf[j][1] = valid ? __ldg(reinterpret_cast<const unsigned int*>(qrow + 16 * j + 8 + 2 * t)) : 0u;
+    }
+  };
+
+  // prologue: fill the ring
+  issue_advance();
+#pragma unroll
+  for (int s = 0; s < kStages; ++s) {
+    if (is_open) {
+      issue_page();
+      issue_advance();
+    }
+  }
+  uint32_t qf[KSTEPS][2];   // Q of the chunk being consumed
+  uint32_t qn[KSTEPS][2];   // Q prefetched for chunk `qn_id`
+  int qn_id = -1;
+  if (fifo_head > 0) {
+    load_q(qn, my_fifo[0].b, my_fifo[0].gh);
+    qn_id = my_fifo[0].id;
+  }
+  if (p.trace && lane == 0) p.trace[w * 8 + 0] = t_start, p.trace[w * 8 + 1] = gtimer();
+
+  float o[MT][4];
+  float m_run[2], l_run[2];
+  int tr_chunks = 0, tr_combines = 0;
+  unsigned long long tr_fix = 0ull;
+
+  // ================================================================ chunk loop
+  while (fifo_tail < fifo_head) {
+    const ChunkDesc d = my_fifo[fifo_tail % kFifo];
+    ++fifo_tail;
+    ++tr_chunks;
+    const int b = d.b, nblk = d.nblk, kv_len = d.kv_len;
+    const int h = d.gh / p.HG, hg = d.gh - h * p.HG;
+    if (qn_id == d.id) {
+#pragma unroll
+      for (int j = 0; j < KSTEPS; ++j) { qf[j][0] = qn[j][0]; qf[j][1] = qn[j][1]; }
+    } else {
+      load_q(qf, b, d.gh);
+    }
+#pragma unroll
+    for (int m = 0; m < MT; ++m) o[m][0] = o[m][1] = o[m][2] = o[m][3] = 0.f;
+    m_run[0] = m_run[1] = -INFINITY;
+    l_run[0] = l_run[1] = 0.f;
+
+    for (int blk = d.blk_begin; blk < d.blk_end; ++blk) {
+      const uint32_t slot = (uint32_t)pages_consumed % kStages;
+      const uint32_t parity = ((uint32_t)pages_consumed / kStages) & 1u;
+      ++pages_consumed;
+      mbar_wait(&my_bars[slot], parity);
+
+      const uint8_t* kpage = my_stages + (size_t)slot * T::kStageBytes;
+      const uint8_t* vpage = kpage + T::kPageBytes;
+      const uint32_t kaddr = smem_u32(kpage);
+      const uint32_t vaddr = smem_u32(vpage);
+      const int page_tok0 = blk * BS;
+      const bool last_partial = (page_tok0 + BS > kv_len);
+
+      if (last_partial) {
+        // zero V columns of tokens >= kv_len so 0 * garbage cannot produce NaN
+        // (attention_kernels.cuh:455-466 does the same per element)
+        const int valid = kv_len - page_tok0;
+        __nv_bfloat16* vp = reinterpret_cast<__nv_bfloat16*>(const_cast<uint8_t*>(vpage));
+        for (int i = lane; i < D * BS; i += 32)
+          if ((i % BS) >= valid) vp[i] = __float2bfloat16(0.f);
+        fence_proxy_async();  // generic-proxy writes before a later TMA refill of this slot
+        __syncwarp();
+      }
+
+#pragma unroll
+      for (int tt = 0; tt < TT; ++tt) {
+        // ---------------- S^T = K_tile x Q^T
+        float s0[4] = {0.f, 0.f, 0.f, 0.f}, s1[4] = {0.f, 0.f, 0.f, 0.f};
+        {
+          // ldmatrix.x4 row address: matrix mi = lane/8 -> (token half = mi&1, chunk = 2j + mi>>1)
+          const int mi = lane >> 3, r = lane & 7;
+          const uint32_t base = kaddr + (uint32_t)(((mi >> 1) * BS + tt * 16 + (mi & 1) * 8 + r) * 16);
+#pragma unroll
+          for (int j = 0; j < KSTEPS; ++j) {
+            uint32_t a[4];
+            ldmatrix_x4(a, base + (uint32_t)(2 * j * BS * 16));
+            if (j & 1) mma_bf16_16816(s1, a, qf[j][0], qf[j][1]);
+            else       mma_bf16_16816(s0, a, qf[j][0], qf[j][1]);
+          }
+        }
+        // s[0]=(tok g, head 2t) s[1]=(tok g, head 2t+1) s[2]=(tok g+8, head 2t) s[3]=(tok g+8, 2t+1)
+        float x0 = (s0[0] + s1[0]) * p.scale_log2, x1 = (s0[1] + s1[1]) * p.scale_log2;
+        float x2 = (s0[2] + s1[2]) * p.scale_log2, x3 = (s0[3] + s1[3]) * p.scale_log2;
+        if (last_partial) {
+          const int tok = page_tok0 + tt * 16 + g;
+          if (tok >= kv_len) { x0 = -INFINITY; x1 = -INFINITY; }
+          if (tok + 8 >= kv_len) { x2 = -INFINITY; x3 = -INFINITY; }
+        }
+        // ---------------- online softmax (per head = per column; rows live in lanes with equal t)
+        float mx0 = fmaxf(x0, x2), mx1 = fmaxf(x1, x3);
+#pragma unroll
+        for (int sh = 4; sh <= 16; sh <<= 1) {
+          mx0 = fmaxf(mx0, __shfl_xor_sync(kFull, mx0, sh));
+          mx1 = fmaxf(mx1, __shfl_xor_sync(kFull, mx1, sh));
+        }
+        const float mn0 = fmaxf(m_run[0], mx0), mn1 = fmaxf(m_run[1], mx1);
+        const float al0 = fast_exp2(m_run[0] - mn0), al1 = fast_exp2(m_run[1] - mn1);
+        m_run[0] = mn0; m_run[1] = mn1;
+        const float p0 = fast_exp2(x0 - mn0), p1 = fast_exp2(x1 - mn1);
+        const float p2 = fast_exp2(x2 - mn0), p3 = fast_exp2(x3 - mn1);
+        l_run[0] = l_run[0] * al0 + (p0 + p2);
+        l_run[1] = l_run[1] * al1 + (p1 + p3);
+        if (__any_sync(kFull, (al0 != 1.f) || (al1 != 1.f))) {
+#pragma unroll
+          for (int m = 0; m < MT; ++m) { o[m][0] *= al0; o[m][1] *= al1; o[m][2] *= al0; o[m][3] *= al1; }
+        }
+        // ---------------- P^T as the B operand: transpose the two 8x8 (tok x head) tiles
+        const uint32_t pb0 = movmatrix_trans(pack_bf16x2(p0, p1));  // tokens 0..7
+        const uint32_t pb1 = movmatrix_trans(pack_bf16x2(p2, p3));  // tokens 8..15
+        // ---------------- O^T += V^T_tile x P^T
+        {
+          // matrix mi -> (dim half = mi&1, token half = mi>>1); row r = dim within the half
+          const int mi = lane >> 3, r = lane & 7;
+          const uint32_t base = vaddr + (uint32_t)((((mi & 1) * 8 + r) * BS + tt * 16 + (mi >> 1) * 8) * 2);
+#pragma unroll
+          for (int m = 0; m < MT; ++m) {
+            uint32_t a[4];
+            ldmatrix_x4(a, base + (uint32_t)(m * 16 * BS * 2));
+            mma_bf16_16816(o[m], a, pb0, pb1);
+          }
+        }
+      }
+
+      // ---------------- fused value_l2 score of the row's last (just filled) block
+      if (p.seq_lens != nullptr && blk == nblk - 1 && hg == 0 && (kv_len % BS) == 0 &&
+          (__ldg(p.seq_lens + b) % BS) == 0) {
+        const __nv_bfloat16* vp = reinterpret_cast<const __nv_bfloat16*>(vpage);
+        const float sc = warp_value_l2_head_score<D, BS>(
+            [&](int tok, int dd) { return __bfloat162float(vp[dd * BS + tok]); });
+        if (lane == 0)
+          score_store(p.score, __ldg(p.block_tables + (size_t)b * p.table_stride + blk), h, sc);
+      }
+
+      // ---------------- refill this slot (the issue side may open the next chunk here)
+      __syncwarp();
+      if (is_open) {
+        const int opened = fifo_head;
+        issue_page();
+        issue_advance();
+        if (fifo_head != opened) {  // a new chunk was opened: prefetch its Q
+          const ChunkDesc& nd = my_fifo[(fifo_head - 1) % kFifo];
+          load_q(qn, nd.b, nd.gh);
+          qn_id = nd.id;
+        }
+      }
+    }
+    if (p.trace && lane == 0) p.trace[w * 8 + 2] = gtimer();
+
+    // ---------------- chunk end
+    const int head0 = h * p.G + hg * 8;       // first q head of this group
+    const int nheads = min(8, p.G - hg * 8);  // valid q heads in the group
+    // l over the 8 row-lanes of each column
+#pragma unroll
+    for (int sh = 4; sh <= 16; sh <<= 1) {
+      l_run[0] += __shfl_xor_sync(kFull, l_run[0], sh);
+      l_run[1] += __shfl_xor_sync(kFull, l_run[1], sh);
+    }
+    const int n_chunks = (nblk + p.chunk_pages - 1) / p.chunk_pages;  // chunks of this group
+    // o[m][0]=(dim 16m+g, head 2t) [1]=(dim 16m+g, head 2t+1) [2]=(dim 16m+g+8, 2t) [3]=(.., 2t+1)
+    if (n_chunks == 1) {  // the whole group was this chunk: final result
+      const float inv0 = 1.f / (l_run[0] + 1e-6f), inv1 = 1.f / (l_run[1] + 1e-6f);
+      __nv_bfloat16* ob = p.out + (size_t)b * p.out_stride + (size_t)head0 * D;
+#pragma unroll
+      for (int m = 0; m < MT; ++m) {
+        if (2 * t < nheads) {
+          ob[(size_t)(2 * t) * D + 16 * m + g] = __float2bfloat16_rn(o[m][0] * inv0);
+          ob[(size_t)(2 * t) * D + 16 * m + g + 8] = __float2bfloat16_rn(o[m][2] * inv0);
+        }
+        if (2 * t + 1 < nheads) {
+          ob[(size_t)(2 * t + 1) * D + 16 * m + g] = __float2bfloat16_rn(o[m][1] * inv1);
+          ob[(size_t)(2 * t + 1) * D + 16 * m + g + 8] = __float2bfloat16_rn(o[m][3] * inv1);
+        }
+      }
+      continue;
+    }
+    // ---- split group: publish the partial, last arriver combines in chunk order
+    {
+      float* po = p.part_o + (size_t)d.id * 8 * D;
+      float* pml = p.part_ml + (size_t)d.id * 16;
+#pragma unroll
+      for (int m = 0; m < MT; ++m) {
+        po[(size_t)(2 * t) * D + 16 * m + g] = o[m][0];
+        po[(size_t)(2 * t) * D + 16 * m + g + 8] = o[m][2];
+        po[(size_t)(2 * t + 1) * D + 16 * m + g] = o[m][1];
+        po[(size_t)(2 * t + 1) * D + 16 * m + g + 8] = o[m][3];
+      }
+      if (g == 0) {
+        pml[(2 * t) * 2 + 0] = m_run[0];
+        pml[(2 * t) * 2 + 1] = l_run[0];
+        pml[(2 * t + 1) * 2 + 0] = m_run[1];
+        pml[(2 * t + 1) * 2 + 1] = l_run[1];
+      }
+    }
+    __syncwarp();
+    int* tk = p.tickets + (size_t)b * p.GH + d.gh;
+    int ticket = 0;
+    const unsigned long long tf0 = p.trace ? gtimer() : 0ull;
+    if (lane == 0) ticket = atom_add_acq_rel(tk, 1);
+    ticket = __shfl_sync(kFull, ticket, 0);
+    if (p.trace) tr_fix += gtimer() - tf0;
+    if (ticket != n_chunks - 1) continue;
+    ++tr_combines;
+    if (lane == 0) *tk = 0;  // leave the workspace clean for the next launch
+    {
+      const int id0 = d.id - d.blk_begin / p.chunk_pages;  // first chunk of the group
+      const int hh = lane >> 2;             // head of the group this lane combines
+      const int d0 = (lane & 3) * (D / 4);  // its D/4 contiguous dims
+      // pass 1: group max per head (lanes sharing a head read the same words: broadcast)
+      float M = -INFINITY;
+#pragma unroll 8
+      for (int s = 0; s < n_chunks; ++s)
+        M = fmaxf(M, __ldcg(p.part_ml + (size_t)(id0 + s) * 16 + hh * 2));
+      // pass 2: weighted sum, 4 chunks (32 independent 16-byte loads per lane) in flight
+      float L = 0.f;
+      float acc[D / 4];
+#pragma unroll
+      for (int i = 0; i < D / 4; ++i) acc[i] = 0.f;
+      constexpr int CU = 4;
+      for (int s0 = 0; s0 < n_chunks; s0 += CU) {
+        float4 v[CU][D / 16];
+        float ms[CU], ls[CU];
+#pragma unroll
+        for (int u = 0; u < CU; ++u) {
+          const int s = min(s0 + u, n_chunks - 1);
+          ms[u] = __ldcg(p.part_ml + (size_t)(id0 + s) * 16 + hh * 2);
+          ls[u] = __ldcg(p.part_ml + (size_t)(id0 + s) * 16 + hh * 2 + 1);
+          const float4* src = reinterpret_cast<const float4*>(p.part_o + ((size_t)(id0 + s) * 8 + hh) * D + d0);
+#pragma unroll
+          for (int i = 0; i < D / 16; ++i) v[u][i] = __ldcg(src + i);
+        }
+#pragma unroll
+        for (int u = 0; u < CU; ++u) {
+          const float wgt = (s0 + u < n_chunks) ? fast_exp2(ms[u] - M) : 0.f;
+          L += wgt * ls[u];
+#pragma unroll
+          for (int i = 0; i < D / 16; ++i) {
+            acc[4 * i + 0] += wgt * v[u][i].x;
+            acc[4 * i + 1] += wgt * v[u][i].y;
+            acc[4 * i + 2] += wgt * v[u][i].z;
+            acc[4 * i + 3] += wgt * v[u][i].w;
+          }
+        }
+      }
+      if (hh < nheads) {
+        const float inv = 1.f / (L + 1e-6f);
+        uint4* dst = reinterpret_cast<uint4*>(p.out + (size_t)b * p.out_stride + (size_t)(head0 + hh) * D + d0);
+#pragma unroll
+        for (int i = 0; i < D / 32; ++i) {
+          uint4 v;
+          v.x = pack_bf16x2(acc[8 * i + 0] * inv, acc[8 * i + 1] * inv);
+          v.y = pack_bf16x2(acc[8 * i + 2] * inv, acc[8 * i + 3] * inv);
+          v.z = pack_bf16x2(acc[8 * i + 4] * inv, acc[8 * i + 5] * inv);
+          v.w = pack_bf16x2(acc[8 * i + 6] * inv, acc[8 * i + 7] * inv);
+          dst[i] = v;
+        }
+      }
+    }
+  }
+  // ---- exit: the last warp of the launch re-arms the chunk counter
+  if (lane == 0) {
+    const int old = atom_add_acq_rel(&p.counters[1], 1);
+    if (old == n_launched - 1) {
+      p.counters[0] = 0;
+      p.counters[1] = 0;
+    }
+    if (p.trace) {
+      p.trace[w * 8 + 3] = gtimer();
+      p.trace[w * 8 + 4] = tr_chunks;
+      p.trace[w * 8 + 5] = tr_combines;
+      unsigned int smid;
+      asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+      p.trace[w * 8 + 6] = smid;
+      p.trace[w * 8 + 7] = tr_fix;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------- host
+// Workspace layout (fixed offsets, so the zeroed regions stay zero whatever the batch):
+//   [counters: 2 i32, 256 B][tickets: kMaxGroups i32][part_ml: chunks*16 f32][part_o: chunks*8*D f32]
+constexpr int kMaxGroups = 1 << 20;
+constexpr size_t kOffTickets = 256;
+constexpr size_t kOffPartials = kOffTickets + (size_t)kMaxGroups * sizeof(int);
+static unsigned long long* g_decode_trace = nullptr;
+void set_decode_trace(void* buf) { g_decode_trace = static_cast<unsigned long long*>(buf); }
+
+struct DecodePlan {
+  int chunk_pages;
+  long long max_chunks;
+  size_t off_part_o, bytes;
+};
+
+// Chunks per group.  Measured on B200 (profiles/r01_decode_policy_sweep.txt, trace hook):
+//  * every chunk of a SPLIT group costs an fp32 partial (8 heads x D, written and re-read),
+//    a release fence + ticket (2-5 us of warp time under load) and its share of a
+//    combine, and the fix-up of a warp's last chunk is exposed at the end of the launch
+//    (~10 us): a group is split only when that buys something;
+//  * small launches (few groups) need chunks ~ half the warps of the chip to pull
+//    enough bytes in flight;
+//  * big launches need a dynamic tail: per-SM HBM bandwidth differs by ~+-15 %, so with
+//    >= 64 pages per warp the groups are cut into >= 64-page chunks, ~4 per warp.
+static int env_int(const char* name, int dflt) {
+  const char* v = getenv(name);
+  return (v && *v) ? atoi(v) : dflt;
+}
+
+static DecodePlan plan_decode(int B, int Hq, int Hkv, int D, int BS, int max_kv_len, int num_sms, int warps) {
+  DecodePlan pl;
+  const int G = Hq / Hkv;
+  const int HG = (G + 7) / 8;
+  const long long groups = (long long)B * Hkv * HG;
+  const long long max_blocks = max_kv_len > 0 ? (max_kv_len + BS - 1) / BS : 1;
+  const long long pages_max = groups * max_blocks;
+  const long long workers = (long long)num_sms * warps;
+  static const int force = env_int("PC_DECODE_CHUNK_PAGES", 0);
+  // (a) parallelism: about workers/2 chunks, never shorter than 8 pages
+  long long n = (workers / 2 + groups / 2) / groups;
+  if (n > max_blocks / 8) n = max_blocks / 8;
+  if (n < 1) n = 1;
+  // (b) balance for big launches
+  if (pages_max / workers >= 64) {
+    long long nb = (4 * workers + groups - 1) / groups;
+    if (nb > max_blocks / 64) nb = max_blocks / 64;
+    if (nb > n) n = nb;
+  }
+  long long cp = (max_blocks + n - 1) / n;
+  if (force > 0) cp = force;
+  if (cp > max_blocks) cp = max_blocks;
+  if (cp < 1) cp = 1;
+  pl.chunk_pages = (int)cp;
+  pl.max_chunks = groups * ((max_blocks + cp - 1) / cp);
+  pl.off_part_o = kOffPartials + ((size_t)pl.max_chunks * 16 * sizeof(float) + 255) / 256 * 256;
+  pl.bytes = pl.off_part_o + (size_t)pl.max_chunks * 8 * D * sizeof(float);
+  return pl;
+}
+
+// warps per CTA for each (D, BS): the ring (warps x stages x (K+V page)) must fit 227 KB
+static int decode_warps(int D, int BS) { return (D == 128 && BS == 32) ? 4 : 8; }
+
+size_t decode_workspace_bytes(int B, int Hq, int Hkv, int D, int BS, int max_kv_len, int num_sms) {
+  if (Hkv <= 0 || Hq < Hkv) return 0;
+  return plan_decode(B, Hq, Hkv, D, BS, max_kv_len, num_sms, decode_warps(D, BS)).bytes;
+}
+
+template <int D, int BS, int kWarps, int kStages>
+static int launch_decode(const DecodeParams& p, int num_sms, long long max_chunks, cudaStream_t stream) {
+  using T = DecodeTraits<D, BS, kWarps, kStages>;
+  auto kern = paged_decode_attn_score_kernel<D, BS, kWarps, kStages>;
+  const size_t smem = T::smem_bytes(p.B);
+  if (smem > 227 * 1024) return set_error(PC_ERR_INVALID, "decode: batch too large for the in-kernel schedule");
+  static size_t smem_set[64] = {0};  // per device: largest dynamic smem opted in so far
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 0 || dev >= 64 || smem_set[dev] < smem) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return set_cuda_error("cudaFuncSetAttribute(decode)", e);
+    if (dev >= 0 && dev < 64) smem_set[dev] = smem;
+  }
+  long long ctas = max_chunks < num_sms ? max_chunks : num_sms;  // spread over SMs first
+  if (ctas < 1) ctas = 1;
+  kern<<<(int)ctas, T::kThreads, smem, stream>>>(p);
+  return check_launch("paged_decode_attn_score_kernel");
+}
+
+int paged_decode_attn_score(const DecodeArgs& a, cudaStream_t stream) {
+  if (a.B <= 0) return 0;
+  if (a.Hkv <= 0 || a.Hq % a.Hkv != 0)
+    return set_error(PC_ERR_INVALID, "num_heads must be a multiple of num_kv_heads");
+  if ((a.out_stride % 8) != 0 || (reinterpret_cast<uintptr_t>(a.out) & 15) != 0 ||
+      (a.q_stride % 2) != 0 || (reinterpret_cast<uintptr_t>(a.q) & 3) != 0)
+    return set_error(PC_ERR_INVALID, "decode: out rows must be 16-byte aligned, query rows 4-byte aligned");
+  const int num_sms = device_sm_count();
+  if (num_sms <= 0) return PC_ERR_CUDA;
+  const DecodePlan pl = plan_decode(a.B, a.Hq, a.Hkv, a.D, a.BS, a.max_kv_len, num_sms, decode_warps(a.D, a.BS));
+  if (a.workspace_bytes < pl.bytes)
+    return set_error(PC_ERR_INVALID, "decode workspace too small (see pc_paged_decode_workspace_bytes)");
+  uint8_t* ws = static_cast<uint8_t*>(a.workspace);
+  DecodeParams p;
+  p.q = static_cast<const __nv_bfloat16*>(a.q);
+  p.k_cache = static_cast<const __nv_bfloat16*>(a.k_cache);
+  p.v_cache = static_cast<const __nv_bfloat16*>(a.v_cache);
+  p.block_tables = a.block_tables;
+  p.kv_lens = a.kv_lens;
+  p.out = static_cast<__nv_bfloat16*>(a.out);
+  p.counters = reinterpret_cast<int*>(ws);
+  p.tickets = reinterpret_cast<int*>(ws + kOffTickets);
+  p.part_ml = reinterpret_cast<float*>(ws + kOffPartials);
+  p.part_o = reinterpret_cast<float*>(ws + pl.off_part_o);
+  p.seq_lens = a.score.n_pools > 0 ? a.seq_lens : nullptr;
+  p.score = a.score;
+  p.B = a.B; p.Hq = a.Hq; p.Hkv = a.Hkv; p.G = a.Hq / a.Hkv; p.HG = (p.G + 7) / 8; p.GH = a.Hkv * p.HG;
+  if ((long long)p.B * p.GH > kMaxGroups)
+    return set_error(PC_ERR_INVALID, "decode: batch x kv heads exceeds the ticket table (1M groups)");
+  p.q_stride = a.q_stride; p.out_stride = a.out_stride;
+  p.table_stride = a.table_stride; p.kv_block_stride = a.kv_block_stride;
+  p.scale_log2 = a.scale * 1.4426950408889634f;
+  p.chunk_pages = pl.chunk_pages;
+  p.trace = g_decode_trace;
+
+  if (a.D == 128 && a.BS == 16) return launch_decode<128, 16, 8, 3>(p, num_sms, pl.max_chunks, stream);
+  if (a.D == 128 && a.BS == 32) return launch_decode<128, 32, 4, 3>(p, num_sms, pl.max_chunks, stream);
+  if (a.D == 64 && a.BS == 16) return launch_decode<64, 16, 8, 6>(p, num_sms, pl.max_chunks, stream);
+  if (a.D == 64 && a.BS == 32) return launch_decode<64, 32, 8, 3>(p, num_sms, pl.max_chunks, stream);
+  // mirrors TORCH_CHECK(false, "Unsupported head size / block size") in
+  // csrc/attention/paged_attention_v1.cu:108-110,160-162
+  return set_error(PC_ERR_UNSUPPORTED, "Unsupported head size / block size (supported: head 64|128, block 16|32)");
+}
+
+}  // namespace pc

@@ -1,0 +1,138 @@
+// On-device decode eviction: trigger test, victim selection (argmin of value_l2 block
+// scores, lowest index wins ties), block-table compaction, kv-length update and
+// score-row compaction -- one CTA per batch row, no host round trip.
+//
+// Replaces the per-layer Python loops of
+//   _prune_decode_reqs_streamingLLM (vllm/attention/backends/torch_cuda_sdpa.py:1375-1433)
+//   _prune_decode_reqs_topk         (:1478-1560, argmin :1536-1541)
+//   _create_updated_block_tables    (:1562-1586; semantics of torch_cuda_sdpa_v1.py /
+//                                    HEAD row 0)
+//   BlockL2NormManager.get_updated_block_tables(is_rmv_l2norm=True)
+//                                   (vllm/attention/block_l2norm_manager.py:95-106)
+//   kv-len adjust                   (vllm/worker/model_runner.py:540-543)
+// Integer / fp32-compare domain: bit-exact against oracle/policy.py.
+#include <float.h>
+
+#include "pc_common.cuh"
+#include "pc_api_internal.h"
+
+namespace pc {
+
+struct EvictParams {
+  const int* __restrict__ block_tables;
+  long long table_stride;
+  const int* __restrict__ n_blocks;
+  const int* __restrict__ seq_lens;
+  const int* __restrict__ kv_lens;
+  pc_evict_policy pol;
+  ScorePool score;
+  int* out_tables;
+  long long out_stride;
+  int* out_kv_lens;
+  int* out_victim;
+  int pre_adjusted;
+};
+
+constexpr int kEvictThreads = 256;
+
+__device__ __forceinline__ bool decode_trigger(const pc_evict_policy& pol, int seq_len, int n) {
+  const int bs = pol.block_size;
+  if (pol.prune_type == 0)  // budget: torch_cuda_sdpa.py:1390-1407,1491-1500
+    return seq_len > pol.cache_budget && (seq_len % bs) == 0;
+  // percentage / evict_freq: torch_cuda_sdpa.py:1310 (commented) + page_evict_kv_util_bak.py:69
+  return (seq_len % (bs * pol.evict_freq)) == 0 &&
+         n * bs > (pol.initial_blocks + pol.num_block_merge) * bs;
+}
+
+__global__ void __launch_bounds__(kEvictThreads) evict_select_compact_kernel(const EvictParams p) {
+  __shared__ float best_v[kEvictThreads / 32];
+  __shared__ int best_i[kEvictThreads / 32];
+  __shared__ int victim_s;
+  const int b = blockIdx.x;
+  const int tid = threadIdx.x;
+  const int n = p.n_blocks[b];
+  const int seq_len = p.seq_lens[b];
+  const int* row = p.block_tables + (size_t)b * p.table_stride;
+  int* orow = p.out_tables + (size_t)b * p.out_stride;
+  const bool trig = (n >= 3) && decode_trigger(p.pol, seq_len, n);
+
+  int victim = -1;
+  if (trig) {
+    if (p.pol.decode_method == 0) {
+      victim = 1;  // streamingLLM: always the block after the sink (torch_cuda_sdpa.py:1404-1405)
+    } else {
+      // candidates [1, hi): global -> n-1 ; local -> min(1 + topk, n-1)   (:1528-1534)
+      const int lo = 1;
+      int hi = n - 1;
+      if (p.pol.topk_blocks > 0) hi = min(hi, 1 + p.pol.topk_blocks);
+      const float* pool = p.score.pools[p.score.local];
+      const int HT = p.score.heads_total;
+      float bv = FLT_MAX;
+      int bi = 0x7fffffff;
+      for (int i = lo + tid; i < hi; i += kEvictThreads) {
+        const float* srow = pool + (size_t)row[i] * HT;  // scores live with the physical block
+        float acc = 0.f;  // heads ascending, then / Hkv: oracle/scoring.py combine_heads
+        for (int hh = 0; hh < HT; ++hh) acc = __fadd_rn(acc, __ldcg(srow + hh));
+        const float sc = __fdiv_rn(acc, (float)HT);
+        if (bi == 0x7fffffff || sc < bv) { bv = sc; bi = i; }  // strict <: lowest index wins
+      }
+      // (value, index) min-reduction; ties -> lower index
+#pragma unroll
+      for (int sh = 16; sh >= 1; sh >>= 1) {
+        const float ov = __shfl_xor_sync(kFull, bv, sh);
+        const int oi = __shfl_xor_sync(kFull, bi, sh);
+        if (oi != 0x7fffffff && (bi == 0x7fffffff || ov < bv || (ov == bv && oi < bi))) { bv = ov; bi = oi; }
+      }
+      if ((tid & 31) == 0) { best_v[tid >> 5] = bv; best_i[tid >> 5] = bi; }
+      __syncthreads();
+      if (tid == 0) {
+        for (int w = 1; w < kEvictThreads / 32; ++w) {
+          const float ov = best_v[w];
+          const int oi = best_i[w];
+          if (oi != 0x7fffffff && (bi == 0x7fffffff || ov < bv || (ov == bv && oi < bi))) { bv = ov; bi = oi; }
+        }
+        victim_s = (bi == 0x7fffffff) ? lo : bi;
+      }
+      __syncthreads();
+      victim = victim_s;
+    }
+  }
+
+  // ---- table compaction: delete column `victim`, shift left, 0-pad
+  const int n_after = n - (victim >= 0 ? 1 : 0);
+  for (int i = tid; i < p.out_stride; i += kEvictThreads) {
+    int v = 0;
+    if (i < n_after) v = (victim >= 0 && i >= victim) ? row[i + 1] : row[i];
+    orow[i] = v;
+  }
+  if (tid == 0) {
+    p.out_victim[b] = victim;
+    if (p.out_kv_lens)
+      p.out_kv_lens[b] = p.kv_lens[b] - ((victim >= 0 && !p.pre_adjusted) ? p.pol.block_size : 0);
+  }
+
+}
+
+int evict_select_compact(const EvictSelectArgs& a, cudaStream_t stream) {
+  if (a.B <= 0) return 0;
+  if (a.pol.block_size <= 0) return set_error(PC_ERR_INVALID, "policy.block_size must be > 0");
+  if (a.pol.decode_method != 0 && a.score.n_pools <= 0)
+    return set_error(PC_ERR_INVALID, "value_l2 eviction needs a score pool");
+  EvictParams p;
+  p.block_tables = a.block_tables;
+  p.table_stride = a.table_stride;
+  p.n_blocks = a.n_blocks;
+  p.seq_lens = a.seq_lens;
+  p.kv_lens = a.kv_lens;
+  p.pol = a.pol;
+  p.score = a.score;
+  p.out_tables = a.out_tables;
+  p.out_stride = a.out_stride;
+  p.out_kv_lens = a.out_kv_lens;
+  p.out_victim = a.out_victim;
+  p.pre_adjusted = a.pre_adjusted;
+  evict_select_compact_kernel<<<a.B, kEvictThreads, 0, stream>>>(p);
+  return check_launch("evict_select_compact_kernel");
+}
+
+}  // namespace pc

@@ -1,0 +1,105 @@
+// Internal (C++) side of the C ABI: argument structs + error plumbing shared by the
+// kernel translation units and c_api.cu.
+#pragma once
+#include <cuda_runtime.h>
+#include <stddef.h>
+#include <stdint.h>
+
+#include "../../include/pagedevict_b200.h"
+
+namespace pc {
+
+// Device-side view of pc_score_pool (passed by value in kernel params).
+struct ScorePool {
+  float* pools[PC_MAX_PEERS];
+  int n_pools;      // 0 = scoring off
+  int local;
+  int heads_total;
+  int head_offset;
+};
+inline ScorePool make_score_pool(const pc_score_pool* s) {
+  ScorePool sp;
+  for (int i = 0; i < PC_MAX_PEERS; ++i) sp.pools[i] = nullptr;
+  sp.n_pools = 0; sp.local = 0; sp.heads_total = 0; sp.head_offset = 0;
+  if (s != nullptr) {
+    for (int i = 0; i < s->n_pools && i < PC_MAX_PEERS; ++i) sp.pools[i] = s->pools[i];
+    sp.n_pools = s->n_pools; sp.local = s->local; sp.heads_total = s->heads_total;
+    sp.head_offset = s->head_offset;
+  }
+  return sp;
+}
+int check_score_pool(const pc_score_pool* s, int num_kv_heads, const char* who);
+
+int set_error(int code, const char* msg);
+int set_cuda_error(const char* what, cudaError_t e);
+int check_launch(const char* kernel_name);
+int device_sm_count();
+
+struct DecodeArgs {
+  void* out;
+  const void* q;
+  const void* k_cache;
+  const void* v_cache;
+  const int* block_tables;
+  long long table_stride;
+  const int* kv_lens;
+  int B, Hq, Hkv, D, BS, max_kv_len;
+  float scale;
+  long long q_stride, out_stride, kv_block_stride;
+  const int* seq_lens;
+  ScorePool score;
+  void* workspace;
+  size_t workspace_bytes;
+};
+size_t decode_workspace_bytes(int B, int Hq, int Hkv, int D, int BS, int max_kv_len, int num_sms);
+int paged_decode_attn_score(const DecodeArgs& a, cudaStream_t stream);
+void set_decode_trace(void* buf);  // debug: per-warp globaltimer stamps, nullptr = off
+
+struct CacheWriteArgs {
+  const void* key;
+  const void* value;
+  void* k_cache;
+  void* v_cache;
+  const long long* slot_mapping;
+  const int* req_meta;      // [R][5] or nullptr (plain reshape_and_cache)
+  const int* tile_offsets;  // [R+1] or nullptr
+  int num_reqs, total_tiles, num_tokens;
+  int Hkv, D, BS;
+  long long key_stride, value_stride, kv_block_stride;
+  ScorePool score;
+};
+int cache_write(const CacheWriteArgs& a, cudaStream_t stream);
+
+struct EvictSelectArgs {
+  const int* block_tables;
+  long long table_stride;
+  const int* n_blocks;
+  const int* seq_lens;
+  const int* kv_lens;
+  int B;
+  pc_evict_policy pol;
+  ScorePool score;
+  int* out_tables;
+  long long out_stride;
+  int* out_kv_lens;
+  int* out_victim;
+  int pre_adjusted;
+};
+int evict_select_compact(const EvictSelectArgs& a, cudaStream_t stream);
+
+struct PrefillArgs {
+  void* out;
+  const void* q;
+  const void* k;
+  const void* v;
+  const int* req_meta;  // [R][6]
+  int num_reqs, max_q_len, Hq, Hkv, D;
+  float scale;
+  long long q_stride, out_stride, key_stride, value_stride;
+};
+int prefill_attn(const PrefillArgs& a, cudaStream_t stream);
+
+int copy_blocks(void* k_cache, void* v_cache, const long long* pairs, int num_pairs,
+                long long block_bytes, cudaStream_t stream);
+
+}  // namespace pc

@@ -1,0 +1,234 @@
+"""Step driver for the paged-eviction hot path: the callers either side of
+`TorchCUDASDPABackendImpl.forward`, reduced to what the path needs.
+
+One `step()` = the slice of `LLMEngine.step` (vllm/engine/llm_engine.py:1280-1420) that
+touches this path:
+  scheduler   : prefill XOR decode batch, block tables + seq_kv_lens per sequence
+                (vllm/core/scheduler.py:1300-1432; chunked prefill asserted off :1306-1307)
+  model runner: context/seq/query lens and the decode-time `seq_kv_lens -= block_size`
+                adjust (vllm/worker/model_runner.py:500-546), metadata builder
+  model       : num_layers x impl.forward(q, k, v, kv_cache[layer], metadata)
+  feedback    : layer 0's get_rmv_block_idx() -> free_prunned_blocks
+                (model_runner.py:1797-1802, llm_engine.py:1179-1193, scheduler.py:1879-1890)
+The model's linear layers / sampler are NOT here: q/k/v come from the caller (tests and
+bench.py feed seeded synthetic activations), which is what the reference's attention
+backend sees too.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass, field
+from typing import Callable, Dict, List, Optional, Tuple
+
+import torch
+
+from .backend import (TorchCUDASDPABackend, TorchCUDASDPABackendImpl, TorchCUDASDPAMetadata,
+                      TorchCUDASDPAMetadataBuilder)
+from .block_manager import SelfAttnBlockSpaceManager
+from .config import CacheConfig
+from .policy import decode_trigger
+
+
+@dataclass
+class _Seq:
+    request_id: str
+    seq_id: int
+    prompt_len: int
+    seq_len: int = 0          # logical tokens so far (prompt + generated)
+    computed: int = 0         # tokens whose KV has been computed
+    prefilled: bool = False
+
+
+@dataclass
+class InterDataForSeqGroup:
+    """The attributes TorchCUDASDPAMetadataBuilder._add_seq_group reads from
+    ModelInputForGPUBuilder.InterDataForSeqGroup (model_runner.py:255-300)."""
+    request_id: str
+    is_prompt: bool
+    seq_ids: List[int]
+    block_tables: Optional[Dict[int, List[int]]]
+    input_tokens: List[List[int]]
+    orig_seq_lens: List[int]
+    seq_lens: List[int]
+    query_lens: List[int]
+    context_lens: List[int]
+    seq_kv_lens: Optional[Dict[int, int]] = None
+    prefix_cache_hit: bool = False
+    curr_sliding_window_blocks: List[int] = field(default_factory=lambda: [0])
+
+
+class _Runner:
+    def __init__(self, device, cache_config, pin_memory=True):
+        self.device, self.cache_config, self.pin_memory = device, cache_config, pin_memory
+
+
+class _InputBuilder:
+    def __init__(self, runner, block_size, inter_data_list):
+        self.runner = runner
+        self.sliding_window = None
+        self.block_size = block_size
+        self.chunked_prefill_enabled = False
+        self.inter_data_list = inter_data_list
+
+
+@dataclass
+class StepOutput:
+    is_prompt: bool
+    request_ids: List[str]
+    seq_lens: List[int]
+    seq_kv_lens: List[int]
+    block_tables: List[List[int]]
+    metadata: TorchCUDASDPAMetadata
+    outputs: List[torch.Tensor]                       # per layer [T, Hq*D]
+    rmv: Dict[int, Tuple[str, int]]                   # layer-0 decision, applied to the host tables
+
+
+QKVFn = Callable[[int, int], Tuple[torch.Tensor, torch.Tensor, torch.Tensor]]
+
+
+class PagedEvictEngine:
+    def __init__(self, num_layers: int, num_heads: int, num_kv_heads: int, head_size: int,
+                 cache_config: CacheConfig, num_gpu_blocks: int, device="cuda:0",
+                 dtype=torch.bfloat16, max_num_batched_tokens: int = 1 << 30, score_exchange=None,
+                 **impl_kwargs) -> None:
+        """num_heads / num_kv_heads are the LOCAL (per tensor-parallel rank) head counts;
+        tp_rank / tp_size go to the impls through impl_kwargs; score_exchange
+        (parallel.ScoreExchange) is required for value_l2 eviction when tp_size > 1."""
+        self.device = torch.device(device)
+        self.cache_config = cache_config
+        self.block_size = cache_config.block_size
+        self.num_layers, self.num_heads = num_layers, num_heads
+        self.num_kv_heads, self.head_size = num_kv_heads, head_size
+        scale = head_size ** -0.5
+        self.score_exchange = score_exchange
+        self.impls = [TorchCUDASDPABackendImpl(num_heads, head_size, scale, num_kv_heads, None, None,
+                                               "auto", cache_config=cache_config,
+                                               prefix=f"model.layers.{i}.self_attn.attn",
+                                               score_exchange=score_exchange, **impl_kwargs)
+                      for i in range(num_layers)]
+        shape = TorchCUDASDPABackend.get_kv_cache_shape(num_gpu_blocks, self.block_size, num_kv_heads,
+                                                        head_size)
+        # CacheEngine._allocate_kv_cache: zero-filled [2, nb, bs*Hkv*D] per layer (cache_engine.py:68-88)
+        self.kv_caches = [torch.zeros(shape, dtype=dtype, device=self.device) for _ in range(num_layers)]
+        self.block_manager = SelfAttnBlockSpaceManager(self.block_size, num_gpu_blocks,
+                                                       cache_config.paged_evict_config)
+        self.max_num_batched_tokens = max_num_batched_tokens
+        self.waiting: List[_Seq] = []
+        self.running: List[_Seq] = []
+        self._next_seq_id = 0
+        self._runner = _Runner(self.device, cache_config)
+
+    # ------------------------------------------------------------------ scheduler side
+    def add_request(self, request_id: str, prompt_len: int) -> None:
+        self.waiting.append(_Seq(request_id, self._next_seq_id, prompt_len, seq_len=prompt_len))
+        self._next_seq_id += 1
+
+    def finish_request(self, request_id: str) -> None:
+        for s in [s for s in self.running if s.request_id == request_id]:
+            self.block_manager.free(s.seq_id)
+            self.running.remove(s)
+
+    def has_unfinished(self) -> bool:
+        return bool(self.waiting or self.running)
+
+    def _schedule(self) -> Tuple[bool, List[_Seq]]:
+        """Prefill batch if anything is waiting and fits, else one decode step for all
+        running sequences (scheduler.py _schedule_default)."""
+        batch: List[_Seq] = []
+        tokens = 0
+        while self.waiting:
+            s = self.waiting[0]
+            if tokens + s.prompt_len > self.max_num_batched_tokens and batch:
+                break
+            if not self.block_manager.can_allocate(s.prompt_len):
+                break
+            self.block_manager.allocate(s.seq_id, s.prompt_len)
+            batch.append(self.waiting.pop(0))
+            tokens += s.prompt_len
+        if batch:
+            return True, batch
+        if not self.block_manager.can_append_slots(len(self.running)):
+            raise RuntimeError("out of KV blocks (preemption is outside the hot path)")
+        for s in self.running:
+            s.seq_len += 1
+            self.block_manager.append_slots(s.seq_id)
+        return False, list(self.running)
+
+    # --------------------------------------------------------------- model-runner side
+    def _inter_data(self, is_prompt: bool, batch: List[_Seq]) -> List[InterDataForSeqGroup]:
+        cfg, bs = self.cache_config.paged_evict_config, self.block_size
+        out = []
+        for s in batch:
+            table = list(self.block_manager.get_block_table(s.seq_id))
+            kv_len = self.block_manager.get_seq_kv_len(s.seq_id)
+            if is_prompt:
+                ctx, q = 0, s.prompt_len
+            else:
+                ctx, q = s.seq_len - 1, 1
+                # model_runner.py:540-543 (budget) / page_evict_kv_util_bak.py:69 (percentage)
+                if cfg is not None and decode_trigger(s.seq_len, kv_len, cfg, bs):
+                    kv_len -= bs
+            out.append(InterDataForSeqGroup(
+                request_id=s.request_id, is_prompt=is_prompt, seq_ids=[s.seq_id],
+                block_tables={s.seq_id: table}, input_tokens=[[0] * q], orig_seq_lens=[s.seq_len],
+                seq_lens=[s.seq_len], query_lens=[q], context_lens=[ctx],
+                seq_kv_lens={s.seq_id: kv_len} if cfg is not None else None))
+        return out
+
+    def build_metadata(self, is_prompt: bool, batch: List[_Seq]) -> TorchCUDASDPAMetadata:
+        inter = self._inter_data(is_prompt, batch)
+        builder = TorchCUDASDPAMetadataBuilder(_InputBuilder(self._runner, self.block_size, inter))
+        seq_lens = [d.seq_lens[0] for d in inter]
+        query_lens = [d.query_lens[0] for d in inter]
+        md = builder.build(seq_lens, query_lens, -1, len(inter))
+        if self.cache_config.paged_evict_config is None:
+            md.seq_kv_lens, md.seq_kv_lens_tensor = None, None
+        return md
+
+    def _scored_blocks(self, is_prompt: bool, batch: List[_Seq]) -> List[int]:
+        """Physical ids of the blocks the layers scored during this step: every full kept
+        block of a prefilled prompt, or the last block of each row that just filled."""
+        cfg, bs = self.cache_config.paged_evict_config, self.block_size
+        if cfg is None or cfg.decode_evict_method != "value_l2":
+            return []
+        ids: List[int] = []
+        for s in batch:
+            table = self.block_manager.get_block_table(s.seq_id)
+            if is_prompt:
+                ids.extend(table[:self.block_manager.get_seq_kv_len(s.seq_id) // bs])
+            elif s.seq_len % bs == 0:
+                ids.append(table[-1])
+        return ids
+
+    # -------------------------------------------------------------------------- step
+    def step(self, qkv_fn: QKVFn, keep_outputs: bool = True,
+             out_fn: Optional[Callable[[int, torch.Tensor], None]] = None) -> StepOutput:
+        """qkv_fn(layer, num_tokens) -> (query [T,Hq*D], key [T,Hkv*D], value [T,Hkv*D])
+        on self.device.  out_fn(layer, out) receives each layer's attention output (the
+        tensor the model's o_proj would consume)."""
+        is_prompt, batch = self._schedule()
+        md = self.build_metadata(is_prompt, batch)
+        n_tok = md.num_prefill_tokens + md.num_decode_tokens
+        outs = []
+        for layer, impl in enumerate(self.impls):
+            q, k, v = qkv_fn(layer, n_tok)
+            o = impl.forward(q, k, v, self.kv_caches[layer], md)
+            if out_fn is not None:
+                out_fn(layer, o)
+            if keep_outputs:
+                outs.append(o)
+        if self.score_exchange is not None:
+            self.score_exchange.publish(self._scored_blocks(is_prompt, batch))
+        # model_runner.py:1797-1802: only layer 0's decision reaches the block manager
+        rmv = dict(self.impls[0].get_rmv_block_idx())
+        out = StepOutput(is_prompt, [s.request_id for s in batch], list(md.seq_lens),
+                         list(md.seq_kv_lens or md.seq_lens),
+                         [list(self.block_manager.get_block_table(s.seq_id)) for s in batch],
+                         md, outs, rmv)
+        by_req = {s.request_id: s for s in batch}
+        for row, (req_id, idx) in rmv.items():           # llm_engine.py:1179-1193
+            self.block_manager.free_prunned_blocks(by_req[req_id].seq_id, idx)
+        if is_prompt:
+            for s in batch:
+                s.prefilled = True
+                self.running.append(s)
+        return out

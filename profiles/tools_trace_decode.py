@@ -1,5 +1,6 @@
 import sys, json, ctypes, torch, numpy as np
-sys.path.insert(0, '/root/repo')
+import os
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from vllm_paged_compression_b200 import _lib, ops, microbench
 lib = _lib.load()
 lib.pc_debug_set_decode_trace.argtypes = [ctypes.c_void_p]

@@ -9,7 +9,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libpagedevict_b200.so")
+LIB_PATH = os.environ.get("PC_LIB_PATH") or os.path.join(_HERE, "libpagedevict_b200.so")
 ABI_VERSION = 3
 MAX_PEERS = 8
 
@@ -40,7 +40,8 @@ class PcDecodeStep(C.Structure):
                 ("out_stride", C.c_int64), ("kv_block_stride", C.c_int64),
                 ("policy", PcEvictPolicy), ("workspace", C.c_void_p), ("workspace_bytes", C.c_size_t),
                 ("dtype", C.c_int32), ("stream", C.c_void_p),
-                ("fuse_cache_write", C.c_int32), ("plan", C.c_void_p)]
+                ("fuse_cache_write", C.c_int32), ("plan", C.c_void_p),
+                ("pdl", C.c_int32)]
 
 
 _P, _I32, _I64, _F, _SZ = C.c_void_p, C.c_int32, C.c_int64, C.c_float, C.c_size_t

@@ -67,7 +67,7 @@ using namespace pc;
 // token and the device-side plan
 struct FuseExtras {
   const void* key; const void* value; const long long* slot_mapping;
-  long long key_stride, value_stride; const int* plan;
+  long long key_stride, value_stride; const int* plan; int pdl;
 };
 static int decode_attn_impl(void* out, const void* query, const void* key_cache, const void* value_cache,
                             const int32_t* block_tables, int64_t table_stride, const int32_t* kv_lens,
@@ -179,7 +179,7 @@ int pc_paged_decode_attn_score(void* out, const void* query, const void* key_cac
                                const int32_t* seq_lens, const pc_score_pool* score,
                                void* workspace, size_t workspace_bytes, int32_t dtype,
                                void* stream) {
-  const FuseExtras none = {nullptr, nullptr, nullptr, 0, 0, nullptr};
+  const FuseExtras none = {nullptr, nullptr, nullptr, 0, 0, nullptr, 0};
   return decode_attn_impl(out, query, key_cache, value_cache, block_tables, table_stride, kv_lens, batch,
                           num_heads, num_kv_heads, head_size, block_size, max_kv_len, scale, q_stride,
                           out_stride, kv_block_stride, seq_lens, score, workspace, workspace_bytes, dtype,
@@ -216,7 +216,7 @@ static int decode_attn_impl(void* out, const void* query, const void* key_cache,
   a.seq_lens = seq_lens; a.score = make_score_pool(score);
   a.workspace = workspace; a.workspace_bytes = workspace_bytes;
   a.new_k = g_fuse.key; a.new_v = g_fuse.value; a.slot_mapping = g_fuse.slot_mapping;
-  a.new_k_stride = g_fuse.key_stride; a.new_v_stride = g_fuse.value_stride; a.plan = g_fuse.plan;
+  a.new_k_stride = g_fuse.key_stride; a.new_v_stride = g_fuse.value_stride; a.plan = g_fuse.plan; a.pdl = g_fuse.pdl;
   return paged_decode_attn_score(a, static_cast<cudaStream_t>(stream));
 }
 
@@ -248,7 +248,9 @@ int pc_decode_layer(const pc_decode_step* st, void* out, const void* query, cons
     if (!st->attend_uncompacted) { tables = st->compact_tables; stride = st->compact_stride; }
   }
   // A2 + S2: attention over the (compacted) tables, scoring the blocks that fill this step
-  FuseExtras g_fuse = {nullptr, nullptr, nullptr, 0, 0, st->plan};
+  // PDL only when the preceding kernel is not this call's own evict_select / cache write
+  FuseExtras g_fuse = {nullptr, nullptr, nullptr, 0, 0, st->plan,
+                       (st->pdl && fuse && !st->any_trigger) ? 1 : 0};
   if (fuse) {
     if (!key || !value || !st->slot_mapping)
       return set_error(PC_ERR_INVALID, "pc_decode_layer: fused cache write needs key, value, slot_mapping");

@@ -42,6 +42,7 @@
 #include "pc_common.cuh"
 #include "score_common.cuh"
 #include <stdlib.h>
+#include <type_traits>
 
 #include "pc_api_internal.h"
 
@@ -77,6 +78,7 @@ struct DecodeParams {
   __nv_bfloat16* k_cache_w;
   __nv_bfloat16* v_cache_w;
   long long new_k_stride, new_v_stride;
+  int pdl;  // launched with programmatic stream serialization: page prefetch runs ahead of the wait
   unsigned long long* trace;  // debug: [warps][8]: 4 globaltimer stamps, chunks, combines, smid, membar ns (nullptr = off)
 };
 
@@ -111,6 +113,38 @@ struct DecodeTraits {
   }
 };
 
+// W1 fused into A2: patch the step's K/V row of kv head h (nk = this lane's 16 bytes of the
+// K row, nv = its D/32 V elements) into the page under attention at in-page offset `off`
+// -- iff slot_mapping says the token lives there -- and store it to the pool at
+// slot_mapping[b] (csrc/cache_kernels.cu:152-205 semantics: K [D/8][BS][8], V [D][BS],
+// slot < 0 = skip).  Only the row's last page runs this (peeled page variant).
+template <int D, int BS>
+__device__ __forceinline__ void write_new_token(__nv_bfloat16* k_cache_w, __nv_bfloat16* v_cache_w,
+                                                long long kv_block_stride, long long nslot, int phys,
+                                                uint8_t* kpage, uint8_t* vpage, uint4 nk,
+                                                const __nv_bfloat16 (&nv)[D / 32], int h, bool store, int off) {
+  const int lane = threadIdx.x & 31;
+  constexpr int VPL = D / 32;  // V dims per lane
+  const bool here = (nslot == (long long)phys * BS + off);
+  store = store && (nslot >= 0);
+  const long long wblk = nslot / BS;
+  const int woff = (int)(nslot - wblk * BS);
+  const size_t wbase = (size_t)wblk * kv_block_stride + (size_t)h * (D * BS);
+  if (lane < D / 8) {
+    if (here) *reinterpret_cast<uint4*>(kpage + (size_t)(lane * BS + off) * 16) = nk;
+    if (store) *reinterpret_cast<uint4*>(k_cache_w + wbase + (size_t)(lane * BS + woff) * 8) = nk;
+  }
+  __nv_bfloat16* vp = reinterpret_cast<__nv_bfloat16*>(vpage);
+#pragma unroll
+  for (int i = 0; i < VPL; ++i) {
+    const int dd = lane * VPL + i;
+    if (here) vp[dd * BS + off] = nv[i];
+    if (store) v_cache_w[wbase + (size_t)dd * BS + woff] = nv[i];
+  }
+  fence_proxy_async();  // generic-proxy writes before a later TMA refill of this slot
+  __syncwarp();
+}
+
 template <int D, int BS, int kWarps, int kStages>
 __global__ void __launch_bounds__(kWarps * 32, 1)
 paged_decode_attn_score_kernel(const DecodeParams p) {
@@ -130,8 +164,6 @@ paged_decode_attn_score_kernel(const DecodeParams p) {
 
   const unsigned long long t_start = p.trace ? gtimer() : 0ull;
   const int chunk_pages = (p.plan != nullptr) ? max(1, __ldg(p.plan)) : p.chunk_pages;
-  uint8_t* my_stages = smem + (size_t)warp * kStages * T::kStageBytes;
-  uint64_t* my_bars = reinterpret_cast<uint64_t*>(smem + T::kRingBytes) + warp * kStages;
   ChunkDesc* my_fifo = reinterpret_cast<ChunkDesc*>(smem + T::kRingBytes + T::kBarBytes) + warp * kFifo;
   int* cpre = reinterpret_cast<int*>(smem + T::kRingBytes + T::kBarBytes + T::kFifoBytes);  // [B + 1]
 
@@ -139,17 +171,20 @@ paged_decode_attn_score_kernel(const DecodeParams p) {
   // counter, fetched only when the issue side runs out of pages (kStages pages before the
   // consumer does), so a slow SM never commits to work ahead of time.
   if (lane == 0) {
+    uint64_t* bars0 = reinterpret_cast<uint64_t*>(smem + T::kRingBytes) + warp * kStages;
 #pragma unroll
-    for (int s = 0; s < kStages; ++s) mbar_init(&my_bars[s], 1);
+    for (int s = 0; s < kStages; ++s) mbar_init(&bars0[s], 1);
   }
   // ---- schedule: chunks per (row, group) -> exclusive prefix sum (same in every CTA)
+  // Programmatic dependent launch: let the next kernel of the stream start as SMs free
+  // up; everything up to pdl_wait() below reads only the step's integer state and the KV
+  // pool pages (written on earlier steps / by earlier layers, never by the preceding
+  // kernel -- the caller's promise when it sets `pdl`), so the first ring of pages is in
+  // flight while the preceding kernel drains.
+  if (p.pdl) asm volatile("griddepcontrol.launch_dependents;");
   for (int r = threadIdx.x; r < p.B; r += T::kThreads) {
     const int len = p.kv_lens[r];
     cpre[r + 1] = ((len + BS - 1) / BS + chunk_pages - 1) / chunk_pages;
-    if (len == 0 && blockIdx.x == 0) {  // empty sequence: defined output (zeros)
-      __nv_bfloat16* o = p.out + (size_t)r * p.out_stride;
-      for (int i = 0; i < p.Hq * D; ++i) o[i] = __float2bfloat16(0.f);
-    }
   }
   __syncthreads();
   if (warp == 0) {
@@ -171,6 +206,12 @@ paged_decode_attn_score_kernel(const DecodeParams p) {
   __syncthreads();
 
   const int C = cpre[p.B] * p.GH;  // chunks in this launch
+
+  // (a runtime ring depth that lends idle warps' slots to busy ones was measured and is
+  // slower: profiles/r01_decode_variants.txt)
+  constexpr int depth = kStages;
+  uint8_t* my_stages = smem + (size_t)warp * depth * T::kStageBytes;
+  uint64_t* my_bars = reinterpret_cast<uint64_t*>(smem + T::kRingBytes) + warp * depth;
 
   // ---- chunk stream: ids -> descriptors (fifo in shared memory, written by the issue side)
   int fifo_head = 0;   // descriptors opened (issue side)
@@ -214,11 +255,23 @@ paged_decode_attn_score_kernel(const DecodeParams p) {
   int is_b = 0, is_h = 0, is_blk = 0, is_end = 0;  // current issue chunk (is_blk == is_end: exhausted)
   bool is_open = false;
   int phys_next = 0;   // table entry of the next page to issue, loaded one page ahead
-  int pages_issued = 0, pages_consumed = 0;
+  int pages_issued = 0;
+  int issue_slot = 0;                 // ring slot the next page goes to
+  int cons_slot = 0;                  // ring slot of the next page to consume
+  uint32_t cons_parity = 0;           // mbarrier phase parity of that slot
 
+  // before the dependency wait (PDL) only the static first chunk may be opened: the
+  // chunk counter still belongs to the preceding launch
+  bool allow_open = !p.pdl;
+  bool is_pending = false;
   auto issue_advance = [&]() {  // make (is_b, is_h, is_blk) point at the next page, if any
     if (is_open && is_blk < is_end) {
       phys_next = __ldg(p.block_tables + (size_t)is_b * p.table_stride + is_blk);
+      return;
+    }
+    if (!allow_open && !first_open) {
+      is_open = false;
+      is_pending = true;
       return;
     }
     is_open = open_chunk();
@@ -228,7 +281,8 @@ paged_decode_attn_score_kernel(const DecodeParams p) {
     phys_next = __ldg(p.block_tables + (size_t)is_b * p.table_stride + is_blk);
   };
   auto issue_page = [&]() {  // issue the page under the cursor into the next ring slot
-    const int slot = pages_issued % kStages;
+    const int slot = issue_slot;
+    issue_slot = (issue_slot + 1 == depth) ? 0 : issue_slot + 1;
     if (lane == 0) {
       uint8_t* dst = my_stages + (size_t)slot * T::kStageBytes;
       const size_t off = ((size_t)phys_next * p.kv_block_stride) + (size_t)is_h * (D * BS);
@@ -254,13 +308,36 @@ paged_decode_attn_score_kernel(const DecodeParams p) {
     }
   };
 
-  // prologue: fill the ring
-  issue_advance();
-#pragma unroll
-  for (int s = 0; s < kStages; ++s) {
-    if (is_open) {
-      issue_page();
-      issue_advance();
+  // prologue: fill the ring.  One copy of the fill loop serves both sides of the PDL
+  // dependency wait (the issue path is large; keeping it to two instances -- here and the
+  // refill in the page loop -- keeps the kernel inside the instruction cache).
+  {
+    bool need_adv = true;  // the cursor does not point at a page yet
+#pragma unroll 1
+    for (int pass = 0; pass < 2; ++pass) {
+      if (pass == 1) {
+        // ---- from here on the kernel reads what the preceding kernel may have produced
+        // (Q, the step's K/V rows) and writes (out, partials, tickets, counters, scores, pool)
+        if (p.pdl) asm volatile("griddepcontrol.wait;" ::: "memory");
+        allow_open = true;
+        if (!is_pending) break;
+        is_pending = false;
+        need_adv = !is_open;
+      }
+#pragma unroll 1
+      while (true) {
+        if (need_adv) { issue_advance(); need_adv = false; }
+        if (pages_issued >= depth || !is_open) break;
+        issue_page();
+        need_adv = true;
+      }
+    }
+  }
+  if (blockIdx.x == 0) {  // empty sequences: defined output (zeros)
+    for (int r = warp; r < p.B; r += kWarps) {
+      if (p.kv_lens[r] != 0) continue;
+      __nv_bfloat16* o = p.out + (size_t)r * p.out_stride;
+      for (int i = lane; i < p.Hq * D; i += 32) o[i] = __float2bfloat16(0.f);
     }
   }
   uint32_t qf[KSTEPS][2];   // Q of the chunk being consumed
@@ -290,34 +367,45 @@ paged_decode_attn_score_kernel(const DecodeParams p) {
     } else {
       load_q(qf, b, d.gh);
     }
+    if (p.new_k != nullptr && d.blk_end == nblk) {
+      // the chunk ends with the row's last page: pull the step's K/V row towards L1 now, so
+      // the loads in the tail page (no registers to spare until then) hit
+      const __nv_bfloat16* ka = p.new_k + (size_t)b * p.new_k_stride + (size_t)h * D + (lane & (D / 8 - 1)) * 8;
+      const __nv_bfloat16* va = p.new_v + (size_t)b * p.new_v_stride + (size_t)h * D + lane * (D / 32);
+      asm volatile("prefetch.global.L1 [%0];" ::"l"(ka));
+      asm volatile("prefetch.global.L1 [%0];" ::"l"(va));
+      if (lane == 0) asm volatile("prefetch.global.L1 [%0];" ::"l"(p.slot_mapping + b));
+    }
 #pragma unroll
     for (int m = 0; m < MT; ++m) o[m][0] = o[m][1] = o[m][2] = o[m][3] = 0.f;
     m_run[0] = m_run[1] = -INFINITY;
     l_run[0] = l_run[1] = 0.f;
 
-    for (int blk = d.blk_begin; blk < d.blk_end; ++blk) {
-      const uint32_t slot = (uint32_t)pages_consumed % kStages;
-      const uint32_t parity = ((uint32_t)pages_consumed / kStages) & 1u;
-      ++pages_consumed;
+    // One page.  kTail = it is the row's LAST page: the only page that can be partially
+    // filled, receive the step's token (fused cache write) or be scored; the interior pages
+    // run the variant without any of that.
+    auto page = [&](const int blk, auto tail_tag) {
+      constexpr bool kTail = decltype(tail_tag)::value;
+      const uint32_t slot = (uint32_t)cons_slot;
+      const uint32_t parity = cons_parity;
+      if (++cons_slot == depth) { cons_slot = 0; cons_parity ^= 1u; }
       const int page_tok0 = blk * BS;
-      const bool last_partial = (page_tok0 + BS > kv_len);
-      const bool write_new = (p.new_k != nullptr) && (blk == nblk - 1);
+      const bool last_partial = kTail && (page_tok0 + BS > kv_len);
+      const bool write_new = kTail && (p.new_k != nullptr);
       // this step's token (W1 fused): its loads overlap the wait for the page
-      constexpr int VPL = D / 32;  // V dims per lane
       uint4 nk = make_uint4(0u, 0u, 0u, 0u);
-      __nv_bfloat16 nv[VPL];
+      __nv_bfloat16 nv[D / 32];
       long long nslot = -1;
-      if (write_new) {
-        nslot = __ldg(p.slot_mapping + b);
-        if (lane < D / 8)
-          nk = __ldg(reinterpret_cast<const uint4*>(p.new_k + (size_t)b * p.new_k_stride + (size_t)h * D + lane * 8));
-        const __nv_bfloat16* vsrc = p.new_v + (size_t)b * p.new_v_stride + (size_t)h * D + lane * VPL;
-        if constexpr (VPL == 4) {
-          const uint2 w2 = __ldg(reinterpret_cast<const uint2*>(vsrc));
-          *reinterpret_cast<uint2*>(nv) = w2;
-        } else {
-          const unsigned int w1 = __ldg(reinterpret_cast<const unsigned int*>(vsrc));
-          *reinterpret_cast<unsigned int*>(nv) = w1;
+      int nphys = 0;
+      if constexpr (kTail) {
+        if (write_new) {
+          nslot = __ldg(p.slot_mapping + b);
+          nphys = __ldg(p.block_tables + (size_t)b * p.table_stride + blk);
+          if (lane < D / 8)
+            nk = __ldg(reinterpret_cast<const uint4*>(p.new_k + (size_t)b * p.new_k_stride + (size_t)h * D + lane * 8));
+          const __nv_bfloat16* vsrc = p.new_v + (size_t)b * p.new_v_stride + (size_t)h * D + lane * (D / 32);
+          if constexpr (D / 32 == 4) *reinterpret_cast<uint2*>(nv) = __ldg(reinterpret_cast<const uint2*>(vsrc));
+          else *reinterpret_cast<unsigned int*>(nv) = __ldg(reinterpret_cast<const unsigned int*>(vsrc));
         }
       }
       mbar_wait(&my_bars[slot], parity);
@@ -327,29 +415,11 @@ paged_decode_attn_score_kernel(const DecodeParams p) {
       const uint32_t kaddr = smem_u32(kpage);
       const uint32_t vaddr = smem_u32(vpage);
 
-      if (write_new) {
-        const int off = kv_len - 1 - page_tok0;  // position of the new token in this page
-        const int phys = __ldg(p.block_tables + (size_t)b * p.table_stride + blk);
-        // the page under attention holds the token iff the slot is where the table says
-        const bool here = (nslot == (long long)phys * BS + off);
-        const bool store = (hg == 0) && (nslot >= 0);
-        const long long wblk = nslot / BS;
-        const int woff = (int)(nslot - wblk * BS);
-        const size_t wbase = (size_t)wblk * p.kv_block_stride + (size_t)h * (D * BS);
-        if (lane < D / 8) {
-          if (here) *reinterpret_cast<uint4*>(const_cast<uint8_t*>(kpage) + (size_t)(lane * BS + off) * 16) = nk;
-          if (store) *reinterpret_cast<uint4*>(p.k_cache_w + wbase + (size_t)(lane * BS + woff) * 8) = nk;
-        }
-        __nv_bfloat16* vp = reinterpret_cast<__nv_bfloat16*>(const_cast<uint8_t*>(vpage));
-#pragma unroll
-        for (int i = 0; i < VPL; ++i) {
-          const int dd = lane * VPL + i;
-          if (here) vp[dd * BS + off] = nv[i];
-          if (store) p.v_cache_w[wbase + (size_t)dd * BS + woff] = nv[i];
-        }
-        fence_proxy_async();  // generic-proxy writes before a later TMA refill of this slot
-        __syncwarp();
-      }
+      if constexpr (kTail) {
+      if (write_new)  // W1 fused: patch the step's token into the page and store it to the pool
+        write_new_token<D, BS>(p.k_cache_w, p.v_cache_w, p.kv_block_stride, nslot, nphys,
+                               const_cast<uint8_t*>(kpage), const_cast<uint8_t*>(vpage), nk, nv, h, hg == 0,
+                               kv_len - 1 - page_tok0);
 
       if (last_partial) {
         // zero V columns of tokens >= kv_len so 0 * garbage cannot produce NaN
@@ -360,6 +430,7 @@ paged_decode_attn_score_kernel(const DecodeParams p) {
           if ((i % BS) >= valid) vp[i] = __float2bfloat16(0.f);
         fence_proxy_async();  // generic-proxy writes before a later TMA refill of this slot
         __syncwarp();
+      }
       }
 
 #pragma unroll
@@ -422,7 +493,7 @@ paged_decode_attn_score_kernel(const DecodeParams p) {
       }
 
       // ---------------- fused value_l2 score of the row's last (just filled) block
-      if (p.seq_lens != nullptr && blk == nblk - 1 && hg == 0 && (kv_len % BS) == 0 &&
+      if (kTail && p.seq_lens != nullptr && hg == 0 && (kv_len % BS) == 0 &&
           (__ldg(p.seq_lens + b) % BS) == 0) {
         const __nv_bfloat16* vp = reinterpret_cast<const __nv_bfloat16*>(vpage);
         const float sc = warp_value_l2_head_score<D, BS>(
@@ -431,18 +502,25 @@ paged_decode_attn_score_kernel(const DecodeParams p) {
           score_store(p.score, __ldg(p.block_tables + (size_t)b * p.table_stride + blk), h, sc);
       }
 
-      // ---------------- refill this slot (the issue side may open the next chunk here)
+      // ---------------- refill this slot (the issue side may open the next chunk here).
+      // Kept inside both page variants: hoisting it into the driver loop measured 2.5 % slower.
       __syncwarp();
       if (is_open) {
         const int opened = fifo_head;
         issue_page();
         issue_advance();
-        if (fifo_head != opened) {  // a new chunk was opened: prefetch its Q
+        if (fifo_head != opened) {
           const ChunkDesc& nd = my_fifo[(fifo_head - 1) % kFifo];
           load_q(qn, nd.b, nd.gh);
           qn_id = nd.id;
         }
       }
+    };
+    {
+      const bool has_tail = (d.blk_end == nblk);  // this chunk holds the row's last page
+      const int body_end = d.blk_end - (has_tail ? 1 : 0);
+      for (int blk = d.blk_begin; blk < body_end; ++blk) page(blk, std::false_type{});
+      if (has_tail) page(nblk - 1, std::true_type{});
     }
     if (p.trace && lane == 0) p.trace[w * 8 + 2] = gtimer();
 
@@ -658,11 +736,24 @@ static int launch_decode(const DecodeParams& p, int num_sms, long long max_chunk
   if (dev < 0 || dev >= 64 || smem_set[dev] < smem) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return set_cuda_error("cudaFuncSetAttribute(decode)", e);
+    static const int carve = env_int("PC_DECODE_CARVEOUT", -1);
+    if (carve >= 0) cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
     if (dev >= 0 && dev < 64) smem_set[dev] = smem;
   }
   long long ctas = max_chunks < num_sms ? max_chunks : num_sms;  // spread over SMs first
   if (ctas < 1) ctas = 1;
-  kern<<<(int)ctas, T::kThreads, smem, stream>>>(p);
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)ctas);
+  cfg.blockDim = dim3(T::kThreads);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = p.pdl ? 1 : 0;
+  const cudaError_t e = cudaLaunchKernelEx(&cfg, kern, p);
+  if (e != cudaSuccess) return set_cuda_error("paged_decode_attn_score_kernel", e);
   return check_launch("paged_decode_attn_score_kernel");
 }
 
@@ -700,6 +791,7 @@ int paged_decode_attn_score(const DecodeArgs& a, cudaStream_t stream) {
   p.scale_log2 = a.scale * 1.4426950408889634f;
   p.chunk_pages = pl.chunk_pages;
   p.plan = a.plan;
+  p.pdl = a.pdl;
   p.trace = g_decode_trace;
   p.new_k = static_cast<const __nv_bfloat16*>(a.new_k);
   p.new_v = static_cast<const __nv_bfloat16*>(a.new_v);

@@ -56,6 +56,7 @@ struct DecodeArgs {
   const long long* slot_mapping;
   long long new_k_stride, new_v_stride;
   const int* plan;  // device {chunk_pages} or nullptr (host plans from max_kv_len)
+  int pdl;          // programmatic dependent launch (see pc_decode_step.pdl)
 };
 size_t decode_workspace_bytes(int B, int Hq, int Hkv, int D, int BS, int max_kv_len, int num_sms);
 int decode_plan_chunk_pages(int B, int Hq, int Hkv, int D, int BS, int max_kv_len, int num_sms);

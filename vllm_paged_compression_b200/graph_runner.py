@@ -35,7 +35,7 @@ from .policy import cdiv
 class DecodeGraphRunner:
     def __init__(self, engine, qkv: Optional[Sequence[Tuple[torch.Tensor, torch.Tensor, torch.Tensor]]],
                  outs: Optional[Sequence[torch.Tensor]] = None, io=None, max_kv_len: Optional[int] = None,
-                 use_graph: bool = True) -> None:
+                 use_graph: bool = True, pdl: bool = True) -> None:
         """engine: PagedEvictEngine whose `running` sequences are all prefilled.
         qkv[l] = (query [B,Hq*D], key [B,Hkv*D], value [B,Hkv*D]) STATIC device tensors the
         caller refills before every step (ignored when `io` is given: PinnedLayerIO supplies
@@ -45,6 +45,7 @@ class DecodeGraphRunner:
         self.device = eng.device
         self.io = io
         self.use_graph = use_graph
+        self.pdl = pdl
         self.seqs = list(eng.running)
         if not self.seqs:
             raise RuntimeError("DecodeGraphRunner needs running (prefilled) sequences")
@@ -122,7 +123,7 @@ class DecodeGraphRunner:
         self._warm()
 
     # ------------------------------------------------------------------ launches
-    def _make_step(self, trig: bool):
+    def _make_step(self, trig: bool, pdl: bool = False):
         eng = self.eng
         q, k, v = self.qkv[0]
         return ops.make_decode_step(
@@ -131,11 +132,14 @@ class DecodeGraphRunner:
             v.stride(0), self.outs[0].stride(0), self.blk_stride,
             policy=eng.impls[0]._policy_struct() if self.cfg is not None else None,
             n_blocks=self.d_nblk, compact_tables=self.d_compact if trig else None, any_trigger=trig,
-            attend_uncompacted=trig and self.attend_unc, plan=self.d_plan, workspace=self.ws)
+            attend_uncompacted=trig and self.attend_unc, plan=self.d_plan, workspace=self.ws, pdl=pdl)
 
     def _launch_layers(self, trig: bool, count: bool = False) -> None:
         """All layers of one decode step on the current stream (captured or eager)."""
         ds = self._make_step(trig)
+        # PDL for a layer whose predecessor in the stream is the previous layer's attention
+        # kernel (another layer's pool): its first pages load while that kernel drains
+        ds_pdl = self._make_step(trig, pdl=True) if (self.pdl and not trig) else ds
         self._launches[trig] = ds._launches * self.L
         io = self.io
         cur = torch.cuda.current_stream(self.device)
@@ -146,7 +150,8 @@ class DecodeGraphRunner:
                 cur.wait_event(io.h2d_done[l // io.group])
             q, k, v = self.qkv[l]
             kptr, vptr, score = self.layers[l]
-            ops.decode_layer(ds, self.outs[l], q, k, v, kptr, vptr, score,
+            chained = l > 0 and (io is None or l % io.group != 0)
+            ops.decode_layer(ds_pdl if chained else ds, self.outs[l], q, k, v, kptr, vptr, score,
                              self.d_victims[l] if trig else None)
             if io is not None:
                 io.put_out(l, self.out_flat[l])

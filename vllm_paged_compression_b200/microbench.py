@@ -57,12 +57,11 @@ def time_shape(device, B, ctx, Hq, Hkv, D=128, bs=16, ragged=False, score=True, 
     q = (torch.rand(B, Hq, D, device=device, generator=g) * 2 * s - s).to(torch.bfloat16)
     out = torch.empty_like(q)
     seq_lens = kv_lens.clone() if score else None
-    table = torch.zeros(B, M + 1, Hkv, dtype=torch.float32, device=device) if score else None
-    slots = torch.arange(B, dtype=torch.int32, device=device) if score else None
+    pool = ops.make_score_pool(torch.zeros(nb, Hkv, dtype=torch.float32, device=device), 0) if score else None
 
     def launch(i):
         ops.paged_decode_attn_score(out, q, kc, vc, tables[i % n_sets], kv_lens, s, max(lens_host),
-                                    seq_lens, table, slots)
+                                    seq_lens, pool)
     for i in range(max(3, n_sets)):
         launch(i)
     torch.cuda.synchronize()

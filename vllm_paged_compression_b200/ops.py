@@ -229,7 +229,7 @@ def make_decode_step(slot_mapping: torch.Tensor, block_tables: torch.Tensor, kv_
                      compact_tables: Optional[torch.Tensor] = None, any_trigger: bool = False,
                      attend_uncompacted: bool = False, fuse_cache_write: bool = True,
                      plan: Optional[torch.Tensor] = None,
-                     workspace: Optional[torch.Tensor] = None) -> PcDecodeStep:
+                     workspace: Optional[torch.Tensor] = None, pdl: bool = False) -> PcDecodeStep:
     """struct pc_decode_step: everything that is the same for every layer of one engine
     step (built once per step, passed by pointer to `decode_layer`)."""
     _req_cuda(slot_mapping, block_tables, kv_lens, seq_lens, n_blocks, compact_tables)
@@ -260,6 +260,7 @@ def make_decode_step(slot_mapping: torch.Tensor, block_tables: torch.Tensor, kv_
     st.fuse_cache_write = int(fused)
     _req_cuda(plan)
     st.plan = _ptr(plan)
+    st.pdl = int(bool(pdl))
     st._keepalive = (slot_mapping, block_tables, kv_lens, seq_lens, n_blocks, compact_tables, ws, plan)
     st._launches = (1 if fused else 2) + (1 if any_trigger else 0)
     return st
