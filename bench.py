@@ -273,7 +273,7 @@ def timed_steps(torch, dist, arm, K, W, world):
     return sec, evictions, ops.launch_count - n0
 
 
-def roofline_leg(torch, arm, reps=20):
+def roofline_leg(torch, arm, args, reps=20):
     """The decode-attention + scoring kernel alone, back to back over every layer's pool
     (distinct memory per launch, total >> L2), on the state the timed region ended in."""
     from vllm_paged_compression_b200 import ops
@@ -286,12 +286,21 @@ def roofline_leg(torch, arm, reps=20):
     caches = [PagedAttention.split_kv_cache(kv, arm.Hkv, arm.D) for kv in eng.kv_caches]
     outs = torch.empty(arm.B, arm.Hq, arm.D, dtype=torch.bfloat16, device=arm.device)
     qs = [q.view(arm.B, arm.Hq, arm.D) for q in arm.q]
+    ks = [k.view(arm.B, arm.Hkv, arm.D) for k in arm.k]
+    vs = [v.view(arm.B, arm.Hkv, arm.D) for v in arm.v]
     scale = arm.D ** -0.5
+    # the launch the product makes (pc_decode_layer on a non-trigger step): the step's K/V row
+    # written by the attention kernel itself, programmatic dependent launch behind the
+    # previous layer's kernel (--no-pdl: plain stream order)
+    ds = ops.make_decode_step(md.slot_mapping, md.block_tables, kv_lens, md.seq_lens_tensor, arm.B, arm.Hq,
+                              arm.Hkv, arm.D, args.block_size, max_kv, scale, qs[0].stride(0), ks[0].stride(0),
+                              vs[0].stride(0), outs.stride(0), caches[0][1].stride(0), fuse_cache_write=True,
+                              pdl=not args.no_pdl)
 
     def run_all():
         for l in range(arm.L):
-            ops.paged_decode_attn_score(outs, qs[l], caches[l][0], caches[l][1], md.block_tables,
-                                        kv_lens, scale, max_kv)
+            ops.decode_layer(ds, outs, qs[l], ks[l], vs[l], caches[l][0].data_ptr(), caches[l][1].data_ptr(),
+                             None, None)
     for _ in range(3):
         run_all()
     torch.cuda.synchronize()
@@ -469,12 +478,12 @@ def main():
     K, W = args.steps, args.warmup
     # ---- value: inputs resident in HBM
     arm = Arm(args, device, rank, world, host_io=False)
+    sampler = ClockSampler(local_rank) if rank == 0 else None   # nvidia-smi needs ~0.3 s to start sampling
     arm.prefill()
     arm.make_runner()
-    sampler = ClockSampler(local_rank) if rank == 0 else None
     sec, evictions, launches = timed_steps(torch, dist, arm, K, W, world)
-    clocks = sampler.stop() if sampler else None
-    per_launch_s, alg_bytes, kv_lens_host = roofline_leg(torch, arm)
+    per_launch_s, alg_bytes, kv_lens_host = roofline_leg(torch, arm, args)
+    clocks = sampler.stop() if sampler else None        # sampled over the timed steps + the roofline leg
     if world > 1:
         t = torch.tensor([per_launch_s], device=device, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -521,6 +530,8 @@ def main():
         "roofline": {"bound": "hbm", "kernel": "paged_decode_attn_score_kernel", "achieved": achieved,
                      "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
                      "peak_source": peak_src, "algorithmic_bytes_per_launch": alg_bytes,
+                     "launch": "pc_decode_layer as in the step: fused cache write" + ("" if args.no_pdl else ", PDL") +
+                               ", back to back over the layers' pools, CUDA events",
                      "us_per_launch": per_launch_s * 1e6},
     }
     # ncu-measured DRAM traffic of the same launch shape, when a summary is committed

@@ -145,8 +145,8 @@ __device__ __forceinline__ void write_new_token(__nv_bfloat16* k_cache_w, __nv_b
   __syncwarp();
 }
 
-template <int D, int BS, int kWarps, int kStages>
-__global__ void __launch_bounds__(kWarps * 32, 1)
+template <int D, int BS, int kWarps, int kStages, bool kPair, int kCtasPerSm = 1>
+__global__ void __launch_bounds__(kWarps * 32, kCtasPerSm)
 paged_decode_attn_score_kernel(const DecodeParams p) {
   using T = DecodeTraits<D, BS, kWarps, kStages>;
   static_assert(kStages < kFifo, "descriptor fifo must outrun the page ring");
@@ -384,11 +384,25 @@ paged_decode_attn_score_kernel(const DecodeParams p) {
     // One page.  kTail = it is the row's LAST page: the only page that can be partially
     // filled, receive the step's token (fused cache write) or be scored; the interior pages
     // run the variant without any of that.
-    auto page = [&](const int blk, auto tail_tag) {
+    // NP consecutive pages processed as ONE softmax tile of NP*BS tokens.  A warp that
+    // streams alone on its SM sub-partition is bound by the dependent chain of a page
+    // (ldmatrix -> HMMA -> shuffle max -> ex2 -> movmatrix -> HMMA), not by HBM (trace hook:
+    // every warp needs ~0.68 us per page however many neighbours it has); two pages share one
+    // max/rescale chain and give the QK^T HMMAs twice the independent accumulators.
+    // kTail = the row's LAST page (NP == 1): the only page that can be partially filled,
+    // receive the step's token (fused cache write) or be scored.
+    auto page = [&](const int blk, auto tail_tag, auto np_tag) {
       constexpr bool kTail = decltype(tail_tag)::value;
-      const uint32_t slot = (uint32_t)cons_slot;
-      const uint32_t parity = cons_parity;
-      if (++cons_slot == depth) { cons_slot = 0; cons_parity ^= 1u; }
+      constexpr int NP = decltype(np_tag)::value;
+      constexpr int J = NP * TT;  // 16-token tiles handled jointly
+      static_assert(!kTail || NP == 1, "the tail page is processed alone");
+      uint32_t slot[NP], parity[NP];
+#pragma unroll
+      for (int pg = 0; pg < NP; ++pg) {
+        slot[pg] = (uint32_t)cons_slot;
+        parity[pg] = cons_parity;
+        if (++cons_slot == depth) { cons_slot = 0; cons_parity ^= 1u; }
+      }
       const int page_tok0 = blk * BS;
       const bool last_partial = kTail && (page_tok0 + BS > kv_len);
       const bool write_new = kTail && (p.new_k != nullptr);
@@ -408,86 +422,115 @@ paged_decode_attn_score_kernel(const DecodeParams p) {
           else *reinterpret_cast<unsigned int*>(nv) = __ldg(reinterpret_cast<const unsigned int*>(vsrc));
         }
       }
-      mbar_wait(&my_bars[slot], parity);
-
-      const uint8_t* kpage = my_stages + (size_t)slot * T::kStageBytes;
+      uint32_t kaddr[NP], vaddr[NP];
+#pragma unroll
+      for (int pg = 0; pg < NP; ++pg) {
+        mbar_wait(&my_bars[slot[pg]], parity[pg]);
+        kaddr[pg] = smem_u32(my_stages + (size_t)slot[pg] * T::kStageBytes);
+        vaddr[pg] = kaddr[pg] + T::kPageBytes;
+      }
+      const uint8_t* kpage = my_stages + (size_t)slot[0] * T::kStageBytes;
       const uint8_t* vpage = kpage + T::kPageBytes;
-      const uint32_t kaddr = smem_u32(kpage);
-      const uint32_t vaddr = smem_u32(vpage);
 
       if constexpr (kTail) {
-      if (write_new)  // W1 fused: patch the step's token into the page and store it to the pool
-        write_new_token<D, BS>(p.k_cache_w, p.v_cache_w, p.kv_block_stride, nslot, nphys,
-                               const_cast<uint8_t*>(kpage), const_cast<uint8_t*>(vpage), nk, nv, h, hg == 0,
-                               kv_len - 1 - page_tok0);
-
-      if (last_partial) {
-        // zero V columns of tokens >= kv_len so 0 * garbage cannot produce NaN
-        // (attention_kernels.cuh:455-466 does the same per element)
-        const int valid = kv_len - page_tok0;
-        __nv_bfloat16* vp = reinterpret_cast<__nv_bfloat16*>(const_cast<uint8_t*>(vpage));
-        for (int i = lane; i < D * BS; i += 32)
-          if ((i % BS) >= valid) vp[i] = __float2bfloat16(0.f);
-        fence_proxy_async();  // generic-proxy writes before a later TMA refill of this slot
-        __syncwarp();
+        if (write_new)  // W1 fused: patch the step's token into the page and store it to the pool
+          write_new_token<D, BS>(p.k_cache_w, p.v_cache_w, p.kv_block_stride, nslot, nphys,
+                                 const_cast<uint8_t*>(kpage), const_cast<uint8_t*>(vpage), nk, nv, h, hg == 0,
+                                 kv_len - 1 - page_tok0);
+        if (last_partial) {
+          // zero V columns of tokens >= kv_len so 0 * garbage cannot produce NaN
+          // (attention_kernels.cuh:455-466 does the same per element)
+          const int valid = kv_len - page_tok0;
+          __nv_bfloat16* vp = reinterpret_cast<__nv_bfloat16*>(const_cast<uint8_t*>(vpage));
+          for (int i = lane; i < D * BS; i += 32)
+            if ((i % BS) >= valid) vp[i] = __float2bfloat16(0.f);
+          fence_proxy_async();  // generic-proxy writes before a later TMA refill of this slot
+          __syncwarp();
+        }
       }
-      }
 
+      // ---------------- S^T = K_tile x Q^T for all J tiles; k-step outer so that consecutive
+      // HMMAs belong to different accumulators (the asm statements keep program order)
+      float sa[J][4], sb[J][4];
 #pragma unroll
-      for (int tt = 0; tt < TT; ++tt) {
-        // ---------------- S^T = K_tile x Q^T
-        float s0[4] = {0.f, 0.f, 0.f, 0.f}, s1[4] = {0.f, 0.f, 0.f, 0.f};
-        {
-          // ldmatrix.x4 row address: matrix mi = lane/8 -> (token half = mi&1, chunk = 2j + mi>>1)
-          const int mi = lane >> 3, r = lane & 7;
-          const uint32_t base = kaddr + (uint32_t)(((mi >> 1) * BS + tt * 16 + (mi & 1) * 8 + r) * 16);
+      for (int jt = 0; jt < J; ++jt) {
+        sa[jt][0] = sa[jt][1] = sa[jt][2] = sa[jt][3] = 0.f;
+        sb[jt][0] = sb[jt][1] = sb[jt][2] = sb[jt][3] = 0.f;
+      }
+      {
+        // ldmatrix.x4 row address: matrix mi = lane/8 -> (token half = mi&1, chunk = 2j + mi>>1)
+        const int mi = lane >> 3, r = lane & 7;
+        const uint32_t koff = (uint32_t)(((mi >> 1) * BS + (mi & 1) * 8 + r) * 16);
 #pragma unroll
-          for (int j = 0; j < KSTEPS; ++j) {
-            uint32_t a[4];
-            ldmatrix_x4(a, base + (uint32_t)(2 * j * BS * 16));
-            if (j & 1) mma_bf16_16816(s1, a, qf[j][0], qf[j][1]);
-            else       mma_bf16_16816(s0, a, qf[j][0], qf[j][1]);
+        for (int j = 0; j < KSTEPS; ++j) {
+          uint32_t a[J][4];
+#pragma unroll
+          for (int jt = 0; jt < J; ++jt)
+            ldmatrix_x4(a[jt], kaddr[jt / TT] + koff + (uint32_t)((jt % TT) * 16 * 16 + 2 * j * BS * 16));
+#pragma unroll
+          for (int jt = 0; jt < J; ++jt) {
+            if (j & 1) mma_bf16_16816(sb[jt], a[jt], qf[j][0], qf[j][1]);
+            else       mma_bf16_16816(sa[jt], a[jt], qf[j][0], qf[j][1]);
           }
         }
-        // s[0]=(tok g, head 2t) s[1]=(tok g, head 2t+1) s[2]=(tok g+8, head 2t) s[3]=(tok g+8, 2t+1)
-        float x0 = (s0[0] + s1[0]) * p.scale_log2, x1 = (s0[1] + s1[1]) * p.scale_log2;
-        float x2 = (s0[2] + s1[2]) * p.scale_log2, x3 = (s0[3] + s1[3]) * p.scale_log2;
+      }
+      // x[jt][0]=(tok g, head 2t) [1]=(tok g, head 2t+1) [2]=(tok g+8, head 2t) [3]=(tok g+8, 2t+1)
+      float x[J][4];
+#pragma unroll
+      for (int jt = 0; jt < J; ++jt) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) x[jt][i] = (sa[jt][i] + sb[jt][i]) * p.scale_log2;
         if (last_partial) {
-          const int tok = page_tok0 + tt * 16 + g;
-          if (tok >= kv_len) { x0 = -INFINITY; x1 = -INFINITY; }
-          if (tok + 8 >= kv_len) { x2 = -INFINITY; x3 = -INFINITY; }
+          const int tok = page_tok0 + jt * 16 + g;
+          if (tok >= kv_len) { x[jt][0] = -INFINITY; x[jt][1] = -INFINITY; }
+          if (tok + 8 >= kv_len) { x[jt][2] = -INFINITY; x[jt][3] = -INFINITY; }
         }
-        // ---------------- online softmax (per head = per column; rows live in lanes with equal t)
-        float mx0 = fmaxf(x0, x2), mx1 = fmaxf(x1, x3);
+      }
+      // ---------------- online softmax over the J*16 tokens (per head = per column; rows live
+      // in lanes with equal t)
+      float mx0 = fmaxf(x[0][0], x[0][2]), mx1 = fmaxf(x[0][1], x[0][3]);
 #pragma unroll
-        for (int sh = 4; sh <= 16; sh <<= 1) {
-          mx0 = fmaxf(mx0, __shfl_xor_sync(kFull, mx0, sh));
-          mx1 = fmaxf(mx1, __shfl_xor_sync(kFull, mx1, sh));
-        }
-        const float mn0 = fmaxf(m_run[0], mx0), mn1 = fmaxf(m_run[1], mx1);
-        const float al0 = fast_exp2(m_run[0] - mn0), al1 = fast_exp2(m_run[1] - mn1);
-        m_run[0] = mn0; m_run[1] = mn1;
-        const float p0 = fast_exp2(x0 - mn0), p1 = fast_exp2(x1 - mn1);
-        const float p2 = fast_exp2(x2 - mn0), p3 = fast_exp2(x3 - mn1);
-        l_run[0] = l_run[0] * al0 + (p0 + p2);
-        l_run[1] = l_run[1] * al1 + (p1 + p3);
-        if (__any_sync(kFull, (al0 != 1.f) || (al1 != 1.f))) {
+      for (int jt = 1; jt < J; ++jt) {
+        mx0 = fmaxf(mx0, fmaxf(x[jt][0], x[jt][2]));
+        mx1 = fmaxf(mx1, fmaxf(x[jt][1], x[jt][3]));
+      }
 #pragma unroll
-          for (int m = 0; m < MT; ++m) { o[m][0] *= al0; o[m][1] *= al1; o[m][2] *= al0; o[m][3] *= al1; }
-        }
-        // ---------------- P^T as the B operand: transpose the two 8x8 (tok x head) tiles
-        const uint32_t pb0 = movmatrix_trans(pack_bf16x2(p0, p1));  // tokens 0..7
-        const uint32_t pb1 = movmatrix_trans(pack_bf16x2(p2, p3));  // tokens 8..15
-        // ---------------- O^T += V^T_tile x P^T
-        {
-          // matrix mi -> (dim half = mi&1, token half = mi>>1); row r = dim within the half
-          const int mi = lane >> 3, r = lane & 7;
-          const uint32_t base = vaddr + (uint32_t)((((mi & 1) * 8 + r) * BS + tt * 16 + (mi >> 1) * 8) * 2);
+      for (int sh = 4; sh <= 16; sh <<= 1) {
+        mx0 = fmaxf(mx0, __shfl_xor_sync(kFull, mx0, sh));
+        mx1 = fmaxf(mx1, __shfl_xor_sync(kFull, mx1, sh));
+      }
+      const float mn0 = fmaxf(m_run[0], mx0), mn1 = fmaxf(m_run[1], mx1);
+      const float al0 = fast_exp2(m_run[0] - mn0), al1 = fast_exp2(m_run[1] - mn1);
+      m_run[0] = mn0; m_run[1] = mn1;
+      uint32_t pb[J][2];  // P^T as the mma B operand: the two 8x8 (tok x head) tiles, transposed
+      float ps0 = 0.f, ps1 = 0.f;
+#pragma unroll
+      for (int jt = 0; jt < J; ++jt) {
+        const float p0 = fast_exp2(x[jt][0] - mn0), p1 = fast_exp2(x[jt][1] - mn1);
+        const float p2 = fast_exp2(x[jt][2] - mn0), p3 = fast_exp2(x[jt][3] - mn1);
+        ps0 += p0 + p2;
+        ps1 += p1 + p3;
+        pb[jt][0] = movmatrix_trans(pack_bf16x2(p0, p1));  // tokens 0..7
+        pb[jt][1] = movmatrix_trans(pack_bf16x2(p2, p3));  // tokens 8..15
+      }
+      l_run[0] = l_run[0] * al0 + ps0;
+      l_run[1] = l_run[1] * al1 + ps1;
+      if (__any_sync(kFull, (al0 != 1.f) || (al1 != 1.f))) {
+#pragma unroll
+        for (int m = 0; m < MT; ++m) { o[m][0] *= al0; o[m][1] *= al1; o[m][2] *= al0; o[m][3] *= al1; }
+      }
+      // ---------------- O^T += V^T_tile x P^T
+      {
+        // matrix mi -> (dim half = mi&1, token half = mi>>1); row r = dim within the half
+        const int mi = lane >> 3, r = lane & 7;
+        const uint32_t voff = (uint32_t)((((mi & 1) * 8 + r) * BS + (mi >> 1) * 8) * 2);
+#pragma unroll
+        for (int jt = 0; jt < J; ++jt) {
 #pragma unroll
           for (int m = 0; m < MT; ++m) {
             uint32_t a[4];
-            ldmatrix_x4(a, base + (uint32_t)(m * 16 * BS * 2));
-            mma_bf16_16816(o[m], a, pb0, pb1);
+            ldmatrix_x4(a, vaddr[jt / TT] + voff + (uint32_t)(((jt % TT) * 16 + m * 16 * BS) * 2));
+            mma_bf16_16816(o[m], a, pb[jt][0], pb[jt][1]);
           }
         }
       }
@@ -502,14 +545,15 @@ paged_decode_attn_score_kernel(const DecodeParams p) {
           score_store(p.score, __ldg(p.block_tables + (size_t)b * p.table_stride + blk), h, sc);
       }
 
-      // ---------------- refill this slot (the issue side may open the next chunk here).
-      // Kept inside both page variants: hoisting it into the driver loop measured 2.5 % slower.
+      // ---------------- refill the consumed slots (the issue side may open the next chunk here)
       __syncwarp();
-      if (is_open) {
+#pragma unroll 1
+      for (int pg = 0; pg < NP; ++pg) {
+        if (!is_open) break;
         const int opened = fifo_head;
         issue_page();
         issue_advance();
-        if (fifo_head != opened) {
+        if (fifo_head != opened) {  // a new chunk was opened: prefetch its Q
           const ChunkDesc& nd = my_fifo[(fifo_head - 1) % kFifo];
           load_q(qn, nd.b, nd.gh);
           qn_id = nd.id;
@@ -519,8 +563,12 @@ paged_decode_attn_score_kernel(const DecodeParams p) {
     {
       const bool has_tail = (d.blk_end == nblk);  // this chunk holds the row's last page
       const int body_end = d.blk_end - (has_tail ? 1 : 0);
-      for (int blk = d.blk_begin; blk < body_end; ++blk) page(blk, std::false_type{});
-      if (has_tail) page(nblk - 1, std::true_type{});
+      int blk = d.blk_begin;
+      if constexpr (kPair) {
+        for (; blk + 1 < body_end; blk += 2) page(blk, std::false_type{}, std::integral_constant<int, 2>{});
+      }
+      for (; blk < body_end; ++blk) page(blk, std::false_type{}, std::integral_constant<int, 1>{});
+      if (has_tail) page(nblk - 1, std::true_type{}, std::integral_constant<int, 1>{});
     }
     if (p.trace && lane == 0) p.trace[w * 8 + 2] = gtimer();
 
@@ -713,7 +761,14 @@ static DecodePlan plan_decode(int B, int Hq, int Hkv, int D, int BS, int max_kv_
 }
 
 // warps per CTA for each (D, BS): the ring (warps x stages x (K+V page)) must fit 227 KB
-static int decode_warps(int D, int BS) { return (D == 128 && BS == 32) ? 4 : 8; }
+static int decode_cfg() {
+  static const int cfg = env_int("PC_DECODE_CFG", 0);
+  return cfg;
+}
+static int decode_warps(int D, int BS) {
+  if (D == 128 && BS == 16) return decode_cfg() == 1 ? 6 : 8;
+  return (D == 128 && BS == 32) ? 4 : 8;
+}
 
 size_t decode_workspace_bytes(int B, int Hq, int Hkv, int D, int BS, int max_kv_len, int num_sms) {
   if (Hkv <= 0 || Hq < Hkv) return 0;
@@ -724,12 +779,12 @@ int decode_plan_chunk_pages(int B, int Hq, int Hkv, int D, int BS, int max_kv_le
   return plan_decode(B, Hq, Hkv, D, BS, max_kv_len, num_sms, decode_warps(D, BS)).chunk_pages;
 }
 
-template <int D, int BS, int kWarps, int kStages>
+template <int D, int BS, int kWarps, int kStages, bool kPair, int kCtasPerSm = 1>
 static int launch_decode(const DecodeParams& p, int num_sms, long long max_chunks, cudaStream_t stream) {
   using T = DecodeTraits<D, BS, kWarps, kStages>;
-  auto kern = paged_decode_attn_score_kernel<D, BS, kWarps, kStages>;
+  auto kern = paged_decode_attn_score_kernel<D, BS, kWarps, kStages, kPair, kCtasPerSm>;
   const size_t smem = T::smem_bytes(p.B);
-  if (smem > 227 * 1024) return set_error(PC_ERR_INVALID, "decode: batch too large for the in-kernel schedule");
+  if (smem > (size_t)(227 * 1024) / kCtasPerSm) return set_error(PC_ERR_INVALID, "decode: batch too large for the in-kernel schedule");
   static size_t smem_set[64] = {0};  // per device: largest dynamic smem opted in so far
   int dev = 0;
   cudaGetDevice(&dev);
@@ -740,7 +795,7 @@ static int launch_decode(const DecodeParams& p, int num_sms, long long max_chunk
     if (carve >= 0) cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
     if (dev >= 0 && dev < 64) smem_set[dev] = smem;
   }
-  long long ctas = max_chunks < num_sms ? max_chunks : num_sms;  // spread over SMs first
+  long long ctas = max_chunks < (long long)num_sms * kCtasPerSm ? max_chunks : (long long)num_sms * kCtasPerSm;  // spread over SMs first
   if (ctas < 1) ctas = 1;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3((unsigned)ctas);
@@ -808,11 +863,16 @@ int paged_decode_attn_score(const DecodeArgs& a, cudaStream_t stream) {
   }
 
   // a device-side plan may change between replays of a captured launch: full grid
-  const long long grid_chunks = a.plan ? (long long)num_sms : pl.max_chunks;
-  if (a.D == 128 && a.BS == 16) return launch_decode<128, 16, 8, 3>(p, num_sms, grid_chunks, stream);
-  if (a.D == 128 && a.BS == 32) return launch_decode<128, 32, 4, 3>(p, num_sms, grid_chunks, stream);
-  if (a.D == 64 && a.BS == 16) return launch_decode<64, 16, 8, 6>(p, num_sms, grid_chunks, stream);
-  if (a.D == 64 && a.BS == 32) return launch_decode<64, 32, 8, 3>(p, num_sms, grid_chunks, stream);
+  const long long grid_chunks = a.plan ? (long long)num_sms * 8 : pl.max_chunks;
+  if (a.D == 128 && a.BS == 16) {
+    // PC_DECODE_CFG=1: 6 warps x 4-stage rings, pages consumed in pairs (one softmax tile of
+    // 32 tokens); measured within +-3 % of the default on every shape (profiles/r01_decode_variants.txt)
+    if (decode_cfg() == 1) return launch_decode<128, 16, 6, 4, true>(p, num_sms, grid_chunks, stream);
+    return launch_decode<128, 16, 8, 3, false>(p, num_sms, grid_chunks, stream);
+  }
+  if (a.D == 128 && a.BS == 32) return launch_decode<128, 32, 4, 3, false>(p, num_sms, grid_chunks, stream);
+  if (a.D == 64 && a.BS == 16) return launch_decode<64, 16, 8, 6, false>(p, num_sms, grid_chunks, stream);
+  if (a.D == 64 && a.BS == 32) return launch_decode<64, 32, 8, 3, false>(p, num_sms, grid_chunks, stream);
   // mirrors TORCH_CHECK(false, "Unsupported head size / block size") in
   // csrc/attention/paged_attention_v1.cu:108-110,160-162
   return set_error(PC_ERR_UNSUPPORTED, "Unsupported head size / block size (supported: head 64|128, block 16|32)");
