@@ -312,4 +312,8 @@ int pc_swap_blocks(const void* src, void* dst, const int64_t* pairs, int32_t num
  * kernel, [warps][4] = {kernel entry, schedule ready, last page consumed, exit}. */
 void pc_debug_set_decode_trace(void* device_buf) { pc::set_decode_trace(device_buf); }
 
+/* Debug hook: 0 = tcgen05/TMEM prefill kernel (product), 1 = the mma.sync baseline kernel
+ * (kept only so the two can be timed side by side). */
+void pc_debug_set_prefill_variant(int32_t v) { pc::set_prefill_variant(v); }
+
 }  // extern "C"

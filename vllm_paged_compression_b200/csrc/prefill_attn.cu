@@ -8,11 +8,13 @@
 // arithmetic (kv head = q head / G) and the pruned K/V is never materialised: rows are
 // gathered on the fly with src = j < first ? j : j + pruned (kvcache_prunner.py:203-215).
 //
-// Round-1 implementation: flash-attention forward on mma.sync m16n8k16 (bf16 in, fp32
+// The product kernel is the tcgen05/TMEM one in prefill_attn_tc.cu; this file keeps the
+// argument checks, the dispatcher, and the first implementation as the measured
+// "recompiled mma.sync" baseline (pc_debug_set_prefill_variant(1)):
+// flash-attention forward on mma.sync m16n8k16 (bf16 in, fp32
 // accumulate, P rounded to bf16 before P.V like torch's flash/mem-efficient kernels),
 // 64-query x 64-key tiles, 4 warps, cp.async double-buffered K/V tiles in XOR-swizzled
-// shared memory.  Tensor-core bound; the tcgen05/TMEM version is the planned upgrade
-// (DESIGN.md "next").
+// shared memory.
 #include "pc_common.cuh"
 #include "pc_api_internal.h"
 
@@ -224,6 +226,9 @@ static int launch_prefill(const PrefillParams& p, const PrefillArgs& a, cudaStre
   return check_launch("prefill_attn_kernel");
 }
 
+static int g_prefill_variant = 0;
+void set_prefill_variant(int v) { g_prefill_variant = v; }
+
 int prefill_attn(const PrefillArgs& a, cudaStream_t stream) {
   if (a.num_reqs <= 0 || a.max_q_len <= 0) return 0;
   if (a.Hq % a.Hkv) return set_error(PC_ERR_INVALID, "num_heads must be a multiple of num_kv_heads");
@@ -232,6 +237,7 @@ int prefill_attn(const PrefillArgs& a, cudaStream_t stream) {
   if ((reinterpret_cast<uintptr_t>(a.q) | reinterpret_cast<uintptr_t>(a.k) |
        reinterpret_cast<uintptr_t>(a.v) | reinterpret_cast<uintptr_t>(a.out)) & 15)
     return set_error(PC_ERR_INVALID, "q/k/v/out pointers must be 16-byte aligned");
+  if (g_prefill_variant == 0) return prefill_attn_tc(a, stream);
   PrefillParams p;
   p.q = static_cast<const __nv_bfloat16*>(a.q);
   p.k = static_cast<const __nv_bfloat16*>(a.k);

@@ -1,0 +1,104 @@
+"""Prefill-attention (A1) microbench: tcgen05/TMEM kernel vs the mma.sync baseline kernel.
+
+flops = 4 * D * Hq * sum_req sum_i min(i + 1, L')  (top-left causal over the kept prompt,
+SURVEY.md 8d).  CUDA events around `reps` back-to-back launches after warm-up; tensor-pipe
+fraction is reported against MEASURED_PEAKS.json bf16_tflops (burst, kernel timed alone).
+    python -m vllm_paged_compression_b200.microbench_prefill [--reqs 16 --len 1024 --evict-freq 2]
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes
+import json
+import os
+
+import torch
+
+from . import _lib, ops
+from .config import PagedEvictConfig  # noqa: F401  (keeps the flag vocabulary in one place)
+
+
+def _peak_tflops():
+    p = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return float(json.load(f)["bf16_tflops"])
+    return 2250.0
+
+
+def prune_layout(L: int, bs: int, evict_freq: int, initial_blocks: int = 1, num_block_merge: int = 2):
+    """Percentage-mode streamingLLM prompt prune (kvcache_prunner_old.py:141-200)."""
+    if evict_freq <= 0 or L <= (initial_blocks + num_block_merge) * bs:
+        return L, 0, L
+    rem = L % bs
+    first = initial_blocks * bs
+    end_mid = L - num_block_merge * bs - rem
+    pruned = bs * (int((end_mid - first) / evict_freq) // bs)
+    return L - pruned, pruned, first
+
+
+def run(device, reqs, L, Hq, Hkv, D, evict_freq, reps, variant, check=None):
+    g = torch.Generator(device=device)
+    g.manual_seed(0)
+    T = reqs * L
+    s = D ** -0.5
+    q = ((torch.rand(T, Hq, D, device=device, generator=g) * 2 - 1)).to(torch.bfloat16)
+    k = ((torch.rand(T, Hkv, D, device=device, generator=g) * 2 - 1)).to(torch.bfloat16)
+    v = ((torch.rand(T, Hkv, D, device=device, generator=g) * 2 - 1)).to(torch.bfloat16)
+    kept, pruned, first = prune_layout(L, 16, evict_freq)
+    meta = torch.tensor([[r * L, L, r * L, kept, first, pruned] for r in range(reqs)],
+                        dtype=torch.int32, device=device)
+    out = torch.zeros(T, Hq, D, dtype=torch.bfloat16, device=device)
+    lib = _lib.load()
+    lib.pc_debug_set_prefill_variant.argtypes = [ctypes.c_int32]
+    lib.pc_debug_set_prefill_variant.restype = None
+    lib.pc_debug_set_prefill_variant(variant)
+
+    def launch():
+        ops.prefill_attn_topleft_causal(out, q, k, v, meta, L, s)
+    for _ in range(3):
+        launch()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        launch()
+    e1.record()
+    torch.cuda.synchronize()
+    lib.pc_debug_set_prefill_variant(0)
+    sec = e0.elapsed_time(e1) / 1e3 / reps
+    vis = sum(min(i + 1, kept) for i in range(L))
+    flops = 4.0 * D * Hq * reqs * vis
+    row = {"kernel": "prefill_attn_tc_kernel" if variant == 0 else "prefill_attn_kernel(mma.sync)",
+           "reqs": reqs, "q_len": L, "kv_kept": kept, "Hq": Hq, "Hkv": Hkv, "D": D,
+           "us": sec * 1e6, "tflops": flops / sec / 1e12,
+           "frac_of_measured_bf16_peak": flops / sec / 1e12 / _peak_tflops()}
+    if check is not None:
+        row["max_abs_diff_vs_other_variant"] = float((out.float() - check.float()).abs().max())
+    return row, out
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--reqs", type=int, default=16)
+    ap.add_argument("--len", type=int, default=1024)
+    ap.add_argument("--Hq", type=int, default=32)
+    ap.add_argument("--Hkv", type=int, default=8)
+    ap.add_argument("--D", type=int, default=128)
+    ap.add_argument("--evict-freq", type=int, default=2)
+    ap.add_argument("--reps", type=int, default=20)
+    ap.add_argument("--only", type=int, default=-1, help="run one variant only (0 tcgen05, 1 mma.sync)")
+    a = ap.parse_args()
+    dev = torch.device("cuda", 0)
+    if a.only >= 0:
+        row, _ = run(dev, a.reqs, a.len, a.Hq, a.Hkv, a.D, a.evict_freq, a.reps, a.only)
+        print(json.dumps(row), flush=True)
+        return
+    base, ref = run(dev, a.reqs, a.len, a.Hq, a.Hkv, a.D, a.evict_freq, a.reps, 1)
+    print(json.dumps(base), flush=True)
+    row, _ = run(dev, a.reqs, a.len, a.Hq, a.Hkv, a.D, a.evict_freq, a.reps, 0, check=ref)
+    print(json.dumps(row), flush=True)
+
+
+if __name__ == "__main__":
+    main()
