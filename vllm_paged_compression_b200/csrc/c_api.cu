@@ -315,5 +315,6 @@ void pc_debug_set_decode_trace(void* device_buf) { pc::set_decode_trace(device_b
 /* Debug hook: 0 = tcgen05/TMEM prefill kernel (product), 1 = the mma.sync baseline kernel
  * (kept only so the two can be timed side by side). */
 void pc_debug_set_prefill_variant(int32_t v) { pc::set_prefill_variant(v); }
+void pc_debug_set_prefill_tc_tile(int32_t tn) { pc::set_prefill_tc_tile(tn); }
 
 }  // extern "C"

@@ -29,9 +29,7 @@ namespace pc {
 namespace {
 
 constexpr int kTM = 128;       // query rows per CTA (UMMA M)
-constexpr int kTN = 128;       // kv rows per tile   (UMMA N of S, K extent of P.V)
 constexpr int kTcThreads = 224;
-constexpr int kTmemCols = 512;
 constexpr float kRescaleThreshold = 8.f;  // log2 domain
 
 struct PrefillTcParams {
@@ -45,8 +43,12 @@ struct PrefillTcParams {
   float scale_log2;
 };
 
-template <int D>
+// TN = kv rows per tile (UMMA N of S, K extent of P.V).  TN = 64 fits two CTAs per SM
+// (112 KB of shared memory and 256 TMEM columns each), TN = 128 one.
+template <int D, int TN>
 struct TcSmem {
+  static constexpr int kTN = TN;
+  static constexpr int kTmemCols = (2 * TN + D) <= 256 ? 256 : 512;
   static constexpr int kQ = kTM * D * 2;
   static constexpr int kKV = kTN * D * 2;      // one K or V stage
   static constexpr int kP = kTM * kTN * 2;
@@ -63,20 +65,34 @@ enum { B_QFULL = 0, B_KFULL = 1, B_VFULL = 3, B_SFULL = 5, B_PFULL = 7, B_PVDONE
 
 // One warp gathers a [rows x D] bf16 tile into chunk-major core-matrix layout:
 //   byte(row, chunk) = chunk * (ROWS * 16) + row * 16      (chunk = 8 elements along D)
-// lane -> (row % 8, chunk % 4): a warp instruction reads 8 rows x 64 contiguous bytes and
-// writes 4 runs of 128 contiguous bytes (bank-conflict free).
+// Lane mapping: the L1TEX tag stage coalesces only ADJACENT lanes (ncu: the first mapping,
+// lane -> (row % 8, chunk / 8), cost 32 tag wavefronts per LDGSTS and made the kernel
+// LSU-bound at 87 % of l1tex__t_output_wavefronts).  kGatherMap 1: lane -> (chunk % 4, row)
+// = 8 rows x 64 B per instruction; 2: lane -> (chunk % 8, row) = 4 rows x 128 B.
+#ifndef PC_GATHER_MAP
+#define PC_GATHER_MAP 2
+#endif
 template <int D, int ROWS, typename RowSrc>
 __device__ __forceinline__ void gather_tile(uint8_t* dst, int lane, RowSrc row_src) {
   constexpr int CH = D / 8;
-  const int r8 = lane & 7, c4 = lane >> 3;
+#if PC_GATHER_MAP == 0
+  constexpr int RPI = 8, CPI = 4;
+  const int rl = lane & 7, cl = lane >> 3;
+#elif PC_GATHER_MAP == 1
+  constexpr int RPI = 8, CPI = 4;
+  const int rl = lane >> 2, cl = lane & 3;
+#else
+  constexpr int RPI = 4, CPI = 8;
+  const int rl = lane >> 3, cl = lane & 7;
+#endif
 #pragma unroll 4
-  for (int rg = 0; rg < ROWS / 8; ++rg) {
-    const int row = rg * 8 + r8;
+  for (int rg = 0; rg < ROWS / RPI; ++rg) {
+    const int row = rg * RPI + rl;
     bool ok;
     const __nv_bfloat16* src = row_src(row, ok);
 #pragma unroll
-    for (int cq = 0; cq < CH / 4; ++cq) {
-      const int c = cq * 4 + c4;
+    for (int cq = 0; cq < CH / CPI; ++cq) {
+      const int c = cq * CPI + cl;
       cp_async_16_zfill(dst + c * (ROWS * 16) + row * 16, src + c * 8, ok);
     }
   }
@@ -86,9 +102,13 @@ __device__ __forceinline__ void gather_tile(uint8_t* dst, int lane, RowSrc row_s
 
 namespace {
 
-template <int D>
-__global__ void __launch_bounds__(kTcThreads, 1) prefill_attn_tc_kernel(const PrefillTcParams p) {
-  using L = TcSmem<D>;
+template <int D, int TN>
+__global__ void __launch_bounds__(kTcThreads, (TN == 64 ? 2 : 1))
+prefill_attn_tc_kernel(const PrefillTcParams p) {
+  using L = TcSmem<D, TN>;
+  constexpr int kTN = TN;
+  constexpr int kTmemCols = L::kTmemCols;
+  constexpr int SC = TN / 32;       // 32-column chunks of an S row
   constexpr int KS = D / 16;        // k-steps of S = Q K^T
   constexpr int PK = kTN / 16;      // k-steps of O += P V
   constexpr uint32_t kIdescS = t5::instr_desc_bf16(kTM, kTN, false);
@@ -206,22 +226,22 @@ __global__ void __launch_bounds__(kTcThreads, 1) prefill_attn_tc_kernel(const Pr
       const int j0 = j * kTN;
       mbar_wait(&bar[B_SFULL + sb], (j >> 1) & 1);
       t5::fence_after_sync();
-      uint32_t sr[4][32];
+      uint32_t sr[SC][32];
 #pragma unroll
-      for (int c = 0; c < 4; ++c) t5::tmem_ld32(sr[c], tmem + lane_base + sb * kTN + c * 32);
+      for (int c = 0; c < SC; ++c) t5::tmem_ld32(sr[c], tmem + lane_base + sb * kTN + c * 32);
       t5::tmem_ld_wait();
       const bool need_mask = (j0 + kTN - 1 > i0) || (j0 + kTN > kv_len);
       if (need_mask) {
         const int lim = min(row, kv_len - 1) - j0;  // columns > lim are masked
 #pragma unroll
-        for (int c = 0; c < 4; ++c)
+        for (int c = 0; c < SC; ++c)
 #pragma unroll
           for (int i = 0; i < 32; ++i)
             if (c * 32 + i > lim) sr[c][i] = 0xff800000u;  // -inf
       }
       float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll
-      for (int c = 0; c < 4; ++c)
+      for (int c = 0; c < SC; ++c)
 #pragma unroll
         for (int i = 0; i < 32; ++i) mx[i & 3] = fmaxf(mx[i & 3], __uint_as_float(sr[c][i]));
       const float m_tile = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3])) * p.scale_log2;
@@ -236,7 +256,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) prefill_attn_tc_kernel(const Pr
       float sum[4] = {0.f, 0.f, 0.f, 0.f};
       const float neg_m = -m_use;
 #pragma unroll
-      for (int c = 0; c < 4; ++c)
+      for (int c = 0; c < SC; ++c)
 #pragma unroll
         for (int i = 0; i < 32; i += 2) {
           const float p0 = fast_exp2(fmaf(__uint_as_float(sr[c][i]), p.scale_log2, neg_m));
@@ -264,7 +284,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) prefill_attn_tc_kernel(const Pr
       }
       // P row -> smem, chunk-major: 8 kv columns (16 bytes) per chunk
 #pragma unroll
-      for (int c = 0; c < 4; ++c)
+      for (int c = 0; c < SC; ++c)
 #pragma unroll
         for (int q4 = 0; q4 < 4; ++q4) {
           const uint4 val = make_uint4(sr[c][q4 * 4], sr[c][q4 * 4 + 1], sr[c][q4 * 4 + 2], sr[c][q4 * 4 + 3]);
@@ -309,16 +329,19 @@ __global__ void __launch_bounds__(kTcThreads, 1) prefill_attn_tc_kernel(const Pr
 
 }  // namespace
 
-template <int D>
+template <int D, int TN>
 static int launch_prefill_tc(const PrefillTcParams& p, const PrefillArgs& a, cudaStream_t stream) {
-  const int smem = TcSmem<D>::kBytes;
-  auto kern = prefill_attn_tc_kernel<D>;
+  const int smem = TcSmem<D, TN>::kBytes;
+  auto kern = prefill_attn_tc_kernel<D, TN>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   if (e != cudaSuccess) return set_cuda_error("cudaFuncSetAttribute(prefill_tc)", e);
   dim3 grid((a.max_q_len + kTM - 1) / kTM, a.Hq, a.num_reqs);
   kern<<<grid, kTcThreads, smem, stream>>>(p);
   return check_launch("prefill_attn_tc_kernel");
 }
+
+static int g_tc_tile_n = 64;
+void set_prefill_tc_tile(int tn) { g_tc_tile_n = (tn == 128) ? 128 : 64; }
 
 int prefill_attn_tc(const PrefillArgs& a, cudaStream_t stream) {
   PrefillTcParams p;
@@ -331,8 +354,12 @@ int prefill_attn_tc(const PrefillArgs& a, cudaStream_t stream) {
   p.q_stride = a.q_stride; p.out_stride = a.out_stride;
   p.key_stride = a.key_stride; p.value_stride = a.value_stride;
   p.scale_log2 = a.scale * 1.4426950408889634f;
-  if (a.D == 128) return launch_prefill_tc<128>(p, a, stream);
-  if (a.D == 64) return launch_prefill_tc<64>(p, a, stream);
+  if (a.D == 128)
+    return g_tc_tile_n == 128 ? launch_prefill_tc<128, 128>(p, a, stream)
+                              : launch_prefill_tc<128, 64>(p, a, stream);
+  if (a.D == 64)
+    return g_tc_tile_n == 128 ? launch_prefill_tc<64, 128>(p, a, stream)
+                              : launch_prefill_tc<64, 64>(p, a, stream);
   return set_error(PC_ERR_UNSUPPORTED, "Unsupported head size (supported: 64|128)");
 }
 

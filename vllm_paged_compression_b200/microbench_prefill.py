@@ -37,7 +37,7 @@ def prune_layout(L: int, bs: int, evict_freq: int, initial_blocks: int = 1, num_
     return L - pruned, pruned, first
 
 
-def run(device, reqs, L, Hq, Hkv, D, evict_freq, reps, variant, check=None):
+def run(device, reqs, L, Hq, Hkv, D, evict_freq, reps, variant, check=None, tile=64):
     g = torch.Generator(device=device)
     g.manual_seed(0)
     T = reqs * L
@@ -53,6 +53,9 @@ def run(device, reqs, L, Hq, Hkv, D, evict_freq, reps, variant, check=None):
     lib.pc_debug_set_prefill_variant.argtypes = [ctypes.c_int32]
     lib.pc_debug_set_prefill_variant.restype = None
     lib.pc_debug_set_prefill_variant(variant)
+    lib.pc_debug_set_prefill_tc_tile.argtypes = [ctypes.c_int32]
+    lib.pc_debug_set_prefill_tc_tile.restype = None
+    lib.pc_debug_set_prefill_tc_tile(tile)
 
     def launch():
         ops.prefill_attn_topleft_causal(out, q, k, v, meta, L, s)
@@ -66,10 +69,11 @@ def run(device, reqs, L, Hq, Hkv, D, evict_freq, reps, variant, check=None):
     e1.record()
     torch.cuda.synchronize()
     lib.pc_debug_set_prefill_variant(0)
+    lib.pc_debug_set_prefill_tc_tile(64)
     sec = e0.elapsed_time(e1) / 1e3 / reps
     vis = sum(min(i + 1, kept) for i in range(L))
     flops = 4.0 * D * Hq * reqs * vis
-    row = {"kernel": "prefill_attn_tc_kernel" if variant == 0 else "prefill_attn_kernel(mma.sync)",
+    row = {"kernel": f"prefill_attn_tc_kernel<TN={tile}>" if variant == 0 else "prefill_attn_kernel(mma.sync)",
            "reqs": reqs, "q_len": L, "kv_kept": kept, "Hq": Hq, "Hkv": Hkv, "D": D,
            "us": sec * 1e6, "tflops": flops / sec / 1e12,
            "frac_of_measured_bf16_peak": flops / sec / 1e12 / _peak_tflops()}
@@ -96,8 +100,9 @@ def main():
         return
     base, ref = run(dev, a.reqs, a.len, a.Hq, a.Hkv, a.D, a.evict_freq, a.reps, 1)
     print(json.dumps(base), flush=True)
-    row, _ = run(dev, a.reqs, a.len, a.Hq, a.Hkv, a.D, a.evict_freq, a.reps, 0, check=ref)
-    print(json.dumps(row), flush=True)
+    for tile in (64, 128):
+        row, _ = run(dev, a.reqs, a.len, a.Hq, a.Hkv, a.D, a.evict_freq, a.reps, 0, check=ref, tile=tile)
+        print(json.dumps(row), flush=True)
 
 
 if __name__ == "__main__":
