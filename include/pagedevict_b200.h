@@ -230,10 +230,13 @@ int pc_decode_layer(const pc_decode_step* step /* HOST */, void* out, const void
  * grouping instead of repeat_interleave; query i sees kv j <= i.
  * K/V rows are read through the same gather as pc_prune_prompt_and_cache, so the
  * pruned K/V never exists in memory.  req_meta int32 [num_reqs][6] =
- * {q_start, q_len, kv_src_start, kv_len(kept), first, pruned}. */
+ * {q_start, q_len, kv_src_start, kv_len(kept), first, pruned}; first and pruned are
+ * multiples of 16 (block sizes 16 / 32).  num_tokens = rows of query / key / value (the
+ * bound of the TMA tensor maps the tcgen05 kernel loads through). */
 int pc_prefill_attn_topleft_causal(void* out, const void* query, const void* key,
                                    const void* value, const int32_t* req_meta,
-                                   int32_t num_reqs, int32_t max_q_len, int32_t num_heads,
+                                   int32_t num_reqs, int32_t max_q_len, int64_t num_tokens,
+                                   int32_t num_heads,
                                    int32_t num_kv_heads, int32_t head_size, float scale,
                                    int64_t q_stride, int64_t out_stride, int64_t key_stride,
                                    int64_t value_stride, int32_t dtype, void* stream);

@@ -65,7 +65,7 @@ PROTOTYPES = {
                                              _I32, _F, _I64, _I64, _I64, _P, _SP, _P, _SZ,
                                              _I32, _P]),
     "pc_decode_layer": (C.c_int, [C.POINTER(PcDecodeStep), _P, _P, _P, _P, _P, _P, _SP, _P]),
-    "pc_prefill_attn_topleft_causal": (C.c_int, [_P, _P, _P, _P, _P, _I32, _I32, _I32, _I32, _I32, _F,
+    "pc_prefill_attn_topleft_causal": (C.c_int, [_P, _P, _P, _P, _P, _I32, _I32, _I64, _I32, _I32, _I32, _F,
                                                  _I64, _I64, _I64, _I64, _I32, _P]),
     "pc_copy_blocks": (C.c_int, [_P, _P, _P, _I32, _I64, _P]),
     "pc_swap_blocks": (C.c_int, [_P, _P, _P, _I32, _I64, _P]),

@@ -268,7 +268,8 @@ int pc_decode_layer(const pc_decode_step* st, void* out, const void* query, cons
 
 int pc_prefill_attn_topleft_causal(void* out, const void* query, const void* key,
                                    const void* value, const int32_t* req_meta,
-                                   int32_t num_reqs, int32_t max_q_len, int32_t num_heads,
+                                   int32_t num_reqs, int32_t max_q_len, int64_t num_tokens,
+                                   int32_t num_heads,
                                    int32_t num_kv_heads, int32_t head_size, float scale,
                                    int64_t q_stride, int64_t out_stride, int64_t key_stride,
                                    int64_t value_stride, int32_t dtype, void* stream) {
@@ -278,7 +279,7 @@ int pc_prefill_attn_topleft_causal(void* out, const void* query, const void* key
     return set_error(PC_ERR_INVALID, "pc_prefill_attn_topleft_causal: null pointer");
   PrefillArgs a{};
   a.out = out; a.q = query; a.k = key; a.v = value; a.req_meta = req_meta;
-  a.num_reqs = num_reqs; a.max_q_len = max_q_len; a.Hq = num_heads; a.Hkv = num_kv_heads;
+  a.num_reqs = num_reqs; a.max_q_len = max_q_len; a.num_tokens = num_tokens; a.Hq = num_heads; a.Hkv = num_kv_heads;
   a.D = head_size; a.scale = scale; a.q_stride = q_stride; a.out_stride = out_stride;
   a.key_stride = key_stride; a.value_stride = value_stride;
   return prefill_attn(a, static_cast<cudaStream_t>(stream));

@@ -104,6 +104,7 @@ struct PrefillArgs {
   int num_reqs, max_q_len, Hq, Hkv, D;
   float scale;
   long long q_stride, out_stride, key_stride, value_stride;
+  long long num_tokens;  // rows of q / k / v (bounds of the TMA tensor maps)
 };
 int prefill_attn(const PrefillArgs& a, cudaStream_t stream);     // dispatcher (tcgen05 unless variant 1)
 int prefill_attn_tc(const PrefillArgs& a, cudaStream_t stream);  // tcgen05/TMEM kernel

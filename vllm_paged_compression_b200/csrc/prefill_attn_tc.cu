@@ -9,9 +9,13 @@
 //   warps 0-3  softmax: thread t owns query row t = TMEM lane t.  S row out of TMEM
 //              (tcgen05.ld), online softmax in the exp2 domain, P (bf16) into shared
 //              memory as the A operand of P.V, lazy rescale of O in TMEM, epilogue.
-//   warp 4     K producer: Q tile once, then K tiles, cp.async gathers into the
-//              no-swizzle core-matrix layout ([16-byte chunk][row], chunk-major).
-//   warp 5     V producer (same layout; V is the MN-major B operand of P.V).
+//   warp 4     K producer (one lane): Q tile once, then K tiles, TMA tensor-map loads
+//              (cp.async.bulk.tensor.2d, SWIZZLE_128B) -- the streamingLLM gather is one
+//              16-row box per kept 16-token run, so the pruned K/V never exists in memory.
+//   warp 5     V producer (same; V is the MN-major B operand of P.V).
+//              (v1 gathered with cp.async: LDGSTS is served one thread per cycle by the
+//              L1TEX t-stage = 16 B/clk/SM, 87 % busy at 22 % tensor-pipe activity --
+//              profiles/r01_prefill_tc_v1_ncu_summary.txt.)
 //   warp 6     MMA issuer (one lane): S_j = Q K_j^T into one of two TMEM S buffers,
 //              O += P_j V_j into the TMEM O accumulator; tcgen05.commit -> mbarriers.
 // S_{j+1} is issued before P_j.V_j so the tensor pipe works on the next scores while the
@@ -21,6 +25,8 @@
 // of a row grows by more than 2^8 the warp rescales its 32 O rows in TMEM (ld, mul, st);
 // smaller increases keep the old reference max -- P and l stay consistent, the result is
 // mathematically identical and P stays <= 256 (exact in fp32, same relative bf16 rounding).
+#include <cuda.h>  // CUtensorMap (types only; the encoder is fetched through the runtime)
+
 #include "pc_api_internal.h"
 #include "tcgen05.cuh"
 
@@ -33,15 +39,13 @@ constexpr int kTcThreads = 224;
 constexpr float kRescaleThreshold = 8.f;  // log2 domain
 
 struct PrefillTcParams {
-  const __nv_bfloat16* __restrict__ q;
-  const __nv_bfloat16* __restrict__ k;
-  const __nv_bfloat16* __restrict__ v;
   __nv_bfloat16* __restrict__ out;
   const int* __restrict__ req_meta;  // [R][6] {q_start, q_len, kv_src_start, kv_len, first, pruned}
   int Hq, Hkv;
-  long long q_stride, out_stride, key_stride, value_stride;
+  long long out_stride;
   float scale_log2;
 };
+constexpr int kBoxRows = 16;   // K/V TMA box = one 16-token run (first, pruned are multiples of 16)
 
 // TN = kv rows per tile (UMMA N of S, K extent of P.V).  TN = 64 fits two CTAs per SM
 // (112 KB of shared memory and 256 TMEM columns each), TN = 128 one.
@@ -63,48 +67,15 @@ struct TcSmem {
 
 enum { B_QFULL = 0, B_KFULL = 1, B_VFULL = 3, B_SFULL = 5, B_PFULL = 7, B_PVDONE = 8, B_COUNT = 9 };
 
-// One warp gathers a [rows x D] bf16 tile into chunk-major core-matrix layout:
-//   byte(row, chunk) = chunk * (ROWS * 16) + row * 16      (chunk = 8 elements along D)
-// Lane mapping: the L1TEX tag stage coalesces only ADJACENT lanes (ncu: the first mapping,
-// lane -> (row % 8, chunk / 8), cost 32 tag wavefronts per LDGSTS and made the kernel
-// LSU-bound at 87 % of l1tex__t_output_wavefronts).  kGatherMap 1: lane -> (chunk % 4, row)
-// = 8 rows x 64 B per instruction; 2: lane -> (chunk % 8, row) = 4 rows x 128 B.
-#ifndef PC_GATHER_MAP
-#define PC_GATHER_MAP 2
-#endif
-template <int D, int ROWS, typename RowSrc>
-__device__ __forceinline__ void gather_tile(uint8_t* dst, int lane, RowSrc row_src) {
-  constexpr int CH = D / 8;
-#if PC_GATHER_MAP == 0
-  constexpr int RPI = 8, CPI = 4;
-  const int rl = lane & 7, cl = lane >> 3;
-#elif PC_GATHER_MAP == 1
-  constexpr int RPI = 8, CPI = 4;
-  const int rl = lane >> 2, cl = lane & 3;
-#else
-  constexpr int RPI = 4, CPI = 8;
-  const int rl = lane >> 3, cl = lane & 7;
-#endif
-#pragma unroll 4
-  for (int rg = 0; rg < ROWS / RPI; ++rg) {
-    const int row = rg * RPI + rl;
-    bool ok;
-    const __nv_bfloat16* src = row_src(row, ok);
-#pragma unroll
-    for (int cq = 0; cq < CH / CPI; ++cq) {
-      const int c = cq * CPI + cl;
-      cp_async_16_zfill(dst + c * (ROWS * 16) + row * 16, src + c * 8, ok);
-    }
-  }
-}
-
 }  // namespace
 
 namespace {
 
 template <int D, int TN>
 __global__ void __launch_bounds__(kTcThreads, (TN == 64 ? 2 : 1))
-prefill_attn_tc_kernel(const PrefillTcParams p) {
+prefill_attn_tc_kernel(const PrefillTcParams p, const __grid_constant__ CUtensorMap tm_q,
+                       const __grid_constant__ CUtensorMap tm_k,
+                       const __grid_constant__ CUtensorMap tm_v) {
   using L = TcSmem<D, TN>;
   constexpr int kTN = TN;
   constexpr int kTmemCols = L::kTmemCols;
@@ -130,9 +101,10 @@ prefill_attn_tc_kernel(const PrefillTcParams p) {
   const int ntiles = (kv_hi + kTN - 1) / kTN;
 
   if (tid == 0) {
-    mbar_init(&bar[B_QFULL], 32);
-    mbar_init(&bar[B_KFULL], 32); mbar_init(&bar[B_KFULL + 1], 32);
-    mbar_init(&bar[B_VFULL], 32); mbar_init(&bar[B_VFULL + 1], 32);
+    if ((smem_u32(smem) & 1023u) != 0u || (pruned != 0 && (((first | pruned) & 15) != 0))) __trap();
+    mbar_init(&bar[B_QFULL], 1);
+    mbar_init(&bar[B_KFULL], 1); mbar_init(&bar[B_KFULL + 1], 1);
+    mbar_init(&bar[B_VFULL], 1); mbar_init(&bar[B_VFULL + 1], 1);
     mbar_init(&bar[B_SFULL], 1);  mbar_init(&bar[B_SFULL + 1], 1);
     mbar_init(&bar[B_PFULL], kTM);
     mbar_init(&bar[B_PVDONE], 1); mbar_init(&bar[B_PVDONE + 1], 1);
@@ -146,38 +118,52 @@ prefill_attn_tc_kernel(const PrefillTcParams p) {
   const uint32_t tmem_o = tmem + 2 * kTN;
 
   if (warp == 4) {
-    // ================================================= Q + K producer
-    gather_tile<D, kTM>(smem + L::oQ, lane, [&](int row, bool& ok) {
-      ok = (i0 + row) < q_len;
-      return p.q + (size_t)(q_start + (ok ? i0 + row : 0)) * p.q_stride + (size_t)hq * D;
-    });
-    t5::cp_async_arrive_noinc(&bar[B_QFULL]);
-    for (int t = 0; t < ntiles; ++t) {
-      const int st = t & 1;
-      if (t >= 2) t5::mbar_wait_relaxed(&bar[B_SFULL + st], ((t - 2) >> 1) & 1);  // S_{t-2} done
-      const int j0 = t * kTN;
-      gather_tile<D, kTN>(smem + L::oK + st * L::kKV, lane, [&](int row, bool& ok) {
-        const int j = j0 + row;
-        ok = j < kv_len;
-        const long long src = (long long)kv_src + (ok ? (j < first ? j : j + pruned) : 0);
-        return p.k + (size_t)src * p.key_stride + (size_t)hkv * D;
-      });
-      t5::cp_async_arrive_noinc(&bar[B_KFULL + st]);
+    // ================================================= Q + K producer (one lane, TMA)
+    if (lane == 0) {
+      t5::tma_prefetch_desc(&tm_q);
+      t5::tma_prefetch_desc(&tm_k);
+      mbar_expect_tx(&bar[B_QFULL], L::kQ);
+#pragma unroll
+      for (int b = 0; b < D / 64; ++b)   // rows past q_len: next request's rows or TMA zero fill
+        t5::tma_load_2d(smem + L::oQ + b * (kTM * 128), &tm_q, hq * D + b * 64, q_start + i0, &bar[B_QFULL]);
+      for (int t = 0; t < ntiles; ++t) {
+        const int st = t & 1;
+        if (t >= 2) t5::mbar_wait_relaxed(&bar[B_SFULL + st], ((t - 2) >> 1) & 1);  // S_{t-2} done
+        mbar_expect_tx(&bar[B_KFULL + st], L::kKV);
+        uint8_t* dst = smem + L::oK + st * L::kKV;
+#pragma unroll
+        for (int g = 0; g < kTN / kBoxRows; ++g) {
+          const int j = t * kTN + g * kBoxRows;
+          const int src = kv_src + (j < first ? j : j + pruned);   // rows >= kv_len are masked
+#pragma unroll
+          for (int b = 0; b < D / 64; ++b)
+            t5::tma_load_2d(dst + b * (kTN * 128) + g * (kBoxRows * 128), &tm_k, hkv * D + b * 64, src,
+                            &bar[B_KFULL + st]);
+        }
+      }
     }
+    __syncwarp();
   } else if (warp == 5) {
-    // ================================================= V producer
-    for (int t = 0; t < ntiles; ++t) {
-      const int st = t & 1;
-      if (t >= 2) t5::mbar_wait_relaxed(&bar[B_PVDONE + st], ((t - 2) >> 1) & 1);  // P.V_{t-2} done
-      const int j0 = t * kTN;
-      gather_tile<D, kTN>(smem + L::oV + st * L::kKV, lane, [&](int row, bool& ok) {
-        const int j = j0 + row;
-        ok = j < kv_len;
-        const long long src = (long long)kv_src + (ok ? (j < first ? j : j + pruned) : 0);
-        return p.v + (size_t)src * p.value_stride + (size_t)hkv * D;
-      });
-      t5::cp_async_arrive_noinc(&bar[B_VFULL + st]);
+    // ================================================= V producer (one lane, TMA)
+    if (lane == 0) {
+      t5::tma_prefetch_desc(&tm_v);
+      for (int t = 0; t < ntiles; ++t) {
+        const int st = t & 1;
+        if (t >= 2) t5::mbar_wait_relaxed(&bar[B_PVDONE + st], ((t - 2) >> 1) & 1);  // P.V_{t-2} done
+        mbar_expect_tx(&bar[B_VFULL + st], L::kKV);
+        uint8_t* dst = smem + L::oV + st * L::kKV;
+#pragma unroll
+        for (int g = 0; g < kTN / kBoxRows; ++g) {
+          const int j = t * kTN + g * kBoxRows;
+          const int src = kv_src + (j < first ? j : j + pruned);
+#pragma unroll
+          for (int b = 0; b < D / 64; ++b)
+            t5::tma_load_2d(dst + b * (kTN * 128) + g * (kBoxRows * 128), &tm_v, hkv * D + b * 64, src,
+                            &bar[B_VFULL + st]);
+        }
+      }
     }
+    __syncwarp();
   } else if (warp == 6) {
     // ================================================= MMA issuer (one lane)
     if (lane == 0) {
@@ -186,12 +172,11 @@ prefill_attn_tc_kernel(const PrefillTcParams p) {
       auto issue_s = [&](int t) {
         const int st = t & 1;
         mbar_wait(&bar[B_KFULL + st], (t >> 1) & 1);
-        fence_proxy_async();
         t5::fence_after_sync();
 #pragma unroll
-        for (int ks = 0; ks < KS; ++ks) {
-          const uint64_t a = t5::smem_desc(sQ + ks * 2 * (kTM * 16), kTM * 16, 128);
-          const uint64_t b = t5::smem_desc(sK + st * L::kKV + ks * 2 * (kTN * 16), kTN * 16, 128);
+        for (int ks = 0; ks < KS; ++ks) {   // 64-element column block ks / 4, 32 bytes per k-step inside it
+          const uint64_t a = t5::smem_desc_sw128(sQ + (ks >> 2) * (kTM * 128) + (ks & 3) * 32, 16, 1024);
+          const uint64_t b = t5::smem_desc_sw128(sK + st * L::kKV + (ks >> 2) * (kTN * 128) + (ks & 3) * 32, 16, 1024);
           t5::mma_f16_ss(tmem + st * kTN, a, b, kIdescS, ks > 0);
         }
         t5::commit(&bar[B_SFULL + st]);
@@ -208,7 +193,7 @@ prefill_attn_tc_kernel(const PrefillTcParams p) {
 #pragma unroll
         for (int kk = 0; kk < PK; ++kk) {
           const uint64_t a = t5::smem_desc(sP + kk * 2 * (kTM * 16), kTM * 16, 128);
-          const uint64_t b = t5::smem_desc(sV + st * L::kKV + kk * 256, 128, kTN * 16);
+          const uint64_t b = t5::smem_desc_sw128(sV + st * L::kKV + kk * (16 * 128), kTN * 128, 1024);
           t5::mma_f16_ss(tmem_o, a, b, kIdescPV, (j > 0 || kk > 0));
         }
         t5::commit(&bar[B_PVDONE + st]);
@@ -329,30 +314,67 @@ prefill_attn_tc_kernel(const PrefillTcParams p) {
 
 }  // namespace
 
+// ---- host: tensor maps.  The encoder is a driver entry point fetched through the runtime
+// (no link against libcuda).
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
+                                  CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                  CUtensorMapFloatOOBfill);
+static EncodeTiledFn encode_tiled_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (fn == nullptr) {
+    void* sym = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(sym);
+  }
+  return fn;
+}
+// [rows, heads*D] bf16 matrix with row stride `stride` elements; box = 64 columns x box_rows,
+// SWIZZLE_128B (the UMMA SW128 canonical layouts), out-of-range rows read as zero.
+static int make_rows_map(CUtensorMap* m, const void* base, long long rows, int inner, long long stride,
+                         int box_rows) {
+  EncodeTiledFn enc = encode_tiled_fn();
+  if (enc == nullptr) return set_error(PC_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
+  const cuuint64_t gdim[2] = {(cuuint64_t)inner, (cuuint64_t)rows};
+  const cuuint64_t gstr[1] = {(cuuint64_t)stride * 2};
+  const cuuint32_t box[2] = {64u, (cuuint32_t)box_rows};
+  const cuuint32_t estr[2] = {1u, 1u};
+  const CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstr, box, estr,
+                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                         CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return set_error(PC_ERR_CUDA, "cuTensorMapEncodeTiled failed (prefill q/k/v map)");
+  return 0;
+}
+
 template <int D, int TN>
 static int launch_prefill_tc(const PrefillTcParams& p, const PrefillArgs& a, cudaStream_t stream) {
+  CUtensorMap tq, tk, tv;
+  if (int rc = make_rows_map(&tq, a.q, a.num_tokens, a.Hq * D, a.q_stride, kTM)) return rc;
+  if (int rc = make_rows_map(&tk, a.k, a.num_tokens, a.Hkv * D, a.key_stride, kBoxRows)) return rc;
+  if (int rc = make_rows_map(&tv, a.v, a.num_tokens, a.Hkv * D, a.value_stride, kBoxRows)) return rc;
   const int smem = TcSmem<D, TN>::kBytes;
   auto kern = prefill_attn_tc_kernel<D, TN>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   if (e != cudaSuccess) return set_cuda_error("cudaFuncSetAttribute(prefill_tc)", e);
   dim3 grid((a.max_q_len + kTM - 1) / kTM, a.Hq, a.num_reqs);
-  kern<<<grid, kTcThreads, smem, stream>>>(p);
+  kern<<<grid, kTcThreads, smem, stream>>>(p, tq, tk, tv);
   return check_launch("prefill_attn_tc_kernel");
 }
 
 static int g_tc_tile_n = 64;
 void set_prefill_tc_tile(int tn) { g_tc_tile_n = (tn == 128) ? 128 : 64; }
 
+// Requirements beyond prefill_attn()'s checks: num_tokens (rows of q/k/v) known, and
+// first / pruned multiples of 16 (block sizes 16 and 32; checked on the device, __trap).
 int prefill_attn_tc(const PrefillArgs& a, cudaStream_t stream) {
+  if (a.num_tokens <= 0) return set_error(PC_ERR_INVALID, "prefill: num_tokens must be the row count of q/k/v");
   PrefillTcParams p;
-  p.q = static_cast<const __nv_bfloat16*>(a.q);
-  p.k = static_cast<const __nv_bfloat16*>(a.k);
-  p.v = static_cast<const __nv_bfloat16*>(a.v);
   p.out = static_cast<__nv_bfloat16*>(a.out);
   p.req_meta = a.req_meta;
   p.Hq = a.Hq; p.Hkv = a.Hkv;
-  p.q_stride = a.q_stride; p.out_stride = a.out_stride;
-  p.key_stride = a.key_stride; p.value_stride = a.value_stride;
+  p.out_stride = a.out_stride;
   p.scale_log2 = a.scale * 1.4426950408889634f;
   if (a.D == 128)
     return g_tc_tile_n == 128 ? launch_prefill_tc<128, 128>(p, a, stream)

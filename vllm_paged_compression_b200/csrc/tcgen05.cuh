@@ -46,6 +46,17 @@ __device__ __forceinline__ uint64_t smem_desc(uint32_t saddr, uint32_t lbo, uint
          ((uint64_t)(sbo >> 4) << 32) | (1ull << 46);
 }
 
+// Same fields for the SWIZZLE_128B canonical layouts (layout type 2 at bits [61,64)), the
+// layout a TMA tensor map with CU_TENSOR_MAP_SWIZZLE_128B writes: rows of 128 bytes, 8-row
+// atoms of 1024 bytes (1024-byte aligned), 16-byte chunks XOR-ed with (row % 8).
+//   K-major operand : sbo = stride between 8-row atoms (1024 when rows are packed); lbo unused
+//       (one atom spans the 64-element K extent); advance K by 16 elements = +32 bytes.
+//   MN-major operand: 64 contiguous elements along M/N per 128-byte row, rows = K index;
+//       sbo = stride between 8-row (K) atoms, lbo = stride between 64-element M/N blocks.
+__device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t saddr, uint32_t lbo, uint32_t sbo) {
+  return smem_desc(saddr, lbo, sbo) | (2ull << 61);
+}
+
 // Instruction descriptor, kind::f16: D fp32 (bits [4,6) = 1), A/B bf16 ([7,10) = [10,13) = 1),
 // A K-major (bit 15 = 0), B major (bit 16), N>>3 at [17,23), M>>4 at [24,29).
 __host__ __device__ constexpr uint32_t instr_desc_bf16(int M, int N, bool b_mn_major) {
@@ -105,6 +116,21 @@ __device__ __forceinline__ void tmem_ld_wait() {
 }
 __device__ __forceinline__ void tmem_st_wait() {
   asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+}
+
+// ---------------------------------------------------------------- TMA (tensor map) loads
+// 2-D tile load global -> smem, completion on an mbarrier (complete_tx::bytes).  c0 = inner
+// (contiguous) coordinate in elements, c1 = row.  SASS: UTMALDG.
+__device__ __forceinline__ void tma_load_2d(void* smem_dst, const void* tmap, int c0, int c1,
+                                            uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes "
+      "[%0], [%1, {%2, %3}], [%4];" ::"r"(smem_u32(smem_dst)),
+      "l"(reinterpret_cast<uint64_t>(tmap)), "r"(c0), "r"(c1), "r"(smem_u32(bar))
+      : "memory");
+}
+__device__ __forceinline__ void tma_prefetch_desc(const void* tmap) {
+  asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(tmap)) : "memory");
 }
 
 // ---------------------------------------------------------------- mbarrier extras

@@ -332,7 +332,7 @@ def prefill_attn_topleft_causal(out: torch.Tensor, query: torch.Tensor, key: tor
             raise RuntimeError("q/k/v/out rows must be dense [H, D]")
     check(_lib.load().pc_prefill_attn_topleft_causal(
         out.data_ptr(), query.data_ptr(), key.data_ptr(), value.data_ptr(), req_meta.data_ptr(),
-        req_meta.shape[0], int(max_q_len), Hq, Hkv, D, float(scale), query.stride(0), out.stride(0),
+        req_meta.shape[0], int(max_q_len), int(min(T, key.shape[0], value.shape[0])), Hq, Hkv, D, float(scale), query.stride(0), out.stride(0),
         key.stride(0), value.stride(0), _dtype_code(query), _stream(query)))
     _launched()
 
