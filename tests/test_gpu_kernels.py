@@ -441,6 +441,67 @@ def test_prefill_attention_topleft_causal(Hq, Hkv, D, mode):
     np.testing.assert_allclose(got.numpy(), ref.numpy(), atol=2e-2, rtol=0)
 
 
+@pytest.mark.parametrize("case", [
+    # (Hq, Hkv, D, block, mode, evict_freq/budget, prompt_lens): tile edges of the tcgen05 kernel
+    # (128-query tiles, 64-wide kv tiles), multi-tile rows, block 32, both prune modes
+    (8, 2, 128, 16, "percentage", 2, [127, 128, 129, 255, 257, 700]),
+    (8, 2, 128, 16, "percentage", 4, [1024, 63, 65, 1500]),
+    (4, 1, 128, 32, "budget", 256, [96, 640, 1111]),
+    (8, 8, 64, 16, "budget", 128, [513, 64, 390]),
+    (16, 2, 128, 16, "none", 0, [300, 1, 900]),
+])
+def test_prefill_attention_tile_edges_and_strided_rows(case):
+    """q/k/v are column slices of one fused [T, (Hq + 2 Hkv) * D] buffer (row stride != H * D),
+    which is how the qkv projection hands them over (and exercises the tensor-map strides)."""
+    Hq, Hkv, D, bs, mode, knob, prompt_lens = case
+    ops = _ops()
+    pol = Policy(block_size=bs, cache_prune_type="budget" if mode == "none" else mode,
+                 cache_budget=(1 << 20) if mode == "none" else (knob if mode == "budget" else 128),
+                 evict_freq=knob if mode == "percentage" else 2)
+    T = sum(prompt_lens)
+    qkv = (rnd(51, T, (Hq + 2 * Hkv) * D).float() * 0.7).to(torch.bfloat16)
+    q = qkv[:, :Hq * D].view(T, Hq, D)
+    k = qkv[:, Hq * D:(Hq + Hkv) * D].view(T, Hkv, D)
+    v = qkv[:, (Hq + Hkv) * D:].view(T, Hkv, D)
+    meta, gidx, kept_l, s = [], [], [], 0
+    for L in prompt_lens:
+        kept, pruned, first = policy.prompt_prune_layout(L, pol)
+        meta.append([s, L, s, kept, first, pruned])
+        gidx.append(torch.from_numpy(policy.prompt_gather_index(L, pol)) + s)
+        kept_l.append(kept)
+        s += L
+    gidx = torch.cat(gidx)
+    ref = paged_ops.prefill_attention(q.contiguous(), k[gidx].contiguous(), v[gidx].contiguous(),
+                                      prompt_lens, kept_l, D ** -0.5).float()
+    dqkv = qkv.to(DEV)
+    dq = dqkv[:, :Hq * D].view(T, Hq, D)
+    dk = dqkv[:, Hq * D:(Hq + Hkv) * D].view(T, Hkv, D)
+    dv = dqkv[:, (Hq + Hkv) * D:].view(T, Hkv, D)
+    out = torch.full((T, Hq, D), float("nan"), dtype=torch.bfloat16, device=DEV)
+    ops.prefill_attn_topleft_causal(out, dq, dk, dv, torch.tensor(meta, dtype=torch.int32, device=DEV),
+                                    max(prompt_lens), D ** -0.5)
+    torch.cuda.synchronize()
+    got = out.float().cpu()
+    assert torch.isfinite(got).all()
+    np.testing.assert_allclose(got.numpy(), ref.numpy(), atol=2e-2, rtol=0)
+
+
+def test_prefill_attention_large_logits_rescale_path():
+    """Scores that grow along the row force the lazy O rescale in TMEM (max jumps > 2^8)."""
+    ops = _ops()
+    Hq, Hkv, D, L = 2, 1, 128, 640
+    q = torch.ones(L, Hq, D, dtype=torch.bfloat16) * 0.5
+    ramp = torch.linspace(0.0, 6.0, L).view(L, 1, 1)
+    k = (ramp * torch.ones(L, Hkv, D)).to(torch.bfloat16)          # logit_j ~ 0.5 * 6 j / L * D * scale
+    v = rnd(61, L, Hkv, D)
+    meta = torch.tensor([[0, L, 0, L, L, 0]], dtype=torch.int32, device=DEV)
+    ref = paged_ops.prefill_attention(q, k, v, [L], [L], D ** -0.5).float()
+    out = torch.full((L, Hq, D), float("nan"), dtype=torch.bfloat16, device=DEV)
+    ops.prefill_attn_topleft_causal(out, q.to(DEV), k.to(DEV), v.to(DEV), meta, L, D ** -0.5)
+    torch.cuda.synchronize()
+    np.testing.assert_allclose(out.float().cpu().numpy(), ref.numpy(), atol=2e-2, rtol=0)
+
+
 # ------------------------------------------------------------------ block maintenance
 def test_copy_and_swap_blocks():
     ops = _ops()
