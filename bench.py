@@ -68,6 +68,7 @@ def parse_args():
     ap.add_argument("--cpu-steps", type=int, default=0, help="0 = derive from a ~15 s budget")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-prefill", action="store_true", help="skip the prefill-attention tensor roofline leg")
     ap.add_argument("--no-graph", action="store_true",
                     help="eager PagedEvictEngine.step (one forward() per layer) instead of CUDA-graph replay")
     ap.add_argument("--no-pdl", action="store_true",
@@ -541,6 +542,24 @@ def main():
             tj = json.load(f)
         line["roofline"]["traffic"] = tj.get("dram_bytes_per_launch")
         line["roofline"]["traffic_source"] = tj.get("source")
+    if rank == 0 and world == 1 and not args.no_prefill:
+        # second roofline: prefill attention (A1) of the same workload, tensor-bound.  One layer's
+        # launch for 16 of the prompts (as the engine batches them), tcgen05 kernel, CUDA events.
+        from vllm_paged_compression_b200 import microbench_prefill
+        peaks = {}
+        ppath = os.path.join(REPO, "MEASURED_PEAKS.json")
+        if os.path.exists(ppath):
+            with open(ppath) as f:
+                peaks = json.load(f)
+        row, _ = microbench_prefill.run(device, 16, args.prompt_len, MODEL["Hq"], MODEL["Hkv"], MODEL["D"],
+                                        args.evict_freq, 20, 0)
+        tpeak = float(peaks.get("bf16_tflops", 2250.0))
+        line["prefill_roofline"] = {
+            "bound": "tensor", "kernel": "prefill_attn_tc_kernel (tcgen05.mma, TMEM accumulators, TMA loads)",
+            "achieved": row["tflops"], "peak": tpeak, "unit": "TFLOP/s", "frac": row["tflops"] / tpeak,
+            "peak_source": "measured burst (MEASURED_PEAKS.json bf16_tflops)" if peaks else "nominal dense bf16",
+            "us_per_launch": row["us"], "launch": f"16 prompts x {args.prompt_len} q, {row['kv_kept']} kept kv, "
+            "top-left causal, one layer", "flops_per_launch": row["tflops"] * 1e12 * row["us"] * 1e-6}
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cpu_args = argparse.Namespace(**vars(args))
         carm = CpuArm(cpu_args, 1)

@@ -100,6 +100,18 @@ prefill_attn_tc_kernel(const PrefillTcParams p, const __grid_constant__ CUtensor
   const int kv_hi = min(kv_len, i0 + kTM);
   const int ntiles = (kv_hi + kTN - 1) / kTN;
 
+  // one K or V tile = one 16-row TMA box per kept 16-token run and 64-column block
+  auto issue_kv = [&](const CUtensorMap* tm, uint8_t* dst, uint64_t* full, int t) {
+    mbar_expect_tx(full, L::kKV);
+#pragma unroll
+    for (int g = 0; g < kTN / kBoxRows; ++g) {
+      const int j = t * kTN + g * kBoxRows;
+      const int src = kv_src + (j < first ? j : j + pruned);   // rows >= kv_len are masked
+#pragma unroll
+      for (int b = 0; b < D / 64; ++b)
+        t5::tma_load_2d(dst + b * (kTN * 128) + g * (kBoxRows * 128), tm, hkv * D + b * 64, src, full);
+    }
+  };
   if (tid == 0) {
     if ((smem_u32(smem) & 1023u) != 0u || (pruned != 0 && (((first | pruned) & 15) != 0))) __trap();
     mbar_init(&bar[B_QFULL], 1);
@@ -109,6 +121,14 @@ prefill_attn_tc_kernel(const PrefillTcParams p, const __grid_constant__ CUtensor
     mbar_init(&bar[B_PFULL], kTM);
     mbar_init(&bar[B_PVDONE], 1); mbar_init(&bar[B_PVDONE + 1], 1);
     mbar_fence_init();
+    // first loads go out before the CTA-wide sync, so their latency overlaps the TMEM
+    // allocation and the role dispatch: Q tile, K_0, V_0
+    mbar_expect_tx(&bar[B_QFULL], L::kQ);
+#pragma unroll
+    for (int b = 0; b < D / 64; ++b)   // rows past q_len: next request's rows or TMA zero fill
+      t5::tma_load_2d(smem + L::oQ + b * (kTM * 128), &tm_q, hq * D + b * 64, q_start + i0, &bar[B_QFULL]);
+    issue_kv(&tm_k, smem + L::oK, &bar[B_KFULL], 0);
+    issue_kv(&tm_v, smem + L::oV, &bar[B_VFULL], 0);
   }
   if (warp == 6) t5::tmem_alloc<kTmemCols>(tmem_slot);
   t5::fence_before_sync();
@@ -118,49 +138,22 @@ prefill_attn_tc_kernel(const PrefillTcParams p, const __grid_constant__ CUtensor
   const uint32_t tmem_o = tmem + 2 * kTN;
 
   if (warp == 4) {
-    // ================================================= Q + K producer (one lane, TMA)
+    // ================================================= K producer (one lane, TMA)
     if (lane == 0) {
-      t5::tma_prefetch_desc(&tm_q);
-      t5::tma_prefetch_desc(&tm_k);
-      mbar_expect_tx(&bar[B_QFULL], L::kQ);
-#pragma unroll
-      for (int b = 0; b < D / 64; ++b)   // rows past q_len: next request's rows or TMA zero fill
-        t5::tma_load_2d(smem + L::oQ + b * (kTM * 128), &tm_q, hq * D + b * 64, q_start + i0, &bar[B_QFULL]);
-      for (int t = 0; t < ntiles; ++t) {
+      for (int t = 1; t < ntiles; ++t) {
         const int st = t & 1;
         if (t >= 2) t5::mbar_wait_relaxed(&bar[B_SFULL + st], ((t - 2) >> 1) & 1);  // S_{t-2} done
-        mbar_expect_tx(&bar[B_KFULL + st], L::kKV);
-        uint8_t* dst = smem + L::oK + st * L::kKV;
-#pragma unroll
-        for (int g = 0; g < kTN / kBoxRows; ++g) {
-          const int j = t * kTN + g * kBoxRows;
-          const int src = kv_src + (j < first ? j : j + pruned);   // rows >= kv_len are masked
-#pragma unroll
-          for (int b = 0; b < D / 64; ++b)
-            t5::tma_load_2d(dst + b * (kTN * 128) + g * (kBoxRows * 128), &tm_k, hkv * D + b * 64, src,
-                            &bar[B_KFULL + st]);
-        }
+        issue_kv(&tm_k, smem + L::oK + st * L::kKV, &bar[B_KFULL + st], t);
       }
     }
     __syncwarp();
   } else if (warp == 5) {
     // ================================================= V producer (one lane, TMA)
     if (lane == 0) {
-      t5::tma_prefetch_desc(&tm_v);
-      for (int t = 0; t < ntiles; ++t) {
+      for (int t = 1; t < ntiles; ++t) {
         const int st = t & 1;
         if (t >= 2) t5::mbar_wait_relaxed(&bar[B_PVDONE + st], ((t - 2) >> 1) & 1);  // P.V_{t-2} done
-        mbar_expect_tx(&bar[B_VFULL + st], L::kKV);
-        uint8_t* dst = smem + L::oV + st * L::kKV;
-#pragma unroll
-        for (int g = 0; g < kTN / kBoxRows; ++g) {
-          const int j = t * kTN + g * kBoxRows;
-          const int src = kv_src + (j < first ? j : j + pruned);
-#pragma unroll
-          for (int b = 0; b < D / 64; ++b)
-            t5::tma_load_2d(dst + b * (kTN * 128) + g * (kBoxRows * 128), &tm_v, hkv * D + b * 64, src,
-                            &bar[B_VFULL + st]);
-        }
+        issue_kv(&tm_v, smem + L::oV + st * L::kKV, &bar[B_VFULL + st], t);
       }
     }
     __syncwarp();
