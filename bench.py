@@ -51,6 +51,29 @@ MODEL = dict(name="Llama-3.1-8B", layers=32, Hq=32, Hkv=8, D=128)
 METRIC = "decode_tok_per_s_paged_eviction_hot_path"
 
 
+_RESULT_FD = None
+
+
+def guard_stdout():
+    """The contract is ONE JSON line on stdout.  Libraries print there too (NCCL's
+    'NCCL version ...' banner when NCCL_DEBUG=VERSION/WARN is set on the box), so fd 1 is
+    pointed at stderr for the whole run and the result goes out through a saved copy."""
+    global _RESULT_FD
+    if _RESULT_FD is None:
+        sys.stdout.flush()
+        _RESULT_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _RESULT_FD is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_RESULT_FD, data)
+
+
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -75,6 +98,9 @@ def parse_args():
                     help="no programmatic dependent launch between consecutive layers' decode kernels")
     ap.add_argument("--score-exchange", default="p2p", choices=["p2p", "nccl"],
                     help="N > 1: how per-head block scores reach the other ranks (parallel.py)")
+    ap.add_argument("--tp-emulate", type=int, default=1,
+                    help="debug: one GPU does ONE rank's work of a TP=N job (heads / N, batch x N, no "
+                         "score exchange) -- for profiling the per-rank launch shape on a 1-GPU box")
     ap.add_argument("--sweep", action="store_true",
                     help="kernel microbench (BASELINE.json configs[1]) -> table on stdout")
     return ap.parse_args()
@@ -158,8 +184,9 @@ class Arm:
         self.torch = torch
         self.args, self.device, self.host_io = args, device, host_io
         self.L = args.layers
-        self.Hq, self.Hkv, self.D = MODEL["Hq"] // world, MODEL["Hkv"] // world, MODEL["D"]
-        self.B = args.batch * world
+        div = world if world > 1 else max(1, getattr(args, "tp_emulate", 1))
+        self.Hq, self.Hkv, self.D = MODEL["Hq"] // div, MODEL["Hkv"] // div, MODEL["D"]
+        self.B = args.batch * div
         bs = args.block_size
         cc = make_cache_config(args, self.B)
         blocks_per_seq = -(-(args.prompt_len + args.steps + args.warmup + 2 * bs) // bs) + 2
@@ -222,10 +249,11 @@ class Arm:
         kv_now = max(self.eng.block_manager.get_seq_kv_len(s.seq_id) for s in self.eng.running)
         bound = kv_now + a.steps + a.warmup + 2 * a.block_size + 64
         if self.host_io:
-            self.runner = DecodeGraphRunner(self.eng, None, io=self.io, max_kv_len=bound, pdl=not a.no_pdl)
+            self.runner = DecodeGraphRunner(self.eng, None, io=self.io, max_kv_len=bound,
+                                            pdl=False if a.no_pdl else None)
         else:
             self.runner = DecodeGraphRunner(self.eng, list(zip(self.q, self.k, self.v)), max_kv_len=bound,
-                                            pdl=not a.no_pdl)
+                                            pdl=False if a.no_pdl else None)
 
     def step(self) -> int:
         """One decode step of the whole batch; -> blocks evicted (layer-0 feedback)."""
@@ -296,7 +324,7 @@ def roofline_leg(torch, arm, args, reps=20):
     ds = ops.make_decode_step(md.slot_mapping, md.block_tables, kv_lens, md.seq_lens_tensor, arm.B, arm.Hq,
                               arm.Hkv, arm.D, args.block_size, max_kv, scale, qs[0].stride(0), ks[0].stride(0),
                               vs[0].stride(0), outs.stride(0), caches[0][1].stride(0), fuse_cache_write=True,
-                              pdl=not args.no_pdl)
+                              pdl=(not args.no_pdl) and ops.pdl_default(arm.B))
 
     def run_all():
         for l in range(arm.L):
@@ -439,7 +467,7 @@ def run_reference(args, rank, world):
         "e2e": {"value": r["value"], "unit": "tok/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ------------------------------------------------------------------------ main
@@ -450,6 +478,8 @@ def main():
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     if world != args.gpus and world > 1:
         args.gpus = world
+    if not args.sweep:
+        guard_stdout()
     if args.impl == "reference":
         run_reference(args, rank, world)
         return
@@ -484,6 +514,8 @@ def main():
     arm.make_runner()
     sec, evictions, launches = timed_steps(torch, dist, arm, K, W, world)
     per_launch_s, alg_bytes, kv_lens_host = roofline_leg(torch, arm, args)
+    from vllm_paged_compression_b200 import ops as _ops
+    pdl_used = (not args.no_pdl) and _ops.pdl_default(arm.B)
     clocks = sampler.stop() if sampler else None        # sampled over the timed steps + the roofline leg
     if world > 1:
         t = torch.tensor([per_launch_s], device=device, dtype=torch.float64)
@@ -531,7 +563,7 @@ def main():
         "roofline": {"bound": "hbm", "kernel": "paged_decode_attn_score_kernel", "achieved": achieved,
                      "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
                      "peak_source": peak_src, "algorithmic_bytes_per_launch": alg_bytes,
-                     "launch": "pc_decode_layer as in the step: fused cache write" + ("" if args.no_pdl else ", PDL") +
+                     "launch": "pc_decode_layer as in the step: fused cache write" + (", PDL" if pdl_used else "") +
                                ", back to back over the layers' pools, CUDA events",
                      "us_per_launch": per_launch_s * 1e6},
     }
@@ -570,7 +602,7 @@ def main():
         line["cpu_baseline"] = {k: v for k, v in carm.run(ck, 1).items() if k != "ms_per_step"}
         line["cpu_baseline"]["unit"] = "tok/s"
     if rank == 0:
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()

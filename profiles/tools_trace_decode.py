@@ -7,11 +7,12 @@ lib.pc_debug_set_decode_trace.argtypes = [ctypes.c_void_p]
 lib.pc_debug_set_decode_trace.restype = None
 dev = torch.device('cuda', 0)
 B, ctx = int(sys.argv[1]), int(sys.argv[2])
+HQ, HKV = (int(sys.argv[3]), int(sys.argv[4])) if len(sys.argv) > 4 else (32, 8)
 buf = torch.zeros(148 * 8 * 8, dtype=torch.int64, device=dev)
 # warm without trace
-print(microbench.time_shape(dev, B, ctx, 32, 8, reps=10)['us'])
+print(microbench.time_shape(dev, B, ctx, HQ, HKV, reps=10)['us'])
 lib.pc_debug_set_decode_trace(buf.data_ptr())
-r = microbench.time_shape(dev, B, ctx, 32, 8, reps=1)
+r = microbench.time_shape(dev, B, ctx, HQ, HKV, reps=1)
 torch.cuda.synchronize()
 lib.pc_debug_set_decode_trace(None)
 raw = buf.cpu().numpy().reshape(-1, 8)

@@ -109,7 +109,7 @@ struct DecodeTraits {
   static constexpr int kFifoBytes = kWarps * kFifo * (int)sizeof(ChunkDesc);
   static constexpr int kThreads = kWarps * 32;
   static size_t smem_bytes(int B) {
-    return (size_t)kRingBytes + kBarBytes + kFifoBytes + ((size_t)B + 1) * 4;
+    return (size_t)kRingBytes + kBarBytes + kFifoBytes + ((size_t)B + 1) * 4 + 64;  // + wsum[kWarps]
   }
 };
 
@@ -182,25 +182,37 @@ paged_decode_attn_score_kernel(const DecodeParams p) {
   // kernel -- the caller's promise when it sets `pdl`), so the first ring of pages is in
   // flight while the preceding kernel drains.
   if (p.pdl) asm volatile("griddepcontrol.launch_dependents;");
-  for (int r = threadIdx.x; r < p.B; r += T::kThreads) {
-    const int len = p.kv_lens[r];
-    cpre[r + 1] = ((len + BS - 1) / BS + chunk_pages - 1) / chunk_pages;
-  }
-  __syncthreads();
-  if (warp == 0) {
+  {
+    // block-wide scan, kThreads rows per pass (a one-warp scan cost 1.2 us of prologue at
+    // B = 512, the per-rank batch of the TP = 8 bench)
+    int* wsum = cpre + p.B + 1;   // [kWarps]
     int carry = 0;
-    for (int base = 0; base < p.B; base += 32) {
-      const int r = base + lane;
-      int n = (r < p.B) ? cpre[r + 1] : 0;
+    for (int base = 0; base < p.B; base += T::kThreads) {
+      const int r = base + threadIdx.x;
+      int n = 0;
+      if (r < p.B) {
+        const int len = p.kv_lens[r];
+        n = ((len + BS - 1) / BS + chunk_pages - 1) / chunk_pages;
+      }
 #pragma unroll
       for (int sh = 1; sh < 32; sh <<= 1) {
         const int v = __shfl_up_sync(kFull, n, sh);
         if (lane >= sh) n += v;
       }
-      if (r < p.B) cpre[r + 1] = carry + n;
-      carry += __shfl_sync(kFull, n, 31);
+      if (lane == 31) wsum[warp] = n;
+      __syncthreads();
+      int off = carry, tot = 0;
+#pragma unroll
+      for (int i = 0; i < kWarps; ++i) {
+        const int v = wsum[i];
+        off += (i < warp) ? v : 0;
+        tot += v;
+      }
+      if (r < p.B) cpre[r + 1] = off + n;
+      carry += tot;
+      __syncthreads();
     }
-    if (lane == 0) cpre[0] = 0;
+    if (threadIdx.x == 0) cpre[0] = 0;
   }
   mbar_fence_init();
   __syncthreads();

@@ -35,7 +35,7 @@ from .policy import cdiv
 class DecodeGraphRunner:
     def __init__(self, engine, qkv: Optional[Sequence[Tuple[torch.Tensor, torch.Tensor, torch.Tensor]]],
                  outs: Optional[Sequence[torch.Tensor]] = None, io=None, max_kv_len: Optional[int] = None,
-                 use_graph: bool = True, pdl: bool = True) -> None:
+                 use_graph: bool = True, pdl: Optional[bool] = None) -> None:
         """engine: PagedEvictEngine whose `running` sequences are all prefilled.
         qkv[l] = (query [B,Hq*D], key [B,Hkv*D], value [B,Hkv*D]) STATIC device tensors the
         caller refills before every step (ignored when `io` is given: PinnedLayerIO supplies
@@ -45,7 +45,7 @@ class DecodeGraphRunner:
         self.device = eng.device
         self.io = io
         self.use_graph = use_graph
-        self.pdl = pdl
+        self.pdl = ops.pdl_default(len(eng.running)) if pdl is None else pdl   # None = measured rule
         self.seqs = list(eng.running)
         if not self.seqs:
             raise RuntimeError("DecodeGraphRunner needs running (prefilled) sequences")

@@ -27,7 +27,7 @@ def _peak():
 
 
 def time_shape(device, B, ctx, Hq, Hkv, D=128, bs=16, ragged=False, score=True, reps=None,
-               max_pool_bytes=48 << 30, seed=0):
+               max_pool_bytes=48 << 30, seed=0, sequential=False):
     g = torch.Generator(device=device)
     g.manual_seed(seed)
     if ragged:
@@ -53,6 +53,8 @@ def time_shape(device, B, ctx, Hq, Hkv, D=128, bs=16, ragged=False, score=True, 
     kc = kv[0].view(nb, Hkv, D // 8, bs, 8)
     vc = kv[1].view(nb, Hkv, D, bs)
     perm = torch.randperm(nb, device=device, generator=g).to(torch.int32)
+    if sequential:                                          # a sequence's blocks are consecutive ids (fresh allocator)
+        perm = torch.arange(nb, device=device, dtype=torch.int32)
     tables = [perm[i * blocks_per_set:(i + 1) * blocks_per_set].view(B, M).contiguous() for i in range(n_sets)]
     q = (torch.rand(B, Hq, D, device=device, generator=g) * 2 * s - s).to(torch.bfloat16)
     out = torch.empty_like(q)
@@ -108,10 +110,13 @@ def main():
     ap.add_argument("--D", type=int, default=128)
     ap.add_argument("--block", type=int, default=16)
     ap.add_argument("--ragged", action="store_true")
+    ap.add_argument("--sequential", action="store_true", help="consecutive block ids per sequence")
+    ap.add_argument("--no-score", action="store_true")
     ap.add_argument("--reps", type=int, default=None)
     a = ap.parse_args()
     dev = torch.device("cuda", 0)
-    print(json.dumps(time_shape(dev, a.B, a.ctx, a.Hq, a.Hkv, a.D, a.block, a.ragged, reps=a.reps)), flush=True)
+    print(json.dumps(time_shape(dev, a.B, a.ctx, a.Hq, a.Hkv, a.D, a.block, a.ragged, score=not a.no_score, reps=a.reps,
+                                sequential=a.sequential)), flush=True)
 
 
 if __name__ == "__main__":

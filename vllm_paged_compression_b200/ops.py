@@ -316,6 +316,15 @@ def paged_attention_v2(out, exp_sums, max_logits, tmp_out, query, key_cache, val
                             max_seq_len)
 
 
+def pdl_default(batch: int) -> bool:
+    """Programmatic dependent launch between consecutive layers' decode kernels: measured on
+    B200 at the bench shape (512 (row, kv-head) groups x 37 pages per launch, us per launch,
+    PDL / plain): B 64 30.4 / 34.6, B 128 32.9 / 34.7, B 256 38.5 / 36.4, B 512 47.5 / 40.5
+    (profiles/r01_tp_shape_pdl.txt) -- the early-launched CTAs pay off only while the batch
+    (and with it the O(B) schedule prologue they run ahead of the dependency wait) is small."""
+    return batch <= 128
+
+
 # ------------------------------------------------------------------------------ A1
 def prefill_attn_topleft_causal(out: torch.Tensor, query: torch.Tensor, key: torch.Tensor,
                                 value: torch.Tensor, req_meta: torch.Tensor, max_q_len: int,
