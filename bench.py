@@ -98,6 +98,8 @@ def parse_args():
                     help="no programmatic dependent launch between consecutive layers' decode kernels")
     ap.add_argument("--score-exchange", default="p2p", choices=["p2p", "nccl"],
                     help="N > 1: how per-head block scores reach the other ranks (parallel.py)")
+    ap.add_argument("--io-group", type=int, default=0,
+                    help="e2e leg: layers per host<->device copy group (PinnedLayerIO); 0 = ramp 1,1,2,4..4,2,1,1")
     ap.add_argument("--tp-emulate", type=int, default=1,
                     help="debug: one GPU does ONE rank's work of a TP=N job (heads / N, batch x N, no "
                          "score exchange) -- for profiling the per-rank launch shape on a 1-GPU box")
@@ -217,7 +219,7 @@ class Arm:
         if host_io:
             from vllm_paged_compression_b200.engine import PinnedLayerIO
             # fused [B, (Hq + 2 Hkv) D] rows per layer in pinned host memory (what qkv_proj emits)
-            self.io = PinnedLayerIO(self.L, self.B, self.Hq, self.Hkv, self.D, device)
+            self.io = PinnedLayerIO(self.L, self.B, self.Hq, self.Hkv, self.D, device, group=args.io_group)
             for l in range(self.L):
                 self.io.qkv_host[l].copy_(torch.cat([self.q[l], self.k[l], self.v[l]], dim=1).cpu())
             self.h2d, self.d2h = self.io.h2d_bytes, self.io.d2h_bytes

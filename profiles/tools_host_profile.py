@@ -9,11 +9,20 @@ args = bench.parse_args()
 dev = torch.device('cuda', 0)
 arm = bench.Arm(args, dev, 0, 1, host_io=False)
 arm.prefill()
+arm.make_runner()
 for _ in range(8):
     arm.step()
 torch.cuda.synchronize()
 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 N = 24
+# host cost of a step with an idle GPU queue (sync before every step): what the e2e leg exposes
+hs = []
+for _ in range(N):
+    torch.cuda.synchronize()
+    t0 = time.perf_counter(); arm.step(); hs.append(time.perf_counter() - t0)
+hs.sort()
+print("host issue time per step, idle queue: p50 %.3f ms  min %.3f  max %.3f" % (hs[N // 2] * 1e3, hs[0] * 1e3, hs[-1] * 1e3))
+torch.cuda.synchronize()
 e0.record(); t0 = time.perf_counter()
 for _ in range(N):
     arm.step()

@@ -16,6 +16,8 @@ backend sees too.
 """
 from __future__ import annotations
 
+import os
+
 from dataclasses import dataclass, field
 from typing import Callable, Dict, List, Optional, Tuple
 
@@ -253,8 +255,29 @@ class PinnedLayerIO:
     """
 
     def __init__(self, num_layers: int, batch: int, num_heads: int, num_kv_heads: int, head_size: int,
-                 device, group: int = 4, dtype=torch.bfloat16) -> None:
-        self.L, self.B, self.group = num_layers, batch, max(1, group)
+                 device, group: int = 4, dtype=torch.bfloat16, duplex: Optional[bool] = None) -> None:
+        self.L, self.B = num_layers, batch
+        # copy groups: `group` layers each, or group=0 -> a ramp (1, 1, 2, 4, ... 4, 2, 1, 1): the first
+        # group's H2D and the last group's D2H are the only copies a step cannot hide behind
+        # compute, so those groups are one layer; the middle ones stay large (a group boundary
+        # costs the next layer its programmatic dependent launch)
+        if group and group > 0:
+            sizes = [min(group, num_layers - lo) for lo in range(0, num_layers, group)]
+        else:
+            head = [1, 1, 2]
+            sizes = head + [4] * max(0, (num_layers - 2 * sum(head)) // 4)
+            sizes += [num_layers - sum(sizes) - sum(head)] if num_layers - sum(sizes) - sum(head) > 0 else []
+            sizes += head[::-1]
+            if sum(sizes) != num_layers or min(sizes) < 1:
+                sizes = [1] * num_layers
+        self.bounds = []
+        lo = 0
+        for n in sizes:
+            self.bounds.append((lo, lo + n))
+            lo += n
+        self.gidx = [gi for gi, (a, b) in enumerate(self.bounds) for _ in range(a, b)]
+        self.is_first = [l == self.bounds[self.gidx[l]][0] for l in range(num_layers)]
+        self.is_last = [l + 1 == self.bounds[self.gidx[l]][1] for l in range(num_layers)]
         self.qw, self.kw = num_heads * head_size, num_kv_heads * head_size
         w = self.qw + 2 * self.kw
         self.device = torch.device(device)
@@ -263,8 +286,13 @@ class PinnedLayerIO:
         self.qkv_dev = torch.empty(num_layers, batch, w, dtype=dtype, device=self.device)
         self.out_dev = torch.empty(num_layers, batch, self.qw, dtype=dtype, device=self.device)
         self.h2d_stream = torch.cuda.Stream(self.device)
-        self.d2h_stream = torch.cuda.Stream(self.device)
-        n_groups = -(-num_layers // self.group)
+        # duplex=False: both directions share ONE copy stream.  Measured on the B200 boxes of
+        # this pool, simultaneous H2D + D2H run at ~12 GB/s each way against 48 / 56 GB/s alone
+        # (profiles/r01_e2e_breakdown.txt), so serialised copies finish sooner than overlapped ones.
+        if duplex is None:
+            duplex = os.environ.get("PC_IO_DUPLEX", "0") == "1"
+        self.d2h_stream = torch.cuda.Stream(self.device) if duplex else self.h2d_stream
+        n_groups = len(self.bounds)
         self.h2d_done = [torch.cuda.Event() for _ in range(n_groups)]
         self.grp_done = [torch.cuda.Event() for _ in range(n_groups)]
         self.step_done = torch.cuda.Event()
@@ -278,13 +306,13 @@ class PinnedLayerIO:
         self.h2d_stream.wait_stream(cur)
         with torch.cuda.stream(self.h2d_stream):
             for gi in range(len(self.h2d_done)):
-                lo, hi = gi * self.group, min(self.L, (gi + 1) * self.group)
+                lo, hi = self.bounds[gi]
                 self.qkv_dev[lo:hi].copy_(self.qkv_host[lo:hi], non_blocking=True)
                 self.h2d_done[gi].record(self.h2d_stream)
 
     def qkv(self, layer: int, n_tok: int, wait: bool = True):
-        if wait and layer % self.group == 0:
-            torch.cuda.current_stream(self.device).wait_event(self.h2d_done[layer // self.group])
+        if wait and self.is_first[layer]:
+            torch.cuda.current_stream(self.device).wait_event(self.h2d_done[self.gidx[layer]])
         row = self.qkv_dev[layer]
         return row[:, :self.qw], row[:, self.qw:self.qw + self.kw], row[:, self.qw + self.kw:]
 
@@ -294,12 +322,12 @@ class PinnedLayerIO:
     def put_out(self, layer: int, out: torch.Tensor) -> None:
         if out.data_ptr() != self.out_dev[layer].data_ptr():
             self.out_dev[layer].copy_(out.view(self.B, self.qw))
-        if (layer + 1) % self.group == 0 or layer == self.L - 1:
-            gi = layer // self.group
+        if self.is_last[layer]:
+            gi = self.gidx[layer]
             cur = torch.cuda.current_stream(self.device)
             self.grp_done[gi].record(cur)
             self.d2h_stream.wait_event(self.grp_done[gi])
-            lo = gi * self.group
+            lo = self.bounds[gi][0]
             with torch.cuda.stream(self.d2h_stream):
                 self.out_host[lo:layer + 1].copy_(self.out_dev[lo:layer + 1], non_blocking=True)
 

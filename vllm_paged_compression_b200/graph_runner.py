@@ -146,11 +146,11 @@ class DecodeGraphRunner:
         if io is not None:
             io.begin_step()
         for l in range(self.L):
-            if io is not None and l % io.group == 0:
-                cur.wait_event(io.h2d_done[l // io.group])
+            if io is not None and io.is_first[l]:
+                cur.wait_event(io.h2d_done[io.gidx[l]])
             q, k, v = self.qkv[l]
             kptr, vptr, score = self.layers[l]
-            chained = l > 0 and (io is None or l % io.group != 0)
+            chained = l > 0 and (io is None or not io.is_first[l])
             ops.decode_layer(ds_pdl if chained else ds, self.outs[l], q, k, v, kptr, vptr, score,
                              self.d_victims[l] if trig else None)
             if io is not None:
