@@ -317,5 +317,6 @@ void pc_debug_set_decode_trace(void* device_buf) { pc::set_decode_trace(device_b
  * (kept only so the two can be timed side by side). */
 void pc_debug_set_prefill_variant(int32_t v) { pc::set_prefill_variant(v); }
 void pc_debug_set_prefill_tc_tile(int32_t tn) { pc::set_prefill_tc_tile(tn); }
+void pc_debug_set_prefill_tc_persistent(int32_t v) { pc::set_prefill_tc_persistent(v); }
 
 }  // extern "C"

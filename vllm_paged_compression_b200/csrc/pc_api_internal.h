@@ -108,6 +108,7 @@ struct PrefillArgs {
 };
 int prefill_attn(const PrefillArgs& a, cudaStream_t stream);     // dispatcher (tcgen05 unless variant 1)
 int prefill_attn_tc(const PrefillArgs& a, cudaStream_t stream);  // tcgen05/TMEM kernel
+void set_prefill_tc_persistent(int v);  // debug: 1 = persistent CTAs (default), 0 = one CTA per query tile
 void set_prefill_tc_tile(int tn);  // debug: kv tile width of the tcgen05 kernel (64 | 128)
 void set_prefill_variant(int v);  // debug: 0 = tcgen05/TMEM (product), 1 = mma.sync baseline kernel
 

@@ -307,6 +307,289 @@ prefill_attn_tc_kernel(const PrefillTcParams p, const __grid_constant__ CUtensor
 
 }  // namespace
 
+// ---------------------------------------------------------------------------------------
+// Persistent variant: a CTA walks work items (query tile, q head, request) k = blockIdx.x,
+// + gridDim.x, ...; heaviest query tiles first.  TMEM allocation, barrier setup and the
+// role dispatch happen once; the mbarrier phases simply keep counting over a CTA-wide tile
+// counter g.  The next item's Q tile is requested as soon as the last S MMA of the current
+// item has read Q, i.e. one tile before the item ends, so its latency hides behind the last
+// softmax + P.V + epilogue (the one-shot kernel pays launch, setup, first-load latency and
+// teardown per 128-query tile: 33 % tensor-pipe activity on 1024-token prompts, ncu).
+struct TcItem {
+  int q_start, q_len, kv_src, kv_len, first, pruned, i0, hq, hkv, ntiles;
+};
+
+template <int D, int TN>
+__global__ void __launch_bounds__(kTcThreads, (TN == 64 ? 2 : 1))
+prefill_attn_tc_persist_kernel(const PrefillTcParams p, const __grid_constant__ CUtensorMap tm_q,
+                               const __grid_constant__ CUtensorMap tm_k,
+                               const __grid_constant__ CUtensorMap tm_v, const int q_tiles,
+                               const int num_reqs) {
+  using L = TcSmem<D, TN>;
+  constexpr int kTN = TN;
+  constexpr int kTmemCols = L::kTmemCols;
+  constexpr int SC = TN / 32;
+  constexpr int KS = D / 16;
+  constexpr int PK = kTN / 16;
+  constexpr uint32_t kIdescS = t5::instr_desc_bf16(kTM, kTN, false);
+  constexpr uint32_t kIdescPV = t5::instr_desc_bf16(kTM, D, true);
+  extern __shared__ __align__(1024) uint8_t smem[];
+  uint64_t* bar = reinterpret_cast<uint64_t*>(smem + L::oBar);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar + B_COUNT);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int per_qt = p.Hq * num_reqs;
+  const int total = q_tiles * per_qt;
+  const int G = p.Hq / p.Hkv;
+
+  // item k -> (query tile descending, request, q head); ntiles == 0: nothing to do
+  auto get_item = [&](int k) {
+    TcItem it;
+    const int qt = q_tiles - 1 - k / per_qt;
+    const int rem = k % per_qt;
+    const int r = rem / p.Hq;
+    it.hq = rem - r * p.Hq;
+    it.hkv = it.hq / G;
+    const int* m = p.req_meta + r * 6;
+    it.q_start = m[0]; it.q_len = m[1]; it.kv_src = m[2]; it.kv_len = m[3]; it.first = m[4]; it.pruned = m[5];
+    it.i0 = qt * kTM;
+    it.ntiles = it.i0 < it.q_len ? (min(it.kv_len, it.i0 + kTM) + kTN - 1) / kTN : 0;
+    return it;
+  };
+  auto issue_kv = [&](const CUtensorMap* tm, uint8_t* dst, uint64_t* full, const TcItem& it, int t) {
+    mbar_expect_tx(full, L::kKV);
+#pragma unroll
+    for (int g = 0; g < kTN / kBoxRows; ++g) {
+      const int j = t * kTN + g * kBoxRows;
+      const int src = it.kv_src + (j < it.first ? j : j + it.pruned);
+#pragma unroll
+      for (int b = 0; b < D / 64; ++b)
+        t5::tma_load_2d(dst + b * (kTN * 128) + g * (kBoxRows * 128), tm, it.hkv * D + b * 64, src, full);
+    }
+  };
+
+  if (tid == 0) {
+    if ((smem_u32(smem) & 1023u) != 0u) __trap();
+    mbar_init(&bar[B_QFULL], 1);
+    mbar_init(&bar[B_KFULL], 1); mbar_init(&bar[B_KFULL + 1], 1);
+    mbar_init(&bar[B_VFULL], 1); mbar_init(&bar[B_VFULL + 1], 1);
+    mbar_init(&bar[B_SFULL], 1);  mbar_init(&bar[B_SFULL + 1], 1);
+    mbar_init(&bar[B_PFULL], kTM);
+    mbar_init(&bar[B_PVDONE], 1); mbar_init(&bar[B_PVDONE + 1], 1);
+    mbar_fence_init();
+  }
+  if (warp == 6) t5::tmem_alloc<kTmemCols>(tmem_slot);
+  t5::fence_before_sync();
+  __syncthreads();
+  t5::fence_after_sync();
+  const uint32_t tmem = *tmem_slot;
+  const uint32_t tmem_o = tmem + 2 * kTN;
+
+  if (warp == 4) {
+    // ================================================= Q + K producer (one lane, TMA)
+    if (lane == 0) {
+      int g = 0;   // tiles issued so far by this CTA (all items)
+      for (int k = blockIdx.x; k < total; k += gridDim.x) {
+        const TcItem it = get_item(k);
+        if (it.ntiles == 0) continue;
+        if (it.pruned != 0 && (((it.first | it.pruned) & 15) != 0)) __trap();
+        // Q buffer is free once the previous item's last S MMA (tile g - 1) has completed
+        if (g > 0) t5::mbar_wait_relaxed(&bar[B_SFULL + ((g - 1) & 1)], ((g - 1) >> 1) & 1);
+        mbar_expect_tx(&bar[B_QFULL], L::kQ);
+#pragma unroll
+        for (int b = 0; b < D / 64; ++b)
+          t5::tma_load_2d(smem + L::oQ + b * (kTM * 128), &tm_q, it.hq * D + b * 64, it.q_start + it.i0,
+                          &bar[B_QFULL]);
+        for (int t = 0; t < it.ntiles; ++t, ++g) {
+          const int st = g & 1;
+          if (g >= 2) t5::mbar_wait_relaxed(&bar[B_SFULL + st], ((g - 2) >> 1) & 1);   // S_{g-2} done
+          issue_kv(&tm_k, smem + L::oK + st * L::kKV, &bar[B_KFULL + st], it, t);
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 5) {
+    // ================================================= V producer (one lane, TMA)
+    if (lane == 0) {
+      int g = 0;
+      for (int k = blockIdx.x; k < total; k += gridDim.x) {
+        const TcItem it = get_item(k);
+        for (int t = 0; t < it.ntiles; ++t, ++g) {
+          const int st = g & 1;
+          if (g >= 2) t5::mbar_wait_relaxed(&bar[B_PVDONE + st], ((g - 2) >> 1) & 1);  // P.V_{g-2} done
+          issue_kv(&tm_v, smem + L::oV + st * L::kKV, &bar[B_VFULL + st], it, t);
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 6) {
+    // ================================================= MMA issuer (one lane)
+    if (lane == 0) {
+      const uint32_t sQ = smem_u32(smem + L::oQ), sK = smem_u32(smem + L::oK);
+      const uint32_t sV = smem_u32(smem + L::oV), sP = smem_u32(smem + L::oP);
+      auto issue_s = [&](int g) {
+        const int st = g & 1;
+        mbar_wait(&bar[B_KFULL + st], (g >> 1) & 1);
+        t5::fence_after_sync();
+#pragma unroll
+        for (int ks = 0; ks < KS; ++ks) {
+          const uint64_t a = t5::smem_desc_sw128(sQ + (ks >> 2) * (kTM * 128) + (ks & 3) * 32, 16, 1024);
+          const uint64_t b = t5::smem_desc_sw128(sK + st * L::kKV + (ks >> 2) * (kTN * 128) + (ks & 3) * 32, 16, 1024);
+          t5::mma_f16_ss(tmem + st * kTN, a, b, kIdescS, ks > 0);
+        }
+        t5::commit(&bar[B_SFULL + st]);
+      };
+      int g = 0, n_item = 0;
+      for (int k = blockIdx.x; k < total; k += gridDim.x) {
+        const TcItem it = get_item(k);
+        if (it.ntiles == 0) continue;
+        mbar_wait(&bar[B_QFULL], n_item & 1);
+        ++n_item;
+        issue_s(g);
+        for (int j = 0; j < it.ntiles; ++j, ++g) {
+          const int st = g & 1;
+          if (j + 1 < it.ntiles) issue_s(g + 1);
+          mbar_wait(&bar[B_VFULL + st], (g >> 1) & 1);
+          mbar_wait(&bar[B_PFULL], g & 1);
+          fence_proxy_async();
+          t5::fence_after_sync();
+#pragma unroll
+          for (int kk = 0; kk < PK; ++kk) {
+            const uint64_t a = t5::smem_desc(sP + kk * 2 * (kTM * 16), kTM * 16, 128);
+            const uint64_t b = t5::smem_desc_sw128(sV + st * L::kKV + kk * (16 * 128), kTN * 128, 1024);
+            t5::mma_f16_ss(tmem_o, a, b, kIdescPV, (j > 0 || kk > 0));
+          }
+          t5::commit(&bar[B_PVDONE + st]);
+        }
+      }
+    }
+    __syncwarp();
+  } else {
+    // ================================================= softmax warps (thread = query row)
+    const uint32_t lane_base = (uint32_t)(warp * 32) << 16;
+    uint8_t* sProw = smem + L::oP + tid * 16;
+    int g = 0;
+    for (int k = blockIdx.x; k < total; k += gridDim.x) {
+      const TcItem it = get_item(k);
+      if (it.ntiles == 0) continue;
+      const int row = it.i0 + tid;
+      float m_use = -INFINITY, l_run = 0.f;
+      for (int j = 0; j < it.ntiles; ++j, ++g) {
+        const int sb = g & 1;
+        const int j0 = j * kTN;
+        mbar_wait(&bar[B_SFULL + sb], (g >> 1) & 1);
+        t5::fence_after_sync();
+        uint32_t sr[SC][32];
+#pragma unroll
+        for (int c = 0; c < SC; ++c) t5::tmem_ld32(sr[c], tmem + lane_base + sb * kTN + c * 32);
+        t5::tmem_ld_wait();
+        const bool need_mask = (j0 + kTN - 1 > it.i0) || (j0 + kTN > it.kv_len);
+        if (need_mask) {
+          const int lim = min(row, it.kv_len - 1) - j0;  // columns > lim are masked
+#pragma unroll
+          for (int c = 0; c < SC; ++c)
+#pragma unroll
+            for (int i = 0; i < 32; ++i)
+              if (c * 32 + i > lim) sr[c][i] = 0xff800000u;  // -inf
+        }
+        float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+#pragma unroll
+        for (int c = 0; c < SC; ++c)
+#pragma unroll
+          for (int i = 0; i < 32; ++i) mx[i & 3] = fmaxf(mx[i & 3], __uint_as_float(sr[c][i]));
+        const float m_tile = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3])) * p.scale_log2;
+        float alpha = 1.f;
+        const bool grow = m_tile > m_use + kRescaleThreshold || m_use == -INFINITY;
+        if (grow) {
+          alpha = (m_use == -INFINITY) ? 0.f : fast_exp2(m_use - m_tile);
+          m_use = m_tile;
+          l_run *= alpha;
+        }
+        float sum[4] = {0.f, 0.f, 0.f, 0.f};
+        const float neg_m = -m_use;
+#pragma unroll
+        for (int c = 0; c < SC; ++c)
+#pragma unroll
+          for (int i = 0; i < 32; i += 2) {
+            const float p0 = fast_exp2(fmaf(__uint_as_float(sr[c][i]), p.scale_log2, neg_m));
+            const float p1 = fast_exp2(fmaf(__uint_as_float(sr[c][i + 1]), p.scale_log2, neg_m));
+            sum[(i >> 1) & 3] += p0 + p1;
+            sr[c][i >> 1] = pack_bf16x2(p0, p1);
+          }
+        l_run += (sum[0] + sum[1]) + (sum[2] + sum[3]);
+
+        if (j > 0) {   // (j == 0: the previous item's epilogue already waited for its last P.V)
+          mbar_wait(&bar[B_PVDONE + ((g - 1) & 1)], ((g - 1) >> 1) & 1);  // P buffer free, O settled
+          t5::fence_after_sync();
+          if (__any_sync(kFull, grow)) {
+#pragma unroll
+            for (int c = 0; c < D / 32; ++c) {
+              uint32_t o[32];
+              t5::tmem_ld32(o, tmem_o + lane_base + c * 32);
+              t5::tmem_ld_wait();
+#pragma unroll
+              for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+              t5::tmem_st32(tmem_o + lane_base + c * 32, o);
+            }
+            t5::tmem_st_wait();
+          }
+        }
+#pragma unroll
+        for (int c = 0; c < SC; ++c)
+#pragma unroll
+          for (int q4 = 0; q4 < 4; ++q4) {
+            const uint4 val = make_uint4(sr[c][q4 * 4], sr[c][q4 * 4 + 1], sr[c][q4 * 4 + 2], sr[c][q4 * 4 + 3]);
+            *reinterpret_cast<uint4*>(sProw + (c * 4 + q4) * (kTM * 16)) = val;
+          }
+        fence_proxy_async();
+        t5::fence_before_sync();
+        t5::mbar_arrive(&bar[B_PFULL]);
+      }
+      // ---- epilogue of the item: O / l -> bf16 -> global (last tile index g - 1)
+      mbar_wait(&bar[B_PVDONE + ((g - 1) & 1)], ((g - 1) >> 1) & 1);
+      t5::fence_after_sync();
+      const float inv = 1.f / l_run;
+      __nv_bfloat16* dst = p.out + (size_t)(it.q_start + (row < it.q_len ? row : 0)) * p.out_stride + (size_t)it.hq * D;
+#pragma unroll
+      for (int c = 0; c < D / 32; ++c) {
+        uint32_t o[32];
+        t5::tmem_ld32(o, tmem_o + lane_base + c * 32);
+        t5::tmem_ld_wait();
+        if (row < it.q_len) {
+#pragma unroll
+          for (int q4 = 0; q4 < 4; ++q4) {
+            uint4 val;
+            val.x = pack_bf16x2(__uint_as_float(o[q4 * 8 + 0]) * inv, __uint_as_float(o[q4 * 8 + 1]) * inv);
+            val.y = pack_bf16x2(__uint_as_float(o[q4 * 8 + 2]) * inv, __uint_as_float(o[q4 * 8 + 3]) * inv);
+            val.z = pack_bf16x2(__uint_as_float(o[q4 * 8 + 4]) * inv, __uint_as_float(o[q4 * 8 + 5]) * inv);
+            val.w = pack_bf16x2(__uint_as_float(o[q4 * 8 + 6]) * inv, __uint_as_float(o[q4 * 8 + 7]) * inv);
+            *reinterpret_cast<uint4*>(dst + c * 32 + q4 * 8) = val;
+          }
+        }
+      }
+      // the next item's first P.V (accumulate = 0) overwrites O only after these loads:
+      // its p_full needs this thread's arrival, which comes after this point
+      t5::fence_before_sync();
+    }
+  }
+
+  // ---- teardown
+  t5::fence_before_sync();
+  __syncthreads();
+  if (warp == 6) {
+    t5::fence_after_sync();
+    t5::tmem_dealloc<kTmemCols>(tmem);
+  }
+}
+
+// -1 = measured rule (default), 0 = one CTA per query tile, 1 = persistent CTAs.  B200, TFLOP/s
+// one-shot / persistent: 16 x 1024 q (544 kept) 625 / 662, 64 x 1024 656 / 667, 16 x 1024 D 64
+// 376 / 428, 8 x 2048 870 / 889, 16 x 2048 (1056 kept) 853 / 828, 8 x 4096 994 / 965,
+// 4 x 8192 1104 / 1055: the persistent walk saves the per-tile setup that dominates short
+// prompts; on long ones the hardware CTA scheduler balances the uneven items better than the
+// static round-robin.
+static int g_tc_persistent = -1;
+void set_prefill_tc_persistent(int v) { g_tc_persistent = v; }
+
 // ---- host: tensor maps.  The encoder is a driver entry point fetched through the runtime
 // (no link against libcuda).
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
@@ -351,6 +634,18 @@ static int launch_prefill_tc(const PrefillTcParams& p, const PrefillArgs& a, cud
   auto kern = prefill_attn_tc_kernel<D, TN>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   if (e != cudaSuccess) return set_cuda_error("cudaFuncSetAttribute(prefill_tc)", e);
+  const bool persist = g_tc_persistent < 0 ? (a.max_q_len <= 1536) : (g_tc_persistent != 0);
+  if (persist) {
+    auto pk = prefill_attn_tc_persist_kernel<D, TN>;
+    e = cudaFuncSetAttribute(pk, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return set_cuda_error("cudaFuncSetAttribute(prefill_tc_persist)", e);
+    const int q_tiles = (a.max_q_len + kTM - 1) / kTM;
+    const long long total = (long long)q_tiles * a.Hq * a.num_reqs;
+    const long long slots = (long long)device_sm_count() * (TN == 64 ? 2 : 1);
+    const int ctas = (int)(total < slots ? total : slots);
+    pk<<<ctas, kTcThreads, smem, stream>>>(p, tq, tk, tv, q_tiles, a.num_reqs);
+    return check_launch("prefill_attn_tc_persist_kernel");
+  }
   dim3 grid((a.max_q_len + kTM - 1) / kTM, a.Hq, a.num_reqs);
   kern<<<grid, kTcThreads, smem, stream>>>(p, tq, tk, tv);
   return check_launch("prefill_attn_tc_kernel");

@@ -37,7 +37,7 @@ def prune_layout(L: int, bs: int, evict_freq: int, initial_blocks: int = 1, num_
     return L - pruned, pruned, first
 
 
-def run(device, reqs, L, Hq, Hkv, D, evict_freq, reps, variant, check=None, tile=64):
+def run(device, reqs, L, Hq, Hkv, D, evict_freq, reps, variant, check=None, tile=64, persistent=-1):
     g = torch.Generator(device=device)
     g.manual_seed(0)
     T = reqs * L
@@ -56,6 +56,9 @@ def run(device, reqs, L, Hq, Hkv, D, evict_freq, reps, variant, check=None, tile
     lib.pc_debug_set_prefill_tc_tile.argtypes = [ctypes.c_int32]
     lib.pc_debug_set_prefill_tc_tile.restype = None
     lib.pc_debug_set_prefill_tc_tile(tile)
+    lib.pc_debug_set_prefill_tc_persistent.argtypes = [ctypes.c_int32]
+    lib.pc_debug_set_prefill_tc_persistent.restype = None
+    lib.pc_debug_set_prefill_tc_persistent(persistent)
 
     def launch():
         ops.prefill_attn_topleft_causal(out, q, k, v, meta, L, s)
@@ -70,10 +73,11 @@ def run(device, reqs, L, Hq, Hkv, D, evict_freq, reps, variant, check=None, tile
     torch.cuda.synchronize()
     lib.pc_debug_set_prefill_variant(0)
     lib.pc_debug_set_prefill_tc_tile(64)
+    lib.pc_debug_set_prefill_tc_persistent(-1)
     sec = e0.elapsed_time(e1) / 1e3 / reps
     vis = sum(min(i + 1, kept) for i in range(L))
     flops = 4.0 * D * Hq * reqs * vis
-    row = {"kernel": f"prefill_attn_tc_kernel<TN={tile}>" if variant == 0 else "prefill_attn_kernel(mma.sync)",
+    row = {"kernel": f"prefill_attn_tc_{ {-1: 'auto_', 0: '', 1: 'persist_'}[persistent] }kernel<TN={tile}>" if variant == 0 else "prefill_attn_kernel(mma.sync)",
            "reqs": reqs, "q_len": L, "kv_kept": kept, "Hq": Hq, "Hkv": Hkv, "D": D,
            "us": sec * 1e6, "tflops": flops / sec / 1e12,
            "frac_of_measured_bf16_peak": flops / sec / 1e12 / _peak_tflops()}
@@ -100,8 +104,9 @@ def main():
         return
     base, ref = run(dev, a.reqs, a.len, a.Hq, a.Hkv, a.D, a.evict_freq, a.reps, 1)
     print(json.dumps(base), flush=True)
-    for tile in (64, 128):
-        row, _ = run(dev, a.reqs, a.len, a.Hq, a.Hkv, a.D, a.evict_freq, a.reps, 0, check=ref, tile=tile)
+    for tile, pers in ((64, 0), (64, 1), (128, 1)):
+        row, _ = run(dev, a.reqs, a.len, a.Hq, a.Hkv, a.D, a.evict_freq, a.reps, 0, check=ref, tile=tile,
+                     persistent=pers)
         print(json.dumps(row), flush=True)
 
 
