@@ -45,6 +45,9 @@ struct PrefillTcParams {
   long long out_stride;
   float scale_log2;
 };
+#ifndef PC_P_TMEM
+#define PC_P_TMEM 1   // P as a TMEM A operand (0: P through shared memory, the first version)
+#endif
 constexpr int kBoxRows = 16;   // K/V TMA box = one 16-token run (first, pruned are multiples of 16)
 
 // TN = kv rows per tile (UMMA N of S, K extent of P.V).  TN = 64 fits two CTAs per SM
@@ -55,7 +58,7 @@ struct TcSmem {
   static constexpr int kTmemCols = (2 * TN + D) <= 256 ? 256 : 512;
   static constexpr int kQ = kTM * D * 2;
   static constexpr int kKV = kTN * D * 2;      // one K or V stage
-  static constexpr int kP = kTM * kTN * 2;
+  static constexpr int kP = PC_P_TMEM ? 0 : kTM * kTN * 2;   // P staging (only when P goes through smem)
   static constexpr int oQ = 0;
   static constexpr int oK = oQ + kQ;           // 2 stages
   static constexpr int oV = oK + 2 * kKV;      // 2 stages
@@ -71,245 +74,10 @@ enum { B_QFULL = 0, B_KFULL = 1, B_VFULL = 3, B_SFULL = 5, B_PFULL = 7, B_PVDONE
 
 namespace {
 
-template <int D, int TN>
-__global__ void __launch_bounds__(kTcThreads, (TN == 64 ? 2 : 1))
-prefill_attn_tc_kernel(const PrefillTcParams p, const __grid_constant__ CUtensorMap tm_q,
-                       const __grid_constant__ CUtensorMap tm_k,
-                       const __grid_constant__ CUtensorMap tm_v) {
-  using L = TcSmem<D, TN>;
-  constexpr int kTN = TN;
-  constexpr int kTmemCols = L::kTmemCols;
-  constexpr int SC = TN / 32;       // 32-column chunks of an S row
-  constexpr int KS = D / 16;        // k-steps of S = Q K^T
-  constexpr int PK = kTN / 16;      // k-steps of O += P V
-  constexpr uint32_t kIdescS = t5::instr_desc_bf16(kTM, kTN, false);
-  constexpr uint32_t kIdescPV = t5::instr_desc_bf16(kTM, D, true);
-  extern __shared__ __align__(1024) uint8_t smem[];
-  uint64_t* bar = reinterpret_cast<uint64_t*>(smem + L::oBar);
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar + B_COUNT);
-
-  const int r = blockIdx.z;
-  const int hq = blockIdx.y;
-  const int* m = p.req_meta + r * 6;
-  const int q_start = m[0], q_len = m[1], kv_src = m[2], kv_len = m[3], first = m[4], pruned = m[5];
-  // heaviest query tiles (most visible kv) are scheduled first
-  const int i0 = (int)(gridDim.x - 1 - blockIdx.x) * kTM;
-  if (i0 >= q_len) return;
-  const int hkv = hq / (p.Hq / p.Hkv);
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int kv_hi = min(kv_len, i0 + kTM);
-  const int ntiles = (kv_hi + kTN - 1) / kTN;
-
-  // one K or V tile = one 16-row TMA box per kept 16-token run and 64-column block
-  auto issue_kv = [&](const CUtensorMap* tm, uint8_t* dst, uint64_t* full, int t) {
-    mbar_expect_tx(full, L::kKV);
-#pragma unroll
-    for (int g = 0; g < kTN / kBoxRows; ++g) {
-      const int j = t * kTN + g * kBoxRows;
-      const int src = kv_src + (j < first ? j : j + pruned);   // rows >= kv_len are masked
-#pragma unroll
-      for (int b = 0; b < D / 64; ++b)
-        t5::tma_load_2d(dst + b * (kTN * 128) + g * (kBoxRows * 128), tm, hkv * D + b * 64, src, full);
-    }
-  };
-  if (tid == 0) {
-    if ((smem_u32(smem) & 1023u) != 0u || (pruned != 0 && (((first | pruned) & 15) != 0))) __trap();
-    mbar_init(&bar[B_QFULL], 1);
-    mbar_init(&bar[B_KFULL], 1); mbar_init(&bar[B_KFULL + 1], 1);
-    mbar_init(&bar[B_VFULL], 1); mbar_init(&bar[B_VFULL + 1], 1);
-    mbar_init(&bar[B_SFULL], 1);  mbar_init(&bar[B_SFULL + 1], 1);
-    mbar_init(&bar[B_PFULL], kTM);
-    mbar_init(&bar[B_PVDONE], 1); mbar_init(&bar[B_PVDONE + 1], 1);
-    mbar_fence_init();
-    // first loads go out before the CTA-wide sync, so their latency overlaps the TMEM
-    // allocation and the role dispatch: Q tile, K_0, V_0
-    mbar_expect_tx(&bar[B_QFULL], L::kQ);
-#pragma unroll
-    for (int b = 0; b < D / 64; ++b)   // rows past q_len: next request's rows or TMA zero fill
-      t5::tma_load_2d(smem + L::oQ + b * (kTM * 128), &tm_q, hq * D + b * 64, q_start + i0, &bar[B_QFULL]);
-    issue_kv(&tm_k, smem + L::oK, &bar[B_KFULL], 0);
-    issue_kv(&tm_v, smem + L::oV, &bar[B_VFULL], 0);
-  }
-  if (warp == 6) t5::tmem_alloc<kTmemCols>(tmem_slot);
-  t5::fence_before_sync();
-  __syncthreads();
-  t5::fence_after_sync();
-  const uint32_t tmem = *tmem_slot;
-  const uint32_t tmem_o = tmem + 2 * kTN;
-
-  if (warp == 4) {
-    // ================================================= K producer (one lane, TMA)
-    if (lane == 0) {
-      for (int t = 1; t < ntiles; ++t) {
-        const int st = t & 1;
-        if (t >= 2) t5::mbar_wait_relaxed(&bar[B_SFULL + st], ((t - 2) >> 1) & 1);  // S_{t-2} done
-        issue_kv(&tm_k, smem + L::oK + st * L::kKV, &bar[B_KFULL + st], t);
-      }
-    }
-    __syncwarp();
-  } else if (warp == 5) {
-    // ================================================= V producer (one lane, TMA)
-    if (lane == 0) {
-      for (int t = 1; t < ntiles; ++t) {
-        const int st = t & 1;
-        if (t >= 2) t5::mbar_wait_relaxed(&bar[B_PVDONE + st], ((t - 2) >> 1) & 1);  // P.V_{t-2} done
-        issue_kv(&tm_v, smem + L::oV + st * L::kKV, &bar[B_VFULL + st], t);
-      }
-    }
-    __syncwarp();
-  } else if (warp == 6) {
-    // ================================================= MMA issuer (one lane)
-    if (lane == 0) {
-      const uint32_t sQ = smem_u32(smem + L::oQ), sK = smem_u32(smem + L::oK);
-      const uint32_t sV = smem_u32(smem + L::oV), sP = smem_u32(smem + L::oP);
-      auto issue_s = [&](int t) {
-        const int st = t & 1;
-        mbar_wait(&bar[B_KFULL + st], (t >> 1) & 1);
-        t5::fence_after_sync();
-#pragma unroll
-        for (int ks = 0; ks < KS; ++ks) {   // 64-element column block ks / 4, 32 bytes per k-step inside it
-          const uint64_t a = t5::smem_desc_sw128(sQ + (ks >> 2) * (kTM * 128) + (ks & 3) * 32, 16, 1024);
-          const uint64_t b = t5::smem_desc_sw128(sK + st * L::kKV + (ks >> 2) * (kTN * 128) + (ks & 3) * 32, 16, 1024);
-          t5::mma_f16_ss(tmem + st * kTN, a, b, kIdescS, ks > 0);
-        }
-        t5::commit(&bar[B_SFULL + st]);
-      };
-      mbar_wait(&bar[B_QFULL], 0);
-      issue_s(0);
-      for (int j = 0; j < ntiles; ++j) {
-        const int st = j & 1;
-        if (j + 1 < ntiles) issue_s(j + 1);
-        mbar_wait(&bar[B_VFULL + st], (j >> 1) & 1);
-        mbar_wait(&bar[B_PFULL], j & 1);
-        fence_proxy_async();
-        t5::fence_after_sync();
-#pragma unroll
-        for (int kk = 0; kk < PK; ++kk) {
-          const uint64_t a = t5::smem_desc(sP + kk * 2 * (kTM * 16), kTM * 16, 128);
-          const uint64_t b = t5::smem_desc_sw128(sV + st * L::kKV + kk * (16 * 128), kTN * 128, 1024);
-          t5::mma_f16_ss(tmem_o, a, b, kIdescPV, (j > 0 || kk > 0));
-        }
-        t5::commit(&bar[B_PVDONE + st]);
-      }
-    }
-    __syncwarp();
-  } else {
-    // ================================================= softmax warps (thread = query row)
-    const int row = i0 + tid;
-    const uint32_t lane_base = (uint32_t)(warp * 32) << 16;
-    uint8_t* sProw = smem + L::oP + tid * 16;
-    float m_use = -INFINITY, l_run = 0.f;
-    for (int j = 0; j < ntiles; ++j) {
-      const int sb = j & 1;
-      const int j0 = j * kTN;
-      mbar_wait(&bar[B_SFULL + sb], (j >> 1) & 1);
-      t5::fence_after_sync();
-      uint32_t sr[SC][32];
-#pragma unroll
-      for (int c = 0; c < SC; ++c) t5::tmem_ld32(sr[c], tmem + lane_base + sb * kTN + c * 32);
-      t5::tmem_ld_wait();
-      const bool need_mask = (j0 + kTN - 1 > i0) || (j0 + kTN > kv_len);
-      if (need_mask) {
-        const int lim = min(row, kv_len - 1) - j0;  // columns > lim are masked
-#pragma unroll
-        for (int c = 0; c < SC; ++c)
-#pragma unroll
-          for (int i = 0; i < 32; ++i)
-            if (c * 32 + i > lim) sr[c][i] = 0xff800000u;  // -inf
-      }
-      float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
-#pragma unroll
-      for (int c = 0; c < SC; ++c)
-#pragma unroll
-        for (int i = 0; i < 32; ++i) mx[i & 3] = fmaxf(mx[i & 3], __uint_as_float(sr[c][i]));
-      const float m_tile = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3])) * p.scale_log2;
-      // lazy rescale: move the reference max only when it grows by more than the threshold
-      float alpha = 1.f;
-      const bool grow = m_tile > m_use + kRescaleThreshold || m_use == -INFINITY;
-      if (grow) {
-        alpha = (m_use == -INFINITY) ? 0.f : fast_exp2(m_use - m_tile);
-        m_use = m_tile;
-        l_run *= alpha;
-      }
-      float sum[4] = {0.f, 0.f, 0.f, 0.f};
-      const float neg_m = -m_use;
-#pragma unroll
-      for (int c = 0; c < SC; ++c)
-#pragma unroll
-        for (int i = 0; i < 32; i += 2) {
-          const float p0 = fast_exp2(fmaf(__uint_as_float(sr[c][i]), p.scale_log2, neg_m));
-          const float p1 = fast_exp2(fmaf(__uint_as_float(sr[c][i + 1]), p.scale_log2, neg_m));
-          sum[(i >> 1) & 3] += p0 + p1;
-          sr[c][i >> 1] = pack_bf16x2(p0, p1);  // packed P overwrites the consumed scores
-        }
-      l_run += (sum[0] + sum[1]) + (sum[2] + sum[3]);
-
-      if (j > 0) {
-        mbar_wait(&bar[B_PVDONE + ((j - 1) & 1)], ((j - 1) >> 1) & 1);  // P buffer free, O settled
-        t5::fence_after_sync();
-        if (__any_sync(kFull, grow)) {
-#pragma unroll
-          for (int c = 0; c < D / 32; ++c) {
-            uint32_t o[32];
-            t5::tmem_ld32(o, tmem_o + lane_base + c * 32);
-            t5::tmem_ld_wait();
-#pragma unroll
-            for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
-            t5::tmem_st32(tmem_o + lane_base + c * 32, o);
-          }
-          t5::tmem_st_wait();
-        }
-      }
-      // P row -> smem, chunk-major: 8 kv columns (16 bytes) per chunk
-#pragma unroll
-      for (int c = 0; c < SC; ++c)
-#pragma unroll
-        for (int q4 = 0; q4 < 4; ++q4) {
-          const uint4 val = make_uint4(sr[c][q4 * 4], sr[c][q4 * 4 + 1], sr[c][q4 * 4 + 2], sr[c][q4 * 4 + 3]);
-          *reinterpret_cast<uint4*>(sProw + (c * 4 + q4) * (kTM * 16)) = val;
-        }
-      fence_proxy_async();
-      t5::fence_before_sync();
-      t5::mbar_arrive(&bar[B_PFULL]);
-    }
-    // ---- epilogue: O / l -> bf16 -> global
-    mbar_wait(&bar[B_PVDONE + ((ntiles - 1) & 1)], ((ntiles - 1) >> 1) & 1);
-    t5::fence_after_sync();
-    const float inv = 1.f / l_run;
-    __nv_bfloat16* dst = p.out + (size_t)(q_start + (row < q_len ? row : 0)) * p.out_stride + (size_t)hq * D;
-#pragma unroll
-    for (int c = 0; c < D / 32; ++c) {
-      uint32_t o[32];
-      t5::tmem_ld32(o, tmem_o + lane_base + c * 32);
-      t5::tmem_ld_wait();
-      if (row < q_len) {
-#pragma unroll
-        for (int q4 = 0; q4 < 4; ++q4) {
-          uint4 val;
-          val.x = pack_bf16x2(__uint_as_float(o[q4 * 8 + 0]) * inv, __uint_as_float(o[q4 * 8 + 1]) * inv);
-          val.y = pack_bf16x2(__uint_as_float(o[q4 * 8 + 2]) * inv, __uint_as_float(o[q4 * 8 + 3]) * inv);
-          val.z = pack_bf16x2(__uint_as_float(o[q4 * 8 + 4]) * inv, __uint_as_float(o[q4 * 8 + 5]) * inv);
-          val.w = pack_bf16x2(__uint_as_float(o[q4 * 8 + 6]) * inv, __uint_as_float(o[q4 * 8 + 7]) * inv);
-          *reinterpret_cast<uint4*>(dst + c * 32 + q4 * 8) = val;
-        }
-      }
-    }
-  }
-
-  // ---- teardown
-  t5::fence_before_sync();
-  __syncthreads();
-  if (warp == 6) {
-    t5::fence_after_sync();
-    t5::tmem_dealloc<kTmemCols>(tmem);
-  }
-}
-
-}  // namespace
-
 // ---------------------------------------------------------------------------------------
-// Persistent variant: a CTA walks work items (query tile, q head, request) k = blockIdx.x,
-// + gridDim.x, ...; heaviest query tiles first.  TMEM allocation, barrier setup and the
+// A CTA walks work items (query tile, q head, request) k = blockIdx.x, + gridDim.x, ...;
+// heaviest query tiles first.  Launched either with one CTA per item (the hardware CTA
+// scheduler balances the uneven items: long prompts) or persistently with 2 CTAs per SM.  TMEM allocation, barrier setup and the
 // role dispatch happen once; the mbarrier phases simply keep counting over a CTA-wide tile
 // counter g.  The next item's Q tile is requested as soon as the last S MMA of the current
 // item has read Q, i.e. one tile before the item ends, so its latency hides behind the last
@@ -321,10 +89,10 @@ struct TcItem {
 
 template <int D, int TN>
 __global__ void __launch_bounds__(kTcThreads, (TN == 64 ? 2 : 1))
-prefill_attn_tc_persist_kernel(const PrefillTcParams p, const __grid_constant__ CUtensorMap tm_q,
+prefill_attn_tc_kernel(const PrefillTcParams p, const __grid_constant__ CUtensorMap tm_q,
                                const __grid_constant__ CUtensorMap tm_k,
                                const __grid_constant__ CUtensorMap tm_v, const int q_tiles,
-                               const int num_reqs) {
+                               const int num_reqs, const int heavy_major) {
   using L = TcSmem<D, TN>;
   constexpr int kTN = TN;
   constexpr int kTmemCols = L::kTmemCols;
@@ -344,8 +112,13 @@ prefill_attn_tc_persist_kernel(const PrefillTcParams p, const __grid_constant__ 
   // item k -> (query tile descending, request, q head); ntiles == 0: nothing to do
   auto get_item = [&](int k) {
     TcItem it;
-    const int qt = q_tiles - 1 - k / per_qt;
-    const int rem = k % per_qt;
+    // heavy_major: all (request, head) pairs of the heaviest query tile first (persistent walk,
+    // short prompts: static round-robin needs the global order).  Otherwise the query tiles of one
+    // (request, head) are adjacent, heaviest first, so the CTAs in flight share few K/V streams
+    // (4 x 8192 tokens: 134 MB of K/V > L2 when every stream is live at once: 1061 vs 1104 TFLOP/s).
+    int qt, rem;
+    if (heavy_major) { qt = q_tiles - 1 - k / per_qt; rem = k % per_qt; }
+    else             { rem = k / q_tiles; qt = q_tiles - 1 - (k - rem * q_tiles); }
     const int r = rem / p.Hq;
     it.hq = rem - r * p.Hq;
     it.hkv = it.hq / G;
@@ -454,9 +227,14 @@ prefill_attn_tc_persist_kernel(const PrefillTcParams p, const __grid_constant__ 
           t5::fence_after_sync();
 #pragma unroll
           for (int kk = 0; kk < PK; ++kk) {
-            const uint64_t a = t5::smem_desc(sP + kk * 2 * (kTM * 16), kTM * 16, 128);
             const uint64_t b = t5::smem_desc_sw128(sV + st * L::kKV + kk * (16 * 128), kTN * 128, 1024);
+#if PC_P_TMEM
+            // P_g lives in the first TN / 2 columns of the S buffer it was computed from
+            t5::mma_f16_ts(tmem_o, tmem + st * kTN + kk * 8, b, kIdescPV, (j > 0 || kk > 0));
+#else
+            const uint64_t a = t5::smem_desc(sP + kk * 2 * (kTM * 16), kTM * 16, 128);
             t5::mma_f16_ss(tmem_o, a, b, kIdescPV, (j > 0 || kk > 0));
+#endif
           }
           t5::commit(&bar[B_PVDONE + st]);
         }
@@ -533,6 +311,18 @@ prefill_attn_tc_persist_kernel(const PrefillTcParams p, const __grid_constant__ 
             t5::tmem_st_wait();
           }
         }
+#if PC_P_TMEM
+        // packed P row -> TMEM, over the scores it came from (A operand of P.V): 32 columns
+        // (= 64 bf16) per store
+#pragma unroll
+        for (int h = 0; h < SC / 2; ++h) {
+          uint32_t pk[32];
+#pragma unroll
+          for (int i = 0; i < 16; ++i) { pk[i] = sr[2 * h][i]; pk[16 + i] = sr[2 * h + 1][i]; }
+          t5::tmem_st32(tmem + lane_base + sb * kTN + h * 32, pk);
+        }
+        t5::tmem_st_wait();
+#else
 #pragma unroll
         for (int c = 0; c < SC; ++c)
 #pragma unroll
@@ -541,6 +331,7 @@ prefill_attn_tc_persist_kernel(const PrefillTcParams p, const __grid_constant__ 
             *reinterpret_cast<uint4*>(sProw + (c * 4 + q4) * (kTM * 16)) = val;
           }
         fence_proxy_async();
+#endif
         t5::fence_before_sync();
         t5::mbar_arrive(&bar[B_PFULL]);
       }
@@ -581,12 +372,15 @@ prefill_attn_tc_persist_kernel(const PrefillTcParams p, const __grid_constant__ 
   }
 }
 
-// -1 = measured rule (default), 0 = one CTA per query tile, 1 = persistent CTAs.  B200, TFLOP/s
-// one-shot / persistent: 16 x 1024 q (544 kept) 625 / 662, 64 x 1024 656 / 667, 16 x 1024 D 64
-// 376 / 428, 8 x 2048 870 / 889, 16 x 2048 (1056 kept) 853 / 828, 8 x 4096 994 / 965,
-// 4 x 8192 1104 / 1055: the persistent walk saves the per-tile setup that dominates short
+}  // namespace
+
+// -1 = measured rule (default), 0 = one CTA per item, 1 = persistent CTAs (2 = persistent with the
+// one-shot item order, debug).  B200, TFLOP/s, one CTA per item / persistent (P in TMEM):
+//   16 x 1024 q (544 kept) 642 / 728    64 x 1024 690 / 718    16 x 1024, D 64 380 / 444
+//   16 x 2048 (1056 kept)  879 / 884     8 x 4096 1026 / 1019   4 x 8192 (no eviction) 1133 / 1082
+// The persistent walk saves the per-item launch / setup / first-load latency that dominates short
 // prompts; on long ones the hardware CTA scheduler balances the uneven items better than the
-// static round-robin.
+// static round-robin, and the per-(request, head) item order keeps the live K/V streams in L2.
 static int g_tc_persistent = -1;
 void set_prefill_tc_persistent(int v) { g_tc_persistent = v; }
 
@@ -634,20 +428,14 @@ static int launch_prefill_tc(const PrefillTcParams& p, const PrefillArgs& a, cud
   auto kern = prefill_attn_tc_kernel<D, TN>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   if (e != cudaSuccess) return set_cuda_error("cudaFuncSetAttribute(prefill_tc)", e);
-  const bool persist = g_tc_persistent < 0 ? (a.max_q_len <= 1536) : (g_tc_persistent != 0);
-  if (persist) {
-    auto pk = prefill_attn_tc_persist_kernel<D, TN>;
-    e = cudaFuncSetAttribute(pk, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    if (e != cudaSuccess) return set_cuda_error("cudaFuncSetAttribute(prefill_tc_persist)", e);
-    const int q_tiles = (a.max_q_len + kTM - 1) / kTM;
-    const long long total = (long long)q_tiles * a.Hq * a.num_reqs;
-    const long long slots = (long long)device_sm_count() * (TN == 64 ? 2 : 1);
-    const int ctas = (int)(total < slots ? total : slots);
-    pk<<<ctas, kTcThreads, smem, stream>>>(p, tq, tk, tv, q_tiles, a.num_reqs);
-    return check_launch("prefill_attn_tc_persist_kernel");
-  }
-  dim3 grid((a.max_q_len + kTM - 1) / kTM, a.Hq, a.num_reqs);
-  kern<<<grid, kTcThreads, smem, stream>>>(p, tq, tk, tv);
+  const bool persist = g_tc_persistent < 0 ? (a.max_q_len <= 2048) : (g_tc_persistent != 0);
+  const int q_tiles = (a.max_q_len + kTM - 1) / kTM;
+  const long long total = (long long)q_tiles * a.Hq * a.num_reqs;
+  const long long slots = (long long)device_sm_count() * (TN == 64 ? 2 : 1);
+  if (total > 0x7fffffffLL) return set_error(PC_ERR_INVALID, "prefill: too many query tiles");
+  const int ctas = (int)((persist && total > slots) ? slots : total);
+  kern<<<ctas, kTcThreads, smem, stream>>>(p, tq, tk, tv, q_tiles, a.num_reqs,
+                                            (persist && g_tc_persistent != 2) ? 1 : 0);   // 2: debug, persistent + local order
   return check_launch("prefill_attn_tc_kernel");
 }
 

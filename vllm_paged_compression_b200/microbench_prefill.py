@@ -77,7 +77,7 @@ def run(device, reqs, L, Hq, Hkv, D, evict_freq, reps, variant, check=None, tile
     sec = e0.elapsed_time(e1) / 1e3 / reps
     vis = sum(min(i + 1, kept) for i in range(L))
     flops = 4.0 * D * Hq * reqs * vis
-    row = {"kernel": f"prefill_attn_tc_{ {-1: 'auto_', 0: '', 1: 'persist_'}[persistent] }kernel<TN={tile}>" if variant == 0 else "prefill_attn_kernel(mma.sync)",
+    row = {"kernel": f"prefill_attn_tc_{ {-1: 'auto_', 0: 'oneshot_', 1: 'persist_', 2: 'persist_localorder_'}[persistent] }kernel<TN={tile}>" if variant == 0 else "prefill_attn_kernel(mma.sync)",
            "reqs": reqs, "q_len": L, "kv_kept": kept, "Hq": Hq, "Hkv": Hkv, "D": D,
            "us": sec * 1e6, "tflops": flops / sec / 1e12,
            "frac_of_measured_bf16_peak": flops / sec / 1e12 / _peak_tflops()}
@@ -104,7 +104,7 @@ def main():
         return
     base, ref = run(dev, a.reqs, a.len, a.Hq, a.Hkv, a.D, a.evict_freq, a.reps, 1)
     print(json.dumps(base), flush=True)
-    for tile, pers in ((64, 0), (64, 1), (128, 1)):
+    for tile, pers in ((64, 0), (64, 1), (64, 2)):
         row, _ = run(dev, a.reqs, a.len, a.Hq, a.Hkv, a.D, a.evict_freq, a.reps, 0, check=ref, tile=tile,
                      persistent=pers)
         print(json.dumps(row), flush=True)
