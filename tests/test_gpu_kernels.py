@@ -486,6 +486,40 @@ def test_prefill_attention_tile_edges_and_strided_rows(case):
     np.testing.assert_allclose(got.numpy(), ref.numpy(), atol=2e-2, rtol=0)
 
 
+@pytest.mark.timeout(120)
+def test_prefill_attention_many_short_items_persistent_walk():
+    """More (tile, head, request) items than resident CTAs (2 x 148), so every CTA of the
+    persistent launch walks several items back to back: phases of all mbarriers keep counting
+    across items, Q is re-loaded behind the previous item's last S MMA, O / P buffers are reused."""
+    ops = _ops()
+    Hq, Hkv, D, bs = 16, 4, 128, 16
+    pol = Policy(block_size=bs, cache_prune_type="percentage", cache_budget=128, evict_freq=2)
+    g = torch.Generator().manual_seed(77)
+    prompt_lens = [int(x) for x in torch.randint(1, 420, (40,), generator=g)] + [512, 384, 129]
+    T = sum(prompt_lens)
+    q = (rnd(71, T, Hq, D).float() * 0.6).to(torch.bfloat16)
+    k = (rnd(72, T, Hkv, D).float() * 0.6).to(torch.bfloat16)
+    v = rnd(73, T, Hkv, D)
+    meta, gidx, kept_l, s = [], [], [], 0
+    for L in prompt_lens:
+        kept, pruned, first = policy.prompt_prune_layout(L, pol)
+        meta.append([s, L, s, kept, first, pruned])
+        gidx.append(torch.from_numpy(policy.prompt_gather_index(L, pol)) + s)
+        kept_l.append(kept)
+        s += L
+    gidx = torch.cat(gidx)
+    ref = paged_ops.prefill_attention(q, k[gidx], v[gidx], prompt_lens, kept_l, D ** -0.5).float()
+    out = torch.full((T, Hq, D), float("nan"), dtype=torch.bfloat16, device=DEV)
+    dq, dk, dv = q.to(DEV), k.to(DEV), v.to(DEV)
+    dm = torch.tensor(meta, dtype=torch.int32, device=DEV)
+    for _ in range(3):                       # repeated launches: no state may leak between them
+        ops.prefill_attn_topleft_causal(out, dq, dk, dv, dm, max(prompt_lens), D ** -0.5)
+    torch.cuda.synchronize()
+    got = out.float().cpu()
+    assert torch.isfinite(got).all()
+    np.testing.assert_allclose(got.numpy(), ref.numpy(), atol=2e-2, rtol=0)
+
+
 def test_prefill_attention_large_logits_rescale_path():
     """Scores that grow along the row force the lazy O rescale in TMEM (max jumps > 2^8)."""
     ops = _ops()

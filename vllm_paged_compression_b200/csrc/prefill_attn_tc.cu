@@ -64,11 +64,14 @@ struct TcSmem {
   static constexpr int oV = oK + 2 * kKV;      // 2 stages
   static constexpr int oP = oV + 2 * kKV;
   static constexpr int oBar = oP + kP;
-  // barriers: q_full, k_full[2], v_full[2], s_full[2], p_full, pv_done  (9) + tmem slot
+  // barriers: q_full, k_full[2], v_full[2], s_full[2], p_full[2], pv_done[2]  (11) + tmem slot
   static constexpr int kBytes = oBar + 16 * 8;
 };
 
-enum { B_QFULL = 0, B_KFULL = 1, B_VFULL = 3, B_SFULL = 5, B_PFULL = 7, B_PVDONE = 8, B_COUNT = 9 };
+// p_full is double-buffered like the S / P buffers: the softmax warps may finish tile g + 1 while
+// the MMA thread still waits for V_g, and a single barrier would then be two phases ahead of its
+// waiter (parity aliasing -> deadlock).
+enum { B_QFULL = 0, B_KFULL = 1, B_VFULL = 3, B_SFULL = 5, B_PFULL = 7, B_PVDONE = 9, B_COUNT = 11 };
 
 }  // namespace
 
@@ -146,7 +149,7 @@ prefill_attn_tc_kernel(const PrefillTcParams p, const __grid_constant__ CUtensor
     mbar_init(&bar[B_KFULL], 1); mbar_init(&bar[B_KFULL + 1], 1);
     mbar_init(&bar[B_VFULL], 1); mbar_init(&bar[B_VFULL + 1], 1);
     mbar_init(&bar[B_SFULL], 1);  mbar_init(&bar[B_SFULL + 1], 1);
-    mbar_init(&bar[B_PFULL], kTM);
+    mbar_init(&bar[B_PFULL], kTM); mbar_init(&bar[B_PFULL + 1], kTM);
     mbar_init(&bar[B_PVDONE], 1); mbar_init(&bar[B_PVDONE + 1], 1);
     mbar_fence_init();
   }
@@ -222,7 +225,7 @@ prefill_attn_tc_kernel(const PrefillTcParams p, const __grid_constant__ CUtensor
           const int st = g & 1;
           if (j + 1 < it.ntiles) issue_s(g + 1);
           mbar_wait(&bar[B_VFULL + st], (g >> 1) & 1);
-          mbar_wait(&bar[B_PFULL], g & 1);
+          mbar_wait(&bar[B_PFULL + st], (g >> 1) & 1);
           fence_proxy_async();
           t5::fence_after_sync();
 #pragma unroll
@@ -295,10 +298,19 @@ prefill_attn_tc_kernel(const PrefillTcParams p, const __grid_constant__ CUtensor
           }
         l_run += (sum[0] + sum[1]) + (sum[2] + sum[3]);
 
+#if PC_P_TMEM
+        // P_g has its own buffer (the S buffer it came from): only a rescale of O has to wait
+        // for the previous P.V
+        if (j > 0 && __any_sync(kFull, grow)) {
+          mbar_wait(&bar[B_PVDONE + ((g - 1) & 1)], ((g - 1) >> 1) & 1);  // O settled
+          t5::fence_after_sync();
+          {
+#else
         if (j > 0) {   // (j == 0: the previous item's epilogue already waited for its last P.V)
           mbar_wait(&bar[B_PVDONE + ((g - 1) & 1)], ((g - 1) >> 1) & 1);  // P buffer free, O settled
           t5::fence_after_sync();
           if (__any_sync(kFull, grow)) {
+#endif
 #pragma unroll
             for (int c = 0; c < D / 32; ++c) {
               uint32_t o[32];
@@ -333,7 +345,7 @@ prefill_attn_tc_kernel(const PrefillTcParams p, const __grid_constant__ CUtensor
         fence_proxy_async();
 #endif
         t5::fence_before_sync();
-        t5::mbar_arrive(&bar[B_PFULL]);
+        t5::mbar_arrive(&bar[B_PFULL + sb]);
       }
       // ---- epilogue of the item: O / l -> bf16 -> global (last tile index g - 1)
       mbar_wait(&bar[B_PVDONE + ((g - 1) & 1)], ((g - 1) >> 1) & 1);
