@@ -47,7 +47,10 @@ REPO = os.path.dirname(os.path.abspath(__file__))
 if REPO not in sys.path:
     sys.path.insert(0, REPO)
 
-MODEL = dict(name="Llama-3.1-8B", layers=32, Hq=32, Hkv=8, D=128)
+MODELS = {"8b": dict(name="Llama-3.1-8B", layers=32, Hq=32, Hkv=8, D=128),      # BASELINE configs[2], [3] (default)
+          "70b": dict(name="Llama-3.1-70B", layers=80, Hq=64, Hkv=8, D=128),    # configs[4] (TP 8)
+          "1b": dict(name="Llama-3.2-1B", layers=16, Hq=32, Hkv=8, D=64)}       # configs[0]
+MODEL = dict(MODELS["8b"])
 METRIC = "decode_tok_per_s_paged_eviction_hot_path"
 
 
@@ -84,7 +87,8 @@ def parse_args():
                     help="README flag: 2 (labelled 25%%) or 4 (labelled 50%%); 0 = eviction off")
     ap.add_argument("--batch", type=int, default=64, help="prompts per GPU")
     ap.add_argument("--prompt-len", type=int, default=1024)
-    ap.add_argument("--layers", type=int, default=MODEL["layers"])
+    ap.add_argument("--model", default="8b", choices=sorted(MODELS), help="attention shapes of the model")
+    ap.add_argument("--layers", type=int, default=0, help="0 = the model's layer count")
     ap.add_argument("--block-size", type=int, default=16)
     ap.add_argument("--cpu-layers", type=int, default=2,
                     help="layers per step in the CPU sample (scaled to the full layer count)")
@@ -105,7 +109,12 @@ def parse_args():
                          "score exchange) -- for profiling the per-rank launch shape on a 1-GPU box")
     ap.add_argument("--sweep", action="store_true",
                     help="kernel microbench (BASELINE.json configs[1]) -> table on stdout")
-    return ap.parse_args()
+    args = ap.parse_args()
+    MODEL.clear()
+    MODEL.update(MODELS[args.model])
+    if args.layers <= 0:
+        args.layers = MODEL["layers"]
+    return args
 
 
 # ------------------------------------------------------------------------ configuration
