@@ -131,7 +131,8 @@ def make_cache_config(args, max_num_seqs):
 
 def workload_name(args, world):
     ev = f"evict-freq {args.evict_freq}" if args.evict_freq > 0 else "no eviction"
-    return (f"{MODEL['name']} attention hot path, {args.layers} layers, {args.batch * world} prompts x "
+    div = world if world > 1 else max(1, getattr(args, "tp_emulate", 1))
+    return (f"{MODEL['name']} attention hot path, {args.layers} layers, {args.batch * div} prompts x "
             f"{args.prompt_len} in, decode steps, block {args.block_size}, percentage/streamingLLM prompt + "
             f"value_l2 decode, {ev}")
 
