@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define PC_ABI_VERSION 3
+#define PC_ABI_VERSION 4
 #define PC_MAX_PEERS 8
 
 typedef enum pc_status {

@@ -10,7 +10,7 @@ import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("PC_LIB_PATH") or os.path.join(_HERE, "libpagedevict_b200.so")
-ABI_VERSION = 3
+ABI_VERSION = 4
 MAX_PEERS = 8
 
 
