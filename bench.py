@@ -514,7 +514,7 @@ def main():
     _lib.load()                                        # fail loudly if the CUDA library is missing
 
     if args.sweep:
-        from vllm_paged_compression_b200 import microbench
+        from benchtools import microbench
         microbench.sweep(device)
         return
 
@@ -589,14 +589,14 @@ def main():
     if rank == 0 and world == 1 and not args.no_prefill:
         # second roofline: prefill attention (A1) of the same workload, tensor-bound.  One layer's
         # launch for 16 of the prompts (as the engine batches them), tcgen05 kernel, CUDA events.
-        from vllm_paged_compression_b200 import microbench_prefill
+        from benchtools import microbench_prefill
         peaks = {}
         ppath = os.path.join(REPO, "MEASURED_PEAKS.json")
         if os.path.exists(ppath):
             with open(ppath) as f:
                 peaks = json.load(f)
         row, _ = microbench_prefill.run(device, 16, args.prompt_len, MODEL["Hq"], MODEL["Hkv"], MODEL["D"],
-                                        args.evict_freq, 20, 0)
+                                        args.evict_freq, 20)
         tpeak = float(peaks.get("bf16_tflops", 2250.0))
         line["prefill_roofline"] = {
             "bound": "tensor", "kernel": "prefill_attn_tc_kernel (tcgen05.mma, TMEM accumulators, TMA loads)",

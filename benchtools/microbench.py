@@ -15,7 +15,7 @@ import os
 
 import torch
 
-from . import ops
+from vllm_paged_compression_b200 import ops
 
 
 def _peak():

@@ -1,9 +1,9 @@
-"""Prefill-attention (A1) microbench: tcgen05/TMEM kernel vs the mma.sync baseline kernel.
+"""Prefill-attention (A1) microbench of the tcgen05/TMEM kernel.
 
 flops = 4 * D * Hq * sum_req sum_i min(i + 1, L')  (top-left causal over the kept prompt,
 SURVEY.md 8d).  CUDA events around `reps` back-to-back launches after warm-up; tensor-pipe
 fraction is reported against MEASURED_PEAKS.json bf16_tflops (burst, kernel timed alone).
-    python -m vllm_paged_compression_b200.microbench_prefill [--reqs 16 --len 1024 --evict-freq 2]
+    python -m benchtools.microbench_prefill [--reqs 16 --len 1024 --evict-freq 2]
 """
 from __future__ import annotations
 
@@ -14,8 +14,7 @@ import os
 
 import torch
 
-from . import _lib, ops
-from .config import PagedEvictConfig  # noqa: F401  (keeps the flag vocabulary in one place)
+from vllm_paged_compression_b200 import _lib, ops
 
 
 def _peak_tflops():
@@ -37,7 +36,21 @@ def prune_layout(L: int, bs: int, evict_freq: int, initial_blocks: int = 1, num_
     return L - pruned, pruned, first
 
 
-def run(device, reqs, L, Hq, Hkv, D, evict_freq, reps, variant, check=None, tile=64, persistent=-1):
+def _debug_knobs(lib, tile, persistent):
+    """kv tile width / launch mode overrides exist only in the PC_DEBUG library
+    (`make -C vllm_paged_compression_b200/csrc debug`, PC_LIB_PATH=...); the product library
+    always runs its measured rule (64-wide tile, persistent for prompts <= 2048)."""
+    if not hasattr(lib, "pc_debug_set_prefill_tc_tile"):
+        if tile != 64 or persistent != -1:
+            raise RuntimeError("tile / persistent overrides need the PC_DEBUG library")
+        return
+    for name, v in (("pc_debug_set_prefill_tc_tile", tile), ("pc_debug_set_prefill_tc_persistent", persistent)):
+        fn = getattr(lib, name)
+        fn.argtypes, fn.restype = [ctypes.c_int32], None
+        fn(v)
+
+
+def run(device, reqs, L, Hq, Hkv, D, evict_freq, reps, variant=0, check=None, tile=64, persistent=-1):
     g = torch.Generator(device=device)
     g.manual_seed(0)
     T = reqs * L
@@ -50,15 +63,7 @@ def run(device, reqs, L, Hq, Hkv, D, evict_freq, reps, variant, check=None, tile
                         dtype=torch.int32, device=device)
     out = torch.zeros(T, Hq, D, dtype=torch.bfloat16, device=device)
     lib = _lib.load()
-    lib.pc_debug_set_prefill_variant.argtypes = [ctypes.c_int32]
-    lib.pc_debug_set_prefill_variant.restype = None
-    lib.pc_debug_set_prefill_variant(variant)
-    lib.pc_debug_set_prefill_tc_tile.argtypes = [ctypes.c_int32]
-    lib.pc_debug_set_prefill_tc_tile.restype = None
-    lib.pc_debug_set_prefill_tc_tile(tile)
-    lib.pc_debug_set_prefill_tc_persistent.argtypes = [ctypes.c_int32]
-    lib.pc_debug_set_prefill_tc_persistent.restype = None
-    lib.pc_debug_set_prefill_tc_persistent(persistent)
+    _debug_knobs(lib, tile, persistent)
 
     def launch():
         ops.prefill_attn_topleft_causal(out, q, k, v, meta, L, s)
@@ -71,13 +76,12 @@ def run(device, reqs, L, Hq, Hkv, D, evict_freq, reps, variant, check=None, tile
         launch()
     e1.record()
     torch.cuda.synchronize()
-    lib.pc_debug_set_prefill_variant(0)
-    lib.pc_debug_set_prefill_tc_tile(64)
-    lib.pc_debug_set_prefill_tc_persistent(-1)
+    _debug_knobs(lib, 64, -1)
     sec = e0.elapsed_time(e1) / 1e3 / reps
     vis = sum(min(i + 1, kept) for i in range(L))
     flops = 4.0 * D * Hq * reqs * vis
-    row = {"kernel": f"prefill_attn_tc_{ {-1: 'auto_', 0: 'oneshot_', 1: 'persist_', 2: 'persist_localorder_'}[persistent] }kernel<TN={tile}>" if variant == 0 else "prefill_attn_kernel(mma.sync)",
+    mode = {-1: "auto_", 0: "oneshot_", 1: "persist_", 2: "persist_localorder_"}[persistent]
+    row = {"kernel": f"prefill_attn_tc_{mode}kernel<TN={tile}>",
            "reqs": reqs, "q_len": L, "kv_kept": kept, "Hq": Hq, "Hkv": Hkv, "D": D,
            "us": sec * 1e6, "tflops": flops / sec / 1e12,
            "frac_of_measured_bf16_peak": flops / sec / 1e12 / _peak_tflops()}
@@ -95,19 +99,16 @@ def main():
     ap.add_argument("--D", type=int, default=128)
     ap.add_argument("--evict-freq", type=int, default=2)
     ap.add_argument("--reps", type=int, default=20)
-    ap.add_argument("--only", type=int, default=-1, help="run one variant only (0 tcgen05, 1 mma.sync)")
+    ap.add_argument("--modes", action="store_true", help="PC_DEBUG library: one-shot / persistent side by side")
     a = ap.parse_args()
     dev = torch.device("cuda", 0)
-    if a.only >= 0:
-        row, _ = run(dev, a.reqs, a.len, a.Hq, a.Hkv, a.D, a.evict_freq, a.reps, a.only)
-        print(json.dumps(row), flush=True)
-        return
-    base, ref = run(dev, a.reqs, a.len, a.Hq, a.Hkv, a.D, a.evict_freq, a.reps, 1)
-    print(json.dumps(base), flush=True)
-    for tile, pers in ((64, 0), (64, 1), (64, 2)):
-        row, _ = run(dev, a.reqs, a.len, a.Hq, a.Hkv, a.D, a.evict_freq, a.reps, 0, check=ref, tile=tile,
-                     persistent=pers)
-        print(json.dumps(row), flush=True)
+    row, ref = run(dev, a.reqs, a.len, a.Hq, a.Hkv, a.D, a.evict_freq, a.reps)
+    print(json.dumps(row), flush=True)
+    if a.modes:
+        for tile, pers in ((64, 0), (64, 1), (64, 2)):
+            row, _ = run(dev, a.reqs, a.len, a.Hq, a.Hkv, a.D, a.evict_freq, a.reps, check=ref, tile=tile,
+                         persistent=pers)
+            print(json.dumps(row), flush=True)
 
 
 if __name__ == "__main__":

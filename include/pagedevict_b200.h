@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define PC_ABI_VERSION 4
+#define PC_ABI_VERSION 5
 #define PC_MAX_PEERS 8
 
 typedef enum pc_status {
@@ -232,14 +232,19 @@ int pc_decode_layer(const pc_decode_step* step /* HOST */, void* out, const void
  * pruned K/V never exists in memory.  req_meta int32 [num_reqs][6] =
  * {q_start, q_len, kv_src_start, kv_len(kept), first, pruned}; first and pruned are
  * multiples of 16 (block sizes 16 / 32).  num_tokens = rows of query / key / value (the
- * bound of the TMA tensor maps the tcgen05 kernel loads through). */
+ * bound of the TMA tensor maps the tcgen05 kernel loads through).
+ * req_meta_host: HOST copy of req_meta (the caller built it on the host anyway) or NULL.
+ * When given, every row is validated before the launch (ranges inside num_tokens, first /
+ * pruned multiples of 16) and a violation returns PC_ERR_INVALID; with NULL a violating row
+ * reaches the kernel's own guard, which traps (and poisons the CUDA context). */
 int pc_prefill_attn_topleft_causal(void* out, const void* query, const void* key,
                                    const void* value, const int32_t* req_meta,
                                    int32_t num_reqs, int32_t max_q_len, int64_t num_tokens,
                                    int32_t num_heads,
                                    int32_t num_kv_heads, int32_t head_size, float scale,
                                    int64_t q_stride, int64_t out_stride, int64_t key_stride,
-                                   int64_t value_stride, int32_t dtype, void* stream);
+                                   int64_t value_stride, const int32_t* req_meta_host /* HOST or NULL */,
+                                   int32_t dtype, void* stream);
 
 /* ---- block maintenance (backend surface, torch_cuda_sdpa.py:75-88) ------------------
  * pc_copy_blocks replaces _C_cache_ops::copy_blocks (csrc/cache_kernels.cu:69-150) for

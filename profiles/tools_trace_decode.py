@@ -1,7 +1,8 @@
 import sys, json, ctypes, torch, numpy as np
 import os
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-from vllm_paged_compression_b200 import _lib, ops, microbench
+from vllm_paged_compression_b200 import _lib, ops
+from benchtools import microbench
 lib = _lib.load()
 lib.pc_debug_set_decode_trace.argtypes = [ctypes.c_void_p]
 lib.pc_debug_set_decode_trace.restype = None

@@ -115,3 +115,141 @@ def run_case(c: Dict, device="cuda:0", num_layers=2, num_blocks=256, check_outpu
                 assert np.array_equal(got.view(np.int32), want.view(np.int32)), \
                     f"layer {layer} req {s.request_id}: block scores differ"
     return stats
+
+
+def _sampled_prefill_ref(q, k, v, seq_lens, kept_idx, rows_per_req, Hq, Hkv, D, scale, seed):
+    """Oracle prefill attention (top-left causal over the kept rows, fp32) for a SAMPLE of
+    query rows per request -- the full [Hq, Lq, Lkv] score tensor of an 8192-token prompt
+    does not fit a test.  -> (global row indices, ref [n, Hq*D])."""
+    G = Hq // Hkv
+    rs = np.random.RandomState(seed)
+    rows, refs = [], []
+    s = 0
+    for L, gi in zip(seq_lens, kept_idx):
+        idx = np.unique(np.concatenate([[0, L - 1, min(L - 1, 127), min(L - 1, 128)],
+                                        rs.randint(0, L, size=rows_per_req)]))
+        kk = k[s:s + L].view(L, Hkv, D)[gi].float().repeat_interleave(G, 1).transpose(0, 1)   # [Hq, L', D]
+        vv = v[s:s + L].view(L, Hkv, D)[gi].float().repeat_interleave(G, 1).transpose(0, 1)
+        qq = q[s:s + L].view(L, Hq, D)[idx].float().transpose(0, 1)                              # [Hq, n, D]
+        sc = scale * (qq @ kk.transpose(1, 2))
+        j = torch.arange(len(gi))[None, :]
+        sc = sc.masked_fill(j > torch.from_numpy(idx)[:, None], float("-inf"))
+        refs.append((torch.softmax(sc, -1) @ vv).transpose(0, 1).reshape(len(idx), Hq * D))
+        rows.append(torch.from_numpy(idx + s))
+        s += L
+    return torch.cat(rows), torch.cat(refs)
+
+
+def run_case_graph(c: Dict, device="cuda:0", num_layers=2, use_graph=True, pdl=None,
+                   prefill_rows=None, native_decode=True) -> Dict:
+    """The configuration bench.py times: prefill through PagedEvictEngine.step, decode through
+    DecodeGraphRunner (packed device state, CUDA-graph replay of all layers, fused cache write,
+    PDL per ops.pdl_default) -- against the oracle at every step.  Shapes are the benched ones
+    (B 64 x 1024 in for configs[2], ...), so the oracle side uses the reference's own compiled
+    CPU kernels (oracle/_ref) for decode when they are available (block 16)."""
+    from oracle import policy as opol
+    from oracle import ref_cpu
+    from vllm_paged_compression_b200.engine import PagedEvictEngine
+    from vllm_paged_compression_b200.graph_runner import DecodeGraphRunner
+    Hq, Hkv, D, bs = c["Hq"], c["Hkv"], c["D"], c["bs"]
+    cache_config, pol = make_configs(c)
+    lens = c["prompt_lens"]
+    B = len(lens)
+    per_seq = -(-max(lens) // bs) + c["steps"] // bs + 3
+    num_blocks = B * per_seq + 8
+    eng = PagedEvictEngine(num_layers, Hq, Hkv, D, cache_config, num_blocks, device=device,
+                           max_num_batched_tokens=c.get("max_num_batched_tokens", 16 * 1024))
+    native = ref_cpu.RefCpuOps if (native_decode and bs == 16 and ref_cpu.available()) else None
+    layers = [OracleLayer(Hq, D, D ** -0.5, Hkv, pol, native_ops=native) for _ in range(num_layers)]
+    kv_ref = [torch.zeros(2, num_blocks, bs * Hkv * D, dtype=torch.bfloat16) for _ in range(num_layers)]
+    for i, L in enumerate(lens):
+        eng.add_request(f"r{i}", L)
+    stats = {"evictions": 0, "layer_disagreements": 0, "steps": 0, "max_err": 0.0, "prefill_max_err": 0.0,
+             "oracle_decode": "reference csrc/cpu kernels" if native else "torch restatement"}
+    step = 0
+    # ---------------------------------------------------------------- prefill (engine.step)
+    while eng.waiting:
+        cpu_in = {}
+
+        def qkv(layer, n_tok):
+            q, k, v = layer_inputs(c["seed"], layer, step, n_tok, Hq, Hkv, D)
+            cpu_in[layer] = (q, k, v)
+            return q.to(device), k.to(device), v.to(device)
+        so = eng.step(qkv)
+        assert so.is_prompt
+        dev_slots = so.metadata.slot_mapping.cpu().tolist()
+        for layer in range(num_layers):
+            q, k, v = cpu_in[layer]
+            orc = layers[layer]
+            full = prefill_rows is None
+            ref = orc.prefill(q, k, v, kv_ref[layer], so.seq_lens, so.block_tables, so.request_ids,
+                              compute_attention=full)
+            assert orc.last["kept"] == so.seq_kv_lens
+            assert dev_slots == orc.last["slots"], "prefill slot mapping differs"
+            got = so.outputs[layer].float().cpu()
+            assert torch.isfinite(got).all()
+            if full:
+                err = (got - ref.float()).abs().max().item()
+            else:
+                kept_idx = [torch.from_numpy(opol.prompt_gather_index(L, pol)) for L in so.seq_lens]
+                rows, ref = _sampled_prefill_ref(q, k, v, so.seq_lens, kept_idx, prefill_rows, Hq, Hkv, D,
+                                                 D ** -0.5, c["seed"] + layer)
+                err = (got[rows] - ref).abs().max().item()
+            stats["prefill_max_err"] = max(stats["prefill_max_err"], err)
+            assert err <= 2e-2, f"prefill layer {layer}: attention output err {err}"
+        step += 1
+    # ---------------------------------------------------------------- decode (graph runner)
+    qs = [tuple(torch.empty(B, w * D, dtype=torch.bfloat16, device=device) for w in (Hq, Hkv, Hkv))
+          for _ in range(num_layers)]
+    runner = DecodeGraphRunner(eng, qs, use_graph=use_graph, pdl=pdl, max_kv_len=c.get("runner_max_kv_len"))
+    runner.record = True
+    req_ids = [s.request_id for s in runner.seqs]
+    for _ in range(c["steps"]):
+        cpu_in = []
+        for layer in range(num_layers):
+            q, k, v = layer_inputs(c["seed"], layer, step, B, Hq, Hkv, D)
+            cpu_in.append((q, k, v))
+            for dst, src in zip(qs[layer], (q, k, v)):
+                dst.copy_(src)
+        rmv0 = runner.step()
+        rec = runner.last
+        torch.cuda.synchronize()
+        trig_rows = rec["trigger_rows"]
+        vict = runner.d_victims.cpu().numpy() if trig_rows else None
+        for layer in range(num_layers):
+            q, k, v = cpu_in[layer]
+            orc = layers[layer]
+            ref, rmv_ref, _ = orc.decode(q, k, v, kv_ref[layer], rec["seq_lens"], rec["kv_lens"],
+                                         rec["tables"], req_ids)
+            assert rec["slots"] == orc.last["slots"], f"slot mapping differs at step {step}"
+            if pol.decode_evict_method == "value_l2":
+                got_rmv = {r: (req_ids[r], int(vict[layer][r])) for r in trig_rows if vict[layer][r] >= 0}
+            else:
+                got_rmv = {r: (req_ids[r], 1) for r in trig_rows}
+            assert got_rmv == rmv_ref, f"step {step} layer {layer}: victims {got_rmv} != oracle {rmv_ref}"
+            if layer == 0:
+                assert rmv0 == rmv_ref
+            elif got_rmv != rmv0:
+                stats["layer_disagreements"] += 1
+            got = runner.out_flat[layer].float().cpu()
+            assert torch.isfinite(got).all()
+            err = (got - ref.float()).abs().max().item()
+            stats["max_err"] = max(stats["max_err"], err)
+            assert err <= 2e-2, f"step {step} layer {layer}: attention output err {err}"
+        stats["evictions"] += len(rmv0)
+        stats["steps"] += 1
+        step += 1
+    stats["recaptures"] = runner.recaptures
+    torch.cuda.synchronize()
+    for layer in range(num_layers):
+        assert np.array_equal(eng.kv_caches[layer].cpu().view(torch.int16).numpy(),
+                              kv_ref[layer].view(torch.int16).numpy()), f"layer {layer}: KV cache bytes differ"
+        if pol.decode_evict_method == "value_l2":
+            pool = eng.impls[layer]._score_pool.cpu().numpy()
+            for s in eng.running:
+                ids = list(eng.block_manager.get_block_table(s.seq_id))
+                n_full = eng.block_manager.get_seq_kv_len(s.seq_id) // bs
+                want = layers[layer].scores_of(ids, n_full)
+                assert np.array_equal(pool[ids[:n_full]].view(np.int32), want.view(np.int32)), \
+                    f"layer {layer} req {s.request_id}: block scores differ"
+    return stats

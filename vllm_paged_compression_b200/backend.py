@@ -460,8 +460,9 @@ class TorchCUDASDPABackendImpl(AttentionImpl[TorchCUDASDPAMetadata]):
             st["total_tiles"] = toff[-1]
             st["kept_tokens"] = dst
             use = m6_full if (cfg is None or cfg.disable_evict_prefill) else m6
+            st["m6_host"] = np.ascontiguousarray(np.asarray(use, np.int32).reshape(-1, 6))
             pack = [np.asarray(m5, np.int32).reshape(-1), np.asarray(toff, np.int32),
-                    np.asarray(use, np.int32).reshape(-1)]
+                    st["m6_host"].reshape(-1)]
             names = ["m5", "toff", "m6"]
         else:
             kv = md.seq_kv_lens if md.seq_kv_lens else md.seq_lens
@@ -532,7 +533,8 @@ class TorchCUDASDPABackendImpl(AttentionImpl[TorchCUDASDPAMetadata]):
                 ops.reshape_and_cache(k, v, key_cache, value_cache, md.slot_mapping)
         # A1: top-left aligned causal mask over the kept rows (or all rows when
         # disable_evict_prefill / eviction off) -- torch_cuda_sdpa.py:1069-1127
-        ops.prefill_attn_topleft_causal(out, q, k, v, st["m6"], md.max_query_len, self.scale)
+        ops.prefill_attn_topleft_causal(out, q, k, v, st["m6"], md.max_query_len, self.scale,
+                                        req_meta_host=st["m6_host"])
 
     def _decode_step_struct(self, q, k, v, out, md, st, blk_stride: int, bs: int):
         """struct pc_decode_step shared by every layer of this engine step."""

@@ -77,6 +77,8 @@ static int decode_attn_impl(void* out, const void* query, const void* key_cache,
                             const pc_score_pool* score, void* workspace, size_t workspace_bytes,
                             int32_t dtype, void* stream, const FuseExtras& g_fuse);
 
+// the library is compiled with -fvisibility=hidden: only the C ABI is exported
+#pragma GCC visibility push(default)
 extern "C" {
 
 int pc_abi_version(void) { return PC_ABI_VERSION; }
@@ -186,6 +188,7 @@ int pc_paged_decode_attn_score(void* out, const void* query, const void* key_cac
                           stream, none);
 }
 }  // extern "C"
+#pragma GCC visibility pop
 
 static int decode_attn_impl(void* out, const void* query, const void* key_cache, const void* value_cache,
                             const int32_t* block_tables, int64_t table_stride, const int32_t* kv_lens,
@@ -220,6 +223,7 @@ static int decode_attn_impl(void* out, const void* query, const void* key_cache,
   return paged_decode_attn_score(a, static_cast<cudaStream_t>(stream));
 }
 
+#pragma GCC visibility push(default)
 extern "C" {
 
 int pc_decode_layer(const pc_decode_step* st, void* out, const void* query, const void* key,
@@ -272,7 +276,8 @@ int pc_prefill_attn_topleft_causal(void* out, const void* query, const void* key
                                    int32_t num_heads,
                                    int32_t num_kv_heads, int32_t head_size, float scale,
                                    int64_t q_stride, int64_t out_stride, int64_t key_stride,
-                                   int64_t value_stride, int32_t dtype, void* stream) {
+                                   int64_t value_stride, const int32_t* req_meta_host, int32_t dtype,
+                                   void* stream) {
   if (int rc = check_dtype(dtype)) return rc;
   if (num_reqs == 0) return PC_OK;
   if (!out || !query || !key || !value || !req_meta)
@@ -282,6 +287,7 @@ int pc_prefill_attn_topleft_causal(void* out, const void* query, const void* key
   a.num_reqs = num_reqs; a.max_q_len = max_q_len; a.num_tokens = num_tokens; a.Hq = num_heads; a.Hkv = num_kv_heads;
   a.D = head_size; a.scale = scale; a.q_stride = q_stride; a.out_stride = out_stride;
   a.key_stride = key_stride; a.value_stride = value_stride;
+  a.req_meta_host = req_meta_host;
   return prefill_attn(a, static_cast<cudaStream_t>(stream));
 }
 
@@ -309,14 +315,14 @@ int pc_swap_blocks(const void* src, void* dst, const int64_t* pairs, int32_t num
   return PC_OK;
 }
 
-/* Debug hook (not part of the drop-in surface): per-warp globaltimer stamps of the decode
- * kernel, [warps][4] = {kernel entry, schedule ready, last page consumed, exit}. */
+#ifdef PC_DEBUG
+/* Debug hooks, only in the PC_DEBUG build (libpagedevict_b200_debug.so, `make debug`); the
+ * product library neither exports them nor reads any environment variable.
+ * decode trace: per-warp globaltimer stamps, [warps][8]. */
 void pc_debug_set_decode_trace(void* device_buf) { pc::set_decode_trace(device_buf); }
-
-/* Debug hook: 0 = tcgen05/TMEM prefill kernel (product), 1 = the mma.sync baseline kernel
- * (kept only so the two can be timed side by side). */
-void pc_debug_set_prefill_variant(int32_t v) { pc::set_prefill_variant(v); }
 void pc_debug_set_prefill_tc_tile(int32_t tn) { pc::set_prefill_tc_tile(tn); }
 void pc_debug_set_prefill_tc_persistent(int32_t v) { pc::set_prefill_tc_persistent(v); }
+#endif
 
 }  // extern "C"
+#pragma GCC visibility pop

@@ -42,6 +42,7 @@
 #include "pc_common.cuh"
 #include "score_common.cuh"
 #include <stdlib.h>
+#include <atomic>
 #include <type_traits>
 
 #include "pc_api_internal.h"
@@ -55,8 +56,10 @@ struct DecodeParams {
   const int* __restrict__ block_tables;
   const int* __restrict__ kv_lens;
   __nv_bfloat16* __restrict__ out;
-  float* part_o;    // [chunks][8][D]
-  float* part_ml;   // [chunks][8][2]
+  float* part;      // split-KV partials, one slot per chunk id: [8][D] O then [8][2] (m, l); the slot
+                    // stride depends on D only, so the layout is the same whatever chunk plan a
+                    // (graph-replayed) launch reads from device memory
+  int cap_chunks;   // slots the workspace holds
   int* counters;    // [0] next chunk id - launched warps, [1] warps that have exited; zero between launches
   int* tickets;     // [B * GH] arrival counters, zero between launches
   const int* __restrict__ seq_lens;     // nullptr: no scoring
@@ -153,6 +156,7 @@ paged_decode_attn_score_kernel(const DecodeParams p) {
   constexpr int KSTEPS = D / 16;   // k-steps of the QK^T contraction
   constexpr int MT = D / 16;       // m-tiles (16 dims) of O^T
   constexpr int TT = BS / 16;      // 16-token tiles per page
+  constexpr int kSlot = 8 * D + 16;  // floats per partial slot (16-byte aligned stride)
 
   extern __shared__ __align__(1024) uint8_t smem[];
   const int warp = threadIdx.x >> 5;
@@ -218,6 +222,9 @@ paged_decode_attn_score_kernel(const DecodeParams p) {
   __syncthreads();
 
   const int C = cpre[p.B] * p.GH;  // chunks in this launch
+  // the host sizes the workspace for the worst plan up to max_kv_len (decode_workspace_bytes);
+  // a device-side plan / kv_lens beyond that must not scribble over other memory
+  if (C > p.cap_chunks) __trap();
 
   // (a runtime ring depth that lends idle warps' slots to busy ones was measured and is
   // slower: profiles/r01_decode_variants.txt)
@@ -613,8 +620,8 @@ paged_decode_attn_score_kernel(const DecodeParams p) {
     }
     // ---- split group: publish the partial, last arriver combines in chunk order
     {
-      float* po = p.part_o + (size_t)d.id * 8 * D;
-      float* pml = p.part_ml + (size_t)d.id * 16;
+      float* po = p.part + (size_t)d.id * kSlot;
+      float* pml = po + 8 * D;
 #pragma unroll
       for (int m = 0; m < MT; ++m) {
         po[(size_t)(2 * t) * D + 16 * m + g] = o[m][0];
@@ -637,6 +644,10 @@ paged_decode_attn_score_kernel(const DecodeParams p) {
     ticket = __shfl_sync(kFull, ticket, 0);
     if (p.trace) tr_fix += gtimer() - tf0;
     if (ticket != n_chunks - 1) continue;
+    // lane 0's acquire must order the OTHER lanes' loads of the peers' partials too: shuffles
+    // are not memory-ordering operations, a warp barrier is (bar.warp.sync orders memory
+    // accesses among the participating threads)
+    __syncwarp();
     ++tr_combines;
     if (lane == 0) *tk = 0;  // leave the workspace clean for the next launch
     {
@@ -647,7 +658,7 @@ paged_decode_attn_score_kernel(const DecodeParams p) {
       float M = -INFINITY;
 #pragma unroll 8
       for (int s = 0; s < n_chunks; ++s)
-        M = fmaxf(M, __ldcg(p.part_ml + (size_t)(id0 + s) * 16 + hh * 2));
+        M = fmaxf(M, __ldcg(p.part + (size_t)(id0 + s) * kSlot + 8 * D + hh * 2));
       // pass 2: weighted sum, 4 chunks (32 independent 16-byte loads per lane) in flight
       float L = 0.f;
       float acc[D / 4];
@@ -660,9 +671,10 @@ paged_decode_attn_score_kernel(const DecodeParams p) {
 #pragma unroll
         for (int u = 0; u < CU; ++u) {
           const int s = min(s0 + u, n_chunks - 1);
-          ms[u] = __ldcg(p.part_ml + (size_t)(id0 + s) * 16 + hh * 2);
-          ls[u] = __ldcg(p.part_ml + (size_t)(id0 + s) * 16 + hh * 2 + 1);
-          const float4* src = reinterpret_cast<const float4*>(p.part_o + ((size_t)(id0 + s) * 8 + hh) * D + d0);
+          const float* slot_s = p.part + (size_t)(id0 + s) * kSlot;
+          ms[u] = __ldcg(slot_s + 8 * D + hh * 2);
+          ls[u] = __ldcg(slot_s + 8 * D + hh * 2 + 1);
+          const float4* src = reinterpret_cast<const float4*>(slot_s + (size_t)hh * D + d0);
 #pragma unroll
           for (int i = 0; i < D / 16; ++i) v[u][i] = __ldcg(src + i);
         }
@@ -714,18 +726,26 @@ paged_decode_attn_score_kernel(const DecodeParams p) {
 }
 
 // ---------------------------------------------------------------------------- host
-// Workspace layout (fixed offsets, so the zeroed regions stay zero whatever the batch):
-//   [counters: 2 i32, 256 B][tickets: kMaxGroups i32][part_ml: chunks*16 f32][part_o: chunks*8*D f32]
+// Workspace layout (fixed offsets, so the zeroed regions stay zero whatever the batch, and so
+// that nothing depends on the chunk plan of one particular launch):
+//   [counters: 2 i32, 256 B][tickets: kMaxGroups i32][partials: one slot per chunk id,
+//    (8*D + 16) f32 = 8 heads x D of O, then 8 x (m, l)]
 constexpr int kMaxGroups = 1 << 20;
 constexpr size_t kOffTickets = 256;
 constexpr size_t kOffPartials = kOffTickets + (size_t)kMaxGroups * sizeof(int);
+static size_t slot_bytes(int D) { return (size_t)(8 * D + 16) * sizeof(float); }
+#ifdef PC_DEBUG
 static unsigned long long* g_decode_trace = nullptr;
 void set_decode_trace(void* buf) { g_decode_trace = static_cast<unsigned long long*>(buf); }
+static int env_int(const char* name, int dflt) {
+  const char* v = getenv(name);
+  return (v && *v) ? atoi(v) : dflt;
+}
+#endif
 
 struct DecodePlan {
   int chunk_pages;
   long long max_chunks;
-  size_t off_part_o, bytes;
 };
 
 // Chunks per group.  Measured on B200 (profiles/r01_decode_policy_sweep.txt, trace hook):
@@ -737,11 +757,6 @@ struct DecodePlan {
 //    enough bytes in flight;
 //  * big launches need a dynamic tail: per-SM HBM bandwidth differs by ~+-15 %, so with
 //    >= 64 pages per warp the groups are cut into >= 64-page chunks, ~4 per warp.
-static int env_int(const char* name, int dflt) {
-  const char* v = getenv(name);
-  return (v && *v) ? atoi(v) : dflt;
-}
-
 static DecodePlan plan_decode(int B, int Hq, int Hkv, int D, int BS, int max_kv_len, int num_sms, int warps) {
   DecodePlan pl;
   const int G = Hq / Hkv;
@@ -750,7 +765,6 @@ static DecodePlan plan_decode(int B, int Hq, int Hkv, int D, int BS, int max_kv_
   const long long max_blocks = max_kv_len > 0 ? (max_kv_len + BS - 1) / BS : 1;
   const long long pages_max = groups * max_blocks;
   const long long workers = (long long)num_sms * warps;
-  static const int force = env_int("PC_DECODE_CHUNK_PAGES", 0);
   // (a) parallelism: about workers/2 chunks, never shorter than 8 pages
   long long n = (workers / 2 + groups / 2) / groups;
   if (n > max_blocks / 8) n = max_blocks / 8;
@@ -762,29 +776,48 @@ static DecodePlan plan_decode(int B, int Hq, int Hkv, int D, int BS, int max_kv_
     if (nb > n) n = nb;
   }
   long long cp = (max_blocks + n - 1) / n;
+#ifdef PC_DEBUG
+  static const int force = env_int("PC_DECODE_CHUNK_PAGES", 0);
   if (force > 0) cp = force;
+#endif
   if (cp > max_blocks) cp = max_blocks;
   if (cp < 1) cp = 1;
   pl.chunk_pages = (int)cp;
   pl.max_chunks = groups * ((max_blocks + cp - 1) / cp);
-  pl.off_part_o = kOffPartials + ((size_t)pl.max_chunks * 16 * sizeof(float) + 255) / 256 * 256;
-  pl.bytes = pl.off_part_o + (size_t)pl.max_chunks * 8 * D * sizeof(float);
+  (void)D;
   return pl;
 }
 
-// warps per CTA for each (D, BS): the ring (warps x stages x (K+V page)) must fit 227 KB
-static int decode_cfg() {
-  static const int cfg = env_int("PC_DECODE_CFG", 0);
-  return cfg;
+// Chunk slots a workspace must hold so that EVERY plan the planner can produce for a
+// longest row of 1 .. max_kv_len tokens fits.  chunks-per-group is not monotone in the
+// length (90 blocks -> 9-page chunks -> 10 per group; 88 blocks -> 8-page chunks -> 11), and
+// under CUDA-graph replay the plan is read from device memory each step, so sizing by the
+// plan of max_kv_len alone is not enough.
+static long long worst_case_chunks(int B, int Hq, int Hkv, int D, int BS, int max_kv_len, int num_sms, int warps) {
+  struct Key { int B, Hq, Hkv, D, BS, max_kv_len, num_sms, warps; long long chunks; };
+  static thread_local Key memo = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+  if (memo.B == B && memo.Hq == Hq && memo.Hkv == Hkv && memo.D == D && memo.BS == BS &&
+      memo.max_kv_len == max_kv_len && memo.num_sms == num_sms && memo.warps == warps)
+    return memo.chunks;
+  const int max_blocks = max_kv_len > 0 ? (max_kv_len + BS - 1) / BS : 1;
+  long long worst = 1;
+  for (int n = 1; n <= max_blocks; ++n) {
+    const long long c = plan_decode(B, Hq, Hkv, D, BS, n * BS, num_sms, warps).max_chunks;
+    if (c > worst) worst = c;
+  }
+  memo = {B, Hq, Hkv, D, BS, max_kv_len, num_sms, warps, worst};
+  return worst;
 }
+
+// warps per CTA for each (D, BS): the ring (warps x stages x (K+V page)) must fit 227 KB
 static int decode_warps(int D, int BS) {
-  if (D == 128 && BS == 16) return decode_cfg() == 1 ? 6 : 8;
   return (D == 128 && BS == 32) ? 4 : 8;
 }
 
 size_t decode_workspace_bytes(int B, int Hq, int Hkv, int D, int BS, int max_kv_len, int num_sms) {
   if (Hkv <= 0 || Hq < Hkv) return 0;
-  return plan_decode(B, Hq, Hkv, D, BS, max_kv_len, num_sms, decode_warps(D, BS)).bytes;
+  return kOffPartials +
+         (size_t)worst_case_chunks(B, Hq, Hkv, D, BS, max_kv_len, num_sms, decode_warps(D, BS)) * slot_bytes(D);
 }
 int decode_plan_chunk_pages(int B, int Hq, int Hkv, int D, int BS, int max_kv_len, int num_sms) {
   if (Hkv <= 0 || Hq < Hkv) return 0;
@@ -797,15 +830,19 @@ static int launch_decode(const DecodeParams& p, int num_sms, long long max_chunk
   auto kern = paged_decode_attn_score_kernel<D, BS, kWarps, kStages, kPair, kCtasPerSm>;
   const size_t smem = T::smem_bytes(p.B);
   if (smem > (size_t)(227 * 1024) / kCtasPerSm) return set_error(PC_ERR_INVALID, "decode: batch too large for the in-kernel schedule");
-  static size_t smem_set[64] = {0};  // per device: largest dynamic smem opted in so far
+  // largest dynamic smem opted in so far, per device (monotone; a racing thread at worst
+  // repeats the idempotent attribute call)
+  static std::atomic<size_t> smem_set[64];
   int dev = 0;
   cudaGetDevice(&dev);
-  if (dev < 0 || dev >= 64 || smem_set[dev] < smem) {
+  if (dev < 0 || dev >= 64 || smem_set[dev].load(std::memory_order_acquire) < smem) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return set_cuda_error("cudaFuncSetAttribute(decode)", e);
-    static const int carve = env_int("PC_DECODE_CARVEOUT", -1);
-    if (carve >= 0) cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
-    if (dev >= 0 && dev < 64) smem_set[dev] = smem;
+    if (dev >= 0 && dev < 64) {
+      size_t cur = smem_set[dev].load(std::memory_order_relaxed);
+      while (cur < smem && !smem_set[dev].compare_exchange_weak(cur, smem, std::memory_order_release)) {
+      }
+    }
   }
   long long ctas = max_chunks < (long long)num_sms * kCtasPerSm ? max_chunks : (long long)num_sms * kCtasPerSm;  // spread over SMs first
   if (ctas < 1) ctas = 1;
@@ -834,7 +871,11 @@ int paged_decode_attn_score(const DecodeArgs& a, cudaStream_t stream) {
   const int num_sms = device_sm_count();
   if (num_sms <= 0) return PC_ERR_CUDA;
   const DecodePlan pl = plan_decode(a.B, a.Hq, a.Hkv, a.D, a.BS, a.max_kv_len, num_sms, decode_warps(a.D, a.BS));
-  if (a.workspace_bytes < pl.bytes)
+  // with a device-side plan (graph replay) any plan up to max_kv_len may be in force
+  const long long need_chunks =
+      a.plan ? worst_case_chunks(a.B, a.Hq, a.Hkv, a.D, a.BS, a.max_kv_len, num_sms, decode_warps(a.D, a.BS))
+             : pl.max_chunks;
+  if (a.workspace_bytes < kOffPartials + (size_t)need_chunks * slot_bytes(a.D))
     return set_error(PC_ERR_INVALID, "decode workspace too small (see pc_paged_decode_workspace_bytes)");
   uint8_t* ws = static_cast<uint8_t*>(a.workspace);
   DecodeParams p;
@@ -846,8 +887,11 @@ int paged_decode_attn_score(const DecodeArgs& a, cudaStream_t stream) {
   p.out = static_cast<__nv_bfloat16*>(a.out);
   p.counters = reinterpret_cast<int*>(ws);
   p.tickets = reinterpret_cast<int*>(ws + kOffTickets);
-  p.part_ml = reinterpret_cast<float*>(ws + kOffPartials);
-  p.part_o = reinterpret_cast<float*>(ws + pl.off_part_o);
+  p.part = reinterpret_cast<float*>(ws + kOffPartials);
+  {
+    const size_t cap = (a.workspace_bytes - kOffPartials) / slot_bytes(a.D);
+    p.cap_chunks = cap > 0x7fffffffull ? 0x7fffffff : (int)cap;
+  }
   p.seq_lens = a.score.n_pools > 0 ? a.seq_lens : nullptr;
   p.score = a.score;
   p.B = a.B; p.Hq = a.Hq; p.Hkv = a.Hkv; p.G = a.Hq / a.Hkv; p.HG = (p.G + 7) / 8; p.GH = a.Hkv * p.HG;
@@ -859,7 +903,11 @@ int paged_decode_attn_score(const DecodeArgs& a, cudaStream_t stream) {
   p.chunk_pages = pl.chunk_pages;
   p.plan = a.plan;
   p.pdl = a.pdl;
+#ifdef PC_DEBUG
   p.trace = g_decode_trace;
+#else
+  p.trace = nullptr;
+#endif
   p.new_k = static_cast<const __nv_bfloat16*>(a.new_k);
   p.new_v = static_cast<const __nv_bfloat16*>(a.new_v);
   p.slot_mapping = a.slot_mapping;
@@ -877,9 +925,8 @@ int paged_decode_attn_score(const DecodeArgs& a, cudaStream_t stream) {
   // a device-side plan may change between replays of a captured launch: full grid
   const long long grid_chunks = a.plan ? (long long)num_sms * 8 : pl.max_chunks;
   if (a.D == 128 && a.BS == 16) {
-    // PC_DECODE_CFG=1: 6 warps x 4-stage rings, pages consumed in pairs (one softmax tile of
-    // 32 tokens); measured within +-3 % of the default on every shape (profiles/r01_decode_variants.txt)
-    if (decode_cfg() == 1) return launch_decode<128, 16, 6, 4, true>(p, num_sms, grid_chunks, stream);
+    // (6 warps x 4-stage rings with pages consumed in pairs measured within +-3 % of this on
+    // every shape, profiles/r01_decode_variants.txt; not built)
     return launch_decode<128, 16, 8, 3, false>(p, num_sms, grid_chunks, stream);
   }
   if (a.D == 128 && a.BS == 32) return launch_decode<128, 32, 4, 3, false>(p, num_sms, grid_chunks, stream);

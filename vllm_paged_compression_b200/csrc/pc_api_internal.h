@@ -61,7 +61,9 @@ struct DecodeArgs {
 size_t decode_workspace_bytes(int B, int Hq, int Hkv, int D, int BS, int max_kv_len, int num_sms);
 int decode_plan_chunk_pages(int B, int Hq, int Hkv, int D, int BS, int max_kv_len, int num_sms);
 int paged_decode_attn_score(const DecodeArgs& a, cudaStream_t stream);
-void set_decode_trace(void* buf);  // debug: per-warp globaltimer stamps, nullptr = off
+#ifdef PC_DEBUG
+void set_decode_trace(void* buf);  // per-warp globaltimer stamps, nullptr = off
+#endif
 
 struct CacheWriteArgs {
   const void* key;
@@ -105,12 +107,13 @@ struct PrefillArgs {
   float scale;
   long long q_stride, out_stride, key_stride, value_stride;
   long long num_tokens;  // rows of q / k / v (bounds of the TMA tensor maps)
+  const int* req_meta_host;  // HOST copy of req_meta for argument validation, or nullptr
 };
-int prefill_attn(const PrefillArgs& a, cudaStream_t stream);     // dispatcher (tcgen05 unless variant 1)
-int prefill_attn_tc(const PrefillArgs& a, cudaStream_t stream);  // tcgen05/TMEM kernel
-void set_prefill_tc_persistent(int v);  // debug: 1 = persistent CTAs (default), 0 = one CTA per query tile
-void set_prefill_tc_tile(int tn);  // debug: kv tile width of the tcgen05 kernel (64 | 128)
-void set_prefill_variant(int v);  // debug: 0 = tcgen05/TMEM (product), 1 = mma.sync baseline kernel
+int prefill_attn(const PrefillArgs& a, cudaStream_t stream);     // tcgen05/TMEM kernel (prefill_attn_tc.cu)
+#ifdef PC_DEBUG
+void set_prefill_tc_persistent(int v);  // 1 = persistent CTAs, 0 = one CTA per query tile, -1 = rule
+void set_prefill_tc_tile(int tn);       // kv tile width of the tcgen05 kernel (64 | 128)
+#endif
 
 int copy_blocks(void* k_cache, void* v_cache, const long long* pairs, int num_pairs,
                 long long block_bytes, cudaStream_t stream);

@@ -386,15 +386,23 @@ prefill_attn_tc_kernel(const PrefillTcParams p, const __grid_constant__ CUtensor
 
 }  // namespace
 
-// -1 = measured rule (default), 0 = one CTA per item, 1 = persistent CTAs (2 = persistent with the
-// one-shot item order, debug).  B200, TFLOP/s, one CTA per item / persistent (P in TMEM):
+// One CTA per item or persistent CTAs.  B200, TFLOP/s, one CTA per item / persistent (P in TMEM):
 //   16 x 1024 q (544 kept) 642 / 728    64 x 1024 690 / 718    16 x 1024, D 64 380 / 444
 //   16 x 2048 (1056 kept)  879 / 884     8 x 4096 1026 / 1019   4 x 8192 (no eviction) 1133 / 1082
 // The persistent walk saves the per-item launch / setup / first-load latency that dominates short
 // prompts; on long ones the hardware CTA scheduler balances the uneven items better than the
 // static round-robin, and the per-(request, head) item order keeps the live K/V streams in L2.
+// Rule: persistent for max_q_len <= 2048.  (PC_DEBUG builds can override: -1 = rule, 0 = one CTA
+// per item, 1 = persistent, 2 = persistent with the one-shot item order.)
+#ifdef PC_DEBUG
 static int g_tc_persistent = -1;
 void set_prefill_tc_persistent(int v) { g_tc_persistent = v; }
+static int g_tc_tile_n = 64;
+void set_prefill_tc_tile(int tn) { g_tc_tile_n = (tn == 128) ? 128 : 64; }
+#else
+constexpr int g_tc_persistent = -1;
+constexpr int g_tc_tile_n = 64;
+#endif
 
 // ---- host: tensor maps.  The encoder is a driver entry point fetched through the runtime
 // (no link against libcuda).
@@ -451,25 +459,45 @@ static int launch_prefill_tc(const PrefillTcParams& p, const PrefillArgs& a, cud
   return check_launch("prefill_attn_tc_kernel");
 }
 
-static int g_tc_tile_n = 64;
-void set_prefill_tc_tile(int tn) { g_tc_tile_n = (tn == 128) ? 128 : 64; }
-
-// Requirements beyond prefill_attn()'s checks: num_tokens (rows of q/k/v) known, and
-// first / pruned multiples of 16 (block sizes 16 and 32; checked on the device, __trap).
-int prefill_attn_tc(const PrefillArgs& a, cudaStream_t stream) {
+// A1 entry: argument checks + launch.  The streamingLLM gather runs as TMA box coordinates, so
+// `first` and `pruned` of every pruned request must be multiples of 16 (true for block sizes
+// 16 / 32 with the reference's policies: both are whole blocks).  The check needs the HOST copy
+// of req_meta; without one (req_meta_host == NULL) a violating request reaches the device-side
+// guard, which is a trap -- callers that cannot vouch for the alignment pass the host copy.
+int prefill_attn(const PrefillArgs& a, cudaStream_t stream) {
+  if (a.num_reqs <= 0 || a.max_q_len <= 0) return 0;
+  if (a.Hkv <= 0 || a.Hq % a.Hkv) return set_error(PC_ERR_INVALID, "num_heads must be a multiple of num_kv_heads");
+  if ((a.q_stride | a.out_stride | a.key_stride | a.value_stride) % 8)
+    return set_error(PC_ERR_INVALID, "q/out/key/value row strides must be multiples of 8 elements");
+  if ((reinterpret_cast<uintptr_t>(a.q) | reinterpret_cast<uintptr_t>(a.k) |
+       reinterpret_cast<uintptr_t>(a.v) | reinterpret_cast<uintptr_t>(a.out)) & 15)
+    return set_error(PC_ERR_INVALID, "q/k/v/out pointers must be 16-byte aligned");
   if (a.num_tokens <= 0) return set_error(PC_ERR_INVALID, "prefill: num_tokens must be the row count of q/k/v");
+  if (a.req_meta_host != nullptr) {
+    for (int r = 0; r < a.num_reqs; ++r) {
+      const int* m = a.req_meta_host + r * 6;
+      if (m[1] < 0 || m[3] < 0 || m[3] > m[1] || m[0] < 0 || m[2] < 0 || m[4] < 0 || m[5] < 0 ||
+          (long long)m[0] + m[1] > a.num_tokens || (long long)m[2] + m[3] + m[5] > a.num_tokens)
+        return set_error(PC_ERR_INVALID, "prefill: req_meta row out of range (q_len >= kv_len >= 0, rows inside num_tokens)");
+      if (m[5] != 0 && (((m[4] | m[5]) & 15) != 0))
+        return set_error(PC_ERR_INVALID,
+                         "prefill: first / pruned must be multiples of 16 tokens (whole blocks of 16 / 32)");
+    }
+  }
   PrefillTcParams p;
   p.out = static_cast<__nv_bfloat16*>(a.out);
   p.req_meta = a.req_meta;
   p.Hq = a.Hq; p.Hkv = a.Hkv;
   p.out_stride = a.out_stride;
   p.scale_log2 = a.scale * 1.4426950408889634f;
-  if (a.D == 128)
-    return g_tc_tile_n == 128 ? launch_prefill_tc<128, 128>(p, a, stream)
-                              : launch_prefill_tc<128, 64>(p, a, stream);
-  if (a.D == 64)
-    return g_tc_tile_n == 128 ? launch_prefill_tc<64, 128>(p, a, stream)
-                              : launch_prefill_tc<64, 64>(p, a, stream);
+#ifdef PC_DEBUG
+  if (g_tc_tile_n == 128) {
+    if (a.D == 128) return launch_prefill_tc<128, 128>(p, a, stream);
+    if (a.D == 64) return launch_prefill_tc<64, 128>(p, a, stream);
+  }
+#endif
+  if (a.D == 128) return launch_prefill_tc<128, 64>(p, a, stream);
+  if (a.D == 64) return launch_prefill_tc<64, 64>(p, a, stream);
   return set_error(PC_ERR_UNSUPPORTED, "Unsupported head size (supported: 64|128)");
 }
 

@@ -60,9 +60,28 @@ class DecodeGraphRunner:
         self.bts = [bm.block_tables[s.seq_id] for s in self.seqs]
         cur_max = max(bt.get_seq_kv_len() for bt in self.bts)
         if max_kv_len is None:
-            # eviction bounds the physical length near where it is now; otherwise leave room
-            max_kv_len = cur_max + (8 * bs * max(getattr(self.cfg, "evict_freq", 1) or 1, 1)
-                                    if self.cfg is not None else 4096)
+            # the bound follows the policy: evict_freq mode holds a row near where it is now;
+            # budget mode lets rows below the budget grow up to it (one block per 16 steps, no
+            # eviction) and then holds them there; without eviction rows just grow.  A row that
+            # still reaches the bound makes step() re-capture with a larger one (_setup).
+            if self.cfg is None:
+                max_kv_len = cur_max + 4096
+            elif self.cfg.cache_prune_type == "budget":
+                max_kv_len = max(int(self.cfg.cache_budget), cur_max) + 8 * bs
+            else:
+                max_kv_len = cur_max + 8 * bs * max(getattr(self.cfg, "evict_freq", 1) or 1, 1)
+        self._qkv_arg, self._outs_arg = qkv, outs
+        self.record = False      # tests: keep the host-side inputs of the last step in self.last
+        self.last: Dict[str, list] = {}
+        self.recaptures = -1
+        self._setup(int(max_kv_len))
+
+    def _setup(self, max_kv_len: int) -> None:
+        """(Re)build everything whose size depends on the table width: the packed device
+        state, the host mirror, the workspace and the captured graphs."""
+        eng, B, bs, L, io = self.eng, self.B, self.bs, self.L, self.io
+        qkv, outs = self._qkv_arg, self._outs_arg
+        self.recaptures += 1
         self.max_kv_len = int(max_kv_len)
         M = self.M = cdiv(self.max_kv_len, bs) + 1
 
@@ -105,9 +124,10 @@ class DecodeGraphRunner:
         self.kv = np.asarray([bt.get_seq_kv_len() for bt in self.bts], dtype=np.int64)
         self.rows = np.arange(B)
 
-        # ---- decode workspace large enough for every plan up to max_kv_len
+        # ---- decode workspace: pc_paged_decode_workspace_bytes covers EVERY plan the device-side
+        # plan word can name for a longest row of up to max_kv_len tokens
         Hq, Hkv, D = eng.num_heads, eng.num_kv_heads, eng.head_size
-        need = max(ops.paged_decode_workspace_bytes(B, Hq, Hkv, D, bs, n * bs) for n in range(1, M + 1))
+        need = ops.paged_decode_workspace_bytes(B, Hq, Hkv, D, bs, M * bs)
         self.ws = torch.zeros(need, dtype=torch.uint8, device=self.device)
         self._plan_cache: Dict[int, int] = {}
 
@@ -199,6 +219,11 @@ class DecodeGraphRunner:
         bm = eng.block_manager
         if not bm.can_append_slots(B):
             raise RuntimeError("out of KV blocks (preemption is outside the hot path)")
+        # a row about to outgrow the captured table width: re-capture with a larger bound
+        grow = self.nblk + (self.kv % bs == 0)
+        if int(grow.max()) > self.M - 1:
+            torch.cuda.current_stream(self.device).synchronize()
+            self._setup(max(2 * self.max_kv_len - int(self.kv.min()), (int(grow.max()) + 8) * bs))
         tab, nblk = self.tab, self.nblk
         for r, (s, bt) in enumerate(zip(self.seqs, self.bts)):      # scheduler.py _schedule_default
             s.seq_len += 1
@@ -221,6 +246,10 @@ class DecodeGraphRunner:
         if plan is None:
             plan = self._plan_cache[mx] = ops.paged_decode_plan(B, eng.num_heads, eng.num_kv_heads,
                                                                 eng.head_size, bs, mx)
+        if self.record:
+            self.last = {"seq_lens": self.seq.tolist(), "kv_lens": kv_pass.tolist(), "slots": slot.tolist(),
+                         "tables": [tab[r, :nblk[r]].tolist() for r in range(B)],
+                         "trigger_rows": np.nonzero(trig)[0].tolist()}
         # ---- one packed H2D
         i = self._ring_i
         self._ring_i = (i + 1) % len(self._ring)

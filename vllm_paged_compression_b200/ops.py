@@ -328,10 +328,18 @@ def pdl_default(batch: int) -> bool:
 # ------------------------------------------------------------------------------ A1
 def prefill_attn_topleft_causal(out: torch.Tensor, query: torch.Tensor, key: torch.Tensor,
                                 value: torch.Tensor, req_meta: torch.Tensor, max_q_len: int,
-                                scale: float) -> None:
+                                scale: float, req_meta_host=None) -> None:
     """query/out [T, Hq, D], key/value [T, Hkv, D] (un-pruned prompt rows); req_meta int32
-    [R,6] = {q_start, q_len, kv_src_start, kv_len(kept), first, pruned}."""
+    [R,6] = {q_start, q_len, kv_src_start, kv_len(kept), first, pruned}.  req_meta_host: the
+    same rows as a contiguous int32 numpy array / CPU tensor -- lets the library validate them
+    before the launch (RuntimeError instead of a device-side trap)."""
     _req_cuda(out, query, key, value, req_meta)
+    host_ptr = None
+    if req_meta_host is not None:
+        h = req_meta_host if isinstance(req_meta_host, torch.Tensor) else torch.from_numpy(req_meta_host)
+        if h.is_cuda or h.dtype != torch.int32 or not h.is_contiguous() or h.numel() != req_meta.numel():
+            raise RuntimeError("req_meta_host must be a contiguous int32 CPU copy of req_meta")
+        host_ptr = h.data_ptr()
     T, Hq, D = query.shape
     Hkv = key.shape[1]
     if req_meta.dtype != torch.int32 or not req_meta.is_contiguous():
@@ -342,7 +350,7 @@ def prefill_attn_topleft_causal(out: torch.Tensor, query: torch.Tensor, key: tor
     check(_lib.load().pc_prefill_attn_topleft_causal(
         out.data_ptr(), query.data_ptr(), key.data_ptr(), value.data_ptr(), req_meta.data_ptr(),
         req_meta.shape[0], int(max_q_len), int(min(T, key.shape[0], value.shape[0])), Hq, Hkv, D, float(scale), query.stride(0), out.stride(0),
-        key.stride(0), value.stride(0), _dtype_code(query), _stream(query)))
+        key.stride(0), value.stride(0), host_ptr, _dtype_code(query), _stream(query)))
     _launched()
 
 
