@@ -299,6 +299,11 @@ class PinnedLayerIO:
         self.h2d_bytes = self.qkv_host.numel() * self.qkv_host.element_size()
         self.d2h_bytes = self.out_host.numel() * self.out_host.element_size()
 
+    def describe(self) -> dict:
+        """Copy schedule, for the bench log."""
+        return {"groups": [b - a for a, b in self.bounds], "duplex_streams": self.d2h_stream is not self.h2d_stream,
+                "h2d_copies_per_step": len(self.bounds), "d2h_copies_per_step": len(self.bounds)}
+
     def begin_step(self) -> None:
         """Queue every layer group's H2D on the copy stream (after the previous step's
         compute has consumed the staging buffers)."""

@@ -71,6 +71,8 @@ class DecodeGraphRunner:
             else:
                 max_kv_len = cur_max + 8 * bs * max(getattr(self.cfg, "evict_freq", 1) or 1, 1)
         self._qkv_arg, self._outs_arg = qkv, outs
+        self.log_victims = False  # bench (TP > 1): keep every trigger step's [L, B] victims on the device
+        self.victim_log: List[torch.Tensor] = []
         self.record = False      # tests: keep the host-side inputs of the last step in self.last
         self.last: Dict[str, list] = {}
         self.recaptures = -1
@@ -281,6 +283,8 @@ class DecodeGraphRunner:
         rmv: Dict[int, Tuple[str, int]] = {}
         if any_trig:
             rows = np.nonzero(trig)[0]
+            if self.log_victims and self.value_l2:
+                self.victim_log.append(self.d_victims.clone())
             if self.value_l2:
                 vict = self.d_victims[0].cpu().numpy()
                 rmv = {int(r): (self.seqs[r].request_id, int(vict[r])) for r in rows if vict[r] >= 0}
