@@ -156,6 +156,7 @@ def parse_args():
                     help="eager PagedEvictEngine.step (one forward() per layer) instead of CUDA-graph replay")
     ap.add_argument("--no-pdl", action="store_true",
                     help="no programmatic dependent launch between consecutive layers' decode kernels")
+    ap.add_argument("--force-pdl", action="store_true", help="PDL whatever the batch (default: ops.pdl_default rule)")
     ap.add_argument("--score-exchange", default="p2p", choices=["p2p", "nccl"],
                     help="N > 1: how per-head block scores reach the other ranks (parallel.py)")
     ap.add_argument("--io-group", type=int, default=0,
@@ -342,7 +343,7 @@ class Arm:
         a = self.args
         kv_now = max(self.eng.block_manager.get_seq_kv_len(s.seq_id) for s in self.eng.running)
         bound = kv_now + total_steps + 2 * self.spec.block_size + 64
-        pdl = False if a.no_pdl else None
+        pdl = False if a.no_pdl else (True if a.force_pdl else None)
         if self.host_io:
             self.runner = DecodeGraphRunner(self.eng, None, io=self.io, max_kv_len=bound, pdl=pdl)
         else:
@@ -437,7 +438,7 @@ def roofline_leg(torch, dist, arm, args, world, reps=20):
     ks = [k.view(arm.B, arm.Hkv, arm.D) for k in arm.k]
     vs = [v.view(arm.B, arm.Hkv, arm.D) for v in arm.v]
     scale = arm.D ** -0.5
-    pdl = (not args.no_pdl) and ops.pdl_default(arm.B)
+    pdl = (not args.no_pdl) and (args.force_pdl or ops.pdl_default(arm.B))
     # the launch the product makes (pc_decode_layer on a non-trigger step): the step's K/V row
     # written by the attention kernel itself, programmatic dependent launch behind the
     # previous layer's kernel (--no-pdl: plain stream order)
@@ -493,6 +494,8 @@ def run_b200(spec: Spec, args, torch, dist, device, rank, world, K, W, e2e: bool
     arm.prefill()
     arm.make_runner(total)
     t = timed_steps(torch, dist, arm, K, W, P, world)
+    if arm.runner is not None:
+        arm.runner.sync_host()          # the roofline leg reads lengths from the host objects
     same, n_vict = victims_identical(torch, dist, arm, world)
     roof = roofline_leg(torch, dist, arm, args, world)
     clocks = sampler.stop() if sampler else None        # sampled over the timed steps + the roofline leg

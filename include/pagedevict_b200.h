@@ -147,7 +147,8 @@ int pc_evict_select_compact(const int32_t* block_tables, int64_t table_stride,
  * score != NULL and seq_lens != NULL, rows with seq_lens[b] % block_size == 0 (and a
  * full last block) get pool[table[b][ceil(kv_len/bs)-1]][head_offset + h] for every
  * local kv head h.
- * workspace: pc_paged_decode_workspace_bytes() bytes, 256-byte aligned.  It must be
+ * workspace: pc_paged_decode_workspace_bytes(max_kv_len) bytes -- enough for every plan the
+ * planner produces for a longest row of up to max_kv_len tokens -- 256-byte aligned.  It must be
  * ZERO-FILLED by the caller before its first use; every call leaves it ready for the
  * next one (arrival tickets are reset in-kernel), so one workspace per stream is
  * allocated once and reused.  A single kernel launch, no memset. */
@@ -201,12 +202,12 @@ typedef struct pc_decode_step {
                                   * (torch_cuda_sdpa.py:565-598): slot_mapping[r] ==
                                   * last_table_entry(r) * block_size + (kv_lens[r] - 1) % block_size.
                                   * Ignored (separate write) when attend_uncompacted is set. */
-  const int32_t* plan;           /* DEVICE int32[1] = {chunk_pages} from pc_paged_decode_plan, read by
-                                  * the kernel at run time instead of being planned from max_kv_len at
+  const int32_t* plan;           /* DEVICE int32[2] = {chunk_pages, team} from pc_paged_decode_plan, read
+                                  * by the kernel at run time instead of being planned from max_kv_len at
                                   * launch time -- lets a captured (CUDA graph) launch be replayed while
-                                  * kv lengths move; NULL = plan on the host.  workspace must then hold
-                                  * pc_paged_decode_workspace_bytes of every max_kv_len it is replayed
-                                  * with. */
+                                  * kv lengths move; NULL = plan on the host.  The workspace
+                                  * (pc_paged_decode_workspace_bytes(max_kv_len)) covers every plan the
+                                  * planner produces for lengths up to max_kv_len. */
   int32_t pdl;                   /* != 0: launch the attention kernel with programmatic stream
                                   * serialization (PDL): its prologue and first ring of KV-page loads
                                   * overlap the tail of the PRECEDING kernel of the stream.  The caller
@@ -216,13 +217,36 @@ typedef struct pc_decode_step {
                                   * K/V rows are read after the dependency wait.  Only honoured with
                                   * fuse_cache_write on non-trigger steps. */
 } pc_decode_step;
-/* chunk_pages the host planner picks for this launch shape (to fill pc_decode_step.plan). */
-int32_t pc_paged_decode_plan(int32_t batch, int32_t num_heads, int32_t num_kv_heads,
-                             int32_t head_size, int32_t block_size, int32_t max_kv_len);
+/* The launch plan the host planner picks for this shape, to fill pc_decode_step.plan:
+ * out_plan[0] = pages per chunk (split-KV granularity), out_plan[1] = warps per team (1|2|4|8:
+ * warps of one CTA that share a chunk and combine through shared memory). */
+int pc_paged_decode_plan(int32_t batch, int32_t num_heads, int32_t num_kv_heads, int32_t head_size,
+                         int32_t block_size, int32_t max_kv_len,
+                         int32_t num_sms /* 0 = the current device's; a pure function of its arguments otherwise */,
+                         int32_t* out_plan /* HOST int32[2] */);
+/* attend_tables (optional): tables [batch][attend_stride] this layer attends over INSTEAD of the
+ * step's -- the layer's rows of pc_evict_select_compact_layers' output.  No selection is run by
+ * this call then (out_victim is not written), and the attention kernel keeps its PDL launch. */
 int pc_decode_layer(const pc_decode_step* step /* HOST */, void* out, const void* query,
                     const void* key, const void* value, void* key_cache, void* value_cache,
                     const pc_score_pool* score /* HOST, NULL = no value_l2 */,
-                    int32_t* out_victim /* [batch] or NULL */);
+                    int32_t* out_victim /* [batch] or NULL */,
+                    const int32_t* attend_tables /* DEVICE or NULL */, int64_t attend_stride);
+
+/* P3 + S4 + C1 for EVERY layer of an engine step in one launch (grid batch x layers).  A
+ * layer's victims depend on the block scores of EARLIER steps and on the step's tables only
+ * (torch_cuda_sdpa.py:1478-1560 reads BlockL2NormManager state written by previous forwards),
+ * so all layers' selections can precede the first layer's attention: one launch instead of one
+ * per layer, and the attention kernels of a trigger step stay PDL-chained.
+ * score_pools: DEVICE array [num_layers] of this rank's pool of each layer (pc_score_pool
+ * .pools[local]), NULL for streamingLLM.  out_tables [num_layers][batch][out_stride] (layer
+ * stride out_layer_stride ints), out_victims [num_layers][batch] (-1 = row did not trigger). */
+int pc_evict_select_compact_layers(const int32_t* block_tables, int64_t table_stride,
+                                   const int32_t* n_blocks, const int32_t* seq_lens, int32_t batch,
+                                   int32_t num_layers, const pc_evict_policy* policy /* HOST */,
+                                   const float* const* score_pools /* DEVICE */, int32_t heads_total,
+                                   int32_t* out_tables, int64_t out_stride, int64_t out_layer_stride,
+                                   int32_t* out_victims, void* stream);
 
 /* ---- A1: prefill attention, TOP-LEFT aligned causal mask over the pruned prompt -----
  * Replaces _run_sdpa_forward (torch_cuda_sdpa.py:1069-1127): per request

@@ -240,6 +240,7 @@ def run_case_graph(c: Dict, device="cuda:0", num_layers=2, use_graph=True, pdl=N
         stats["steps"] += 1
         step += 1
     stats["recaptures"] = runner.recaptures
+    runner.sync_host()            # per-token counters of _Seq / BlockTable are booked lazily
     torch.cuda.synchronize()
     for layer in range(num_layers):
         assert np.array_equal(eng.kv_caches[layer].cpu().view(torch.int16).numpy(),

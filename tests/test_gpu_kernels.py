@@ -242,6 +242,42 @@ def test_evict_select_compact_bit_exact(method, topk, mode, tie):
     assert len(victims) > 3
 
 
+@pytest.mark.parametrize("method", ["value_l2", "streamingLLM"])
+def test_evict_select_compact_layers_matches_per_layer(method):
+    """One launch for every layer of a step (grid batch x layers) == one launch per layer."""
+    ops = _ops()
+    from vllm_paged_compression_b200._lib import PcEvictPolicy
+    bs, B, M, L = 16, 29, 50, 5
+    pol = Policy(block_size=bs, cache_prune_type="percentage", evict_freq=2, decode_evict_method=method,
+                 topk_blocks=-1)
+    rs = np.random.RandomState(77)
+    tables, n_blocks, seq_lens, scores, Hkv, pool = _evict_case(B, M, pol, rs, False)
+    cpol = PcEvictPolicy(1, bs, 128, 2, 1, 2, 0 if method == "streamingLLM" else 1, -1)
+    d = lambda a: torch.from_numpy(a).to(DEV)
+    dt, dn, ds = d(tables), d(n_blocks), d(seq_lens)
+    Ls = L if method == "value_l2" else 1
+    pools = [d((pool * (1.0 + 0.5 * np.sin(np.arange(pool.size).reshape(pool.shape) * (l + 1)))).astype(np.float32))
+             for l in range(Ls)]
+    ref_t, ref_v = [], []
+    for l in range(Ls):
+        out_t = torch.full((B, M), -7, dtype=torch.int32, device=DEV)
+        out_v = torch.zeros(B, dtype=torch.int32, device=DEV)
+        ops.evict_select_compact(dt, dn, ds, None, cpol, Hkv, out_t, None, out_v,
+                                 ops.make_score_pool(pools[l]) if method == "value_l2" else None)
+        ref_t.append(out_t)
+        ref_v.append(out_v)
+    got_t = torch.full((Ls, B, M), -9, dtype=torch.int32, device=DEV)
+    got_v = torch.zeros(Ls, B, dtype=torch.int32, device=DEV)
+    ptrs = torch.tensor([p_.data_ptr() for p_ in pools], dtype=torch.int64, device=DEV) if method == "value_l2" else None
+    ops.evict_select_compact_layers(dt, dn, ds, cpol, ptrs, Hkv if method == "value_l2" else 0, got_t, got_v)
+    torch.cuda.synchronize()
+    assert torch.equal(got_t, torch.stack(ref_t))
+    assert torch.equal(got_v, torch.stack(ref_v))
+    assert int((got_v >= 0).sum()) > 3
+    if method == "value_l2":
+        assert not torch.equal(got_v[0], got_v[1])      # the layers' pools differ, so do their victims
+
+
 def test_compaction_known_answer_from_survey():
     """SURVEY.md 8c KAT: [[10..14],[20..24],[30..34]], victim 1 in every row ->
     [[10,12,13,14],[20,22,23,24],[30,32,33,34]] (v1 semantics; HEAD rows>=1 are buggy)."""

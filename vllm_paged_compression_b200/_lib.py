@@ -60,11 +60,13 @@ PROTOTYPES = {
     "pc_evict_select_compact": (C.c_int, [_P, _I64, _P, _P, _P, _I32, C.POINTER(PcEvictPolicy), _SP,
                                           _I32, _P, _I64, _P, _P, _I32, _P]),
     "pc_paged_decode_workspace_bytes": (_SZ, [_I32, _I32, _I32, _I32, _I32, _I32]),
-    "pc_paged_decode_plan": (_I32, [_I32, _I32, _I32, _I32, _I32, _I32]),
+    "pc_paged_decode_plan": (C.c_int, [_I32, _I32, _I32, _I32, _I32, _I32, _I32, C.POINTER(C.c_int32)]),
     "pc_paged_decode_attn_score": (C.c_int, [_P, _P, _P, _P, _P, _I64, _P, _I32, _I32, _I32, _I32, _I32,
                                              _I32, _F, _I64, _I64, _I64, _P, _SP, _P, _SZ,
                                              _I32, _P]),
-    "pc_decode_layer": (C.c_int, [C.POINTER(PcDecodeStep), _P, _P, _P, _P, _P, _P, _SP, _P]),
+    "pc_decode_layer": (C.c_int, [C.POINTER(PcDecodeStep), _P, _P, _P, _P, _P, _P, _SP, _P, _P, _I64]),
+    "pc_evict_select_compact_layers": (C.c_int, [_P, _I64, _P, _P, _I32, _I32, C.POINTER(PcEvictPolicy), _P, _I32,
+                                                 _P, _I64, _I64, _P, _P]),
     "pc_prefill_attn_topleft_causal": (C.c_int, [_P, _P, _P, _P, _P, _I32, _I32, _I64, _I32, _I32, _I32, _F,
                                                  _I64, _I64, _I64, _I64, _P, _I32, _P]),
     "pc_copy_blocks": (C.c_int, [_P, _P, _P, _I32, _I64, _P]),

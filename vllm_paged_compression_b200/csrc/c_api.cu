@@ -162,14 +162,25 @@ size_t pc_paged_decode_workspace_bytes(int32_t batch, int32_t num_heads, int32_t
                                        int32_t max_kv_len) {
   const int sms = device_sm_count();
   if (sms <= 0 || batch <= 0 || num_kv_heads <= 0 || num_heads % num_kv_heads) return 0;
+  if ((head_size != 64 && head_size != 128) || (block_size != 16 && block_size != 32)) return 0;
   return decode_workspace_bytes(batch, num_heads, num_kv_heads, head_size, block_size, max_kv_len, sms);
 }
 
-int32_t pc_paged_decode_plan(int32_t batch, int32_t num_heads, int32_t num_kv_heads,
-                             int32_t head_size, int32_t block_size, int32_t max_kv_len) {
-  const int sms = device_sm_count();
-  if (sms <= 0 || batch <= 0 || num_kv_heads <= 0 || num_heads % num_kv_heads) return 0;
-  return decode_plan_chunk_pages(batch, num_heads, num_kv_heads, head_size, block_size, max_kv_len, sms);
+int pc_paged_decode_plan(int32_t batch, int32_t num_heads, int32_t num_kv_heads, int32_t head_size,
+                         int32_t block_size, int32_t max_kv_len, int32_t num_sms, int32_t* out_plan) {
+  if (!out_plan) return set_error(PC_ERR_INVALID, "pc_paged_decode_plan: null out_plan");
+  out_plan[0] = out_plan[1] = 0;
+  const int sms = num_sms > 0 ? num_sms : device_sm_count();
+  if (sms <= 0) return PC_ERR_CUDA;
+  if (batch <= 0 || num_kv_heads <= 0 || num_heads % num_kv_heads)
+    return set_error(PC_ERR_INVALID, "pc_paged_decode_plan: bad shape");
+  if ((head_size != 64 && head_size != 128) || (block_size != 16 && block_size != 32))
+    return set_error(PC_ERR_UNSUPPORTED, "Unsupported head size / block size (supported: head 64|128, block 16|32)");
+  int pl[2];
+  decode_plan(batch, num_heads, num_kv_heads, head_size, block_size, max_kv_len, sms, pl);
+  out_plan[0] = pl[0];
+  out_plan[1] = pl[1];
+  return PC_OK;
 }
 
 int pc_paged_decode_attn_score(void* out, const void* query, const void* key_cache,
@@ -226,9 +237,29 @@ static int decode_attn_impl(void* out, const void* query, const void* key_cache,
 #pragma GCC visibility push(default)
 extern "C" {
 
+int pc_evict_select_compact_layers(const int32_t* block_tables, int64_t table_stride,
+                                   const int32_t* n_blocks, const int32_t* seq_lens, int32_t batch,
+                                   int32_t num_layers, const pc_evict_policy* policy,
+                                   const float* const* score_pools, int32_t heads_total,
+                                   int32_t* out_tables, int64_t out_stride, int64_t out_layer_stride,
+                                   int32_t* out_victims, void* stream) {
+  if (batch == 0 || num_layers == 0) return PC_OK;
+  if (!block_tables || !n_blocks || !seq_lens || !policy || !out_tables || !out_victims)
+    return set_error(PC_ERR_INVALID, "pc_evict_select_compact_layers: null pointer");
+  if (out_layer_stride < (int64_t)batch * out_stride)
+    return set_error(PC_ERR_INVALID, "pc_evict_select_compact_layers: out_layer_stride < batch * out_stride");
+  EvictLayersArgs a{};
+  a.block_tables = block_tables; a.table_stride = table_stride; a.n_blocks = n_blocks; a.seq_lens = seq_lens;
+  a.B = batch; a.L = num_layers; a.pol = *policy; a.pools = score_pools; a.heads_total = heads_total;
+  a.out_tables = out_tables; a.out_stride = out_stride; a.out_layer_stride = out_layer_stride;
+  a.out_victims = out_victims;
+  return evict_select_compact_layers(a, static_cast<cudaStream_t>(stream));
+}
+
 int pc_decode_layer(const pc_decode_step* st, void* out, const void* query, const void* key,
                     const void* value, void* key_cache, void* value_cache,
-                    const pc_score_pool* score, int32_t* out_victim) {
+                    const pc_score_pool* score, int32_t* out_victim, const int32_t* attend_tables,
+                    int64_t attend_stride) {
   if (!st) return set_error(PC_ERR_INVALID, "pc_decode_layer: null step");
   if (st->batch == 0) return PC_OK;
   // W1: this step's K/V rows into the pool -- inside the attention kernel when fused
@@ -240,7 +271,12 @@ int pc_decode_layer(const pc_decode_step* st, void* out, const void* query, cons
       return rc;
   const int32_t* tables = st->block_tables;
   int64_t stride = st->table_stride;
-  if (st->any_trigger) {
+  const bool preselected = attend_tables != nullptr;   // pc_evict_select_compact_layers ran for this step
+  if (preselected) {
+    if (!fuse) return set_error(PC_ERR_INVALID, "pc_decode_layer: attend_tables needs the fused cache write");
+    tables = attend_tables;
+    stride = attend_stride;
+  } else if (st->any_trigger) {
     // P3 + S4 + C1: victims from the scores of blocks filled on EARLIER steps, compacted tables
     if (!out_victim || !st->compact_tables || !st->n_blocks)
       return set_error(PC_ERR_INVALID, "pc_decode_layer: trigger step needs out_victim, compact_tables, n_blocks");
@@ -254,7 +290,7 @@ int pc_decode_layer(const pc_decode_step* st, void* out, const void* query, cons
   // A2 + S2: attention over the (compacted) tables, scoring the blocks that fill this step
   // PDL only when the preceding kernel is not this call's own evict_select / cache write
   FuseExtras g_fuse = {nullptr, nullptr, nullptr, 0, 0, st->plan,
-                       (st->pdl && fuse && !st->any_trigger) ? 1 : 0};
+                       (st->pdl && fuse && (preselected || !st->any_trigger)) ? 1 : 0};
   if (fuse) {
     if (!key || !value || !st->slot_mapping)
       return set_error(PC_ERR_INVALID, "pc_decode_layer: fused cache write needs key, value, slot_mapping");
@@ -320,6 +356,7 @@ int pc_swap_blocks(const void* src, void* dst, const int64_t* pairs, int32_t num
  * product library neither exports them nor reads any environment variable.
  * decode trace: per-warp globaltimer stamps, [warps][8]. */
 void pc_debug_set_decode_trace(void* device_buf) { pc::set_decode_trace(device_buf); }
+void pc_debug_set_decode_plan(int32_t chunk_pages, int32_t team) { pc::set_decode_plan_override(chunk_pages, team); }
 void pc_debug_set_prefill_tc_tile(int32_t tn) { pc::set_prefill_tc_tile(tn); }
 void pc_debug_set_prefill_tc_persistent(int32_t v) { pc::set_prefill_tc_persistent(v); }
 #endif

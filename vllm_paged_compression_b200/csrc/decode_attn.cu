@@ -11,9 +11,17 @@
 //     (cp.async.bulk -> UBLKCP) that complete on one mbarrier.
 //   * schedule: every (row, group) is cut into CHUNKS of `chunk_pages` consecutive pages
 //     (a fixed, deterministic partition); chunks are numbered in (b, h, hg, chunk) order.
-//     A WARP is a worker: its first chunk is static (id = warp x grid + cta, so
-//     neighbouring chunks land on different SMs), further chunks come from a global
-//     atomic counter.  The hand-out must be dynamic: per-SM HBM bandwidth differs by
+//     A TEAM of T = 1, 2, 4 or 8 warps of one CTA is a worker (T from the host planner):
+//     member j of the team streams pages begin + j, + T, ... of the chunk through its own
+//     page ring, and at the end of the chunk the members hand their (m, l, O) to member 0
+//     through SHARED memory (one mbarrier pair per member) -- no global partial, no fence,
+//     no ticket.  With T = 1 a single warp needs ~0.7 us per page whatever its neighbours
+//     do (dependent chain + a 3-deep ring), so a launch with fewer chunks than warps is
+//     latency-bound (the 64 x ~590-token bench shape: 512 chunks on 1184 warps); teams put
+//     every warp of an SM on the SM's chunks.  A team's first chunk is static (id = team x
+//     grid + cta, so neighbouring chunks land on different SMs); with T = 1 further chunks
+//     come from a global atomic counter, with T > 1 the planner keeps the launch to one
+//     wave (chunks <= teams).  The hand-out must be dynamic: per-SM HBM bandwidth differs by
 //     ~+-15 % across the chip (measured with the trace hook, profiles/), a static equal
 //     split loses that much at the tail.  Everything on the hand-out path is prefetched
 //     one chunk ahead -- the counter atomic, the chunk descriptor (binary search of a
@@ -41,6 +49,7 @@
 //     pool[physical block][head] of every rank's score pool (peer stores under TP).
 #include "pc_common.cuh"
 #include "score_common.cuh"
+#include <math.h>
 #include <stdlib.h>
 #include <atomic>
 #include <type_traits>
@@ -71,7 +80,9 @@ struct DecodeParams {
   long long kv_block_stride;  // elements between blocks in k/v cache
   float scale_log2;
   int chunk_pages;            // pages per chunk (the last chunk of a group may be shorter)
-  const int* __restrict__ plan;  // device-side {chunk_pages} overriding the field above (CUDA-graph replay), or nullptr
+  int team;                   // warps per team (1, 2, 4, 8; <= team_cap)
+  int team_cap;               // largest team the launch has shared memory for
+  const int* __restrict__ plan;  // device-side {chunk_pages, team} overriding the two fields above (CUDA-graph replay), or nullptr
   // fused reshape_and_cache of this step's token (nullptr = the caller wrote the cache):
   // the warp that owns a row's LAST page patches the new token's K/V into the page it has
   // in shared memory and stores it to the pool at slot_mapping[b]
@@ -110,9 +121,14 @@ struct DecodeTraits {
   static constexpr int kRingBytes = kWarps * kStages * kStageBytes;
   static constexpr int kBarBytes = kWarps * kStages * 8;
   static constexpr int kFifoBytes = kWarps * kFifo * (int)sizeof(ChunkDesc);
+  static constexpr int kTeamBarBytes = 2 * kWarps * 8;          // pfull[kWarps], pfree[kWarps]
+  // a member's hand-over buffer: its O^T fragments [D/4 regs][32 lanes] fp32 + (m, l) of the 8 heads
+  static constexpr int kPartBytes = 32 * (D / 4) * 4 + 64;
   static constexpr int kThreads = kWarps * 32;
-  static size_t smem_bytes(int B) {
-    return (size_t)kRingBytes + kBarBytes + kFifoBytes + ((size_t)B + 1) * 4 + 64;  // + wsum[kWarps]
+  static constexpr int followers(int team) { return team > 1 ? kWarps - kWarps / team : 0; }
+  static size_t smem_bytes(int B, int team_cap) {
+    return (size_t)kRingBytes + kBarBytes + kFifoBytes + kTeamBarBytes + (size_t)followers(team_cap) * kPartBytes +
+           ((size_t)B + 1) * 4 + 64;  // + wsum[kWarps] + flags
   }
 };
 
@@ -148,8 +164,8 @@ __device__ __forceinline__ void write_new_token(__nv_bfloat16* k_cache_w, __nv_b
   __syncwarp();
 }
 
-template <int D, int BS, int kWarps, int kStages, bool kPair, int kCtasPerSm = 1>
-__global__ void __launch_bounds__(kWarps * 32, kCtasPerSm)
+template <int D, int BS, int kWarps, int kStages>
+__global__ void __launch_bounds__(kWarps * 32, 1)
 paged_decode_attn_score_kernel(const DecodeParams p) {
   using T = DecodeTraits<D, BS, kWarps, kStages>;
   static_assert(kStages < kFifo, "descriptor fifo must outrun the page ring");
@@ -164,12 +180,22 @@ paged_decode_attn_score_kernel(const DecodeParams p) {
   const int g = lane >> 2;  // fragment row group
   const int t = lane & 3;   // fragment column pair
   const int n_launched = gridDim.x * kWarps;
-  const int w = warp * gridDim.x + blockIdx.x;  // interleaved over SMs
 
   const unsigned long long t_start = p.trace ? gtimer() : 0ull;
   const int chunk_pages = (p.plan != nullptr) ? max(1, __ldg(p.plan)) : p.chunk_pages;
+  // team geometry: TS warps per team (power of two), member tw of team `team_in_cta`
+  int TS = (p.plan != nullptr) ? __ldg(p.plan + 1) : p.team;
+  TS = (TS >= 8 && kWarps >= 8 && p.team_cap >= 8) ? 8 : (TS >= 4 && kWarps >= 4 && p.team_cap >= 4) ? 4
+       : (TS >= 2 && p.team_cap >= 2) ? 2 : 1;
+  const int tw = warp & (TS - 1);
+  const int team_in_cta = warp / TS;
+  const int n_teams = gridDim.x * (kWarps / TS);
+  const int w = team_in_cta * gridDim.x + blockIdx.x;  // team id, interleaved over SMs
   ChunkDesc* my_fifo = reinterpret_cast<ChunkDesc*>(smem + T::kRingBytes + T::kBarBytes) + warp * kFifo;
-  int* cpre = reinterpret_cast<int*>(smem + T::kRingBytes + T::kBarBytes + T::kFifoBytes);  // [B + 1]
+  uint64_t* pfull = reinterpret_cast<uint64_t*>(smem + T::kRingBytes + T::kBarBytes + T::kFifoBytes);  // [kWarps]
+  uint64_t* pfree = pfull + kWarps;                                                                       // [kWarps]
+  uint8_t* part_base = smem + T::kRingBytes + T::kBarBytes + T::kFifoBytes + T::kTeamBarBytes;
+  int* cpre = reinterpret_cast<int*>(part_base + (size_t)T::followers(p.team_cap) * T::kPartBytes);  // [B + 1]
 
   // chunk ids of this warp: the first one is static (= w), the rest come from a global
   // counter, fetched only when the issue side runs out of pages (kStages pages before the
@@ -178,6 +204,8 @@ paged_decode_attn_score_kernel(const DecodeParams p) {
     uint64_t* bars0 = reinterpret_cast<uint64_t*>(smem + T::kRingBytes) + warp * kStages;
 #pragma unroll
     for (int s = 0; s < kStages; ++s) mbar_init(&bars0[s], 1);
+    mbar_init(&pfull[warp], 1);
+    mbar_init(&pfree[warp], 1);
   }
   // ---- schedule: chunks per (row, group) -> exclusive prefix sum (same in every CTA)
   // Programmatic dependent launch: let the next kernel of the stream start as SMs free
@@ -189,14 +217,17 @@ paged_decode_attn_score_kernel(const DecodeParams p) {
   {
     // block-wide scan, kThreads rows per pass (a one-warp scan cost 1.2 us of prologue at
     // B = 512, the per-rank batch of the TP = 8 bench)
-    int* wsum = cpre + p.B + 1;   // [kWarps]
+    int* wsum = cpre + p.B + 1;   // [kWarps], then [kWarps] = "some row is empty"
+    if (threadIdx.x == 0) wsum[kWarps] = 0;
     int carry = 0;
+    bool saw_empty = false;
     for (int base = 0; base < p.B; base += T::kThreads) {
       const int r = base + threadIdx.x;
       int n = 0;
       if (r < p.B) {
         const int len = p.kv_lens[r];
         n = ((len + BS - 1) / BS + chunk_pages - 1) / chunk_pages;
+        saw_empty |= (len == 0);
       }
 #pragma unroll
       for (int sh = 1; sh < 32; sh <<= 1) {
@@ -217,9 +248,11 @@ paged_decode_attn_score_kernel(const DecodeParams p) {
       __syncthreads();
     }
     if (threadIdx.x == 0) cpre[0] = 0;
+    if (saw_empty) wsum[kWarps] = 1;   // after the loop's last barrier, before the one below
   }
   mbar_fence_init();
   __syncthreads();
+  const bool any_empty_row = (cpre + p.B + 1)[kWarps] != 0;
 
   const int C = cpre[p.B] * p.GH;  // chunks in this launch
   // the host sizes the workspace for the worst plan up to max_kv_len (decode_workspace_bytes);
@@ -237,8 +270,12 @@ paged_decode_attn_score_kernel(const DecodeParams p) {
   int fifo_tail = 0;   // descriptors retired (consume side)
   int next_id = w;     // id the next open_chunk() will decode
   bool first_open = true;
+  int static_next = w;  // teams: ids w, w + n_teams, ... (every member derives the same sequence)
   auto open_chunk = [&]() -> bool {  // all lanes, uniform
-    if (!first_open) {
+    if (TS > 1) {
+      next_id = static_next;
+      static_next += n_teams;
+    } else if (!first_open) {
       int nid = 0;
       if (lane == 0) nid = atomicAdd(&p.counters[0], 1);
       next_id = __shfl_sync(kFull, nid, 0) + n_launched;
@@ -246,7 +283,7 @@ paged_decode_attn_score_kernel(const DecodeParams p) {
     first_open = false;
     if (next_id >= C) return false;
     const int id = next_id;
-    next_id = C;  // the following id is fetched on demand (fetch_next)
+    next_id = C;  // the following id is fetched on demand
     const int key = id / p.GH;
     int lo = 0, hi = p.B;  // largest b with cpre[b] <= key (cpre[B] > key)
     while (hi - lo > 1) {
@@ -270,33 +307,40 @@ paged_decode_attn_score_kernel(const DecodeParams p) {
     return true;
   };
 
-  // ---- issue side: walks pages of successive chunks, kStages ahead of the consumer
-  int is_b = 0, is_h = 0, is_blk = 0, is_end = 0;  // current issue chunk (is_blk == is_end: exhausted)
+  // ---- issue side: walks this member's pages of successive chunks, up to kStages ahead of the
+  // consumer.  Invariant: when is_open, the cursor (is_b, is_h, is_blk) names a page of this
+  // member that is not issued yet and phys_next holds its table entry (loaded one page ahead).
+  int is_b = 0, is_h = 0, is_blk = 0, is_end = 0;
   bool is_open = false;
-  int phys_next = 0;   // table entry of the next page to issue, loaded one page ahead
-  int pages_issued = 0;
+  int phys_next = 0;
+  int in_flight = 0;                  // pages issued and not yet consumed
   int issue_slot = 0;                 // ring slot the next page goes to
   int cons_slot = 0;                  // ring slot of the next page to consume
   uint32_t cons_parity = 0;           // mbarrier phase parity of that slot
 
-  // before the dependency wait (PDL) only the static first chunk may be opened: the
-  // chunk counter still belongs to the preceding launch
+  // before the dependency wait (PDL) only static chunk ids may be opened: the chunk counter
+  // still belongs to the preceding launch.  is_pending: the cursor stopped short of a chunk it
+  // may open later (dependency wait not passed, or the descriptor fifo is full).
   bool allow_open = !p.pdl;
   bool is_pending = false;
-  auto issue_advance = [&]() {  // make (is_b, is_h, is_blk) point at the next page, if any
+  auto issue_advance = [&]() {
     if (is_open && is_blk < is_end) {
       phys_next = __ldg(p.block_tables + (size_t)is_b * p.table_stride + is_blk);
       return;
     }
-    if (!allow_open && !first_open) {
-      is_open = false;
-      is_pending = true;
-      return;
+#pragma unroll 1
+    while (true) {
+      if ((TS == 1 && !allow_open && !first_open) || fifo_head - fifo_tail >= kFifo - 1) {
+        is_open = false;
+        is_pending = true;
+        return;
+      }
+      is_open = open_chunk();
+      if (!is_open) return;
+      const ChunkDesc& d = my_fifo[(fifo_head - 1) % kFifo];
+      is_b = d.b; is_h = d.gh / p.HG; is_blk = d.blk_begin + tw; is_end = d.blk_end;
+      if (is_blk < is_end) break;   // (a member beyond the chunk's page count sits this chunk out)
     }
-    is_open = open_chunk();
-    if (!is_open) return;
-    const ChunkDesc& d = my_fifo[(fifo_head - 1) % kFifo];
-    is_b = d.b; is_h = d.gh / p.HG; is_blk = d.blk_begin; is_end = d.blk_end;
     phys_next = __ldg(p.block_tables + (size_t)is_b * p.table_stride + is_blk);
   };
   auto issue_page = [&]() {  // issue the page under the cursor into the next ring slot
@@ -309,8 +353,8 @@ paged_decode_attn_score_kernel(const DecodeParams p) {
       tma_load_1d(dst, p.k_cache + off, T::kPageBytes, &my_bars[slot]);
       tma_load_1d(dst + T::kPageBytes, p.v_cache + off, T::kPageBytes, &my_bars[slot]);
     }
-    ++pages_issued;
-    ++is_blk;
+    ++in_flight;
+    is_blk += TS;
   };
 
   // Q^T as the mma B operand: b0 = Q[head g][16j + 2t..], b1 = Q[head g][16j + 8 + 2t..]
@@ -326,59 +370,76 @@ paged_decode_attn_score_kernel(const DecodeParams p) {
       qf[j][1] = valid ? __ldg(reinterpret_cast<const unsigned int*>(qrow + 16 * j + 8 + 2 * t)) : 0u;
     }
   };
-
-  // prologue: fill the ring.  One copy of the fill loop serves both sides of the PDL
-  // dependency wait (the issue path is large; keeping it to two instances -- here and the
-  // refill in the page loop -- keeps the kernel inside the instruction cache).
-  {
-    bool need_adv = true;  // the cursor does not point at a page yet
+  uint32_t qf[KSTEPS][2];   // Q of the chunk being consumed
+  uint32_t qn[KSTEPS][2];   // Q prefetched for chunk `qn_id`
+  int qn_id = -1;
+  // top up the ring; prefetches Q of a chunk opened on the way.  One instance of this loop serves
+  // the prologue (both sides of the PDL dependency wait), the refill after every page and the
+  // retry of a pending cursor (the issue path is large; few instances keep the kernel inside the
+  // instruction cache).
+  auto fill = [&](bool want_q) {
+    if (is_pending) {
+      is_pending = false;
+      issue_advance();
+    }
 #pragma unroll 1
-    for (int pass = 0; pass < 2; ++pass) {
-      if (pass == 1) {
-        // ---- from here on the kernel reads what the preceding kernel may have produced
-        // (Q, the step's K/V rows) and writes (out, partials, tickets, counters, scores, pool)
-        if (p.pdl) asm volatile("griddepcontrol.wait;" ::: "memory");
-        allow_open = true;
-        if (!is_pending) break;
-        is_pending = false;
-        need_adv = !is_open;
-      }
-#pragma unroll 1
-      while (true) {
-        if (need_adv) { issue_advance(); need_adv = false; }
-        if (pages_issued >= depth || !is_open) break;
-        issue_page();
-        need_adv = true;
+    while (in_flight < depth && is_open) {
+      const int opened = fifo_head;
+      issue_page();
+      issue_advance();
+      if (want_q && fifo_head != opened) {  // a new chunk was opened: prefetch its Q
+        const ChunkDesc& nd = my_fifo[(fifo_head - 1) % kFifo];
+        load_q(qn, nd.b, nd.gh);
+        qn_id = nd.id;
       }
     }
+  };
+
+  // prologue: fill the ring
+  issue_advance();
+  fill(false);
+  // ---- from here on the kernel reads what the preceding kernel may have produced (Q, the
+  // step's K/V rows) and writes (out, partials, tickets, counters, scores, pool)
+  if (p.pdl) {
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    allow_open = true;
+    fill(false);
   }
-  if (blockIdx.x == 0) {  // empty sequences: defined output (zeros)
+  if (any_empty_row && blockIdx.x == 0) {  // empty sequences: defined output (zeros)
     for (int r = warp; r < p.B; r += kWarps) {
       if (p.kv_lens[r] != 0) continue;
       __nv_bfloat16* o = p.out + (size_t)r * p.out_stride;
       for (int i = lane; i < p.Hq * D; i += 32) o[i] = __float2bfloat16(0.f);
     }
   }
-  uint32_t qf[KSTEPS][2];   // Q of the chunk being consumed
-  uint32_t qn[KSTEPS][2];   // Q prefetched for chunk `qn_id`
-  int qn_id = -1;
   if (fifo_head > 0) {
     load_q(qn, my_fifo[0].b, my_fifo[0].gh);
     qn_id = my_fifo[0].id;
   }
-  if (p.trace && lane == 0) p.trace[w * 8 + 0] = t_start, p.trace[w * 8 + 1] = gtimer();
+  if (p.trace && lane == 0) p.trace[(warp * gridDim.x + blockIdx.x) * 8 + 0] = t_start,
+                            p.trace[(warp * gridDim.x + blockIdx.x) * 8 + 1] = gtimer();
 
   float o[MT][4];
   float m_run[2], l_run[2];
   int tr_chunks = 0, tr_combines = 0;
   unsigned long long tr_fix = 0ull;
+  int pf_sent = 0;            // follower: hand-overs written so far (mbarrier phase of pfree / pfull)
+  uint32_t pf_parity = 0u;    // leader: bit f = parity of the next hand-over expected from member f
 
   // ================================================================ chunk loop
-  while (fifo_tail < fifo_head) {
+  while (true) {
+    if (fifo_tail == fifo_head) {
+      if (!is_pending) break;
+      fill(true);   // a cursor parked on a full descriptor fifo
+      if (fifo_tail == fifo_head) break;
+    }
     const ChunkDesc d = my_fifo[fifo_tail % kFifo];
     ++fifo_tail;
-    ++tr_chunks;
     const int b = d.b, nblk = d.nblk, kv_len = d.kv_len;
+    // members of the team that have pages in this chunk; the others sit it out
+    const int n_active = min(TS, d.blk_end - d.blk_begin);
+    if (tw >= n_active) continue;
+    ++tr_chunks;
     const int h = d.gh / p.HG, hg = d.gh - h * p.HG;
     if (qn_id == d.id) {
 #pragma unroll
@@ -386,8 +447,10 @@ paged_decode_attn_score_kernel(const DecodeParams p) {
     } else {
       load_q(qf, b, d.gh);
     }
-    if (p.new_k != nullptr && d.blk_end == nblk) {
-      // the chunk ends with the row's last page: pull the step's K/V row towards L1 now, so
+    // the row's last page belongs to this member iff it is one of its pages of this chunk
+    const bool has_tail = (d.blk_end == nblk) && (((nblk - 1 - d.blk_begin) & (TS - 1)) == tw);
+    if (p.new_k != nullptr && has_tail) {
+      // this member ends with the row's last page: pull the step's K/V row towards L1 now, so
       // the loads in the tail page (no registers to spare until then) hit
       const __nv_bfloat16* ka = p.new_k + (size_t)b * p.new_k_stride + (size_t)h * D + (lane & (D / 8 - 1)) * 8;
       const __nv_bfloat16* va = p.new_v + (size_t)b * p.new_v_stride + (size_t)h * D + lane * (D / 32);
@@ -566,30 +629,17 @@ paged_decode_attn_score_kernel(const DecodeParams p) {
 
       // ---------------- refill the consumed slots (the issue side may open the next chunk here)
       __syncwarp();
-#pragma unroll 1
-      for (int pg = 0; pg < NP; ++pg) {
-        if (!is_open) break;
-        const int opened = fifo_head;
-        issue_page();
-        issue_advance();
-        if (fifo_head != opened) {  // a new chunk was opened: prefetch its Q
-          const ChunkDesc& nd = my_fifo[(fifo_head - 1) % kFifo];
-          load_q(qn, nd.b, nd.gh);
-          qn_id = nd.id;
-        }
-      }
+      in_flight -= NP;
+      fill(true);
     };
     {
-      const bool has_tail = (d.blk_end == nblk);  // this chunk holds the row's last page
       const int body_end = d.blk_end - (has_tail ? 1 : 0);
-      int blk = d.blk_begin;
-      if constexpr (kPair) {
-        for (; blk + 1 < body_end; blk += 2) page(blk, std::false_type{}, std::integral_constant<int, 2>{});
-      }
-      for (; blk < body_end; ++blk) page(blk, std::false_type{}, std::integral_constant<int, 1>{});
+#pragma unroll 1
+      for (int blk = d.blk_begin + tw; blk < body_end; blk += TS) page(blk, std::false_type{}, std::integral_constant<int, 1>{});
       if (has_tail) page(nblk - 1, std::true_type{}, std::integral_constant<int, 1>{});
     }
-    if (p.trace && lane == 0) p.trace[w * 8 + 2] = gtimer();
+    const int tix = (warp * gridDim.x + blockIdx.x) * 8;   // trace row of this warp
+    if (p.trace && lane == 0) p.trace[tix + 2] = gtimer();
 
     // ---------------- chunk end
     const int head0 = h * p.G + hg * 8;       // first q head of this group
@@ -599,6 +649,52 @@ paged_decode_attn_score_kernel(const DecodeParams p) {
     for (int sh = 4; sh <= 16; sh <<= 1) {
       l_run[0] += __shfl_xor_sync(kFull, l_run[0], sh);
       l_run[1] += __shfl_xor_sync(kFull, l_run[1], sh);
+    }
+    // ---- team hand-over through shared memory: members 1 .. n_active-1 pass (m, l, O) in the
+    // mma fragment layout ([register][lane]: conflict-free, no cross-lane traffic) to member 0
+    if (n_active > 1) {
+      constexpr int NR = MT * 4;   // O registers per lane
+      if (tw > 0) {
+        const int fidx = warp - team_in_cta - 1;   // followers before this one in the CTA
+        float* pb = reinterpret_cast<float*>(part_base + (size_t)fidx * T::kPartBytes);
+        if (pf_sent > 0) mbar_wait(&pfree[warp], (uint32_t)(pf_sent - 1) & 1u);  // previous hand-over consumed
+#pragma unroll
+        for (int m = 0; m < MT; ++m)
+#pragma unroll
+          for (int i = 0; i < 4; ++i) pb[(m * 4 + i) * 32 + lane] = o[m][i];
+        if (g == 0) {
+          float* ml = pb + NR * 32 + t * 4;
+          ml[0] = m_run[0]; ml[1] = l_run[0]; ml[2] = m_run[1]; ml[3] = l_run[1];
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&pfull[warp]);
+        ++pf_sent;
+        continue;
+      }
+#pragma unroll 1
+      for (int f = 1; f < n_active; ++f) {
+        const int fw = warp + f;
+        const float* pb = reinterpret_cast<const float*>(part_base + (size_t)(fw - team_in_cta - 1) * T::kPartBytes);
+        mbar_wait(&pfull[fw], (pf_parity >> f) & 1u);
+        pf_parity ^= 1u << f;
+        const float* ml = pb + NR * 32 + t * 4;
+        const float mf0 = ml[0], lf0 = ml[1], mf1 = ml[2], lf1 = ml[3];
+        const float M0 = fmaxf(m_run[0], mf0), M1 = fmaxf(m_run[1], mf1);
+        const float a0 = fast_exp2(m_run[0] - M0), b0 = fast_exp2(mf0 - M0);
+        const float a1 = fast_exp2(m_run[1] - M1), b1 = fast_exp2(mf1 - M1);
+        m_run[0] = M0; m_run[1] = M1;
+        l_run[0] = l_run[0] * a0 + lf0 * b0;
+        l_run[1] = l_run[1] * a1 + lf1 * b1;
+#pragma unroll
+        for (int m = 0; m < MT; ++m) {
+          o[m][0] = o[m][0] * a0 + pb[(m * 4 + 0) * 32 + lane] * b0;
+          o[m][1] = o[m][1] * a1 + pb[(m * 4 + 1) * 32 + lane] * b1;
+          o[m][2] = o[m][2] * a0 + pb[(m * 4 + 2) * 32 + lane] * b0;
+          o[m][3] = o[m][3] * a1 + pb[(m * 4 + 3) * 32 + lane] * b1;
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&pfree[fw]);
+      }
     }
     const int n_chunks = (nblk + chunk_pages - 1) / chunk_pages;  // chunks of this group
     // o[m][0]=(dim 16m+g, head 2t) [1]=(dim 16m+g, head 2t+1) [2]=(dim 16m+g+8, 2t) [3]=(.., 2t+1)
@@ -714,13 +810,14 @@ paged_decode_attn_score_kernel(const DecodeParams p) {
       p.counters[1] = 0;
     }
     if (p.trace) {
-      p.trace[w * 8 + 3] = gtimer();
-      p.trace[w * 8 + 4] = tr_chunks;
-      p.trace[w * 8 + 5] = tr_combines;
+      const int tix = (warp * gridDim.x + blockIdx.x) * 8;
+      p.trace[tix + 3] = gtimer();
+      p.trace[tix + 4] = tr_chunks;
+      p.trace[tix + 5] = tr_combines;
       unsigned int smid;
       asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
-      p.trace[w * 8 + 6] = smid;
-      p.trace[w * 8 + 7] = tr_fix;
+      p.trace[tix + 6] = smid;
+      p.trace[tix + 7] = tr_fix;
     }
   }
 }
@@ -737,54 +834,131 @@ static size_t slot_bytes(int D) { return (size_t)(8 * D + 16) * sizeof(float); }
 #ifdef PC_DEBUG
 static unsigned long long* g_decode_trace = nullptr;
 void set_decode_trace(void* buf) { g_decode_trace = static_cast<unsigned long long*>(buf); }
-static int env_int(const char* name, int dflt) {
-  const char* v = getenv(name);
-  return (v && *v) ? atoi(v) : dflt;
+static int g_force_chunk_pages = 0, g_force_team = 0;   // planner overrides (calibration sweeps)
+static int g_plan_epoch = 0;
+void set_decode_plan_override(int chunk_pages, int team) {
+  g_force_chunk_pages = chunk_pages;
+  g_force_team = team;
+  ++g_plan_epoch;   // invalidates the worst-case memo
 }
+#else
+constexpr int g_plan_epoch = 0;
 #endif
 
 struct DecodePlan {
   int chunk_pages;
+  int team;
   long long max_chunks;
 };
 
-// Chunks per group.  Measured on B200 (profiles/r01_decode_policy_sweep.txt, trace hook):
-//  * every chunk of a SPLIT group costs an fp32 partial (8 heads x D, written and re-read),
-//    a release fence + ticket (2-5 us of warp time under load) and its share of a
-//    combine, and the fix-up of a warp's last chunk is exposed at the end of the launch
-//    (~10 us): a group is split only when that buys something;
-//  * small launches (few groups) need chunks ~ half the warps of the chip to pull
-//    enough bytes in flight;
-//  * big launches need a dynamic tail: per-SM HBM bandwidth differs by ~+-15 %, so with
-//    >= 64 pages per warp the groups are cut into >= 64-page chunks, ~4 per warp.
-static DecodePlan plan_decode(int B, int Hq, int Hkv, int D, int BS, int max_kv_len, int num_sms, int warps) {
+// kernel configuration per (D, BS): the ring (warps x stages x (K + V page)) must fit 227 KB
+struct DecodeCfg { int warps, stages; };
+static DecodeCfg decode_cfg(int D, int BS) {
+  if (D == 128 && BS == 32) return {4, 3};
+  if (D == 64 && BS == 16) return {8, 6};
+  return {8, 3};   // (128, 16), (64, 32)
+}
+// dynamic shared memory of a launch (mirrors DecodeTraits::smem_bytes)
+static size_t decode_smem_bytes(int D, int BS, int B, int team_cap) {
+  const DecodeCfg c = decode_cfg(D, BS);
+  const size_t ring = (size_t)c.warps * c.stages * 2 * BS * D * 2;
+  const size_t followers = team_cap > 1 ? c.warps - c.warps / team_cap : 0;
+  return ring + (size_t)c.warps * c.stages * 8 + (size_t)c.warps * kFifo * sizeof(ChunkDesc) + 2 * c.warps * 8 +
+         followers * (32 * (D / 4) * 4 + 64) + ((size_t)B + 1) * 4 + 64;
+}
+constexpr size_t kSmemLimit = 227 * 1024;
+// largest team whose hand-over buffers still fit next to the ring and the O(B) schedule
+static int decode_team_cap(int D, int BS, int B) {
+  const DecodeCfg c = decode_cfg(D, BS);
+  for (int t = c.warps; t > 1; t >>= 1)
+    if (decode_smem_bytes(D, BS, B, t) <= kSmemLimit) return t;
+  return 1;
+}
+
+// The launch plan: chunks per group (n, as chunk_pages) and warps per team (T), picked by a
+// small cost model calibrated on B200 (profiles/r02_decode_team_sweep.txt: every (T, n) of a
+// grid timed for ten launch shapes; profiles/r01_decode_policy_sweep.txt for the split costs):
+//  * one warp streams a page (8 KiB at D 128 / block 16) in ~0.6 us whatever its neighbours do
+//    (dependent chain + a 3-deep ring): a launch with fewer chunks than warps is latency-bound
+//    unless the idle warps join the busy ones' chunks (teams, ~0.5 us per hand-over);
+//  * an SM pulls at most ~77 GB/s, so HBM is saturated only while most SMs stream: chunks
+//    are spread over SMs first, and an uneven chunks-per-SM count is paid in full;
+//  * every chunk of a SPLIT group (n > 1) costs an fp32 partial (8 heads x D, written and
+//    re-read), a release fence + ticket (2-5 us of warp time under load), and the last arriver
+//    combines n partials: ~4 + 0.6 n us.  Large launches are NOT split for balance any more:
+//    64 x 8192 tokens runs 334 us whole against 370 us in 64-page chunks.
+// T > 1 launches are kept to one wave (chunks <= teams: the teams' chunk ids are static);
+// T = 1 launches may run several waves off the global chunk counter.
+struct PlanModel {
+  double hbm_bytes_per_us = 6.4e6;    // whole chip
+  double sm_bytes_per_us = 7.7e4;     // one SM
+  double page_us_base = 0.25, page_us_per_8k = 0.35;   // one page through one warp
+  double split_us = 4.0, split_us_per_chunk = 0.6;     // global split-KV combine
+  double team_us = 0.5;
+};
+
+static double plan_cost(const PlanModel& m, long long groups, long long max_blocks, long long cp, int T, int sms,
+                        int warps, int page_bytes) {
+  const long long n = (max_blocks + cp - 1) / cp;
+  const long long C = groups * n;
+  const long long workers = (long long)sms * warps;
+  const double page_us = m.page_us_base + m.page_us_per_8k * page_bytes / 8192.0;
+  const long long waves = T == 1 ? (C + workers - 1) / workers : 1;
+  // (a split chunk also stalls its warp ~3 us in the release fence + ticket)
+  const double t_warp = (double)waves * ((double)((cp + T - 1) / T) * page_us + (n > 1 ? 3.0 : 0.0));
+  const double t_sm = (double)((C + sms - 1) / sms) * cp * page_bytes / m.sm_bytes_per_us;
+  const long long busy = C < sms ? C : sms;
+  double hbm = m.hbm_bytes_per_us * sms / 148.0;
+  if (busy * m.sm_bytes_per_us < hbm) hbm = busy * m.sm_bytes_per_us;
+  const double t_hbm = (double)groups * max_blocks * page_bytes / hbm;
+  // the per-warp chain and the bandwidth bound overlap imperfectly while a launch ramps up
+  // and drains: a quarter of the smaller one is exposed, saturating at ~7.5 us
+  const double t_bw = t_sm > t_hbm ? t_sm : t_hbm;
+  const double lo = t_warp < t_bw ? t_warp : t_bw;
+  double t = (t_warp > t_bw ? t_warp : t_bw) + 0.25 * lo * 30.0 / (30.0 + lo);
+  if (n > 1) t += m.split_us + m.split_us_per_chunk * n;
+  if (T > 1) t += m.team_us;
+  return t;
+}
+
+static DecodePlan plan_decode(int B, int Hq, int Hkv, int D, int BS, int max_kv_len, int num_sms, int team_cap) {
   DecodePlan pl;
+  const int warps = decode_cfg(D, BS).warps;
   const int G = Hq / Hkv;
   const int HG = (G + 7) / 8;
   const long long groups = (long long)B * Hkv * HG;
   const long long max_blocks = max_kv_len > 0 ? (max_kv_len + BS - 1) / BS : 1;
-  const long long pages_max = groups * max_blocks;
   const long long workers = (long long)num_sms * warps;
-  // (a) parallelism: about workers/2 chunks, never shorter than 8 pages
-  long long n = (workers / 2 + groups / 2) / groups;
-  if (n > max_blocks / 8) n = max_blocks / 8;
-  if (n < 1) n = 1;
-  // (b) balance for big launches
-  if (pages_max / workers >= 64) {
-    long long nb = (4 * workers + groups - 1) / groups;
-    if (nb > max_blocks / 64) nb = max_blocks / 64;
-    if (nb > n) n = nb;
+  const PlanModel m;
+  const int page_bytes = 2 * BS * D * 2;
+  long long cp = max_blocks;
+  int team = 1;
+  double best = plan_cost(m, groups, max_blocks, cp, 1, num_sms, warps, page_bytes);
+  for (int T = 1; T <= team_cap && T <= warps; T <<= 1) {
+    const long long teams = workers / T;
+    long long last_c = -1;
+    for (long long nn = 1; nn <= max_blocks; nn = nn < 16 ? nn + 1 : nn + nn / 8) {
+      const long long c = (max_blocks + nn - 1) / nn;
+      if (c == last_c) continue;
+      last_c = c;
+      if (nn > 1 && c < 4) break;                                          // never shorter than 4 pages
+      if (nn > 1 && c < 2LL * T) break;                                    // >= 2 pages per member when splitting
+      const long long C = groups * ((max_blocks + c - 1) / c);
+      if (T > 1 && C > teams) break;                                       // one wave only
+      if (T == 1 && C > 8 * workers && nn > 1) break;
+      const double t = plan_cost(m, groups, max_blocks, c, T, num_sms, warps, page_bytes);
+      if (t < best - 1e-9) { best = t; cp = c; team = T; }
+    }
   }
-  long long cp = (max_blocks + n - 1) / n;
 #ifdef PC_DEBUG
-  static const int force = env_int("PC_DECODE_CHUNK_PAGES", 0);
-  if (force > 0) cp = force;
+  if (g_force_chunk_pages > 0) cp = g_force_chunk_pages;
+  if (g_force_team > 0) team = g_force_team < team_cap ? g_force_team : team_cap;
 #endif
   if (cp > max_blocks) cp = max_blocks;
   if (cp < 1) cp = 1;
   pl.chunk_pages = (int)cp;
+  pl.team = team;
   pl.max_chunks = groups * ((max_blocks + cp - 1) / cp);
-  (void)D;
   return pl;
 }
 
@@ -793,43 +967,43 @@ static DecodePlan plan_decode(int B, int Hq, int Hkv, int D, int BS, int max_kv_
 // length (90 blocks -> 9-page chunks -> 10 per group; 88 blocks -> 8-page chunks -> 11), and
 // under CUDA-graph replay the plan is read from device memory each step, so sizing by the
 // plan of max_kv_len alone is not enough.
-static long long worst_case_chunks(int B, int Hq, int Hkv, int D, int BS, int max_kv_len, int num_sms, int warps) {
-  struct Key { int B, Hq, Hkv, D, BS, max_kv_len, num_sms, warps; long long chunks; };
-  static thread_local Key memo = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+static long long worst_case_chunks(int B, int Hq, int Hkv, int D, int BS, int max_kv_len, int num_sms) {
+  struct Key { int B, Hq, Hkv, D, BS, max_kv_len, num_sms, epoch; long long chunks; };
+  static thread_local Key memo = {0, 0, 0, 0, 0, 0, 0, -1, 0};
   if (memo.B == B && memo.Hq == Hq && memo.Hkv == Hkv && memo.D == D && memo.BS == BS &&
-      memo.max_kv_len == max_kv_len && memo.num_sms == num_sms && memo.warps == warps)
+      memo.max_kv_len == max_kv_len && memo.num_sms == num_sms && memo.epoch == g_plan_epoch)
     return memo.chunks;
   const int max_blocks = max_kv_len > 0 ? (max_kv_len + BS - 1) / BS : 1;
+  const int cap = decode_team_cap(D, BS, B);
   long long worst = 1;
   for (int n = 1; n <= max_blocks; ++n) {
-    const long long c = plan_decode(B, Hq, Hkv, D, BS, n * BS, num_sms, warps).max_chunks;
+    const long long c = plan_decode(B, Hq, Hkv, D, BS, n * BS, num_sms, cap).max_chunks;
     if (c > worst) worst = c;
   }
-  memo = {B, Hq, Hkv, D, BS, max_kv_len, num_sms, warps, worst};
+  memo = {B, Hq, Hkv, D, BS, max_kv_len, num_sms, g_plan_epoch, worst};
   return worst;
-}
-
-// warps per CTA for each (D, BS): the ring (warps x stages x (K+V page)) must fit 227 KB
-static int decode_warps(int D, int BS) {
-  return (D == 128 && BS == 32) ? 4 : 8;
 }
 
 size_t decode_workspace_bytes(int B, int Hq, int Hkv, int D, int BS, int max_kv_len, int num_sms) {
   if (Hkv <= 0 || Hq < Hkv) return 0;
-  return kOffPartials +
-         (size_t)worst_case_chunks(B, Hq, Hkv, D, BS, max_kv_len, num_sms, decode_warps(D, BS)) * slot_bytes(D);
+  return kOffPartials + (size_t)worst_case_chunks(B, Hq, Hkv, D, BS, max_kv_len, num_sms) * slot_bytes(D);
 }
-int decode_plan_chunk_pages(int B, int Hq, int Hkv, int D, int BS, int max_kv_len, int num_sms) {
-  if (Hkv <= 0 || Hq < Hkv) return 0;
-  return plan_decode(B, Hq, Hkv, D, BS, max_kv_len, num_sms, decode_warps(D, BS)).chunk_pages;
+void decode_plan(int B, int Hq, int Hkv, int D, int BS, int max_kv_len, int num_sms, int* out2) {
+  out2[0] = out2[1] = 0;
+  if (Hkv <= 0 || Hq < Hkv) return;
+  const DecodePlan pl = plan_decode(B, Hq, Hkv, D, BS, max_kv_len, num_sms, decode_team_cap(D, BS, B));
+  out2[0] = pl.chunk_pages;
+  out2[1] = pl.team;
 }
 
-template <int D, int BS, int kWarps, int kStages, bool kPair, int kCtasPerSm = 1>
-static int launch_decode(const DecodeParams& p, int num_sms, long long max_chunks, cudaStream_t stream) {
+template <int D, int BS, int kWarps, int kStages>
+static int launch_decode(const DecodeParams& p, int num_sms, long long max_teams, cudaStream_t stream) {
   using T = DecodeTraits<D, BS, kWarps, kStages>;
-  auto kern = paged_decode_attn_score_kernel<D, BS, kWarps, kStages, kPair, kCtasPerSm>;
-  const size_t smem = T::smem_bytes(p.B);
-  if (smem > (size_t)(227 * 1024) / kCtasPerSm) return set_error(PC_ERR_INVALID, "decode: batch too large for the in-kernel schedule");
+  auto kern = paged_decode_attn_score_kernel<D, BS, kWarps, kStages>;
+  const size_t smem = T::smem_bytes(p.B, p.team_cap);
+  if (smem != decode_smem_bytes(D, BS, p.B, p.team_cap) || decode_cfg(D, BS).warps != kWarps)
+    return set_error(PC_ERR_INVALID, "decode: internal shared-memory accounting mismatch");
+  if (smem > kSmemLimit) return set_error(PC_ERR_INVALID, "decode: batch too large for the in-kernel schedule");
   // largest dynamic smem opted in so far, per device (monotone; a racing thread at worst
   // repeats the idempotent attribute call)
   static std::atomic<size_t> smem_set[64];
@@ -844,7 +1018,7 @@ static int launch_decode(const DecodeParams& p, int num_sms, long long max_chunk
       }
     }
   }
-  long long ctas = max_chunks < (long long)num_sms * kCtasPerSm ? max_chunks : (long long)num_sms * kCtasPerSm;  // spread over SMs first
+  long long ctas = max_teams < (long long)num_sms ? max_teams : (long long)num_sms;  // spread over SMs first
   if (ctas < 1) ctas = 1;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3((unsigned)ctas);
@@ -870,11 +1044,15 @@ int paged_decode_attn_score(const DecodeArgs& a, cudaStream_t stream) {
     return set_error(PC_ERR_INVALID, "decode: out rows must be 16-byte aligned, query rows 4-byte aligned");
   const int num_sms = device_sm_count();
   if (num_sms <= 0) return PC_ERR_CUDA;
-  const DecodePlan pl = plan_decode(a.B, a.Hq, a.Hkv, a.D, a.BS, a.max_kv_len, num_sms, decode_warps(a.D, a.BS));
+  if (a.D != 64 && a.D != 128 || a.BS != 16 && a.BS != 32)
+    // mirrors TORCH_CHECK(false, "Unsupported head size / block size") in
+    // csrc/attention/paged_attention_v1.cu:108-110,160-162
+    return set_error(PC_ERR_UNSUPPORTED, "Unsupported head size / block size (supported: head 64|128, block 16|32)");
+  const int team_cap = decode_team_cap(a.D, a.BS, a.B);
+  const DecodePlan pl = plan_decode(a.B, a.Hq, a.Hkv, a.D, a.BS, a.max_kv_len, num_sms, team_cap);
   // with a device-side plan (graph replay) any plan up to max_kv_len may be in force
   const long long need_chunks =
-      a.plan ? worst_case_chunks(a.B, a.Hq, a.Hkv, a.D, a.BS, a.max_kv_len, num_sms, decode_warps(a.D, a.BS))
-             : pl.max_chunks;
+      a.plan ? worst_case_chunks(a.B, a.Hq, a.Hkv, a.D, a.BS, a.max_kv_len, num_sms) : pl.max_chunks;
   if (a.workspace_bytes < kOffPartials + (size_t)need_chunks * slot_bytes(a.D))
     return set_error(PC_ERR_INVALID, "decode workspace too small (see pc_paged_decode_workspace_bytes)");
   uint8_t* ws = static_cast<uint8_t*>(a.workspace);
@@ -901,6 +1079,8 @@ int paged_decode_attn_score(const DecodeArgs& a, cudaStream_t stream) {
   p.table_stride = a.table_stride; p.kv_block_stride = a.kv_block_stride;
   p.scale_log2 = a.scale * 1.4426950408889634f;
   p.chunk_pages = pl.chunk_pages;
+  p.team = pl.team;
+  p.team_cap = team_cap;
   p.plan = a.plan;
   p.pdl = a.pdl;
 #ifdef PC_DEBUG
@@ -923,18 +1103,11 @@ int paged_decode_attn_score(const DecodeArgs& a, cudaStream_t stream) {
   }
 
   // a device-side plan may change between replays of a captured launch: full grid
-  const long long grid_chunks = a.plan ? (long long)num_sms * 8 : pl.max_chunks;
-  if (a.D == 128 && a.BS == 16) {
-    // (6 warps x 4-stage rings with pages consumed in pairs measured within +-3 % of this on
-    // every shape, profiles/r01_decode_variants.txt; not built)
-    return launch_decode<128, 16, 8, 3, false>(p, num_sms, grid_chunks, stream);
-  }
-  if (a.D == 128 && a.BS == 32) return launch_decode<128, 32, 4, 3, false>(p, num_sms, grid_chunks, stream);
-  if (a.D == 64 && a.BS == 16) return launch_decode<64, 16, 8, 6, false>(p, num_sms, grid_chunks, stream);
-  if (a.D == 64 && a.BS == 32) return launch_decode<64, 32, 8, 3, false>(p, num_sms, grid_chunks, stream);
-  // mirrors TORCH_CHECK(false, "Unsupported head size / block size") in
-  // csrc/attention/paged_attention_v1.cu:108-110,160-162
-  return set_error(PC_ERR_UNSUPPORTED, "Unsupported head size / block size (supported: head 64|128, block 16|32)");
+  const long long grid_teams = a.plan ? (long long)num_sms : pl.max_chunks;
+  if (a.D == 128 && a.BS == 16) return launch_decode<128, 16, 8, 3>(p, num_sms, grid_teams, stream);
+  if (a.D == 128 && a.BS == 32) return launch_decode<128, 32, 4, 3>(p, num_sms, grid_teams, stream);
+  if (a.D == 64 && a.BS == 16) return launch_decode<64, 16, 8, 6>(p, num_sms, grid_teams, stream);
+  return launch_decode<64, 32, 8, 3>(p, num_sms, grid_teams, stream);
 }
 
 }  // namespace pc

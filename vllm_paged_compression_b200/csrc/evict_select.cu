@@ -44,29 +44,25 @@ __device__ __forceinline__ bool decode_trigger(const pc_evict_policy& pol, int s
          n * bs > (pol.initial_blocks + pol.num_block_merge) * bs;
 }
 
-__global__ void __launch_bounds__(kEvictThreads) evict_select_compact_kernel(const EvictParams p) {
+// One batch row: trigger test, victim, compacted row.  All threads of the CTA take part;
+// returns the victim (-1 = row did not trigger).
+__device__ __forceinline__ int evict_row(const pc_evict_policy& pol, const int* __restrict__ row, int n, int seq_len,
+                                         const float* __restrict__ pool, int HT, int* orow, long long out_stride) {
   __shared__ float best_v[kEvictThreads / 32];
   __shared__ int best_i[kEvictThreads / 32];
   __shared__ int victim_s;
-  const int b = blockIdx.x;
   const int tid = threadIdx.x;
-  const int n = p.n_blocks[b];
-  const int seq_len = p.seq_lens[b];
-  const int* row = p.block_tables + (size_t)b * p.table_stride;
-  int* orow = p.out_tables + (size_t)b * p.out_stride;
-  const bool trig = (n >= 3) && decode_trigger(p.pol, seq_len, n);
+  const bool trig = (n >= 3) && decode_trigger(pol, seq_len, n);
 
   int victim = -1;
   if (trig) {
-    if (p.pol.decode_method == 0) {
+    if (pol.decode_method == 0) {
       victim = 1;  // streamingLLM: always the block after the sink (torch_cuda_sdpa.py:1404-1405)
     } else {
       // candidates [1, hi): global -> n-1 ; local -> min(1 + topk, n-1)   (:1528-1534)
       const int lo = 1;
       int hi = n - 1;
-      if (p.pol.topk_blocks > 0) hi = min(hi, 1 + p.pol.topk_blocks);
-      const float* pool = p.score.pools[p.score.local];
-      const int HT = p.score.heads_total;
+      if (pol.topk_blocks > 0) hi = min(hi, 1 + pol.topk_blocks);
       float bv = FLT_MAX;
       int bi = 0x7fffffff;
       for (int i = lo + tid; i < hi; i += kEvictThreads) {
@@ -100,17 +96,66 @@ __global__ void __launch_bounds__(kEvictThreads) evict_select_compact_kernel(con
 
   // ---- table compaction: delete column `victim`, shift left, 0-pad
   const int n_after = n - (victim >= 0 ? 1 : 0);
-  for (int i = tid; i < p.out_stride; i += kEvictThreads) {
+  for (int i = tid; i < out_stride; i += kEvictThreads) {
     int v = 0;
     if (i < n_after) v = (victim >= 0 && i >= victim) ? row[i + 1] : row[i];
     orow[i] = v;
   }
-  if (tid == 0) {
+  return victim;
+}
+
+__global__ void __launch_bounds__(kEvictThreads) evict_select_compact_kernel(const EvictParams p) {
+  const int b = blockIdx.x;
+  const int victim = evict_row(p.pol, p.block_tables + (size_t)b * p.table_stride, p.n_blocks[b], p.seq_lens[b],
+                               p.score.n_pools > 0 ? p.score.pools[p.score.local] : nullptr, p.score.heads_total,
+                               p.out_tables + (size_t)b * p.out_stride, p.out_stride);
+  if (threadIdx.x == 0) {
     p.out_victim[b] = victim;
     if (p.out_kv_lens)
       p.out_kv_lens[b] = p.kv_lens[b] - ((victim >= 0 && !p.pre_adjusted) ? p.pol.block_size : 0);
   }
+}
 
+// Every layer of an engine step in ONE launch: grid (batch, layers).  A layer's victims depend
+// only on the block scores written on EARLIER steps and on the step's tables, never on this
+// step's attention, so the selections of all layers can run before the first layer's attention
+// -- one launch instead of one per layer, and the attention kernels of a trigger step keep
+// their programmatic dependent launch chain.
+struct EvictLayersParams {
+  const int* __restrict__ block_tables;
+  long long table_stride;
+  const int* __restrict__ n_blocks;
+  const int* __restrict__ seq_lens;
+  pc_evict_policy pol;
+  const float* const* __restrict__ pools;   // [layers] this rank's score pool of every layer
+  int heads_total;
+  int* out_tables;                          // [layers][batch][out_stride]
+  long long out_stride, out_layer_stride;
+  int* out_victims;                         // [layers][batch]
+};
+
+__global__ void __launch_bounds__(kEvictThreads) evict_select_compact_layers_kernel(const EvictLayersParams p) {
+  const int b = blockIdx.x, layer = blockIdx.y;
+  const float* pool = p.pools != nullptr ? p.pools[layer] : nullptr;
+  const int victim = evict_row(p.pol, p.block_tables + (size_t)b * p.table_stride, p.n_blocks[b], p.seq_lens[b], pool,
+                               p.heads_total, p.out_tables + (size_t)layer * p.out_layer_stride + (size_t)b * p.out_stride,
+                               p.out_stride);
+  if (threadIdx.x == 0) p.out_victims[(size_t)layer * gridDim.x + b] = victim;
+}
+
+int evict_select_compact_layers(const EvictLayersArgs& a, cudaStream_t stream) {
+  if (a.B <= 0 || a.L <= 0) return 0;
+  if (a.pol.block_size <= 0) return set_error(PC_ERR_INVALID, "policy.block_size must be > 0");
+  if (a.pol.decode_method != 0 && (a.pools == nullptr || a.heads_total <= 0))
+    return set_error(PC_ERR_INVALID, "value_l2 eviction needs the per-layer score pools");
+  if (a.L > 65535) return set_error(PC_ERR_INVALID, "too many layers for one launch");
+  EvictLayersParams p;
+  p.block_tables = a.block_tables; p.table_stride = a.table_stride; p.n_blocks = a.n_blocks;
+  p.seq_lens = a.seq_lens; p.pol = a.pol; p.pools = a.pools; p.heads_total = a.heads_total;
+  p.out_tables = a.out_tables; p.out_stride = a.out_stride; p.out_layer_stride = a.out_layer_stride;
+  p.out_victims = a.out_victims;
+  evict_select_compact_layers_kernel<<<dim3(a.B, a.L), kEvictThreads, 0, stream>>>(p);
+  return check_launch("evict_select_compact_layers_kernel");
 }
 
 int evict_select_compact(const EvictSelectArgs& a, cudaStream_t stream) {

@@ -55,14 +55,15 @@ struct DecodeArgs {
   const void* new_v;
   const long long* slot_mapping;
   long long new_k_stride, new_v_stride;
-  const int* plan;  // device {chunk_pages} or nullptr (host plans from max_kv_len)
+  const int* plan;  // device {chunk_pages, team} or nullptr (host plans from max_kv_len)
   int pdl;          // programmatic dependent launch (see pc_decode_step.pdl)
 };
 size_t decode_workspace_bytes(int B, int Hq, int Hkv, int D, int BS, int max_kv_len, int num_sms);
-int decode_plan_chunk_pages(int B, int Hq, int Hkv, int D, int BS, int max_kv_len, int num_sms);
+void decode_plan(int B, int Hq, int Hkv, int D, int BS, int max_kv_len, int num_sms, int* out2);  // {chunk_pages, team}
 int paged_decode_attn_score(const DecodeArgs& a, cudaStream_t stream);
 #ifdef PC_DEBUG
 void set_decode_trace(void* buf);  // per-warp globaltimer stamps, nullptr = off
+void set_decode_plan_override(int chunk_pages, int team);  // 0 = planner's choice
 #endif
 
 struct CacheWriteArgs {
@@ -96,6 +97,21 @@ struct EvictSelectArgs {
   int pre_adjusted;
 };
 int evict_select_compact(const EvictSelectArgs& a, cudaStream_t stream);
+
+struct EvictLayersArgs {
+  const int* block_tables;
+  long long table_stride;
+  const int* n_blocks;
+  const int* seq_lens;
+  int B, L;
+  pc_evict_policy pol;
+  const float* const* pools;   // DEVICE array [L] of this rank's score pools, or nullptr (streamingLLM)
+  int heads_total;
+  int* out_tables;
+  long long out_stride, out_layer_stride;
+  int* out_victims;
+};
+int evict_select_compact_layers(const EvictLayersArgs& a, cudaStream_t stream);
 
 struct PrefillArgs {
   void* out;

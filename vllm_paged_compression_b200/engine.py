@@ -16,8 +16,6 @@ backend sees too.
 """
 from __future__ import annotations
 
-import os
-
 from dataclasses import dataclass, field
 from typing import Callable, Dict, List, Optional, Tuple
 
@@ -244,40 +242,58 @@ class PinnedLayerIO:
 
     The reference's model runner hands `forward` device tensors; a caller that keeps q/k/v
     on the host (bench.py's e2e leg, an offloaded model) would otherwise pay one blocking
-    copy per tensor per layer on the compute stream.  Here the step's inputs travel as one
-    fused `[B, (Hq + 2 Hkv) D]` row block per layer (the layout `qkv_proj` produces,
-    vllm/model_executor/models/llama.py:195-199) on a copy stream that runs ahead of the
-    compute stream in groups of `group` layers, and every group's attention output is
-    drained on a third stream while later layers compute.  PCIe is full duplex, so the
-    step costs max(compute, H2D, D2H) plus the first group's H2D and the last group's D2H.
+    copy per tensor per layer on the compute stream.  Here the step's inputs sit in ONE
+    contiguous pinned arena as fused `[B, (Hq + 2 Hkv) D]` row blocks per layer (the layout
+    `qkv_proj` produces, vllm/model_executor/models/llama.py:195-199), the outputs in a second
+    one, and a step moves them with a handful of large copies:
+
+      H2D  groups of 1, 1, 2, 4, 8, 16 ... layers on a copy stream that runs ahead of compute
+           (the link moves a layer's rows about twice as fast as the layer computes, so a
+           group that doubles arrives before the previous one is consumed; only the first
+           layer's copy is exposed);
+      D2H  the mirror image, ... 16, 8, 4, 2, 1, 1 on a SECOND stream, each group as soon as its
+           last layer is done; only the last layer's copy is exposed.
+
+    PCIe is full duplex on these boxes: 55 GB/s either way alone, 45 GB/s each way together
+    (profiles/r02_pcie.txt; round 1's "12 GB/s duplex" was a measurement bug), so the two
+    directions get their own streams.  A step costs max(compute, H2D, D2H) + the first H2D +
+    the last D2H.
 
     Use:  io.begin_step(); engine.step(io.qkv, out_fn=io.put_out, out_buf_fn=io.out_buf); io.end_step()
     """
 
     def __init__(self, num_layers: int, batch: int, num_heads: int, num_kv_heads: int, head_size: int,
-                 device, group: int = 4, dtype=torch.bfloat16, duplex: Optional[bool] = None) -> None:
+                 device, group: int = 0, dtype=torch.bfloat16, duplex: bool = True) -> None:
         self.L, self.B = num_layers, batch
-        # copy groups: `group` layers each, or group=0 -> a ramp (1, 1, 2, 4, ... 4, 2, 1, 1): the first
-        # group's H2D and the last group's D2H are the only copies a step cannot hide behind
-        # compute, so those groups are one layer; the middle ones stay large (a group boundary
-        # costs the next layer its programmatic dependent launch)
-        if group and group > 0:
-            sizes = [min(group, num_layers - lo) for lo in range(0, num_layers, group)]
+
+        def doubling(n):
+            sizes, left, nxt = [], n, 1
+            while left > 0:
+                g = min(nxt, left)
+                sizes.append(g)
+                left -= g
+                if len(sizes) >= 2:
+                    nxt *= 2
+            return sizes
+        if group and group > 0:       # fixed group size, both directions
+            h_sizes = [min(group, num_layers - lo) for lo in range(0, num_layers, group)]
+            d_sizes = list(h_sizes)
         else:
-            head = [1, 1, 2]
-            sizes = head + [4] * max(0, (num_layers - 2 * sum(head)) // 4)
-            sizes += [num_layers - sum(sizes) - sum(head)] if num_layers - sum(sizes) - sum(head) > 0 else []
-            sizes += head[::-1]
-            if sum(sizes) != num_layers or min(sizes) < 1:
-                sizes = [1] * num_layers
-        self.bounds = []
-        lo = 0
-        for n in sizes:
-            self.bounds.append((lo, lo + n))
-            lo += n
+            h_sizes = doubling(num_layers)
+            d_sizes = h_sizes[::-1]
+
+        def bounds(sizes):
+            out, lo = [], 0
+            for n in sizes:
+                out.append((lo, lo + n))
+                lo += n
+            return out
+        self.bounds = bounds(h_sizes)          # H2D groups
+        self.d_bounds = bounds(d_sizes)        # D2H groups
         self.gidx = [gi for gi, (a, b) in enumerate(self.bounds) for _ in range(a, b)]
+        self.d_gidx = [gi for gi, (a, b) in enumerate(self.d_bounds) for _ in range(a, b)]
         self.is_first = [l == self.bounds[self.gidx[l]][0] for l in range(num_layers)]
-        self.is_last = [l + 1 == self.bounds[self.gidx[l]][1] for l in range(num_layers)]
+        self.is_last = [l + 1 == self.d_bounds[self.d_gidx[l]][1] for l in range(num_layers)]
         self.qw, self.kw = num_heads * head_size, num_kv_heads * head_size
         w = self.qw + 2 * self.kw
         self.device = torch.device(device)
@@ -286,23 +302,18 @@ class PinnedLayerIO:
         self.qkv_dev = torch.empty(num_layers, batch, w, dtype=dtype, device=self.device)
         self.out_dev = torch.empty(num_layers, batch, self.qw, dtype=dtype, device=self.device)
         self.h2d_stream = torch.cuda.Stream(self.device)
-        # duplex=False: both directions share ONE copy stream.  Measured on the B200 boxes of
-        # this pool, simultaneous H2D + D2H run at ~12 GB/s each way against 48 / 56 GB/s alone
-        # (profiles/r01_e2e_breakdown.txt), so serialised copies finish sooner than overlapped ones.
-        if duplex is None:
-            duplex = os.environ.get("PC_IO_DUPLEX", "0") == "1"
         self.d2h_stream = torch.cuda.Stream(self.device) if duplex else self.h2d_stream
-        n_groups = len(self.bounds)
-        self.h2d_done = [torch.cuda.Event() for _ in range(n_groups)]
-        self.grp_done = [torch.cuda.Event() for _ in range(n_groups)]
+        self.h2d_done = [torch.cuda.Event() for _ in self.bounds]
+        self.grp_done = [torch.cuda.Event() for _ in self.d_bounds]
         self.step_done = torch.cuda.Event()
         self.h2d_bytes = self.qkv_host.numel() * self.qkv_host.element_size()
         self.d2h_bytes = self.out_host.numel() * self.out_host.element_size()
 
     def describe(self) -> dict:
         """Copy schedule, for the bench log."""
-        return {"groups": [b - a for a, b in self.bounds], "duplex_streams": self.d2h_stream is not self.h2d_stream,
-                "h2d_copies_per_step": len(self.bounds), "d2h_copies_per_step": len(self.bounds)}
+        return {"h2d_groups": [b - a for a, b in self.bounds], "d2h_groups": [b - a for a, b in self.d_bounds],
+                "duplex_streams": self.d2h_stream is not self.h2d_stream,
+                "h2d_copies_per_step": len(self.bounds), "d2h_copies_per_step": len(self.d_bounds)}
 
     def begin_step(self) -> None:
         """Queue every layer group's H2D on the copy stream (after the previous step's
@@ -328,11 +339,11 @@ class PinnedLayerIO:
         if out.data_ptr() != self.out_dev[layer].data_ptr():
             self.out_dev[layer].copy_(out.view(self.B, self.qw))
         if self.is_last[layer]:
-            gi = self.gidx[layer]
+            gi = self.d_gidx[layer]
             cur = torch.cuda.current_stream(self.device)
             self.grp_done[gi].record(cur)
             self.d2h_stream.wait_event(self.grp_done[gi])
-            lo = self.bounds[gi][0]
+            lo = self.d_bounds[gi][0]
             with torch.cuda.stream(self.d2h_stream):
                 self.out_host[lo:layer + 1].copy_(self.out_dev[lo:layer + 1], non_blocking=True)
 

@@ -110,8 +110,12 @@ class DecodeGraphRunner:
         self.d_plan = m[o_plan:o_tab]
         self.d_tab = m[o_tab:].view(B, M)
         self._off = (o_slot, o_kv, o_seq, o_nblk, o_plan, o_tab)
-        self.d_compact = torch.zeros(B, M, dtype=torch.int32, device=self.device)
-        self.d_victims = torch.full((L, B), -1, dtype=torch.int32, device=self.device)
+        # trigger steps: every layer's compacted tables / victims from ONE selection launch
+        # (value_l2: per layer; streamingLLM: the victim is index 1 for every layer, one copy)
+        self.Lsel = L if self.value_l2 else 1
+        self.d_compact = torch.zeros(self.Lsel, B, M, dtype=torch.int32, device=self.device)
+        self.d_victims = torch.full((self.Lsel, B), -1, dtype=torch.int32, device=self.device)
+        self._vict_host = torch.empty(B, dtype=torch.int32).pin_memory()
 
         # ---- host mirror
         self.tab = np.zeros((B, M), dtype=np.int32)
@@ -125,13 +129,18 @@ class DecodeGraphRunner:
         self.seq = np.asarray([s.seq_len for s in self.seqs], dtype=np.int64)
         self.kv = np.asarray([bt.get_seq_kv_len() for bt in self.bts], dtype=np.int64)
         self.rows = np.arange(B)
+        self.cols = np.arange(M)
+        # decode tokens not yet booked on the host objects (_Seq.seq_len, BlockTable slot
+        # counters): the numpy mirrors are authoritative while the runner steps, the objects are
+        # brought up to date when a row takes a new block and by sync_host()
+        self.pend = np.zeros(B, dtype=np.int64)
 
         # ---- decode workspace: pc_paged_decode_workspace_bytes covers EVERY plan the device-side
         # plan word can name for a longest row of up to max_kv_len tokens
         Hq, Hkv, D = eng.num_heads, eng.num_kv_heads, eng.head_size
         need = ops.paged_decode_workspace_bytes(B, Hq, Hkv, D, bs, M * bs)
         self.ws = torch.zeros(need, dtype=torch.uint8, device=self.device)
-        self._plan_cache: Dict[int, int] = {}
+        self._plan_cache: Dict[int, Tuple[int, int]] = {}
 
         # ---- per-layer pointers
         self.layers = []
@@ -140,12 +149,21 @@ class DecodeGraphRunner:
             score = impl._scores(self.device, eng.kv_caches[l].shape[1]) if self.value_l2 else None
             self.layers.append((kptr, vptr, score))
         self.blk_stride = blk_stride
+        self.d_pool_ptrs = None
+        if self.value_l2:
+            ptrs = [sc.pools[sc.local] for _, _, sc in self.layers]
+            self.d_pool_ptrs = torch.tensor(ptrs, dtype=torch.int64, device=self.device)
+            self.heads_total = self.layers[0][2].heads_total
         self._graphs: Dict[bool, object] = {}
         self._launches: Dict[bool, int] = {}
+        self._ahead = None          # next step's packed host state, prepared while the device runs
         self._warm()
+        if self.use_graph:          # capture both variants now, not inside somebody's timed step
+            for trig in ((False, True) if self.cfg is not None else (False,)):
+                self._graph(trig)
 
     # ------------------------------------------------------------------ launches
-    def _make_step(self, trig: bool, pdl: bool = False):
+    def _make_step(self, pdl: bool = False):
         eng = self.eng
         q, k, v = self.qkv[0]
         return ops.make_decode_step(
@@ -153,28 +171,38 @@ class DecodeGraphRunner:
             eng.head_size, self.bs, self.max_kv_len, eng.impls[0].scale, q.stride(0), k.stride(0),
             v.stride(0), self.outs[0].stride(0), self.blk_stride,
             policy=eng.impls[0]._policy_struct() if self.cfg is not None else None,
-            n_blocks=self.d_nblk, compact_tables=self.d_compact if trig else None, any_trigger=trig,
-            attend_uncompacted=trig and self.attend_unc, plan=self.d_plan, workspace=self.ws, pdl=pdl)
+            n_blocks=self.d_nblk, plan=self.d_plan, workspace=self.ws, pdl=pdl)
 
     def _launch_layers(self, trig: bool, count: bool = False) -> None:
-        """All layers of one decode step on the current stream (captured or eager)."""
-        ds = self._make_step(trig)
+        """All layers of one decode step on the current stream (captured or eager).
+        Trigger step: ONE selection launch for all layers (a layer's victims depend on scores
+        written on earlier steps only), then the same attention launches as a plain step, each
+        over its layer's compacted tables -- so the PDL chain between the layers' kernels
+        survives trigger steps."""
+        ds = self._make_step()
         # PDL for a layer whose predecessor in the stream is the previous layer's attention
         # kernel (another layer's pool): its first pages load while that kernel drains
-        ds_pdl = self._make_step(trig, pdl=True) if (self.pdl and not trig) else ds
-        self._launches[trig] = ds._launches * self.L
+        ds_pdl = self._make_step(pdl=True) if self.pdl else ds
+        self._launches[trig] = self.L + (1 if trig else 0)
         io = self.io
         cur = torch.cuda.current_stream(self.device)
         if io is not None:
             io.begin_step()
+        uncompacted = trig and self.attend_unc     # HEAD's streamingLLM behaviour (DESIGN D5)
+        if trig:
+            ops.evict_select_compact_layers(self.d_tab, self.d_nblk, self.d_seq, ds.policy, self.d_pool_ptrs,
+                                            self.heads_total if self.value_l2 else 0, self.d_compact,
+                                            self.d_victims)
         for l in range(self.L):
             if io is not None and io.is_first[l]:
                 cur.wait_event(io.h2d_done[io.gidx[l]])
             q, k, v = self.qkv[l]
             kptr, vptr, score = self.layers[l]
             chained = l > 0 and (io is None or not io.is_first[l])
-            ops.decode_layer(ds_pdl if chained else ds, self.outs[l], q, k, v, kptr, vptr, score,
-                             self.d_victims[l] if trig else None)
+            tables = None
+            if trig and not uncompacted:
+                tables = self.d_compact[l if self.value_l2 else 0]
+            ops.decode_layer(ds_pdl if chained else ds, self.outs[l], q, k, v, kptr, vptr, score, None, tables)
             if io is not None:
                 io.put_out(l, self.out_flat[l])
         if io is not None:
@@ -203,15 +231,55 @@ class DecodeGraphRunner:
         return g
 
     # ---------------------------------------------------------------------- step
-    def _trigger(self) -> np.ndarray:
+    def sync_host(self) -> None:
+        """Book the decode tokens the runner has stepped through on the host objects
+        (`_Seq.seq_len`, BlockTable slot counters).  Block ids, evictions and frees are always
+        current; only these per-token counters are batched (a per-sequence Python loop per step
+        costs more than the step at batch 512).  Call before reading them."""
+        for r in np.nonzero(self.pend)[0].tolist():
+            n = int(self.pend[r])
+            self.bts[r].append_slots(n)          # never crosses a block boundary: those rows are booked at once
+            self.seqs[r].seq_len += n
+        self.pend[:] = 0
+
+    def _trigger(self, seq: np.ndarray) -> np.ndarray:
         cfg, bs = self.cfg, self.bs
         if cfg is None:
             return np.zeros(self.B, dtype=bool)
         ok = self.nblk >= 3
         if cfg.cache_prune_type == "budget":
-            return ok & (self.seq > cfg.cache_budget) & (self.seq % bs == 0)
-        return (ok & (self.seq % (bs * cfg.evict_freq) == 0)
+            return ok & (seq > cfg.cache_budget) & (seq % bs == 0)
+        return (ok & (seq % (bs * cfg.evict_freq) == 0)
                 & (self.nblk.astype(np.int64) * bs > (cfg.initial_blocks + cfg.num_block_merge) * bs))
+
+    def _pack(self, seq: np.ndarray, kv: np.ndarray):
+        """Everything the device needs for the step at logical lengths `seq` / physical lengths
+        `kv` (tables as they are now), packed into the next pinned ring buffer.
+        -> (trigger mask, any trigger, kv lens handed to attention, slot mapping, ring index)"""
+        eng, bs, B = self.eng, self.bs, self.B
+        tab, nblk = self.tab, self.nblk
+        trig = self._trigger(seq)
+        any_trig = bool(trig.any())
+        kv_pass = kv - bs * trig if self.cfg is not None else seq               # model_runner.py:540-543
+        slot = tab[self.rows, nblk - 1].astype(np.int64) * bs + (seq - 1) % bs
+        mx = int(kv_pass.max())
+        plan = self._plan_cache.get(mx)
+        if plan is None:
+            plan = self._plan_cache[mx] = ops.paged_decode_plan(B, eng.num_heads, eng.num_kv_heads,
+                                                                eng.head_size, bs, mx)
+        i = self._ring_i
+        self._ring_i = (i + 1) % len(self._ring)
+        if self._ring_ev[i] is not None:
+            self._ring_ev[i].synchronize()
+        host = self._ring[i].numpy()
+        o_slot, o_kv, o_seq, o_nblk, o_plan, o_tab = self._off
+        host[o_slot:o_kv].view(np.int64)[:] = slot
+        host[o_kv:o_seq] = kv_pass
+        host[o_seq:o_nblk] = seq
+        host[o_nblk:o_plan] = nblk
+        host[o_plan:o_plan + 2] = plan
+        host[o_tab:] = tab.reshape(-1)
+        return trig, any_trig, kv_pass, slot, i
 
     def step(self) -> Dict[int, Tuple[str, int]]:
         """One decode step of every sequence.  The caller has refilled the static q/k/v
@@ -225,46 +293,32 @@ class DecodeGraphRunner:
         grow = self.nblk + (self.kv % bs == 0)
         if int(grow.max()) > self.M - 1:
             torch.cuda.current_stream(self.device).synchronize()
+            self.sync_host()
             self._setup(max(2 * self.max_kv_len - int(self.kv.min()), (int(grow.max()) + 8) * bs))
         tab, nblk = self.tab, self.nblk
-        for r, (s, bt) in enumerate(zip(self.seqs, self.bts)):      # scheduler.py _schedule_default
-            s.seq_len += 1
-            n0 = int(nblk[r])
-            bt.append_slots(1)
-            ids = bt.physical_block_ids
-            if len(ids) != n0:
-                if len(ids) > self.M:
-                    raise RuntimeError("sequence outgrew the runner's max_kv_len")
-                tab[r, n0] = ids[-1]
-                nblk[r] = n0 + 1
+        # scheduler.py _schedule_default, vectorised: only rows whose last block is full touch
+        # their BlockTable (allocator order = row order, like the per-sequence loop)
+        new_rows = np.nonzero(self.kv % bs == 0)[0]
+        self.pend += 1
+        if len(new_rows):
+            for r in new_rows.tolist():
+                bt = self.bts[r]
+                bt.append_slots(int(self.pend[r]))
+                self.seqs[r].seq_len += int(self.pend[r])
+                tab[r, nblk[r]] = bt.physical_block_ids[-1]
+            self.pend[new_rows] = 0
+            nblk[new_rows] += 1
         self.seq += 1
         self.kv += 1
-        trig = self._trigger()
-        any_trig = bool(trig.any())
-        kv_pass = self.kv - bs * trig if self.cfg is not None else self.seq     # model_runner.py:540-543
-        slot = tab[self.rows, nblk - 1].astype(np.int64) * bs + (self.seq - 1) % bs
-        mx = int(kv_pass.max())
-        plan = self._plan_cache.get(mx)
-        if plan is None:
-            plan = self._plan_cache[mx] = ops.paged_decode_plan(B, eng.num_heads, eng.num_kv_heads,
-                                                                eng.head_size, bs, mx)
+        ahead, self._ahead = self._ahead, None
+        if ahead is None:
+            ahead = self._pack(self.seq, self.kv)
+        trig, any_trig, kv_pass, slot, i = ahead
         if self.record:
             self.last = {"seq_lens": self.seq.tolist(), "kv_lens": kv_pass.tolist(), "slots": slot.tolist(),
                          "tables": [tab[r, :nblk[r]].tolist() for r in range(B)],
                          "trigger_rows": np.nonzero(trig)[0].tolist()}
         # ---- one packed H2D
-        i = self._ring_i
-        self._ring_i = (i + 1) % len(self._ring)
-        if self._ring_ev[i] is not None:
-            self._ring_ev[i].synchronize()
-        host = self._ring[i].numpy()
-        o_slot, o_kv, o_seq, o_nblk, o_plan, o_tab = self._off
-        host[o_slot:o_kv].view(np.int64)[:] = slot
-        host[o_kv:o_seq] = kv_pass
-        host[o_seq:o_nblk] = self.seq
-        host[o_nblk:o_plan] = nblk
-        host[o_plan] = plan
-        host[o_tab:] = tab.reshape(-1)
         self.meta.copy_(self._ring[i], non_blocking=True)
         ev = self._ring_ev[i] or torch.cuda.Event()
         ev.record(torch.cuda.current_stream(self.device))
@@ -275,9 +329,16 @@ class DecodeGraphRunner:
             ops._launched(self._launches[any_trig])      # kernel nodes of the replayed graph
         else:
             self._launch_layers(any_trig)                # ops.decode_layer counts its own
+        # ---- host work of the NEXT step while the device runs this one (matters when the caller
+        # waits for every step's result, e.g. host-resident activations): valid when this step
+        # changes no table (no eviction) and the next one appends no block
+        if not any_trig and not bool((self.kv % bs == 0).any()):
+            self._ahead = self._pack(self.seq + 1, self.kv + 1)
         if eng.score_exchange is not None:
-            scored = [int(tab[r, nblk[r] - 1]) for r in range(B) if self.seq[r] % bs == 0] \
-                if self.value_l2 else []
+            scored = []
+            if self.value_l2:
+                rs = np.nonzero(self.seq % bs == 0)[0]
+                scored = tab[rs, nblk[rs] - 1].tolist()
             eng.score_exchange.publish(scored)
         # ---- layer-0 feedback (model_runner.py:1797-1802)
         rmv: Dict[int, Tuple[str, int]] = {}
@@ -286,17 +347,24 @@ class DecodeGraphRunner:
             if self.log_victims and self.value_l2:
                 self.victim_log.append(self.d_victims.clone())
             if self.value_l2:
-                vict = self.d_victims[0].cpu().numpy()
-                rmv = {int(r): (self.seqs[r].request_id, int(vict[r])) for r in rows if vict[r] >= 0}
+                self._vict_host.copy_(self.d_victims[0], non_blocking=True)
+                torch.cuda.current_stream(self.device).synchronize()
+                vict = self._vict_host.numpy()
+                rows = rows[vict[rows] >= 0]
+                idx = vict[rows].astype(np.int64)
             else:
-                rmv = {int(r): (self.seqs[r].request_id, 1) for r in rows}
-            for r, (_, idx) in rmv.items():
-                self.bts[r].free_prunned_blocks(idx)
-                n = int(nblk[r])
-                tab[r, idx:n - 1] = tab[r, idx + 1:n]
-                tab[r, n - 1] = 0
-                nblk[r] = n - 1
-                self.kv[r] -= bs
+                idx = np.ones(len(rows), dtype=np.int64)
+            seqs, bts = self.seqs, self.bts
+            for r, i in zip(rows.tolist(), idx.tolist()):        # llm_engine.py:1179-1193, row order
+                rmv[r] = (seqs[r].request_id, i)
+                bts[r].free_prunned_blocks(i)
+            if len(rows):
+                # delete column idx of every evicted row, shift left, 0-pad: all rows at once
+                sel = tab[rows]
+                shifted = np.concatenate([sel[:, 1:], np.zeros((len(rows), 1), dtype=sel.dtype)], axis=1)
+                tab[rows] = np.where(self.cols[None, :] >= idx[:, None], shifted, sel)
+                nblk[rows] -= 1
+                self.kv[rows] -= bs
         if self.io is not None:
             torch.cuda.current_stream(self.device).synchronize()    # the caller owns out_host now
         return rmv

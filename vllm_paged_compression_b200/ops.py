@@ -267,21 +267,47 @@ def make_decode_step(slot_mapping: torch.Tensor, block_tables: torch.Tensor, kv_
 
 
 def paged_decode_plan(batch: int, num_heads: int, num_kv_heads: int, head_size: int, block_size: int,
-                      max_kv_len: int) -> int:
-    """chunk_pages the host planner picks for this launch shape (pc_decode_step.plan)."""
-    return int(_lib.load().pc_paged_decode_plan(batch, num_heads, num_kv_heads, head_size, block_size,
-                                                max_kv_len))
+                      max_kv_len: int, num_sms: int = 0) -> Tuple[int, int]:
+    """(chunk_pages, team) the host planner picks for this launch shape (pc_decode_step.plan);
+    num_sms = 0: the current device's SM count."""
+    out = (C.c_int32 * 2)()
+    check(_lib.load().pc_paged_decode_plan(batch, num_heads, num_kv_heads, head_size, block_size,
+                                           max_kv_len, int(num_sms), out))
+    return int(out[0]), int(out[1])
 
 
 def decode_layer(step: PcDecodeStep, out: torch.Tensor, query: torch.Tensor, key: torch.Tensor,
                  value: torch.Tensor, key_cache_ptr: int, value_cache_ptr: int,
-                 score: Optional[PcScorePool] = None, out_victim: Optional[torch.Tensor] = None) -> None:
+                 score: Optional[PcScorePool] = None, out_victim: Optional[torch.Tensor] = None,
+                 attend_tables: Optional[torch.Tensor] = None) -> None:
     """One layer's decode step in one native call (cache write -> [select + compact] ->
-    attention + scoring).  Shapes / strides were validated when `step` was built."""
+    attention + scoring).  Shapes / strides were validated when `step` was built.
+    attend_tables [B, W] int32: this layer's tables from `evict_select_compact_layers` (the call
+    then runs no selection of its own)."""
     check(_lib.load().pc_decode_layer(C.byref(step), out.data_ptr(), query.data_ptr(), key.data_ptr(),
                                       value.data_ptr(), key_cache_ptr, value_cache_ptr, _sp(score),
-                                      _ptr(out_victim)))
-    _launched(step._launches)
+                                      _ptr(out_victim), _ptr(attend_tables),
+                                      attend_tables.stride(0) if attend_tables is not None else 0))
+    _launched(1 if attend_tables is not None else step._launches)
+
+
+def evict_select_compact_layers(block_tables: torch.Tensor, n_blocks: torch.Tensor, seq_lens: torch.Tensor,
+                                policy: PcEvictPolicy, pool_ptrs: Optional[torch.Tensor], heads_total: int,
+                                out_tables: torch.Tensor, out_victims: torch.Tensor) -> None:
+    """P3 + S4 + C1 of every layer in one launch.  pool_ptrs int64 [L] on the device (data
+    pointers of this rank's score pool of each layer) or None (streamingLLM); out_tables int32
+    [L, B, W]; out_victims int32 [L, B]."""
+    _req_cuda(block_tables, n_blocks, seq_lens, pool_ptrs, out_tables, out_victims)
+    L, B, W = out_tables.shape
+    if out_victims.shape != (L, B) or not out_tables.is_contiguous() or not out_victims.is_contiguous():
+        raise RuntimeError("out_tables must be contiguous [L, B, W], out_victims contiguous [L, B]")
+    if pool_ptrs is not None and (pool_ptrs.dtype != torch.int64 or pool_ptrs.numel() != L):
+        raise RuntimeError("pool_ptrs must be int64 [L]")
+    check(_lib.load().pc_evict_select_compact_layers(
+        block_tables.data_ptr(), block_tables.stride(0), n_blocks.data_ptr(), seq_lens.data_ptr(), B, L,
+        C.byref(policy), _ptr(pool_ptrs), int(heads_total), out_tables.data_ptr(), W, B * W,
+        out_victims.data_ptr(), _stream(block_tables)))
+    _launched()
 
 
 def _check_compat(kv_cache_dtype, k_scale, v_scale, alibi_slopes, blocksparse_vert_stride):
@@ -317,12 +343,13 @@ def paged_attention_v2(out, exp_sums, max_logits, tmp_out, query, key_cache, val
 
 
 def pdl_default(batch: int) -> bool:
-    """Programmatic dependent launch between consecutive layers' decode kernels: measured on
-    B200 at the bench shape (512 (row, kv-head) groups x 37 pages per launch, us per launch,
-    PDL / plain): B 64 30.4 / 34.6, B 128 32.9 / 34.7, B 256 38.5 / 36.4, B 512 47.5 / 40.5
-    (profiles/r01_tp_shape_pdl.txt) -- the early-launched CTAs pay off only while the batch
-    (and with it the O(B) schedule prologue they run ahead of the dependency wait) is small."""
-    return batch <= 128
+    """Programmatic dependent launch between consecutive layers' decode kernels: the schedule
+    prologue and the first ring of pages of layer l+1 load while layer l drains.  Measured on
+    B200 at the bench shape and its tensor-parallel per-rank shapes (us per launch, PDL / plain):
+    B 64 28.1 / 34.6, B 128 28.1 / 34.6, B 256 28.2 / 34.5, B 512 28.8 / 35.1
+    (profiles/r02_tp_shape_pdl.txt).  Round 1 saw PDL lose above 128 rows; that was an O(B) scan
+    for empty rows on CTA 0 inside the kernel, not PDL -- with the scan gone PDL wins everywhere."""
+    return True
 
 
 # ------------------------------------------------------------------------------ A1
