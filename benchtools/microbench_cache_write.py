@@ -75,8 +75,21 @@ def main():
     ap.add_argument("--block", type=int, default=16)
     ap.add_argument("--evict-freq", type=int, default=2)
     ap.add_argument("--reps", type=int, default=40)
+    ap.add_argument("--no-score", action="store_true")
+    ap.add_argument("--hc", type=int, default=0,
+                    help="heads per CTA override (PC_DEBUG library only, PC_LIB_PATH=...debug.so)")
     a = ap.parse_args()
-    print(json.dumps(run(torch.device("cuda", 0), a.reqs, a.len, a.Hkv, a.D, a.block, a.evict_freq, a.reps)), flush=True)
+    if a.hc:
+        from vllm_paged_compression_b200._lib import load
+        import ctypes
+        fn = load().pc_debug_set_cache_write_block_heads
+        fn.argtypes = [ctypes.c_int32]
+        fn.restype = None
+        fn(a.hc)
+    r = run(torch.device("cuda", 0), a.reqs, a.len, a.Hkv, a.D, a.block, a.evict_freq, a.reps, score=not a.no_score)
+    if a.hc:
+        r["hc"] = a.hc
+    print(json.dumps(r), flush=True)
 
 
 if __name__ == "__main__":

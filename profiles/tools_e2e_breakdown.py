@@ -1,77 +1,83 @@
-"""Where the e2e step time goes: PCIe bandwidth of the box, host time of a step (cProfile),
-GPU time of a step.  usage (GPU box): python profiles/tools_e2e_breakdown.py"""
+"""Where does an e2e step (host-resident activations, bench.py `e2e`) spend its time?
+
+Per step of the timed window: wall clock of runner.step(), host time before the graph launch,
+device time of the replayed graph (events around the replay), host time after the launch call
+returns (bookkeeping + the wait for the device).  Run for several PinnedLayerIO copy schedules.
+    python profiles/tools_e2e_breakdown.py [--io-group 0,1,2,4] [--steps 24]
+"""
 import argparse
-import cProfile
+import json
 import os
-import pstats
+import statistics
 import sys
 import time
 
-import torch
-
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+import torch  # noqa: E402
+
 import bench  # noqa: E402
 
 
-def bw():
-    n = 24 << 20
-    h = torch.empty(n, dtype=torch.uint8).pin_memory()
-    d = torch.empty(n, dtype=torch.uint8, device="cuda")
-    for name, a, b in (("h2d", d, h), ("d2h", h, d)):
-        for _ in range(3):
-            a.copy_(b, non_blocking=True)
-        torch.cuda.synchronize()
+def one(io_group, K, W, extra):
+    sys.argv = ["bench.py", "--steps", str(K), "--warmup", str(W), "--io-group", str(io_group)] + extra
+    args = bench.parse_args()
+    device = torch.device("cuda", 0)
+    torch.cuda.set_device(device)
+    spec = bench.main_spec(args, 1)
+    P = bench.preroll_steps(spec, K, W, True)
+    arm = bench.Arm(spec, args, device, 0, 1, host_io=True, total_steps=P + W + K)
+    arm.prefill()
+    arm.make_runner(P + W + K)
+    runner = arm.runner
+    marks = {}
+    inner = runner._graph
+
+    class Wrapped:
+        def __init__(self, g):
+            self.g = g
+
+        def replay(self):
+            cur = torch.cuda.current_stream(device)
+            marks["t_launch"] = time.perf_counter()
+            marks["e0"] = torch.cuda.Event(enable_timing=True)
+            marks["e1"] = torch.cuda.Event(enable_timing=True)
+            marks["e0"].record(cur)
+            self.g.replay()
+            marks["e1"].record(cur)
+            marks["t_launched"] = time.perf_counter()
+
+    runner._graph = lambda trig: Wrapped(inner(trig))
+    for _ in range(P + W):
+        arm.step()
+    torch.cuda.synchronize()
+    rows = []
+    for _ in range(K):
         t0 = time.perf_counter()
-        for _ in range(10):
-            a.copy_(b, non_blocking=True)
-        torch.cuda.synchronize()
-        dt = (time.perf_counter() - t0) / 10
-        print(f"{name}: {n / dt / 1e9:.1f} GB/s ({dt * 1e6:.0f} us per {n >> 20} MiB)")
-    s2 = torch.cuda.Stream()
-    torch.cuda.synchronize()
-    t0 = time.perf_counter()
-    for _ in range(10):
-        d.copy_(h, non_blocking=True)
-        with torch.cuda.stream(s2):
-            h2 = getattr(bw, "h2", None)
-            if h2 is None:
-                bw.h2 = h2 = torch.empty(n, dtype=torch.uint8).pin_memory()
-                bw.d2 = torch.empty(n, dtype=torch.uint8, device="cuda")
-            h2.copy_(bw.d2, non_blocking=True)
-    torch.cuda.synchronize()
-    dt = (time.perf_counter() - t0) / 10
-    print(f"duplex: {n / dt / 1e9:.1f} GB/s each way")
+        n = arm.step()
+        t1 = time.perf_counter()
+        rows.append({"wall_us": (t1 - t0) * 1e6, "pre_us": (marks["t_launch"] - t0) * 1e6,
+                     "launch_call_us": (marks["t_launched"] - marks["t_launch"]) * 1e6,
+                     "graph_us": marks["e0"].elapsed_time(marks["e1"]) * 1e3,
+                     "post_us": (t1 - marks["t_launched"]) * 1e6, "trigger": n > 0})
+    plain = [r for r in rows if not r["trigger"]]
+    out = {"io_group": io_group, "io": arm.io.describe(), "steps": K,
+           "plain": {k: statistics.mean(r[k] for r in plain) for k in rows[0] if k != "trigger"},
+           "trigger": {k: statistics.mean(r[k] for r in rows if r["trigger"]) for k in rows[0] if k != "trigger"}
+           if any(r["trigger"] for r in rows) else None}
+    del arm, runner
+    torch.cuda.empty_cache()
+    return out
 
 
 def main():
-    bw()
-    sys.argv = [sys.argv[0]]
-    args = bench.parse_args()
-    dev = torch.device("cuda", 0)
-    for host_io in (False, True):
-        arm = bench.Arm(args, dev, 0, 1, host_io=host_io)
-        arm.prefill()
-        for _ in range(8):
-            arm.step()
-        torch.cuda.synchronize()
-        # host-only time: how long the Python side of a step takes when it never waits
-        t0 = time.perf_counter()
-        for _ in range(32):
-            arm.step()
-        t_host = (time.perf_counter() - t0) / 32
-        torch.cuda.synchronize()
-        t_all = (time.perf_counter() - t0) / 32
-        print(f"host_io={host_io}: python issue time {t_host * 1e3:.3f} ms/step, wall incl. drain {t_all * 1e3:.3f} ms/step")
-        pr = cProfile.Profile()
-        pr.enable()
-        for _ in range(16):
-            arm.step()
-        pr.disable()
-        torch.cuda.synchronize()
-        st = pstats.Stats(pr)
-        st.sort_stats("cumulative").print_stats(22)
-        del arm
-        torch.cuda.empty_cache()
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--io-group", default="0,1,2,4")
+    ap.add_argument("--steps", type=int, default=24)
+    ap.add_argument("--warmup", type=int, default=5)
+    a, extra = ap.parse_known_args()
+    for g in a.io_group.split(","):
+        print(json.dumps(one(int(g), a.steps, a.warmup, extra)), flush=True)
 
 
 if __name__ == "__main__":

@@ -129,11 +129,15 @@ def _prompt_batch(prompt_lens, pol, nb, rs):
     return tables, slots, meta, tile_off
 
 
-@pytest.mark.parametrize("D,bs", [(64, 16), (128, 16), (128, 32)])
+@pytest.mark.parametrize("D,bs,Hkv", [(64, 16, 4), (128, 16, 4), (128, 32, 4), (128, 16, 8), (128, 16, 1),
+                                      (128, 32, 8), (64, 32, 6), (128, 16, 3)])
 @pytest.mark.parametrize("mode", ["budget", "percentage"])
-def test_prune_prompt_and_cache(D, bs, mode):
+def test_prune_prompt_and_cache(D, bs, Hkv, mode):
+    """R1 + W1 + S3.  Hkv 8 / 4 / 6 / 3 / 1 walk the block kernel's heads-per-CTA variants
+    (8, 4, 2, 1); prompt lengths cover whole blocks, the partial last block (element-wise
+    path) and prompts shorter than a block."""
     ops = _ops()
-    Hkv, nb = 4, 256
+    nb = 256
     pol = Policy(block_size=bs, cache_prune_type=mode, cache_budget=8 * bs, evict_freq=2)
     prompt_lens = [5, bs, 8 * bs, 8 * bs + 1, 13 * bs + 5, 20 * bs]
     rs = np.random.RandomState(D + bs)

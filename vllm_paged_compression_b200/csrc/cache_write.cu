@@ -13,6 +13,8 @@
 // shared memory and emit the cache layout K [D/8][BS][8] / V [D][BS] with 16-byte
 // stores that are contiguous across lanes whenever the tile maps onto one block
 // (always true for prefill).  HBM-bound: N*Hkv*D*2 B read + the same written.
+#include <atomic>
+
 #include "pc_common.cuh"
 #include "score_common.cuh"
 #include "pc_api_internal.h"
@@ -141,6 +143,234 @@ __global__ void __launch_bounds__(128) cache_write_kernel(const CacheWriteParams
   }
 }
 
+// ------------------------------------------------------------------------------------------
+// Prompt-time fast path: one CTA = one cache BLOCK (BS kept tokens) x HC kv heads.
+//
+// In the cache a block is one contiguous run per pool: K [Hkv][D/8][BS][8], V [Hkv][D][BS].
+//   K needs no element transposition, only a permutation of 16-byte units ([tok][h][c] ->
+//     [h][c][tok]): a warp loads 8 tokens x 4 consecutive units (64 contiguous bytes per
+//     token row) and stores 4 x 128 contiguous bytes -- registers only, full sectors both ways.
+//   V is a real [tok][h*D] -> [h*D][tok] transposition: the BS token rows arrive by TMA 1-D bulk
+//     copies (one per gathered row: the streamingLLM prune is the row index) into a padded
+//     staging tile, ldmatrix.trans + stmatrix move 8x8 tiles into the block image, and ONE
+//     bulk store (cp.async.bulk shared -> global) writes the HC*D*BS*2 contiguous bytes.
+//   The prompt block score (S3) reads the staged V rows: zero extra HBM bytes.
+// Tiles that do not map onto one whole block in slot order (the last, partial tile of a prompt;
+// callers with arbitrary slot mappings) take an element-wise path in the same kernel.
+__device__ __forceinline__ void ldmatrix_x4_trans_(uint32_t (&r)[4], uint32_t addr) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+               : "r"(addr));
+}
+__device__ __forceinline__ void stmatrix_x4(uint32_t addr, const uint32_t (&r)[4]) {
+  asm volatile("stmatrix.sync.aligned.m8n8.x4.shared.b16 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(r[0]), "r"(r[1]),
+               "r"(r[2]), "r"(r[3])
+               : "memory");
+}
+__device__ __forceinline__ void bulk_store(void* gdst, const void* ssrc, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(smem_u32(ssrc)),
+               "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_commit_wait_read() {
+  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+  asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+}
+
+constexpr int kBlockThreads = 256;
+
+template <int D, int BS, int HC>
+struct BlockWriteSmem {
+  static constexpr int kRowBytes = HC * D * 2;            // one token's rows of the CTA's heads
+  static constexpr int kPitch = kRowBytes + 16;           // staging pitch: ldmatrix rows hit distinct banks
+  static constexpr int kStage = BS * kPitch;
+  static constexpr int kImage = HC * D * BS * 2;          // the V block image of these heads
+  static constexpr int kBytes = kStage + kImage + 64;
+};
+
+template <int D, int BS, int HC>
+__global__ void __launch_bounds__(kBlockThreads) cache_write_block_kernel(const CacheWriteParams p) {
+  using L = BlockWriteSmem<D, BS, HC>;
+  extern __shared__ __align__(128) uint8_t smem[];
+  uint8_t* vstage = smem;
+  uint8_t* vimage = smem + L::kStage;
+  uint64_t* bar = reinterpret_cast<uint64_t*>(smem + L::kStage + L::kImage);
+  constexpr int NW = kBlockThreads / 32;
+
+  const int tile = blockIdx.x;
+  const int h0 = blockIdx.y * HC;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+
+  // ---- which request: r = #{1 <= i < R : tile_offsets[i] <= tile}; every load independent, so
+  // the CTA pays one memory latency here instead of a dependent binary search
+  int r = 0;
+  for (int base = 1; base < p.num_reqs; base += kBlockThreads) {
+    const int i = base + tid;
+    r += __syncthreads_count(i < p.num_reqs && __ldg(p.tile_offsets + i) <= tile);
+  }
+  const int* m = p.req_meta + r * 5;
+  const int src_start = __ldg(m), kept = __ldg(m + 1), first = __ldg(m + 2), pruned = __ldg(m + 3),
+            dst_start = __ldg(m + 4);
+  const int j = tile - __ldg(p.tile_offsets + r);
+  const int ntok = min(BS, kept - j * BS);
+  if (ntok <= 0) return;
+  // source row of the tile's token tk: the streamingLLM prune is index arithmetic
+  auto src_row = [&](int tk) -> size_t {
+    const int jj = j * BS + tk;
+    return (size_t)src_start + (size_t)(jj < first ? jj : jj + pruned);
+  };
+
+  // ---- V rows leave for shared memory as soon as the request is known (no slot needed)
+  if (warp == 0) {
+    if (lane == 0) {
+      mbar_init(bar, 1);
+      mbar_fence_init();
+      mbar_expect_tx(bar, ntok * L::kRowBytes);
+    }
+    __syncwarp();
+    if (lane < ntok)
+      tma_load_1d(vstage + lane * L::kPitch, p.value + src_row(lane) * p.value_stride + (size_t)h0 * D,
+                  L::kRowBytes, bar);
+  }
+
+  // ---- K: unit (tok, u) -> (u, tok), u = 16-byte unit inside the CTA's heads' row.  One warp
+  // instruction = 8 tokens x 4 units: 64 contiguous bytes per token row in, 4 x 128 contiguous
+  // bytes out.  The first batch of loads is in flight before the slots are known.
+  constexpr int U = L::kRowBytes / 16;          // units per token row
+  constexpr int TH = BS / 8;                    // 8-token groups
+  constexpr int GROUPS = TH * (U / 4);
+  constexpr int KB = 8;                         // loads in flight per thread
+  const int tok_lo = lane & 7, q4 = lane >> 3;
+  uint4 kreg[KB];
+  auto k_load = [&](int g0) {
+#pragma unroll
+    for (int i = 0; i < KB; ++i) {
+      const int gi = g0 + i * NW + warp;
+      if (gi < GROUPS) {
+        const int tok = (gi % TH) * 8 + tok_lo, u = (gi / TH) * 4 + q4;
+        if (tok < ntok)
+          kreg[i] = __ldg(reinterpret_cast<const uint4*>(p.key + src_row(tok) * p.key_stride + (size_t)h0 * D) + u);
+      }
+    }
+  };
+  k_load(0);
+
+  // ---- slots: the tile must be one whole block, in order
+  const long long slot0 = p.slot_mapping[dst_start + j * BS];
+  bool ok = (ntok == BS) && slot0 >= 0 && (slot0 % BS == 0);
+  if (tid < ntok) ok = ok && (p.slot_mapping[dst_start + j * BS + tid] == slot0 + tid);
+  const bool whole = __syncthreads_and(ok) != 0;   // also publishes the mbarrier init
+
+  if (!whole) {
+    // element-wise path (csrc/cache_kernels.cu:152-205 semantics; slot < 0 = skip)
+    mbar_wait(bar, 0);                             // the staged rows must land before the CTA exits
+    for (int i = tid; i < ntok * HC * D; i += kBlockThreads) {
+      const int tl = i / (HC * D), e = i - tl * (HC * D);
+      const int h = e / D, d = e - h * D;
+      const long long slot = p.slot_mapping[dst_start + j * BS + tl];
+      if (slot < 0) continue;
+      const long long blk = slot / BS;
+      const int off = (int)(slot - blk * BS);
+      const size_t base = (size_t)blk * p.kv_block_stride + (size_t)(h0 + h) * (D * BS);
+      p.k_cache[base + (size_t)((d >> 3) * BS + off) * 8 + (d & 7)] =
+          p.key[src_row(tl) * p.key_stride + (size_t)(h0 + h) * D + d];
+      p.v_cache[base + (size_t)d * BS + off] = p.value[src_row(tl) * p.value_stride + (size_t)(h0 + h) * D + d];
+    }
+    return;
+  }
+
+  const long long blk = slot0 / BS;
+  const size_t gbase = (size_t)blk * p.kv_block_stride + (size_t)h0 * (D * BS);
+  {
+    uint4* kdst = reinterpret_cast<uint4*>(p.k_cache + gbase);
+    for (int g0 = 0; g0 < GROUPS; g0 += KB * NW) {
+      if (g0 > 0) k_load(g0);
+#pragma unroll
+      for (int i = 0; i < KB; ++i) {
+        const int gi = g0 + i * NW + warp;
+        if (gi < GROUPS) {
+          const int tok = (gi % TH) * 8 + tok_lo, u = (gi / TH) * 4 + q4;
+          kdst[u * BS + tok] = kreg[i];
+        }
+      }
+    }
+  }
+
+  // ---- V: staged rows -> transposed block image
+  mbar_wait(bar, 0);
+  {
+    constexpr int TQ = BS / 8;                    // 8-token groups per block
+    constexpr int EG = 4 / TQ;                    // 8-element groups per ldmatrix.x4
+    constexpr int OPS = HC * D / (8 * EG);
+    const int mj = lane >> 3, rr = lane & 7;      // this lane addresses row rr of matrix mj
+    const int tg = mj % TQ, eg = mj / TQ;
+    const uint32_t s_stage = smem_u32(vstage), s_image = smem_u32(vimage);
+    for (int op = warp; op < OPS; op += NW) {
+      const int e0 = op * 8 * EG;
+      uint32_t frag[4];
+      // source tile mj: tokens 8 tg .. +7, elements e0 + 8 eg .. +7 (row = token)
+      ldmatrix_x4_trans_(frag, s_stage + (uint32_t)((tg * 8 + rr) * L::kPitch + (e0 + 8 * eg) * 2));
+      // transposed tile mj: rows = elements e0 + 8 eg + rr, 8 tokens (16 bytes) at token group tg
+      stmatrix_x4(s_image + (uint32_t)((e0 + 8 * eg + rr) * (BS * 2) + tg * 16), frag);
+    }
+  }
+  fence_proxy_async();   // the image was written through the generic proxy
+  __syncthreads();
+  if (tid == 0) bulk_store(p.v_cache + gbase, vimage, L::kImage);
+  // ---- prompt block score per kv head, fixed fp32 order (one warp per head), while the store drains
+  if (p.score.n_pools > 0) {
+    for (int h = warp; h < HC; h += NW) {
+      const float sc = warp_value_l2_head_score<D, BS>([&](int tok, int d) {
+        return __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(vstage + tok * L::kPitch + (h * D + d) * 2));
+      });
+      if (lane == 0) score_store(p.score, blk, h0 + h, sc);
+    }
+  }
+  if (tid == 0) bulk_commit_wait_read();
+}
+
+template <int D, int BS, int HC>
+static int launch_block_write(const CacheWriteParams& p, int tiles, cudaStream_t stream) {
+  using L = BlockWriteSmem<D, BS, HC>;
+  auto kern = cache_write_block_kernel<D, BS, HC>;
+  static std::atomic<int> opted[64];
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 0 || dev >= 64 || !opted[dev].load(std::memory_order_acquire)) {
+    const cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kBytes);
+    if (e != cudaSuccess) return set_cuda_error("cudaFuncSetAttribute(cache_write_block)", e);
+    if (dev >= 0 && dev < 64) opted[dev].store(1, std::memory_order_release);
+  }
+  dim3 grid(tiles, p.Hkv / HC);
+  kern<<<grid, kBlockThreads, L::kBytes, stream>>>(p);
+  return check_launch("cache_write_block_kernel");
+}
+
+#ifdef PC_DEBUG
+static int g_force_block_hc = 0;   // heads per CTA override (sweeps)
+void set_cache_write_block_heads(int hc) { g_force_block_hc = hc; }
+#endif
+
+// heads per CTA of the block kernel: as many as keep staging + image under ~75 KB (3 CTAs / SM)
+template <int D, int BS>
+static int dispatch_block_write(const CacheWriteParams& p, int tiles, cudaStream_t stream) {
+  constexpr int kMaxHC = (D * BS <= 2048) ? 8 : (D * BS <= 4096 ? 4 : 2);   // D*BS*2*2 bytes per head
+#ifdef PC_DEBUG
+  if (g_force_block_hc > 0 && p.Hkv % g_force_block_hc == 0) {
+    switch (g_force_block_hc) {
+      case 1: return launch_block_write<D, BS, 1>(p, tiles, stream);
+      case 2: return launch_block_write<D, BS, 2>(p, tiles, stream);
+      case 4: if (kMaxHC >= 4) return launch_block_write<D, BS, (kMaxHC >= 4 ? 4 : 1)>(p, tiles, stream); break;
+      case 8: if (kMaxHC >= 8) return launch_block_write<D, BS, (kMaxHC >= 8 ? 8 : 1)>(p, tiles, stream); break;
+    }
+  }
+#endif
+  if (kMaxHC >= 8 && p.Hkv % 8 == 0) return launch_block_write<D, BS, (kMaxHC >= 8 ? 8 : kMaxHC)>(p, tiles, stream);
+  if (kMaxHC >= 4 && p.Hkv % 4 == 0) return launch_block_write<D, BS, (kMaxHC >= 4 ? 4 : kMaxHC)>(p, tiles, stream);
+  if (p.Hkv % 2 == 0) return launch_block_write<D, BS, 2>(p, tiles, stream);
+  return launch_block_write<D, BS, 1>(p, tiles, stream);
+}
+
 template <int D, int BS>
 static int launch_cache_write(const CacheWriteParams& p, int tiles, cudaStream_t stream) {
   dim3 grid(tiles, p.Hkv);
@@ -171,6 +401,14 @@ int cache_write(const CacheWriteArgs& a, cudaStream_t stream) {
   p.score = a.score;
   const int tiles = a.req_meta ? a.total_tiles : (a.num_tokens + a.BS - 1) / a.BS;
   if (tiles <= 0) return 0;
+  if (a.req_meta != nullptr) {   // prompt-time: whole blocks, the block kernel
+    if (a.D == 128 && a.BS == 16) return dispatch_block_write<128, 16>(p, tiles, stream);
+    if (a.D == 128 && a.BS == 32) return dispatch_block_write<128, 32>(p, tiles, stream);
+    if (a.D == 64 && a.BS == 16) return dispatch_block_write<64, 16>(p, tiles, stream);
+    if (a.D == 64 && a.BS == 32) return dispatch_block_write<64, 32>(p, tiles, stream);
+    return set_error(PC_ERR_UNSUPPORTED,
+                     "Unsupported head size / block size (supported: head 64|128, block 16|32)");
+  }
   if (a.D == 128 && a.BS == 16) return launch_cache_write<128, 16>(p, tiles, stream);
   if (a.D == 128 && a.BS == 32) return launch_cache_write<128, 32>(p, tiles, stream);
   if (a.D == 64 && a.BS == 16) return launch_cache_write<64, 16>(p, tiles, stream);

@@ -129,6 +129,7 @@ int prefill_attn(const PrefillArgs& a, cudaStream_t stream);     // tcgen05/TMEM
 #ifdef PC_DEBUG
 void set_prefill_tc_persistent(int v);  // 1 = persistent CTAs, 0 = one CTA per query tile, -1 = rule
 void set_prefill_tc_tile(int tn);       // kv tile width of the tcgen05 kernel (64 | 128)
+void set_cache_write_block_heads(int hc);  // heads per CTA of cache_write_block_kernel, 0 = rule
 #endif
 
 int copy_blocks(void* k_cache, void* v_cache, const long long* pairs, int num_pairs,
