@@ -161,6 +161,9 @@ def parse_args():
                     help="N > 1: how per-head block scores reach the other ranks (parallel.py)")
     ap.add_argument("--io-group", type=int, default=0,
                     help="e2e leg: layers per host<->device copy group (PinnedLayerIO); 0 = default schedule")
+    ap.add_argument("--no-io-prefetch", action="store_true",
+                    help="e2e leg: upload a step's inputs inside that step (layer groups) instead of one "
+                         "copy a step ahead")
     ap.add_argument("--no-numa-bind", action="store_true",
                     help="do not bind the rank to the NUMA node of its GPU before allocating pinned memory")
     ap.add_argument("--tp-emulate", type=int, default=1,
@@ -312,7 +315,10 @@ class Arm:
         if host_io:
             from vllm_paged_compression_b200.engine import PinnedLayerIO
             # fused [B, (Hq + 2 Hkv) D] rows per layer in pinned host memory (what qkv_proj emits)
-            self.io = PinnedLayerIO(self.L, self.B, self.Hq, self.Hkv, self.D, device, group=args.io_group)
+            # runner path: the step's inputs are uploaded as ONE copy, one step ahead (the next
+            # step's activations land while this step computes)
+            self.io = PinnedLayerIO(self.L, self.B, self.Hq, self.Hkv, self.D, device, group=args.io_group,
+                                    prefetch=not (args.no_io_prefetch or args.no_graph))
             for l in range(self.L):
                 self.io.qkv_host[l].copy_(torch.cat([self.q[l], self.k[l], self.v[l]], dim=1).cpu())
             self.h2d, self.d2h = self.io.h2d_bytes, self.io.d2h_bytes

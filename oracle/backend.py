@@ -36,7 +36,8 @@ from .policy import Policy
 
 class OracleLayer:
     def __init__(self, num_heads: int, head_size: int, scale: float, num_kv_heads: int,
-                 pol: Optional[Policy], head_compat_uncompacted: bool = False, native_ops=None):
+                 pol: Optional[Policy], head_compat_uncompacted: bool = False, native_ops=None,
+                 rng=None):
         """native_ops: object providing reshape_and_cache / paged_attention with the
         signatures of oracle/paged_ops.py (default: that torch restatement;
         oracle/ref_cpu.RefCpuOps = the reference's own compiled CPU kernels)."""
@@ -44,6 +45,9 @@ class OracleLayer:
         self.pol = pol
         self.ops = native_ops if native_ops is not None else paged_ops
         self.compat = head_compat_uncompacted
+        # HEAD's process-wide `random` (torch_cuda_sdpa.py:796): ONE random.Random(1234) shared by
+        # every layer of the model, drawn from in layer order, rows in row order
+        self.rng = rng
         # physical block id -> per-head partial scores [Hkv] fp32 (D3)
         self.block_scores: Dict[int, np.ndarray] = {}
         self.last = {}
@@ -102,24 +106,35 @@ class OracleLayer:
         rmv: Dict[int, Tuple[str, int]] = {}
         attn_tables: List[List[int]] = []
         slots = []
+        zero_slots = []
+        stream_like = p.decode_evict_method in ("streamingLLM", "streamingLLM-1")
         for r in range(B):
             tab = list(block_tables[r])
             n = len(tab)
             slots.append(policy.decode_slot_mapping(tab, seq_lens[r] - 1, bs))
+            zs = policy.zero_slot(self.rng, seq_lens[r], tab, p)          # W2
+            if zs is not None:
+                zero_slots.append(zs)
             if policy.decode_trigger(seq_lens[r], n * bs, p):
                 lo, hi = policy.victim_candidates(n, p)
-                if p.decode_evict_method == "streamingLLM":
+                if stream_like:
                     idx = 1
+                elif p.decode_evict_method == "random":
+                    idx = policy.random_victim(self.rng, n, p)
                 else:
                     sc = scoring.combine_heads(np.stack([self.block_scores[int(t)] for t in tab[:n - 1]]))
                     idx = policy.argmin_lowest_index(sc, lo, hi)
                 rmv[r] = (req_ids[r], idx)
-                if not (self.compat and p.decode_evict_method == "streamingLLM"):
+                if not (self.compat and stream_like):
                     del tab[idx]
             attn_tables.append(tab)
         k = key.view(-1, self.Hkv, self.D)
         v = value.view(-1, self.Hkv, self.D)
-        self.ops.reshape_and_cache(k, v, kc, vc, torch.tensor(slots, dtype=torch.long))
+        if zero_slots:     # torch_cuda_sdpa.py:919-933: zero rows appended to the step's K/V
+            z = torch.zeros(len(zero_slots), self.Hkv, self.D, dtype=k.dtype)
+            k = torch.cat([k, z])
+            v = torch.cat([v, z])
+        self.ops.reshape_and_cache(k, v, kc, vc, torch.tensor(slots + zero_slots, dtype=torch.long))
         out = self.ops.paged_attention(query.view(-1, self.Hq, self.D), kc, vc,
                                         attn_tables, list(kv_lens), self.scale)
         for r in range(B):                                                # D2
@@ -127,7 +142,7 @@ class OracleLayer:
                 last_blk = block_tables[r][-1]
                 vb = paged_ops.depage_v_block(vc, last_blk).float().numpy()
                 self.block_scores[int(last_blk)] = scoring.per_head_block_score(vb)
-        self.last = {"slots": slots}
+        self.last = {"slots": slots, "zero_slots": zero_slots}
         return out.view(-1, self.Hq * self.D), rmv, attn_tables
 
     def scores_of(self, table: Sequence[int], n_full: int) -> np.ndarray:

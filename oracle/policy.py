@@ -27,7 +27,9 @@ class Policy:
     initial_blocks: int = 1
     num_block_merge: int = 2                  # percentage mode only
     prompt_evict_method: str = "streamingLLM"
-    decode_evict_method: str = "value_l2"     # "streamingLLM" | "value_l2"
+    # "streamingLLM" | "value_l2" | "random" (HEAD as shipped for local/global)
+    # | "streamingLLM-1" | "inverse_key_l2" (slot-zeroing variants, W2)
+    decode_evict_method: str = "value_l2"
     topk_blocks: int = -1                     # -1 = global, >1 = local window
     disable_evict_prefill: bool = False
 
@@ -116,6 +118,8 @@ def decode_trigger(seq_len: int, kv_len_before: int, p: Policy) -> bool:
     percentage: torch_cuda_sdpa.py:1310 (commented) + page_evict_kv_util_bak.py:69
     """
     bs = p.block_size
+    if p.decode_evict_method == "inverse_key_l2":        # model_runner.py:545-547: never frees
+        return False
     if p.cache_prune_type == "budget":
         return seq_len > p.cache_budget and seq_len % bs == 0
     return (seq_len % (bs * p.evict_freq) == 0
@@ -133,11 +137,41 @@ def victim_candidates(n_blocks_before: int, p: Policy) -> Tuple[int, int]:
     """[lo, hi) table indices eligible for eviction (torch_cuda_sdpa.py:1404-1405,
     1528-1534): streamingLLM -> {1}; global -> [1, n-1); local -> [1, 1+topk)
     (clamped to n-1: the just-filled last block is never a candidate)."""
-    if p.decode_evict_method == "streamingLLM":
+    if p.decode_evict_method in ("streamingLLM", "streamingLLM-1"):
         return 1, 2
     if p.topk_blocks is None or p.topk_blocks < 0:
         return 1, n_blocks_before - 1
     return 1, min(1 + p.topk_blocks, n_blocks_before - 1)
+
+
+def random_victim(rng, n_blocks_before: int, p: Policy) -> int:
+    """HEAD as shipped (`enable_random_evict = True`, torch_cuda_sdpa.py:802): one
+    `random.randint` per triggered row from the process-wide Python RNG every layer re-seeds
+    with 1234 in its constructor (:796); window :1504-1513 -- local [1, topk] (NOT clamped
+    to the table), global [1, n-2]."""
+    if p.topk_blocks is not None and p.topk_blocks > 0:
+        return rng.randint(1, 1 + p.topk_blocks - 1)
+    return rng.randint(1, n_blocks_before - 1 - 1)
+
+
+def zero_slot(rng, seq_len: int, table: Sequence[int], p: Policy) -> Optional[int]:
+    """W2: the cache slot whose K and V rows are overwritten with zeros on this step, or None.
+    streamingLLM-1 (torch_cuda_sdpa.py:1390-1401): over budget, not a block boundary ->
+      slot (seq_len % bs - 1) of the table's 2nd block (the next victim is zeroed token by token).
+    inverse_key_l2 (:1444-1454): over budget -> a random slot of a random middle block, two
+      randint draws per row (block first)."""
+    bs = p.block_size
+    if seq_len <= p.cache_budget:
+        return None
+    if p.decode_evict_method == "streamingLLM-1":
+        if seq_len % bs == 0:
+            return None
+        return table[1] * bs + (seq_len % bs - 1)
+    if p.decode_evict_method == "inverse_key_l2":
+        blk = rng.randint(1, len(table) - 2)
+        off = rng.randint(0, bs - 1)
+        return table[blk] * bs + off
+    return None
 
 
 def argmin_lowest_index(scores: np.ndarray, lo: int, hi: int) -> int:

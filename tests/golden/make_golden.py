@@ -86,6 +86,7 @@ CAPTURE = {}
 
 def _write_to_paged_cache(key, value, key_cache, value_cache, slot_mapping,
                           kv_cache_dtype, k_scale, v_scale):
+    CAPTURE["write_slots"] = slot_mapping.flatten().tolist()
     ref_cpu.reshape_and_cache(key.contiguous(), value.contiguous(), key_cache,
                               value_cache, slot_mapping.flatten().contiguous())
 
@@ -325,15 +326,22 @@ def ops_kats():
 
 # ------------------------------------------------------------------ forward() traces
 def drive_forward(mod, method, budget, bs, Hq, Hkv, D, prompt_lens, steps, seed,
-                  disable_evict_prefill=False, random_evict=False, record_scores=False):
+                  disable_evict_prefill=False, random_evict=False, record_scores=False,
+                  layers=1, topk=3):
     """Mini engine loop around the reference impl: reference BlockTable for the host
     bookkeeping, reference builder logic for slot mapping / kv-len adjust, reference
     forward() for the layer.  One layer (layer 0 is the only one the host listens to)."""
-    impl, pe, cc = make_impl(mod, method, budget, bs, Hq, Hkv, D,
-                             disable_evict_prefill=disable_evict_prefill,
-                             random_evict=random_evict)
+    # `layers` attention layers share the process-wide `random` exactly like the layers of a
+    # model (every constructor re-seeds it with 1234, torch_cuda_sdpa.py:796); the host only
+    # listens to layer 0 (model_runner.py:1797-1802)
+    impls = []
+    for _ in range(layers):
+        impl, pe, cc = make_impl(mod, method, budget, bs, Hq, Hkv, D, topk=topk,
+                                 disable_evict_prefill=disable_evict_prefill,
+                                 random_evict=random_evict)
+        impls.append(impl)
     nblocks = 256
-    kv_cache = torch.zeros(2, nblocks, bs * Hkv * D, dtype=torch.bfloat16)
+    kv_caches = [torch.zeros(2, nblocks, bs * Hkv * D, dtype=torch.bfloat16) for _ in range(layers)]
     alloc = CpuGpuBlockAllocator.create("naive", nblocks, 0, bs)
     fake = types.SimpleNamespace(sliding_window=None)
     B = len(prompt_lens)
@@ -346,7 +354,8 @@ def drive_forward(mod, method, budget, bs, Hq, Hkv, D, prompt_lens, steps, seed,
         toks.append(t)
     trace = {"cfg": dict(method=method, budget=budget, bs=bs, Hq=Hq, Hkv=Hkv, D=D,
                          prompt_lens=prompt_lens, steps=steps, seed=seed,
-                         disable_evict_prefill=disable_evict_prefill, module=mod.__name__),
+                         disable_evict_prefill=disable_evict_prefill, module=mod.__name__,
+                         random_evict=random_evict, layers=layers, topk=topk),
              "steps": []}
     arrays = {}
 
@@ -363,50 +372,57 @@ def drive_forward(mod, method, budget, bs, Hq, Hkv, D, prompt_lens, steps, seed,
         else:
             n_tok = B
             for i in range(B):
-                if seq_lens[i] > budget and seq_lens[i] % bs == 0:   # model_runner.py:540-543
-                    kv_lens[i] -= bs
+                if method != "inverse_key_l2" and seq_lens[i] > budget and seq_lens[i] % bs == 0:
+                    kv_lens[i] -= bs                                  # model_runner.py:540-547
                 HEAD.TorchCUDASDPAMetadataBuilder._compute_slot_mapping(
                     fake, False, False, slot, i, 1, seq_lens[i] - 1, bs, tabs[f"r{i}"])
-        q = (rnd(seed * 1000 + step * 3 + 0, n_tok, Hq * D).float() * 0.5).to(torch.bfloat16)
-        k = (rnd(seed * 1000 + step * 3 + 1, n_tok, Hkv * D).float() * 0.5).to(torch.bfloat16)
-        v = rnd(seed * 1000 + step * 3 + 2, n_tok, Hkv * D)
         from vllm.utils import make_tensor_with_pad
         block_tables = make_tensor_with_pad(
             [[] if is_prompt else tabs[f"r{i}"][i] for i in range(B)], pad=0, dtype=torch.int)
-        md = mod.TorchCUDASDPAMetadata(
-            num_prefills=B if is_prompt else 0,
-            num_prefill_tokens=n_tok if is_prompt else 0,
-            num_decode_tokens=0 if is_prompt else B,
-            slot_mapping=torch.tensor(slot, dtype=torch.long),
-            multi_modal_placeholder_index_maps=None,
-            seq_lens_tensor=torch.tensor(seq_lens, dtype=torch.int),
-            max_prefill_seq_len=max(seq_lens) if is_prompt else 0,
-            max_decode_seq_len=0 if is_prompt else max(seq_lens),
-            use_cuda_graph=False,
-            seq_lens=seq_lens,
-            seq_start_loc=None, context_lens_tensor=None,
-            max_query_len=max(seq_lens) if is_prompt else 1,
-            max_decode_query_len=1, query_start_loc=None,
-            block_tables=block_tables,
-            seq_kv_lens=kv_lens,
-            seq_kv_lens_tensor=torch.tensor(kv_lens, dtype=torch.int),
-            reqid_mapping_blocktables=tabs)
-        CAPTURE.clear()
-        out = impl.forward(q, k, v, kv_cache, md)
-        rmv = impl.get_rmv_block_idx()
         rec = {"is_prompt": is_prompt, "seq_lens": seq_lens, "kv_lens": kv_lens,
-               "tables": [tabs[f"r{i}"][i] for i in range(B)], "slots": slot,
-               "rmv": {str(kk): [vv[0], int(vv[1])] for kk, vv in rmv.items()}}
-        if "decode_block_tables" in CAPTURE:
-            rec["attn_tables"] = CAPTURE["decode_block_tables"].tolist()
-            rec["attn_kv_lens"] = CAPTURE["decode_kv_lens"].tolist()
-        if record_scores:
-            rec["l2norms"] = {rid: [float(x) for x in d[int(rid[1:])]]
-                              for rid, d in impl.block_l2norm_mgr.reqid_mapping_block_l2norms.items()}
-        arrays[f"out_{step}"] = out.float().numpy()
+               "tables": [tabs[f"r{i}"][i] for i in range(B)], "slots": slot}
+        for li, impl in enumerate(impls):
+            sd = seed * 1000 + step * 3 + li * 500000        # layer 0 keeps the round-1 streams
+            q = (rnd(sd + 0, n_tok, Hq * D).float() * 0.5).to(torch.bfloat16)
+            k = (rnd(sd + 1, n_tok, Hkv * D).float() * 0.5).to(torch.bfloat16)
+            v = rnd(sd + 2, n_tok, Hkv * D)
+            md = mod.TorchCUDASDPAMetadata(
+                num_prefills=B if is_prompt else 0,
+                num_prefill_tokens=n_tok if is_prompt else 0,
+                num_decode_tokens=0 if is_prompt else B,
+                slot_mapping=torch.tensor(slot, dtype=torch.long),
+                multi_modal_placeholder_index_maps=None,
+                seq_lens_tensor=torch.tensor(seq_lens, dtype=torch.int),
+                max_prefill_seq_len=max(seq_lens) if is_prompt else 0,
+                max_decode_seq_len=0 if is_prompt else max(seq_lens),
+                use_cuda_graph=False,
+                seq_lens=seq_lens,
+                seq_start_loc=None, context_lens_tensor=None,
+                max_query_len=max(seq_lens) if is_prompt else 1,
+                max_decode_query_len=1, query_start_loc=None,
+                block_tables=block_tables,
+                seq_kv_lens=kv_lens,
+                seq_kv_lens_tensor=torch.tensor(kv_lens, dtype=torch.int),
+                reqid_mapping_blocktables=tabs)
+            CAPTURE.clear()
+            out = impl.forward(q, k, v, kv_caches[li], md)
+            rmv = impl.get_rmv_block_idx()
+            sfx = "" if li == 0 else f"_l{li}"
+            rec["rmv" + sfx] = {str(kk): [vv[0], int(vv[1])] for kk, vv in rmv.items()}
+            if "decode_block_tables" in CAPTURE:
+                rec["attn_tables" + sfx] = CAPTURE["decode_block_tables"].tolist()
+                rec["attn_kv_lens" + sfx] = CAPTURE["decode_kv_lens"].tolist()
+            if "write_slots" in CAPTURE and not is_prompt:
+                rec["write_slots" + sfx] = CAPTURE["write_slots"]
+            if record_scores and li == 0:
+                rec["l2norms"] = {rid: [float(x) for x in d[int(rid[1:])]]
+                                  for rid, d in impl.block_l2norm_mgr.reqid_mapping_block_l2norms.items()}
+            arrays[f"out_{step}" + sfx] = out.float().numpy()
+            if li == 0:
+                rmv0 = dict(rmv)
         trace["steps"].append(rec)
         # engine feedback (llm_engine.py:1179-1193 -> scheduler.py:1879-1890)
-        for row, (rid, idx) in rmv.items():
+        for row, (rid, idx) in rmv0.items():
             bts[int(rid[1:])].free_prunned_blocks(idx)
 
     run(True, 0)
@@ -415,7 +431,9 @@ def drive_forward(mod, method, budget, bs, Hq, Hkv, D, prompt_lens, steps, seed,
             toks[i].append(len(toks[i]))
             bts[i].append_token_ids([toks[i][-1]])
         run(False, s)
-    arrays["kv_cache_final"] = kv_cache.view(torch.int16).numpy().copy()
+    arrays["kv_cache_final"] = kv_caches[0].view(torch.int16).numpy().copy()
+    for li in range(1, layers):
+        arrays[f"kv_cache_final_l{li}"] = kv_caches[li].view(torch.int16).numpy().copy()
     return trace, arrays
 
 
@@ -437,6 +455,29 @@ def main():
     }
     for name, (mod, m, bud, bs, Hq, Hkv, D, pl, st, seed, dep) in runs.items():
         tr, ar = drive_forward(mod, m, bud, bs, Hq, Hkv, D, pl, st, seed, disable_evict_prefill=dep)
+        traces[name] = tr
+        for k, v in ar.items():
+            arrs[f"{name}__{k}"] = v.astype(np.float16) if v.dtype == np.float32 else v
+    # HEAD's remaining --evict-method choices, as shipped: random block
+    # eviction for local / global (enable_random_evict = True), slot zeroing for streamingLLM-1
+    # and inverse_key_l2.  Prompts of the local / global / inverse_key_l2 runs stay within the
+    # budget, so the token-level prompt scoring (f3) is not part of these traces.  Multi-row runs
+    # use the v1 module (HEAD's compaction loses the last block of rows >= 1).
+    runs2 = {
+        "head_global_random_b1_l2": dict(mod=HEAD, method="global", prompt_lens=[120], steps=70, seed=5,
+                                         random_evict=True, layers=2),
+        "v1_global_random_b3_l2": dict(mod=V1, method="global", prompt_lens=[120, 100, 127], steps=70, seed=6,
+                                       random_evict=True, layers=2),
+        "v1_local_random_b3": dict(mod=V1, method="local", prompt_lens=[125, 128, 90], steps=70, seed=7,
+                                   random_evict=True, topk=3),
+        "head_stream1_b1": dict(mod=HEAD, method="streamingLLM-1", prompt_lens=[200], steps=40, seed=8),
+        "v1_stream1_b3": dict(mod=V1, method="streamingLLM-1", prompt_lens=[200, 131, 100], steps=60, seed=9),
+        "v1_invkey_b2_l2": dict(mod=V1, method="inverse_key_l2", prompt_lens=[120, 90], steps=60, seed=10,
+                                layers=2),
+    }
+    for name, kw in runs2.items():
+        tr, ar = drive_forward(kw.pop("mod"), kw.pop("method"), 128, 16, 8, 2, 64, kw.pop("prompt_lens"),
+                               kw.pop("steps"), kw.pop("seed"), **kw)
         traces[name] = tr
         for k, v in ar.items():
             arrs[f"{name}__{k}"] = v.astype(np.float16) if v.dtype == np.float32 else v

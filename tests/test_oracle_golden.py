@@ -8,7 +8,7 @@ import torch
 from oracle import paged_ops, policy, scoring
 from oracle.backend import OracleLayer
 from oracle.policy import Policy
-from tests.util import load_json, load_npz, rnd, step_inputs
+from tests.util import HEAD_POLICY_TRACES, trace_decode_method, load_json, load_npz, rnd, step_inputs
 
 POL = load_json("ref_policy.json")
 
@@ -157,6 +157,73 @@ def test_forward_trace_streaming(name):
         ref = arr[f"{name}__out_{step}"].astype(np.float32)
         np.testing.assert_allclose(out.float().numpy(), ref, atol=2e-2, rtol=0)
     assert np.array_equal(kv.view(torch.int16).numpy(), arr[f"{name}__kv_cache_final"])
+
+
+@pytest.mark.parametrize("name", HEAD_POLICY_TRACES)
+def test_forward_trace_head_policies(name):
+    """HEAD's other --evict-method choices as shipped: random block eviction for local / global
+    (host RNG replay: ONE random.Random(1234) shared by the layers, drawn in layer order, rows in
+    row order), streamingLLM-1 and inverse_key_l2 slot zeroing.  Victims of every layer, every
+    slot written (step tokens + zeroed slots), tables handed to attention: exact."""
+    import random
+    tr = load_json("ref_forward.json")[name]
+    arr = load_npz("ref_forward.npz")
+    c = tr["cfg"]
+    method, topk = trace_decode_method(c)
+    p = Policy(block_size=c["bs"], cache_budget=c["budget"], decode_evict_method=method, topk_blocks=topk)
+    L = c.get("layers", 1)
+    rng = random.Random(1234)
+    layers = [OracleLayer(c["Hq"], c["D"], c["D"] ** -0.5, c["Hkv"], p, head_compat_uncompacted=True, rng=rng)
+              for _ in range(L)]
+    kvs = [torch.zeros(2, 256, c["bs"] * c["Hkv"] * c["D"], dtype=torch.bfloat16) for _ in range(L)]
+    B = len(c["prompt_lens"])
+    rids = [f"r{i}" for i in range(B)]
+    n_evict = n_zero = 0
+    for step, rec in enumerate(tr["steps"]):
+        n_tok = sum(rec["seq_lens"]) if rec["is_prompt"] else B
+        for li, layer in enumerate(layers):
+            sfx = "" if li == 0 else f"_l{li}"
+            q, k, v = step_inputs(c["seed"], step, n_tok, c["Hq"], c["Hkv"], c["D"], layer=li)
+            if rec["is_prompt"]:
+                out = layer.prefill(q, k, v, kvs[li], rec["seq_lens"], rec["tables"], rids)
+                assert layer.last["kept"] == rec["kv_lens"]
+            else:
+                out, rmv, attn_tables = layer.decode(q, k, v, kvs[li], rec["seq_lens"], rec["kv_lens"],
+                                                     rec["tables"], rids)
+                assert {str(r): [rid, idx] for r, (rid, idx) in rmv.items()} == rec["rmv" + sfx], (step, li)
+                assert layer.last["slots"] + layer.last["zero_slots"] == rec["write_slots" + sfx], (step, li)
+                n_evict += len(rmv)
+                n_zero += len(layer.last["zero_slots"])
+                for r in range(B):
+                    n = len(attn_tables[r])
+                    assert rec["attn_tables" + sfx][r][:n] == attn_tables[r]
+            ref = arr[f"{name}__out_{step}{sfx}"].astype(np.float32)
+            np.testing.assert_allclose(out.float().numpy(), ref, atol=2e-2, rtol=0)
+    for li in range(L):
+        sfx = "" if li == 0 else f"_l{li}"
+        assert np.array_equal(kvs[li].view(torch.int16).numpy(), arr[f"{name}__kv_cache_final{sfx}"])
+    if method == "inverse_key_l2":
+        assert n_evict == 0 and n_zero > 0
+    else:
+        assert n_evict > 0 and (n_zero > 0) == (method == "streamingLLM-1")
+
+
+def test_head_l2_branch_argmin_bookkeeping():
+    """`head_global_b1_quirks`: HEAD with enable_random_evict = False.  Its block scores carry
+    the reference's layout / dtype quirks and are not reproduced; what IS pinned is
+    the selection over them -- strict `<` scan of [1, n-1), lowest index wins
+    (torch_cuda_sdpa.py:1528-1541) -- on the score lists the reference recorded."""
+    tr = load_json("ref_forward.json")["head_global_b1_quirks"]
+    p = Policy(block_size=16, cache_budget=128, decode_evict_method="value_l2", topk_blocks=-1)
+    n = 0
+    for rec in tr["steps"]:
+        if rec["is_prompt"] or not rec["rmv"]:
+            continue
+        sc = np.asarray(rec["l2norms"]["r0"], dtype=np.float32)
+        lo, hi = policy.victim_candidates(len(sc), p)
+        assert policy.argmin_lowest_index(sc, lo, hi) == rec["rmv"]["0"][1]
+        n += 1
+    assert n >= 3
 
 
 def test_value_l2_definition_properties():

@@ -22,9 +22,23 @@ def load_npz(name):
     return np.load(os.path.join(GOLDEN, name))
 
 
-def step_inputs(seed, step, n_tok, Hq, Hkv, D):
-    """q/k/v of one engine step, as make_golden.drive_forward generated them."""
-    q = (rnd(seed * 1000 + step * 3 + 0, n_tok, Hq * D).float() * 0.5).to(torch.bfloat16)
-    k = (rnd(seed * 1000 + step * 3 + 1, n_tok, Hkv * D).float() * 0.5).to(torch.bfloat16)
-    v = rnd(seed * 1000 + step * 3 + 2, n_tok, Hkv * D)
+def step_inputs(seed, step, n_tok, Hq, Hkv, D, layer=0):
+    """q/k/v of one engine step (of attention layer `layer`), as make_golden.drive_forward
+    generated them."""
+    sd = seed * 1000 + step * 3 + layer * 500000
+    q = (rnd(sd + 0, n_tok, Hq * D).float() * 0.5).to(torch.bfloat16)
+    k = (rnd(sd + 1, n_tok, Hkv * D).float() * 0.5).to(torch.bfloat16)
+    v = rnd(sd + 2, n_tok, Hkv * D)
     return q, k, v
+
+
+HEAD_POLICY_TRACES = ["head_global_random_b1_l2", "v1_global_random_b3_l2", "v1_local_random_b3",
+                      "head_stream1_b1", "v1_stream1_b3", "v1_invkey_b2_l2"]
+
+
+def trace_decode_method(cfg):
+    """--evict-method of a golden trace -> (decode method, topk) as the reference ran it."""
+    m = cfg["method"]
+    if m in ("local", "global"):
+        return ("random" if cfg.get("random_evict") else "value_l2"), (cfg.get("topk", 3) if m == "local" else -1)
+    return m, -1

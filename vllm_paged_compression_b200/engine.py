@@ -259,12 +259,21 @@ class PinnedLayerIO:
     directions get their own streams.  A step costs max(compute, H2D, D2H) + the first H2D +
     the last D2H.
 
+    prefetch=True (DecodeGraphRunner only): the whole step's input arena moves as ONE copy, one
+    step AHEAD -- while step n computes from landing buffer n % 2, the copy stream fills the other
+    one with `qkv_host`, i.e. with step n + 1's activations, so no layer ever waits on the link
+    and the attention kernels keep one unbroken programmatic-dependent-launch chain (each
+    cross-stream edge inside a captured step costs ~3 us, profiles/r02_e2e_breakdown.txt).
+    Contract: runner.step() attends over what the PREVIOUS step() (or prime()) uploaded.
+
     Use:  io.begin_step(); engine.step(io.qkv, out_fn=io.put_out, out_buf_fn=io.out_buf); io.end_step()
     """
 
     def __init__(self, num_layers: int, batch: int, num_heads: int, num_kv_heads: int, head_size: int,
-                 device, group: int = 0, dtype=torch.bfloat16, duplex: bool = True) -> None:
+                 device, group: int = 0, dtype=torch.bfloat16, duplex: bool = True,
+                 prefetch: bool = False) -> None:
         self.L, self.B = num_layers, batch
+        self.prefetch = bool(prefetch)
 
         def doubling(n):
             sizes, left, nxt = [], n, 1
@@ -292,14 +301,17 @@ class PinnedLayerIO:
         self.d_bounds = bounds(d_sizes)        # D2H groups
         self.gidx = [gi for gi, (a, b) in enumerate(self.bounds) for _ in range(a, b)]
         self.d_gidx = [gi for gi, (a, b) in enumerate(self.d_bounds) for _ in range(a, b)]
-        self.is_first = [l == self.bounds[self.gidx[l]][0] for l in range(num_layers)]
+        self.is_first = [l == self.bounds[self.gidx[l]][0] and not self.prefetch for l in range(num_layers)]
         self.is_last = [l + 1 == self.d_bounds[self.d_gidx[l]][1] for l in range(num_layers)]
         self.qw, self.kw = num_heads * head_size, num_kv_heads * head_size
         w = self.qw + 2 * self.kw
         self.device = torch.device(device)
         self.qkv_host = torch.empty(num_layers, batch, w, dtype=dtype).pin_memory()
         self.out_host = torch.empty(num_layers, batch, self.qw, dtype=dtype).pin_memory()
-        self.qkv_dev = torch.empty(num_layers, batch, w, dtype=dtype, device=self.device)
+        # landing buffers: one, or two alternating ones when the upload runs a step ahead
+        self.qkv_bufs = torch.empty(2 if self.prefetch else 1, num_layers, batch, w, dtype=dtype,
+                                    device=self.device)
+        self.qkv_dev = self.qkv_bufs[0]
         self.out_dev = torch.empty(num_layers, batch, self.qw, dtype=dtype, device=self.device)
         self.h2d_stream = torch.cuda.Stream(self.device)
         self.d2h_stream = torch.cuda.Stream(self.device) if duplex else self.h2d_stream
@@ -311,25 +323,37 @@ class PinnedLayerIO:
 
     def describe(self) -> dict:
         """Copy schedule, for the bench log."""
-        return {"h2d_groups": [b - a for a, b in self.bounds], "d2h_groups": [b - a for a, b in self.d_bounds],
+        h2d = [self.L] if self.prefetch else [b - a for a, b in self.bounds]
+        return {"h2d_groups": h2d, "d2h_groups": [b - a for a, b in self.d_bounds],
                 "duplex_streams": self.d2h_stream is not self.h2d_stream,
-                "h2d_copies_per_step": len(self.bounds), "d2h_copies_per_step": len(self.d_bounds)}
+                "h2d_copies_per_step": len(h2d), "d2h_copies_per_step": len(self.d_bounds),
+                "h2d_one_step_ahead": self.prefetch}
 
-    def begin_step(self) -> None:
+    def prime(self, buf: int = 0) -> None:
+        """prefetch mode: upload `qkv_host` into landing buffer `buf` now (before the first step)."""
+        self.qkv_bufs[buf].copy_(self.qkv_host, non_blocking=True)
+        torch.cuda.current_stream(self.device).synchronize()
+
+    def begin_step(self, buf: int = 0) -> None:
         """Queue every layer group's H2D on the copy stream (after the previous step's
-        compute has consumed the staging buffers)."""
+        compute has consumed the staging buffers).  prefetch mode: the step computes from landing
+        buffer `buf`; ONE copy fills the other buffer for the next step."""
         cur = torch.cuda.current_stream(self.device)
         self.h2d_stream.wait_stream(cur)
+        if self.prefetch:
+            with torch.cuda.stream(self.h2d_stream):
+                self.qkv_bufs[1 - buf].copy_(self.qkv_host, non_blocking=True)
+            return
         with torch.cuda.stream(self.h2d_stream):
             for gi in range(len(self.h2d_done)):
                 lo, hi = self.bounds[gi]
                 self.qkv_dev[lo:hi].copy_(self.qkv_host[lo:hi], non_blocking=True)
                 self.h2d_done[gi].record(self.h2d_stream)
 
-    def qkv(self, layer: int, n_tok: int, wait: bool = True):
+    def qkv(self, layer: int, n_tok: int, wait: bool = True, buf: int = 0):
         if wait and self.is_first[layer]:
             torch.cuda.current_stream(self.device).wait_event(self.h2d_done[self.gidx[layer]])
-        row = self.qkv_dev[layer]
+        row = self.qkv_bufs[buf][layer]
         return row[:, :self.qw], row[:, self.qw:self.qw + self.kw], row[:, self.qw + self.kw:]
 
     def out_buf(self, layer: int, n_tok: int) -> torch.Tensor:

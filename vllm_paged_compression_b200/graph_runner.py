@@ -87,13 +87,18 @@ class DecodeGraphRunner:
         self.max_kv_len = int(max_kv_len)
         M = self.M = cdiv(self.max_kv_len, bs) + 1
 
+        qkv_alt = None
         if io is not None:
             qkv = [io.qkv(l, B, wait=False) for l in range(L)]
             outs = [io.out_dev[l] for l in range(L)]
+            if io.prefetch:      # two landing buffers, the step's parity picks one
+                qkv_alt = [io.qkv(l, B, wait=False, buf=1) for l in range(L)]
         if outs is None:
             outs = [torch.empty(B, eng.num_heads * eng.head_size, dtype=torch.bfloat16, device=self.device)
                     for _ in range(L)]
-        self.qkv = [tuple(t.view(B, -1, eng.head_size) for t in x) for x in qkv]
+        views = lambda xs: [tuple(t.view(B, -1, eng.head_size) for t in x) for x in xs]
+        self.qkv_par = [views(qkv)] + ([views(qkv_alt)] if qkv_alt is not None else [])
+        self.qkv = self.qkv_par[0]
         self.outs = [o.view(B, eng.num_heads, eng.head_size) for o in outs]
         self.out_flat = list(outs)
 
@@ -154,13 +159,17 @@ class DecodeGraphRunner:
             ptrs = [sc.pools[sc.local] for _, _, sc in self.layers]
             self.d_pool_ptrs = torch.tensor(ptrs, dtype=torch.int64, device=self.device)
             self.heads_total = self.layers[0][2].heads_total
-        self._graphs: Dict[bool, object] = {}
+        self._graphs: Dict[Tuple[bool, int], object] = {}
         self._launches: Dict[bool, int] = {}
         self._ahead = None          # next step's packed host state, prepared while the device runs
         self._warm()
-        if self.use_graph:          # capture both variants now, not inside somebody's timed step
+        if self.use_graph:          # capture every variant now, not inside somebody's timed step
             for trig in ((False, True) if self.cfg is not None else (False,)):
-                self._graph(trig)
+                for par in range(len(self.qkv_par)):
+                    self._graph(trig, par)
+        if io is not None and io.prefetch and self.recaptures == 0:
+            self._io_par = 0
+            io.prime(0)             # the first step's activations; later ones arrive a step ahead
 
     # ------------------------------------------------------------------ launches
     def _make_step(self, pdl: bool = False):
@@ -173,7 +182,7 @@ class DecodeGraphRunner:
             policy=eng.impls[0]._policy_struct() if self.cfg is not None else None,
             n_blocks=self.d_nblk, plan=self.d_plan, workspace=self.ws, pdl=pdl)
 
-    def _launch_layers(self, trig: bool, count: bool = False) -> None:
+    def _launch_layers(self, trig: bool, par: int = 0) -> None:
         """All layers of one decode step on the current stream (captured or eager).
         Trigger step: ONE selection launch for all layers (a layer's victims depend on scores
         written on earlier steps only), then the same attention launches as a plain step, each
@@ -187,7 +196,7 @@ class DecodeGraphRunner:
         io = self.io
         cur = torch.cuda.current_stream(self.device)
         if io is not None:
-            io.begin_step()
+            io.begin_step(par)
         uncompacted = trig and self.attend_unc     # HEAD's streamingLLM behaviour (DESIGN D5)
         if trig:
             ops.evict_select_compact_layers(self.d_tab, self.d_nblk, self.d_seq, ds.policy, self.d_pool_ptrs,
@@ -196,7 +205,7 @@ class DecodeGraphRunner:
         for l in range(self.L):
             if io is not None and io.is_first[l]:
                 cur.wait_event(io.h2d_done[io.gidx[l]])
-            q, k, v = self.qkv[l]
+            q, k, v = self.qkv_par[par][l]
             kptr, vptr, score = self.layers[l]
             chained = l > 0 and (io is None or not io.is_first[l])
             tables = None
@@ -221,13 +230,13 @@ class DecodeGraphRunner:
             self.io = io
         torch.cuda.current_stream(self.device).synchronize()
 
-    def _graph(self, trig: bool):
-        g = self._graphs.get(trig)
+    def _graph(self, trig: bool, par: int = 0):
+        g = self._graphs.get((trig, par))
         if g is None:
             g = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g):
-                self._launch_layers(trig)
-            self._graphs[trig] = g
+                self._launch_layers(trig, par)
+            self._graphs[(trig, par)] = g
         return g
 
     # ---------------------------------------------------------------------- step
@@ -324,11 +333,15 @@ class DecodeGraphRunner:
         ev.record(torch.cuda.current_stream(self.device))
         self._ring_ev[i] = ev
         # ---- all layers
+        par = 0
+        if self.io is not None and self.io.prefetch:
+            par = self._io_par                           # landing buffer the previous step filled
+            self._io_par = 1 - par
         if self.use_graph:
-            self._graph(any_trig).replay()
+            self._graph(any_trig, par).replay()
             ops._launched(self._launches[any_trig])      # kernel nodes of the replayed graph
         else:
-            self._launch_layers(any_trig)                # ops.decode_layer counts its own
+            self._launch_layers(any_trig, par)           # ops.decode_layer counts its own
         # ---- host work of the NEXT step while the device runs this one (matters when the caller
         # waits for every step's result, e.g. host-resident activations): valid when this step
         # changes no table (no eviction) and the next one appends no block
