@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define PC_ABI_VERSION 5
+#define PC_ABI_VERSION 6
 #define PC_MAX_PEERS 8
 
 typedef enum pc_status {
@@ -54,7 +54,11 @@ typedef struct pc_evict_policy {
   int32_t evict_freq;      /* percentage mode: one block per evict_freq blocks */
   int32_t initial_blocks;  /* sink blocks, reference hard-codes 1 */
   int32_t num_block_merge; /* percentage mode lower bound, reference default 2 */
-  int32_t decode_method;   /* 0 = streamingLLM (victim = block 1), 1 = value_l2 argmin */
+  int32_t decode_method;   /* 0 = streamingLLM (victim = block 1), 1 = value_l2 argmin,
+                            * 2 = victim chosen by the HOST (HEAD as shipped: enable_random_evict = True,
+                            *     torch_cuda_sdpa.py:802 -- a random.randint per triggered row, :1504-1513):
+                            *     the caller pre-fills out_victim / out_victims, the kernel applies the
+                            *     trigger test and compacts; an index outside [1, n_blocks) evicts nothing */
   int32_t topk_blocks;     /* <0: global window [1, n-1); >0: local window [1, 1+topk) */
 } pc_evict_policy;
 
@@ -128,6 +132,7 @@ int pc_prune_prompt_and_cache(const void* key, const void* value, void* key_cach
  * block_size : 0).  value_l2: score of table entry i = (sum over all heads_total heads,
  * ascending, of pool[table[i]][h]) / heads_total, read from score->pools[score->local];
  * ties in the argmin go to the lowest index (strict <, torch_cuda_sdpa.py:1536-1541).
+ * decode_method 2: out_victim is IN/OUT -- on entry the host's choice for every row.
  * num_kv_heads is unused when score is given (kept for call-site symmetry). */
 int pc_evict_select_compact(const int32_t* block_tables, int64_t table_stride,
                             const int32_t* n_blocks, const int32_t* seq_lens,
@@ -240,7 +245,8 @@ int pc_decode_layer(const pc_decode_step* step /* HOST */, void* out, const void
  * per layer, and the attention kernels of a trigger step stay PDL-chained.
  * score_pools: DEVICE array [num_layers] of this rank's pool of each layer (pc_score_pool
  * .pools[local]), NULL for streamingLLM.  out_tables [num_layers][batch][out_stride] (layer
- * stride out_layer_stride ints), out_victims [num_layers][batch] (-1 = row did not trigger). */
+ * stride out_layer_stride ints), out_victims [num_layers][batch] (-1 = row did not trigger;
+ * decode_method 2: IN/OUT, pre-filled with the host's choices in (layer, row) order). */
 int pc_evict_select_compact_layers(const int32_t* block_tables, int64_t table_stride,
                                    const int32_t* n_blocks, const int32_t* seq_lens, int32_t batch,
                                    int32_t num_layers, const pc_evict_policy* policy /* HOST */,
@@ -269,6 +275,23 @@ int pc_prefill_attn_topleft_causal(void* out, const void* query, const void* key
                                    int64_t q_stride, int64_t out_stride, int64_t key_stride,
                                    int64_t value_stride, const int32_t* req_meta_host /* HOST or NULL */,
                                    int32_t dtype, void* stream);
+
+/* ---- W2: slot zeroing of `streamingLLM-1` / `inverse_key_l2` --------------------------
+ * Replaces the all-zero K/V rows the reference appends to the decode step's reshape_and_cache
+ * call (TmpCacheSingleton rows, torch_cuda_sdpa.py:919-933,962-975; slots chosen at :1396-1401 --
+ * slot (seq_len % bs - 1) of the table's 2nd block -- and :1444-1454 -- a random slot of a random
+ * middle block).  slots int64 [num_slots] (DEVICE), < 0 = skip: the K and V rows of every kv head
+ * at each slot become zero.  The _layers form zeroes [num_layers][slot_stride] slots in the
+ * pools key_caches[l] / value_caches[l] (DEVICE arrays of pool base pointers) in ONE launch: the
+ * slots are host decisions known before the step, so the zeros land ahead of the first layer's
+ * attention and the layers' attention kernels keep their PDL chain. */
+int pc_zero_cache_slots(void* key_cache, void* value_cache, const int64_t* slots, int32_t num_slots,
+                        int32_t num_kv_heads, int32_t head_size, int32_t block_size,
+                        int64_t kv_block_stride, void* stream);
+int pc_zero_cache_slots_layers(void* const* key_caches /* DEVICE */, void* const* value_caches /* DEVICE */,
+                               const int64_t* slots, int64_t slot_stride, int32_t num_slots,
+                               int32_t num_layers, int32_t num_kv_heads, int32_t head_size,
+                               int32_t block_size, int64_t kv_block_stride, void* stream);
 
 /* ---- block maintenance (backend surface, torch_cuda_sdpa.py:75-88) ------------------
  * pc_copy_blocks replaces _C_cache_ops::copy_blocks (csrc/cache_kernels.cu:69-150) for

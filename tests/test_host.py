@@ -106,6 +106,7 @@ def test_slot_mapping_builder_golden():
 
 
 def test_cli_flag_sets():
+    from vllm_paged_compression_b200.config import PagedEvictConfig as _PEC
     p = add_cli_args(argparse.ArgumentParser())
     # README flags (README.md:38-45)
     a = p.parse_args("--enable-paged-eviction --cache-prune-type percentage --prompt-evict-method streamingLLM "
@@ -124,8 +125,19 @@ def test_cli_flag_sets():
     a = p.parse_args("--enable-paged-eviction --evict-method streamingLLM --cache-budget 64".split())
     assert paged_evict_config_from_args(a).cache_budget == 128            # floored, vllm/config.py:977-980
     assert paged_evict_config_from_args(p.parse_args([])) is None
-    with pytest.raises(NotImplementedError):
-        paged_evict_config_from_args(p.parse_args("--enable-paged-eviction --evict-method inverse_key_l2".split()))
+    # every HEAD --evict-method (scripts/diff_page_sizes.sh:12) resolves to a (prompt, decode) pair
+    want = {"streamingLLM": ("streamingLLM", "streamingLLM"), "streamingLLM-1": ("streamingLLM", "streamingLLM-1"),
+            "inverse_key_l2": ("token_inverse_key_l2", "inverse_key_l2"),
+            "local": ("streamingLLM", "value_l2"), "global": ("streamingLLM", "value_l2")}
+    for m, pair in want.items():
+        c = paged_evict_config_from_args(p.parse_args(f"--enable-paged-eviction --evict-method {m}".split()))
+        assert (c.prompt_evict_method, c.decode_evict_method) == pair
+    # HEAD as shipped: enable_random_evict = True (torch_cuda_sdpa.py:802)
+    c = paged_evict_config_from_args(p.parse_args(
+        "--enable-paged-eviction --evict-method global --head-random-evict".split()))
+    assert (c.prompt_evict_method, c.decode_evict_method, c.topk_blocks) == ("token_value_l2", "random", -1)
+    with pytest.raises(ValueError):       # the HEAD-only methods exist in budget mode only
+        _PEC(cache_prune_type="percentage", evict_method="streamingLLM-1")
     with pytest.raises(ValueError):
         CacheConfig(block_size=16, paged_evict_config=_budget(200))       # budget % block_size != 0
 

@@ -10,7 +10,7 @@ import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("PC_LIB_PATH") or os.path.join(_HERE, "libpagedevict_b200.so")
-ABI_VERSION = 5
+ABI_VERSION = 6
 MAX_PEERS = 8
 
 
@@ -69,6 +69,8 @@ PROTOTYPES = {
                                                  _P, _I64, _I64, _P, _P]),
     "pc_prefill_attn_topleft_causal": (C.c_int, [_P, _P, _P, _P, _P, _I32, _I32, _I64, _I32, _I32, _I32, _F,
                                                  _I64, _I64, _I64, _I64, _P, _I32, _P]),
+    "pc_zero_cache_slots": (C.c_int, [_P, _P, _P, _I32, _I32, _I32, _I32, _I64, _P]),
+    "pc_zero_cache_slots_layers": (C.c_int, [_P, _P, _P, _I64, _I32, _I32, _I32, _I32, _I32, _I64, _P]),
     "pc_copy_blocks": (C.c_int, [_P, _P, _P, _I32, _I64, _P]),
     "pc_swap_blocks": (C.c_int, [_P, _P, _P, _I32, _I64, _P]),
 }

@@ -19,6 +19,7 @@ instead of being dropped whenever the batch composition changes
 from __future__ import annotations
 
 import os
+import random
 from dataclasses import dataclass, field
 from itertools import accumulate
 from typing import Any, Dict, List, Optional, Tuple, Type
@@ -30,7 +31,7 @@ from . import ops
 from .abstract import (PAD_SLOT_ID, AttentionBackend, AttentionImpl, AttentionMetadata,
                        AttentionMetadataBuilder, AttentionType, CommonAttentionState)
 from .config import CacheConfig, PagedEvictConfig
-from .policy import decode_trigger, prompt_prune_layout
+from .policy import decode_trigger, prompt_prune_layout, random_victim, zero_slot
 
 
 # =============================================================================== ops
@@ -344,6 +345,11 @@ class TorchCUDASDPABackendImpl(AttentionImpl[TorchCUDASDPAMetadata]):
                          (vllm/model_executor/models/llama.py:117-130)
       score_exchange     parallel.ScoreExchange: allocates the per-layer score pools so that
                          every rank can store into every rank's pool (None = single GPU)
+      rng                source of the host-side draws of the `random` / `inverse_key_l2` decode
+                         methods: an object with randint(a, b).  Default = Python's process-wide
+                         `random` module, re-seeded with 1234 by every layer's constructor exactly
+                         like HEAD (torch_cuda_sdpa.py:796), so a model built from these impls draws
+                         the same sequence as the fork: layer order, rows in row order.
     """
 
     def __init__(self, num_heads: int, head_size: int, scale: float, num_kv_heads: Optional[int] = None,
@@ -391,6 +397,11 @@ class TorchCUDASDPABackendImpl(AttentionImpl[TorchCUDASDPAMetadata]):
         # the flag reproduces HEAD for the golden traces.
         self.head_compat_uncompacted = bool(kwargs.get(
             "head_compat_uncompacted", os.environ.get("PC_HEAD_COMPAT_UNCOMPACTED", "0") == "1"))
+        self.rng = kwargs.get("rng", None)
+        if self.rng is None and self.enabled_paged_eviction and \
+                self.paged_evict_config.decode_evict_method in ("random", "inverse_key_l2"):
+            random.seed(1234)              # torch_cuda_sdpa.py:796
+            self.rng = random
         self.reqids_mapping_rmv_blockIdx: Dict[int, Tuple[str, int]] = {}
         self._pending_victims = None      # (device int32 [B], rows) of the last value_l2 step
         self._score_pool: Optional[torch.Tensor] = None   # fp32 [num_blocks, Hkv * tp_size]
@@ -402,6 +413,10 @@ class TorchCUDASDPABackendImpl(AttentionImpl[TorchCUDASDPAMetadata]):
     @property
     def _value_l2(self) -> bool:
         return self.enabled_paged_eviction and self.paged_evict_config.decode_evict_method == "value_l2"
+
+    @property
+    def _decode_method(self) -> Optional[str]:
+        return self.paged_evict_config.decode_evict_method if self.enabled_paged_eviction else None
 
     def _policy_struct(self):
         if self._c_policy is None:
@@ -475,6 +490,13 @@ class TorchCUDASDPABackendImpl(AttentionImpl[TorchCUDASDPAMetadata]):
             # on trigger rows kv lens arrive already reduced by block_size (model_runner.py:540-543)
             st["trigger_rows"] = [i for i, t in enumerate(trig) if t]
             st["max_kv_len"] = max(kv, default=0)
+            st["nblk_host"] = nblk
+            if cfg is not None and cfg.decode_evict_method in ("streamingLLM-1", "inverse_key_l2"):
+                st["tables_host"] = [t for tabs in md.reqid_mapping_blocktables.values() for t in tabs.values()]
+                if cfg.decode_evict_method == "streamingLLM-1":      # W2: the same slots in every layer
+                    zs = [zero_slot(None, s, t, cfg, bs) for s, t in zip(md.seq_lens, st["tables_host"])]
+                    st["zero_slots"] = (_h2d(np.asarray(zs, np.int64), device, True)
+                                        if any(z >= 0 for z in zs) else None)
             pack = [np.asarray(nblk, np.int32)]
             names = ["nblk"]
         flat = np.concatenate(pack) if pack else np.empty(0, np.int32)
@@ -555,7 +577,8 @@ class TorchCUDASDPABackendImpl(AttentionImpl[TorchCUDASDPAMetadata]):
             if compact is None:
                 compact = torch.empty_like(tables)
                 st["compact"] = compact
-        attend_unc = bool(trig) and (not self._value_l2) and self.head_compat_uncompacted
+        attend_unc = bool(trig) and self.head_compat_uncompacted and \
+            self._decode_method in ("streamingLLM", "streamingLLM-1")
         ds = ops.make_decode_step(
             md.slot_mapping, tables, kv_lens, md.seq_lens_tensor, q.shape[0], self.num_heads,
             self.num_kv_heads, self.head_size, bs, st["max_kv_len"], self.scale, q.stride(0),
@@ -572,15 +595,38 @@ class TorchCUDASDPABackendImpl(AttentionImpl[TorchCUDASDPAMetadata]):
         ds = self._decode_step_struct(q, k, v, out, md, st, blk_stride, bs)
         score = self._scores(q.device, kv_cache.shape[1]) if self._value_l2 else None
         trig = st.get("trigger_rows", [])
+        method = self._decode_method
+        # W2: this step's zeroed slots land before the attention reads the pool
+        zs = st.get("zero_slots")
+        if method == "inverse_key_l2":        # two draws per over-budget row, every layer its own
+            cfg = self.paged_evict_config
+            host = [zero_slot(self.rng, s, t, cfg, bs) for s, t in zip(md.seq_lens, st["tables_host"])]
+            zs = _h2d(np.asarray(host, np.int64), q.device, True) if any(z >= 0 for z in host) else None
+        if zs is not None:
+            kc, vc, _ = self._caches(kv_cache)
+            ops.zero_cache_slots(kc, vc, zs)
         victims = None
+        host_victims = None
         if trig:
-            victims = torch.empty(q.shape[0], dtype=torch.int32, device=q.device)
+            if method == "random":            # HEAD as shipped: one draw per triggered row, row order
+                host_victims = {r: random_victim(self.rng, st["nblk_host"][r], self.paged_evict_config)
+                                for r in trig}
+                hv = np.full(q.shape[0], -1, np.int32)
+                for r, i in host_victims.items():
+                    if not 1 <= i < st["nblk_host"][r]:
+                        raise RuntimeError(f"random victim {i} outside the row's {st['nblk_host'][r]} blocks")
+                    hv[r] = i
+                victims = _h2d(hv, q.device, True)
+            else:
+                victims = torch.empty(q.shape[0], dtype=torch.int32, device=q.device)
         ops.decode_layer(ds, out, q, k, v, kptr, vptr, score, victims)
         if trig:
             rows = st["rows"]
             if self._value_l2:
                 self._pending_victims = (victims, trig, rows)
-            else:                          # streamingLLM: the victim is always table index 1
+            elif host_victims is not None:
+                self.reqids_mapping_rmv_blockIdx = {r: (rows[r][0], i) for r, i in host_victims.items()}
+            else:                          # streamingLLM(-1): the victim is always table index 1
                 self.reqids_mapping_rmv_blockIdx = {r: (rows[r][0], 1) for r in trig}
 
     def get_rmv_block_idx(self) -> Dict[int, Tuple[str, int]]:

@@ -5,28 +5,43 @@ CacheConfig (vllm/config.py:1040,1051) and the argparse block of
 vllm/engine/arg_utils.py:202-212,971-1036,1132-1156.  Both flag sets are accepted:
 
   HEAD  : --enable-paged-eviction --disable-evict-prefill --cache-prune-type budget
-          --evict-method {streamingLLM,local,global} --cache-budget N --topk-blocks K
+          --evict-method {streamingLLM,streamingLLM-1,inverse_key_l2,local,global}
+          --cache-budget N --topk-blocks K
   README: --cache-prune-type percentage --prompt-evict-method streamingLLM
           --decode-evict-method {streamingLLM,value_l2} --evict-freq N
           (README.md:38-45; semantics from kvcache_prunner_old.py / page_evict_kv_util_bak.py,
           benchmarks/llama3.1_8b_test.txt:1 -> initial_blocks=1, num_blocks_merge=2)
 
-`--evict-method` is an alias: streamingLLM -> prompt streamingLLM + decode streamingLLM;
-global/local -> prompt streamingLLM slice + decode value_l2 over the global / local
-window (kvcache_prunner.py:13 sub_evict_method = "value_l2").  The token-level prompt
-scoring of HEAD's global/local and the slot-zeroing methods (streamingLLM-1,
-inverse_key_l2) are outside the hot path and rejected loudly.
+`--evict-method` resolves into a (prompt, decode) method pair:
+
+  streamingLLM    prompt streamingLLM slice, decode: evict table entry 1
+  streamingLLM-1  the same, plus W2: while over budget and off a block boundary, slot
+                  (seq_len % bs - 1) of the table's 2nd block is zeroed (torch_cuda_sdpa.py:1396-1401)
+  inverse_key_l2  prompt: token-level 1/||K|| top-k drop; decode: W2 only -- a random slot of a random
+                  middle block is zeroed every step over budget, nothing is ever freed
+                  (torch_cuda_sdpa.py:1444-1454, model_runner.py:545-547)
+  global / local  decode value_l2 argmin over the global / local window (kvcache_prunner.py:13
+                  sub_evict_method = "value_l2"); prompt = streamingLLM slice by default.
+                  `head_random_evict=True` (--head-random-evict, env PC_HEAD_RANDOM_EVICT=1)
+                  reproduces HEAD as shipped: `enable_random_evict = True` (torch_cuda_sdpa.py:802)
+                  evicts a random window block drawn from Python's `random` (seeded 1234), and the
+                  prompt is pruned token by token (value_l2 top-k drop, kvcache_prunner.py:220-279).
 """
 from __future__ import annotations
 
 import argparse
 import logging
+import os
 from dataclasses import dataclass, field
 from typing import Optional
 
 logger = logging.getLogger(__name__)
 
 _HEAD_METHODS = ["streamingLLM", "streamingLLM-1", "inverse_key_l2", "local", "global"]
+# prompt: the streamingLLM slice, or the per-head token top-k drop of kvcache_prunner.py:220-279
+_PROMPT_METHODS = ["streamingLLM", "token_value_l2", "token_inverse_key_l2"]
+# decode: "random" = HEAD's enable_random_evict for local / global; the last two are the W2 variants
+_DECODE_METHODS = ["streamingLLM", "value_l2", "random", "streamingLLM-1", "inverse_key_l2"]
 
 
 class PagedEvictConfig:
@@ -43,7 +58,8 @@ class PagedEvictConfig:
                  decode_evict_method: Optional[str] = None,
                  evict_freq: int = 2,
                  initial_blocks: int = 1,
-                 num_block_merge: int = 2) -> None:
+                 num_block_merge: int = 2,
+                 head_random_evict: Optional[bool] = None) -> None:
         self.disable_evict_prefill = disable_evict_prefill
         self.cache_prune_type = cache_prune_type
         self.evict_method = evict_method
@@ -54,30 +70,40 @@ class PagedEvictConfig:
         self.num_block_merge = num_block_merge
         self.prompt_evict_method = prompt_evict_method
         self.decode_evict_method = decode_evict_method
+        if head_random_evict is None:
+            head_random_evict = os.environ.get("PC_HEAD_RANDOM_EVICT", "0") == "1"
+        self.head_random_evict = bool(head_random_evict)
         self._verify_args()
 
     def _verify_args(self) -> None:
         if self.cache_prune_type not in ["percentage", "budget"]:
             raise ValueError("Cache prune type must be either 'percentage' or 'budget'. Got "
                              f"{self.cache_prune_type}.")
-        # resolve the --evict-method alias into (prompt, decode) methods
+        # resolve --evict-method into (prompt, decode) methods
         if self.decode_evict_method is None or self.prompt_evict_method is None:
             em = self.evict_method or "streamingLLM"
             if em not in _HEAD_METHODS:
                 raise ValueError(f"Unknown evict_method {em!r}")
-            if em in ("streamingLLM-1", "inverse_key_l2"):
-                raise NotImplementedError(
-                    f"evict_method={em!r} (slot-zeroing variants) is outside the B200 hot path; "
-                    "supported: streamingLLM, local, global")
-            self.prompt_evict_method = self.prompt_evict_method or "streamingLLM"
-            self.decode_evict_method = self.decode_evict_method or (
-                "streamingLLM" if em == "streamingLLM" else "value_l2")
-        if self.prompt_evict_method != "streamingLLM":
-            raise NotImplementedError("prompt_evict_method must be 'streamingLLM' (token-level prompt "
-                                      "scoring is outside the hot path)")
-        if self.decode_evict_method not in ("streamingLLM", "value_l2"):
-            raise ValueError(f"decode_evict_method must be streamingLLM or value_l2, got "
+            if em in ("streamingLLM", "streamingLLM-1"):
+                prompt, decode = "streamingLLM", em
+            elif em == "inverse_key_l2":
+                prompt, decode = "token_inverse_key_l2", "inverse_key_l2"
+            elif self.head_random_evict:
+                prompt, decode = "token_value_l2", "random"
+            else:
+                prompt, decode = "streamingLLM", "value_l2"
+            self.prompt_evict_method = self.prompt_evict_method or prompt
+            self.decode_evict_method = self.decode_evict_method or decode
+        if self.prompt_evict_method not in _PROMPT_METHODS:
+            raise ValueError(f"prompt_evict_method must be one of {_PROMPT_METHODS}, got "
+                             f"{self.prompt_evict_method!r}")
+        if self.decode_evict_method not in _DECODE_METHODS:
+            raise ValueError(f"decode_evict_method must be one of {_DECODE_METHODS}, got "
                              f"{self.decode_evict_method!r}")
+        if (self.decode_evict_method in ("random", "streamingLLM-1", "inverse_key_l2")
+                or self.prompt_evict_method != "streamingLLM") and self.cache_prune_type != "budget":
+            raise ValueError(f"{self.decode_evict_method!r} / {self.prompt_evict_method!r} exist in budget "
+                             "mode only (kvcache_prunner.py:11)")
         if self.initial_blocks != 1:
             raise ValueError("initial_blocks must be 1 (vllm/config.py:967)")
         if self.cache_prune_type == "budget":
@@ -96,9 +122,8 @@ class PagedEvictConfig:
         if self.evict_method == "local" and self.topk_blocks <= 1:   # vllm/config.py:982-984
             raise ValueError("Topk blocks must be > 1 when using 'local' evict method. "
                              f"Got {self.topk_blocks}.")
-        if self.evict_method == "global" or (self.evict_method not in ("local",)
-                                              and self.decode_evict_method == "value_l2"
-                                              and self.evict_method != "local"):
+        if self.evict_method == "global" or (self.evict_method != "local"
+                                              and self.decode_evict_method in ("value_l2", "random")):
             self.topk_blocks = -1                                     # vllm/config.py:986-988
 
     def verify_with_block_size(self, block_size: int) -> None:
@@ -154,6 +179,10 @@ def add_cli_args(parser: argparse.ArgumentParser) -> argparse.ArgumentParser:
                         help="The number of tokens to keep in the KV cache for each request after pruning")
     parser.add_argument("--topk-blocks", type=int, default=3,
                         help="The number of top-k blocks to compare when pruning")
+    parser.add_argument("--head-random-evict", action="store_true", default=False,
+                        help="local / global as HEAD ships them (enable_random_evict = True, "
+                             "torch_cuda_sdpa.py:802): random window block at decode time, token-level "
+                             "value_l2 prompt prune.")
     parser.add_argument("--block-size", type=int, default=16, choices=[16, 32],
                         help="Token block size")
     return parser
@@ -177,4 +206,5 @@ def paged_evict_config_from_args(args: argparse.Namespace) -> Optional[PagedEvic
         topk_blocks=topk,
         prompt_evict_method=args.prompt_evict_method,
         decode_evict_method=args.decode_evict_method,
-        evict_freq=args.evict_freq)
+        evict_freq=args.evict_freq,
+        head_random_evict=True if getattr(args, "head_random_evict", False) else None)

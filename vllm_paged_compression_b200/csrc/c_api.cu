@@ -336,6 +336,35 @@ int pc_copy_blocks(void* key_cache, void* value_cache, const int64_t* pairs, int
                      block_bytes, static_cast<cudaStream_t>(stream));
 }
 
+int pc_zero_cache_slots(void* key_cache, void* value_cache, const int64_t* slots, int32_t num_slots,
+                        int32_t num_kv_heads, int32_t head_size, int32_t block_size,
+                        int64_t kv_block_stride, void* stream) {
+  if (num_slots == 0) return PC_OK;
+  if (!key_cache || !value_cache || !slots) return set_error(PC_ERR_INVALID, "pc_zero_cache_slots: null pointer");
+  ZeroSlotsArgs a{};
+  a.k_caches = nullptr; a.v_caches = nullptr; a.k0 = key_cache; a.v0 = value_cache;
+  a.slots = reinterpret_cast<const long long*>(slots); a.slot_stride = num_slots;
+  a.num_slots = num_slots; a.num_layers = 1; a.Hkv = num_kv_heads; a.D = head_size; a.BS = block_size;
+  a.kv_block_stride = kv_block_stride;
+  return zero_cache_slots(a, static_cast<cudaStream_t>(stream));
+}
+
+int pc_zero_cache_slots_layers(void* const* key_caches, void* const* value_caches, const int64_t* slots,
+                               int64_t slot_stride, int32_t num_slots, int32_t num_layers,
+                               int32_t num_kv_heads, int32_t head_size, int32_t block_size,
+                               int64_t kv_block_stride, void* stream) {
+  if (num_slots == 0 || num_layers == 0) return PC_OK;
+  if (!key_caches || !value_caches || !slots)
+    return set_error(PC_ERR_INVALID, "pc_zero_cache_slots_layers: null pointer");
+  if (slot_stride < num_slots) return set_error(PC_ERR_INVALID, "pc_zero_cache_slots_layers: slot_stride < num_slots");
+  ZeroSlotsArgs a{};
+  a.k_caches = key_caches; a.v_caches = value_caches; a.k0 = nullptr; a.v0 = nullptr;
+  a.slots = reinterpret_cast<const long long*>(slots); a.slot_stride = slot_stride;
+  a.num_slots = num_slots; a.num_layers = num_layers; a.Hkv = num_kv_heads; a.D = head_size; a.BS = block_size;
+  a.kv_block_stride = kv_block_stride;
+  return zero_cache_slots(a, static_cast<cudaStream_t>(stream));
+}
+
 int pc_swap_blocks(const void* src, void* dst, const int64_t* pairs, int32_t num_pairs,
                    int64_t block_bytes, void* stream) {
   if (num_pairs == 0) return PC_OK;

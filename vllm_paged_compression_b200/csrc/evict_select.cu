@@ -46,8 +46,11 @@ __device__ __forceinline__ bool decode_trigger(const pc_evict_policy& pol, int s
 
 // One batch row: trigger test, victim, compacted row.  All threads of the CTA take part;
 // returns the victim (-1 = row did not trigger).
+// `given`: decode_method 2 only -- the victim the HOST chose for this row (HEAD as shipped draws it
+// from Python's `random`, torch_cuda_sdpa.py:802,1504-1513); used iff the row triggers.
 __device__ __forceinline__ int evict_row(const pc_evict_policy& pol, const int* __restrict__ row, int n, int seq_len,
-                                         const float* __restrict__ pool, int HT, int* orow, long long out_stride) {
+                                         const float* __restrict__ pool, int HT, int* orow, long long out_stride,
+                                         int given) {
   __shared__ float best_v[kEvictThreads / 32];
   __shared__ int best_i[kEvictThreads / 32];
   __shared__ int victim_s;
@@ -58,6 +61,8 @@ __device__ __forceinline__ int evict_row(const pc_evict_policy& pol, const int* 
   if (trig) {
     if (pol.decode_method == 0) {
       victim = 1;  // streamingLLM: always the block after the sink (torch_cuda_sdpa.py:1404-1405)
+    } else if (pol.decode_method == 2) {
+      victim = (given >= 1 && given < n) ? given : -1;   // host-chosen; an index outside the row evicts nothing
     } else {
       // candidates [1, hi): global -> n-1 ; local -> min(1 + topk, n-1)   (:1528-1534)
       const int lo = 1;
@@ -106,9 +111,11 @@ __device__ __forceinline__ int evict_row(const pc_evict_policy& pol, const int* 
 
 __global__ void __launch_bounds__(kEvictThreads) evict_select_compact_kernel(const EvictParams p) {
   const int b = blockIdx.x;
+  const int given = p.pol.decode_method == 2 ? p.out_victim[b] : -1;
   const int victim = evict_row(p.pol, p.block_tables + (size_t)b * p.table_stride, p.n_blocks[b], p.seq_lens[b],
                                p.score.n_pools > 0 ? p.score.pools[p.score.local] : nullptr, p.score.heads_total,
-                               p.out_tables + (size_t)b * p.out_stride, p.out_stride);
+                               p.out_tables + (size_t)b * p.out_stride, p.out_stride, given);
+  __syncthreads();   // every thread has read `given` before thread 0 overwrites it
   if (threadIdx.x == 0) {
     p.out_victim[b] = victim;
     if (p.out_kv_lens)
@@ -137,16 +144,18 @@ struct EvictLayersParams {
 __global__ void __launch_bounds__(kEvictThreads) evict_select_compact_layers_kernel(const EvictLayersParams p) {
   const int b = blockIdx.x, layer = blockIdx.y;
   const float* pool = p.pools != nullptr ? p.pools[layer] : nullptr;
+  const int given = p.pol.decode_method == 2 ? p.out_victims[(size_t)layer * gridDim.x + b] : -1;
   const int victim = evict_row(p.pol, p.block_tables + (size_t)b * p.table_stride, p.n_blocks[b], p.seq_lens[b], pool,
                                p.heads_total, p.out_tables + (size_t)layer * p.out_layer_stride + (size_t)b * p.out_stride,
-                               p.out_stride);
+                               p.out_stride, given);
+  __syncthreads();   // every thread has read `given` before thread 0 overwrites it
   if (threadIdx.x == 0) p.out_victims[(size_t)layer * gridDim.x + b] = victim;
 }
 
 int evict_select_compact_layers(const EvictLayersArgs& a, cudaStream_t stream) {
   if (a.B <= 0 || a.L <= 0) return 0;
   if (a.pol.block_size <= 0) return set_error(PC_ERR_INVALID, "policy.block_size must be > 0");
-  if (a.pol.decode_method != 0 && (a.pools == nullptr || a.heads_total <= 0))
+  if (a.pol.decode_method == 1 && (a.pools == nullptr || a.heads_total <= 0))
     return set_error(PC_ERR_INVALID, "value_l2 eviction needs the per-layer score pools");
   if (a.L > 65535) return set_error(PC_ERR_INVALID, "too many layers for one launch");
   EvictLayersParams p;
@@ -161,7 +170,7 @@ int evict_select_compact_layers(const EvictLayersArgs& a, cudaStream_t stream) {
 int evict_select_compact(const EvictSelectArgs& a, cudaStream_t stream) {
   if (a.B <= 0) return 0;
   if (a.pol.block_size <= 0) return set_error(PC_ERR_INVALID, "policy.block_size must be > 0");
-  if (a.pol.decode_method != 0 && a.score.n_pools <= 0)
+  if (a.pol.decode_method == 1 && a.score.n_pools <= 0)
     return set_error(PC_ERR_INVALID, "value_l2 eviction needs a score pool");
   EvictParams p;
   p.block_tables = a.block_tables;

@@ -109,7 +109,7 @@ struct EvictLayersArgs {
   int heads_total;
   int* out_tables;
   long long out_stride, out_layer_stride;
-  int* out_victims;
+  int* out_victims;             // decode_method 2: IN (the host's choice per triggered row) and OUT
 };
 int evict_select_compact_layers(const EvictLayersArgs& a, cudaStream_t stream);
 
@@ -131,6 +131,18 @@ void set_prefill_tc_persistent(int v);  // 1 = persistent CTAs, 0 = one CTA per 
 void set_prefill_tc_tile(int tn);       // kv tile width of the tcgen05 kernel (64 | 128)
 void set_cache_write_block_heads(int hc);  // heads per CTA of cache_write_block_kernel, 0 = rule
 #endif
+
+struct ZeroSlotsArgs {
+  void* const* k_caches;   // DEVICE [num_layers] pool pointers, or nullptr: k0 / v0 is the one layer
+  void* const* v_caches;
+  void* k0;
+  void* v0;
+  const long long* slots;  // DEVICE [num_layers][slot_stride]
+  long long slot_stride;
+  int num_slots, num_layers, Hkv, D, BS;
+  long long kv_block_stride;
+};
+int zero_cache_slots(const ZeroSlotsArgs& a, cudaStream_t stream);
 
 int copy_blocks(void* k_cache, void* v_cache, const long long* pairs, int num_pairs,
                 long long block_bytes, cudaStream_t stream);

@@ -19,6 +19,8 @@ from __future__ import annotations
 from dataclasses import dataclass, field
 from typing import Callable, Dict, List, Optional, Tuple
 
+import random
+
 import torch
 
 from .backend import (TorchCUDASDPABackend, TorchCUDASDPABackendImpl, TorchCUDASDPAMetadata,
@@ -100,6 +102,10 @@ class PagedEvictEngine:
         self.num_kv_heads, self.head_size = num_kv_heads, head_size
         scale = head_size ** -0.5
         self.score_exchange = score_exchange
+        # ONE host RNG for every layer, as in HEAD where all layers share Python's process-wide
+        # `random` (seeded 1234, torch_cuda_sdpa.py:796); an instance keeps engines independent
+        impl_kwargs.setdefault("rng", random.Random(1234))
+        self.rng = impl_kwargs["rng"]
         self.impls = [TorchCUDASDPABackendImpl(num_heads, head_size, scale, num_kv_heads, None, None,
                                                "auto", cache_config=cache_config,
                                                prefix=f"model.layers.{i}.self_attn.attn",

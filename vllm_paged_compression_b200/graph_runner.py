@@ -29,7 +29,7 @@ import numpy as np
 import torch
 
 from . import ops
-from .policy import cdiv
+from .policy import cdiv, random_victim, zero_slot
 
 
 class DecodeGraphRunner:
@@ -55,7 +55,12 @@ class DecodeGraphRunner:
         self.cfg = eng.cache_config.paged_evict_config
         impl0 = eng.impls[0]
         self.value_l2 = impl0._value_l2
-        self.attend_unc = (self.cfg is not None) and (not self.value_l2) and impl0.head_compat_uncompacted
+        self.method = impl0._decode_method       # None = eviction off
+        # HEAD's remaining policies: victims drawn on the host ("random"), W2 slot zeroing
+        self.host_victims = self.method == "random"
+        self.zeroing = self.method in ("streamingLLM-1", "inverse_key_l2")
+        self.rng = impl0.rng                     # one RNG for every layer (torch_cuda_sdpa.py:796)
+        self.attend_unc = (self.method in ("streamingLLM", "streamingLLM-1")) and impl0.head_compat_uncompacted
         bm = eng.block_manager
         self.bts = [bm.block_tables[s.seq_id] for s in self.seqs]
         cur_max = max(bt.get_seq_kv_len() for bt in self.bts)
@@ -104,7 +109,14 @@ class DecodeGraphRunner:
 
         # ---- packed int32 state: device buffer + ring of pinned host copies
         o_slot, o_kv, o_seq, o_nblk, o_plan, o_tab = 0, 2 * B, 3 * B, 4 * B, 5 * B, 5 * B + 4
-        self.n_meta = o_tab + B * M
+        per_layer = self.value_l2 or self.host_victims
+        self.Lsel = L if per_layer else 1
+        # host-decided extras ride in the same packed copy: victims [Lsel, B] int32 ("random"),
+        # zeroed slots [L, B] int64 (W2)
+        o_vict = o_tab + B * M
+        o_zero = o_vict + (self.Lsel * B if self.host_victims else 0)
+        o_zero += o_zero & 1                     # int64 alignment
+        self.n_meta = o_zero + (2 * L * B if self.zeroing else 0)
         self.meta = torch.zeros(self.n_meta, dtype=torch.int32, device=self.device)
         self._ring = [torch.zeros(self.n_meta, dtype=torch.int32).pin_memory() for _ in range(4)]
         self._ring_ev = [None] * len(self._ring)
@@ -113,13 +125,17 @@ class DecodeGraphRunner:
         self.d_slot = m[o_slot:o_kv].view(torch.int64)
         self.d_kv, self.d_seq, self.d_nblk = m[o_kv:o_seq], m[o_seq:o_nblk], m[o_nblk:o_plan]
         self.d_plan = m[o_plan:o_tab]
-        self.d_tab = m[o_tab:].view(B, M)
+        self.d_tab = m[o_tab:o_vict].view(B, M)
         self._off = (o_slot, o_kv, o_seq, o_nblk, o_plan, o_tab)
+        self._off_vict, self._off_zero = o_vict, o_zero
         # trigger steps: every layer's compacted tables / victims from ONE selection launch
-        # (value_l2: per layer; streamingLLM: the victim is index 1 for every layer, one copy)
-        self.Lsel = L if self.value_l2 else 1
+        # (value_l2 / random: per layer; streamingLLM: the victim is index 1 for every layer, one copy)
         self.d_compact = torch.zeros(self.Lsel, B, M, dtype=torch.int32, device=self.device)
-        self.d_victims = torch.full((self.Lsel, B), -1, dtype=torch.int32, device=self.device)
+        if self.host_victims:        # IN/OUT of the selection kernel: uploaded with the packed state
+            self.d_victims = m[o_vict:o_vict + self.Lsel * B].view(self.Lsel, B)
+        else:
+            self.d_victims = torch.full((self.Lsel, B), -1, dtype=torch.int32, device=self.device)
+        self.d_zero = m[o_zero:o_zero + 2 * L * B].view(torch.int64).view(L, B) if self.zeroing else None
         self._vict_host = torch.empty(B, dtype=torch.int32).pin_memory()
 
         # ---- host mirror
@@ -154,6 +170,9 @@ class DecodeGraphRunner:
             score = impl._scores(self.device, eng.kv_caches[l].shape[1]) if self.value_l2 else None
             self.layers.append((kptr, vptr, score))
         self.blk_stride = blk_stride
+        if self.zeroing:
+            self.d_kptrs = torch.tensor([x[0] for x in self.layers], dtype=torch.int64, device=self.device)
+            self.d_vptrs = torch.tensor([x[1] for x in self.layers], dtype=torch.int64, device=self.device)
         self.d_pool_ptrs = None
         if self.value_l2:
             ptrs = [sc.pools[sc.local] for _, _, sc in self.layers]
@@ -188,16 +207,20 @@ class DecodeGraphRunner:
         written on earlier steps only), then the same attention launches as a plain step, each
         over its layer's compacted tables -- so the PDL chain between the layers' kernels
         survives trigger steps."""
+        eng = self.eng
         ds = self._make_step()
         # PDL for a layer whose predecessor in the stream is the previous layer's attention
         # kernel (another layer's pool): its first pages load while that kernel drains
         ds_pdl = self._make_step(pdl=True) if self.pdl else ds
-        self._launches[trig] = self.L + (1 if trig else 0)
+        self._launches[trig] = self.L + (1 if trig else 0) + (1 if self.zeroing else 0)
         io = self.io
         cur = torch.cuda.current_stream(self.device)
         if io is not None:
             io.begin_step(par)
         uncompacted = trig and self.attend_unc     # HEAD's streamingLLM behaviour (DESIGN D5)
+        if self.zeroing:     # W2: every layer's zeroed slots in one launch, ahead of the first attention
+            ops.zero_cache_slots_layers(self.d_kptrs, self.d_vptrs, self.d_zero, eng.num_kv_heads,
+                                        eng.head_size, self.bs, self.blk_stride)
         if trig:
             ops.evict_select_compact_layers(self.d_tab, self.d_nblk, self.d_seq, ds.policy, self.d_pool_ptrs,
                                             self.heads_total if self.value_l2 else 0, self.d_compact,
@@ -210,7 +233,7 @@ class DecodeGraphRunner:
             chained = l > 0 and (io is None or not io.is_first[l])
             tables = None
             if trig and not uncompacted:
-                tables = self.d_compact[l if self.value_l2 else 0]
+                tables = self.d_compact[l if self.Lsel > 1 else 0]
             ops.decode_layer(ds_pdl if chained else ds, self.outs[l], q, k, v, kptr, vptr, score, None, tables)
             if io is not None:
                 io.put_out(l, self.out_flat[l])
@@ -222,6 +245,8 @@ class DecodeGraphRunner:
         """Load every kernel (lazy module loading must not happen under capture): one eager
         pass of both variants over rows of length zero -- no page is read or written."""
         self.meta.zero_()
+        if self.zeroing:
+            self.d_zero.fill_(-1)        # slot 0 is a real slot
         io, self.io = self.io, None
         try:
             for trig in ((False, True) if self.cfg is not None else (False,)):
@@ -253,7 +278,7 @@ class DecodeGraphRunner:
 
     def _trigger(self, seq: np.ndarray) -> np.ndarray:
         cfg, bs = self.cfg, self.bs
-        if cfg is None:
+        if cfg is None or self.method == "inverse_key_l2":     # model_runner.py:545-547: never frees
             return np.zeros(self.B, dtype=bool)
         ok = self.nblk >= 3
         if cfg.cache_prune_type == "budget":
@@ -287,8 +312,32 @@ class DecodeGraphRunner:
         host[o_seq:o_nblk] = seq
         host[o_nblk:o_plan] = nblk
         host[o_plan:o_plan + 2] = plan
-        host[o_tab:] = tab.reshape(-1)
-        return trig, any_trig, kv_pass, slot, i
+        host[o_tab:o_tab + tab.size] = tab.reshape(-1)
+        # host decisions of HEAD's remaining policies, drawn in HEAD's order: layer by layer, rows
+        # in row order (every layer's forward() walks the batch, torch_cuda_sdpa.py:1389,1440,1503)
+        hv = None
+        if self.host_victims and any_trig:
+            hv = np.full((self.Lsel, B), -1, dtype=np.int32)
+            rows = np.nonzero(trig)[0].tolist()
+            for l in range(self.Lsel):
+                for r in rows:
+                    v = random_victim(self.rng, int(nblk[r]), self.cfg)
+                    if not 1 <= v < nblk[r]:
+                        raise RuntimeError(f"random victim {v} outside the row's {nblk[r]} blocks")
+                    hv[l, r] = v
+            host[self._off_vict:self._off_vict + hv.size] = hv.reshape(-1)
+        if self.zeroing:
+            z = host[self._off_zero:self._off_zero + 2 * self.L * B].view(np.int64).reshape(self.L, B)
+            z[:] = -1
+            over = np.nonzero(seq > self.cfg.cache_budget)[0].tolist()
+            if self.method == "streamingLLM-1":       # the same slot in every layer, no draw
+                for r in over:
+                    z[:, r] = zero_slot(None, int(seq[r]), tab[r], self.cfg, bs)
+            else:
+                for l in range(self.L):
+                    for r in over:
+                        z[l, r] = zero_slot(self.rng, int(seq[r]), tab[r, :nblk[r]], self.cfg, bs)
+        return trig, any_trig, kv_pass, slot, i, hv
 
     def step(self) -> Dict[int, Tuple[str, int]]:
         """One decode step of every sequence.  The caller has refilled the static q/k/v
@@ -322,7 +371,7 @@ class DecodeGraphRunner:
         ahead, self._ahead = self._ahead, None
         if ahead is None:
             ahead = self._pack(self.seq, self.kv)
-        trig, any_trig, kv_pass, slot, i = ahead
+        trig, any_trig, kv_pass, slot, i, host_vict = ahead
         if self.record:
             self.last = {"seq_lens": self.seq.tolist(), "kv_lens": kv_pass.tolist(), "slots": slot.tolist(),
                          "tables": [tab[r, :nblk[r]].tolist() for r in range(B)],
@@ -357,9 +406,11 @@ class DecodeGraphRunner:
         rmv: Dict[int, Tuple[str, int]] = {}
         if any_trig:
             rows = np.nonzero(trig)[0]
-            if self.log_victims and self.value_l2:
+            if self.log_victims and self.Lsel > 1:
                 self.victim_log.append(self.d_victims.clone())
-            if self.value_l2:
+            if self.host_victims:                  # the host chose them: nothing to read back
+                idx = host_vict[0][rows].astype(np.int64)
+            elif self.value_l2:
                 self._vict_host.copy_(self.d_victims[0], non_blocking=True)
                 torch.cuda.current_stream(self.device).synchronize()
                 vict = self._vict_host.numpy()

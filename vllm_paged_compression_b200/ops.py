@@ -26,7 +26,9 @@ def _launched(n: int = 1) -> None:
     global launch_count
     launch_count += n
 
-_DECODE_METHOD = {"streamingLLM": 0, "value_l2": 1}
+# struct pc_evict_policy.decode_method: "random" = victim chosen by the host; the W2 variants
+# evict like streamingLLM (table entry 1) / never (inverse_key_l2: the host never triggers)
+_DECODE_METHOD = {"streamingLLM": 0, "value_l2": 1, "random": 2, "streamingLLM-1": 0, "inverse_key_l2": 0}
 
 
 def _stream(t: torch.Tensor) -> int:
@@ -378,6 +380,39 @@ def prefill_attn_topleft_causal(out: torch.Tensor, query: torch.Tensor, key: tor
         out.data_ptr(), query.data_ptr(), key.data_ptr(), value.data_ptr(), req_meta.data_ptr(),
         req_meta.shape[0], int(max_q_len), int(min(T, key.shape[0], value.shape[0])), Hq, Hkv, D, float(scale), query.stride(0), out.stride(0),
         key.stride(0), value.stride(0), host_ptr, _dtype_code(query), _stream(query)))
+    _launched()
+
+
+# ------------------------------------------------------------------------------ W2
+def zero_cache_slots(key_cache: torch.Tensor, value_cache: torch.Tensor, slots: torch.Tensor) -> None:
+    """Zero the K and V rows (all kv heads) at `slots` (int64 on the device, negative = skip): the
+    zero-row write of streamingLLM-1 / inverse_key_l2 (torch_cuda_sdpa.py:919-933,962-975)."""
+    _req_cuda(key_cache, value_cache, slots)
+    if slots.numel() == 0:
+        return
+    Hkv, D, bs, blk_stride = _cache_dims(key_cache, value_cache)
+    _dtype_code(key_cache)
+    if slots.dtype != torch.int64 or not slots.is_contiguous():
+        raise RuntimeError("slots must be a contiguous int64 tensor")
+    check(_lib.load().pc_zero_cache_slots(key_cache.data_ptr(), value_cache.data_ptr(), slots.data_ptr(),
+                                          slots.numel(), Hkv, D, bs, blk_stride, _stream(key_cache)))
+    _launched()
+
+
+def zero_cache_slots_layers(key_ptrs: torch.Tensor, value_ptrs: torch.Tensor, slots: torch.Tensor,
+                            num_kv_heads: int, head_size: int, block_size: int, kv_block_stride: int) -> None:
+    """The same for every layer of a step in one launch.  key_ptrs / value_ptrs int64 [L] on the
+    device (pool base pointers per layer), slots int64 [L, n] on the device."""
+    _req_cuda(key_ptrs, value_ptrs, slots)
+    L, n = slots.shape
+    if key_ptrs.dtype != torch.int64 or value_ptrs.dtype != torch.int64 or key_ptrs.numel() != L \
+            or value_ptrs.numel() != L:
+        raise RuntimeError("key_ptrs / value_ptrs must be int64 [L]")
+    if slots.dtype != torch.int64 or slots.stride(1) != 1:
+        raise RuntimeError("slots must be int64 [L, n] with contiguous rows")
+    check(_lib.load().pc_zero_cache_slots_layers(key_ptrs.data_ptr(), value_ptrs.data_ptr(), slots.data_ptr(),
+                                                 slots.stride(0), n, L, num_kv_heads, head_size, block_size,
+                                                 kv_block_stride, _stream(slots)))
     _launched()
 
 

@@ -54,7 +54,7 @@ def decode_trigger(seq_len: int, kv_len_before: int, cfg, block_size: int) -> bo
     one block?  kv_len_before = physical KV length including the new token.
     budget: torch_cuda_sdpa.py:1390-1407, model_runner.py:540-543.
     percentage: torch_cuda_sdpa.py:1310 + page_evict_kv_util_bak.py:69."""
-    if cfg is None:
+    if cfg is None or cfg.decode_evict_method == "inverse_key_l2":   # model_runner.py:545-547: never frees
         return False
     n_blocks = cdiv(kv_len_before, block_size)
     if n_blocks < 3:                                 # sink + victim + just-filled block
@@ -63,3 +63,33 @@ def decode_trigger(seq_len: int, kv_len_before: int, cfg, block_size: int) -> bo
         return seq_len > cfg.cache_budget and seq_len % block_size == 0
     return (seq_len % (block_size * cfg.evict_freq) == 0
             and n_blocks * block_size > (cfg.initial_blocks + cfg.num_block_merge) * block_size)
+
+
+def random_victim(rng, n_blocks: int, cfg) -> int:
+    """HEAD as shipped (`enable_random_evict = True`, torch_cuda_sdpa.py:802): the victim of a
+    triggered row is one `randint` from the process-wide Python RNG (:796 seeds it with 1234 in
+    every layer's constructor) -- local window [1, topk] (:1504-1509, not clamped to the table),
+    global [1, n-2] (:1510-1513)."""
+    if cfg.topk_blocks is not None and cfg.topk_blocks > 0:
+        return rng.randint(1, cfg.topk_blocks)
+    return rng.randint(1, n_blocks - 2)
+
+
+def zero_slot(rng, seq_len: int, table, cfg, block_size: int) -> int:
+    """W2: the cache slot whose K and V rows are zeroed on this decode step, or -1.
+    streamingLLM-1 (torch_cuda_sdpa.py:1390-1401): over budget and off a block boundary -> slot
+      (seq_len % bs - 1) of the table's 2nd block.
+    inverse_key_l2 (:1444-1454): over budget -> a random slot of a random middle block, two draws
+      per row (block, then slot)."""
+    if seq_len <= cfg.cache_budget:
+        return -1
+    m = cfg.decode_evict_method
+    if m == "streamingLLM-1":
+        if seq_len % block_size == 0:
+            return -1
+        return int(table[1]) * block_size + (seq_len % block_size - 1)
+    if m == "inverse_key_l2":
+        blk = rng.randint(1, len(table) - 2)
+        off = rng.randint(0, block_size - 1)
+        return int(table[blk]) * block_size + off
+    return -1
