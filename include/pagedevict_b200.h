@@ -276,6 +276,28 @@ int pc_prefill_attn_topleft_causal(void* out, const void* query, const void* key
                                    int64_t value_stride, const int32_t* req_meta_host /* HOST or NULL */,
                                    int32_t dtype, void* stream);
 
+/* ---- f3: token-level prompt prune of `local` / `global` / `inverse_key_l2` ---------------
+ * Replaces the second branch of KVCachePruner.prune_prompt_inplace
+ * (vllm/attention/kvcache_prunner.py:220-279) for a whole prefill batch.  Request r:
+ * req_meta int32 [num_reqs][6] = {src_start, q_len, first, mid, k_drop, dst_start}: source rows
+ * [src_start, src_start + q_len); tokens [0, first) and [first + mid, q_len) are copied; of the
+ * middle tokens [first, first + mid) every kv HEAD drops its k_drop lowest-scoring ones
+ * (score_kind 0: ||V[t,h,:]||_2, 1: 1 / (||K[t,h,:]||_2 + 1e-8); fp32, fixed order of
+ * csrc/score_common.cuh; equal scores: lowest token index goes first).  The q_len - k_drop
+ * output rows start at out row dst_start.  head_mixing_repack != 0 reproduces the reference's
+ * `middle[mask].view(-1, H, D)` (survivors in token-major, head-minor order re-chunked H at a
+ * time, so a column mixes source heads -- SURVEY.md 0.5); 0 keeps each head's survivors in its
+ * own column.  mid_offsets / tok_offsets int32 [num_reqs + 1] = prefix sums of mid / q_len.
+ * workspace: pc_prompt_token_prune_workspace_bytes(total_mid, heads) bytes, 256-byte aligned. */
+size_t pc_prompt_token_prune_workspace_bytes(int64_t total_mid, int32_t num_kv_heads);
+int pc_prompt_token_prune(const void* key, const void* value, void* out_key, void* out_value,
+                          const int32_t* req_meta, const int32_t* mid_offsets, const int32_t* tok_offsets,
+                          int32_t num_reqs, int64_t total_tokens, int64_t total_mid, int32_t num_kv_heads,
+                          int32_t head_size, int32_t score_kind, int32_t head_mixing_repack,
+                          int64_t key_stride, int64_t value_stride, int64_t out_key_stride,
+                          int64_t out_value_stride, void* workspace, size_t workspace_bytes, int32_t dtype,
+                          void* stream);
+
 /* ---- W2: slot zeroing of `streamingLLM-1` / `inverse_key_l2` --------------------------
  * Replaces the all-zero K/V rows the reference appends to the decode step's reshape_and_cache
  * call (TmpCacheSingleton rows, torch_cuda_sdpa.py:919-933,962-975; slots chosen at :1396-1401 --

@@ -30,14 +30,14 @@ from typing import Dict, List, Optional, Sequence, Tuple
 import numpy as np
 import torch
 
-from . import paged_ops, policy, scoring
+from . import paged_ops, policy, scoring, token_prune
 from .policy import Policy
 
 
 class OracleLayer:
     def __init__(self, num_heads: int, head_size: int, scale: float, num_kv_heads: int,
                  pol: Optional[Policy], head_compat_uncompacted: bool = False, native_ops=None,
-                 rng=None):
+                 rng=None, head_mixing_repack: bool = True):
         """native_ops: object providing reshape_and_cache / paged_attention with the
         signatures of oracle/paged_ops.py (default: that torch restatement;
         oracle/ref_cpu.RefCpuOps = the reference's own compiled CPU kernels)."""
@@ -48,6 +48,7 @@ class OracleLayer:
         # HEAD's process-wide `random` (torch_cuda_sdpa.py:796): ONE random.Random(1234) shared by
         # every layer of the model, drawn from in layer order, rows in row order
         self.rng = rng
+        self.repack = head_mixing_repack
         # physical block id -> per-head partial scores [Hkv] fp32 (D3)
         self.block_scores: Dict[int, np.ndarray] = {}
         self.last = {}
@@ -64,16 +65,23 @@ class OracleLayer:
         k = key.view(-1, self.Hkv, self.D)
         v = value.view(-1, self.Hkv, self.D)
         kc, vc = paged_ops.split_kv_cache(kv_cache, self.Hkv, self.D)
-        gidx, kept, slots = [], [], []
+        kept, slots, kps, vps = [], [], [], []
         s = 0
+        tok_kind = {"token_value_l2": "value_l2", "token_inverse_key_l2": "inverse_key_l2"}.get(p.prompt_evict_method)
         for L, tab in zip(seq_lens, block_tables):
-            gi = policy.prompt_gather_index(L, p)
-            gidx.append(torch.from_numpy(gi) + s)
-            kept.append(len(gi))
+            if tok_kind is not None:      # f3: per-head token drop + the reference's re-pack
+                pk, pv = token_prune.prune_prompt(k[s:s + L].float().numpy(), v[s:s + L].float().numpy(),
+                                                  p.cache_budget, bs, tok_kind, repack=self.repack)
+                kps.append(torch.from_numpy(pk).to(k.dtype))
+                vps.append(torch.from_numpy(pv).to(v.dtype))
+            else:
+                gi = torch.from_numpy(policy.prompt_gather_index(L, p)) + s
+                kps.append(k[gi])
+                vps.append(v[gi])
+            kept.append(kps[-1].shape[0])
             slots.extend(policy.prefill_slot_mapping(list(tab), L, bs))
             s += L
-        gidx = torch.cat(gidx)
-        kp, vp = k[gidx], v[gidx]
+        kp, vp = torch.cat(kps), torch.cat(vps)
         assert len(slots) == kp.shape[0]
         self.ops.reshape_and_cache(kp, vp, kc, vc, torch.tensor(slots, dtype=torch.long))
         # scores of every FULL cached prompt block (D2)

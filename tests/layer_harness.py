@@ -28,12 +28,13 @@ def make_configs(c: Dict):
     pe = PagedEvictConfig(
         disable_evict_prefill=c.get("disable_evict_prefill", False), cache_prune_type=c["prune"],
         evict_method=None if topk < 0 else "local", cache_budget=c.get("budget", 128),
-        topk_blocks=topk if topk > 0 else 3, prompt_evict_method="streamingLLM",
+        topk_blocks=topk if topk > 0 else 3, prompt_evict_method=c.get("prompt", "streamingLLM"),
         decode_evict_method=decode, evict_freq=c.get("evict_freq", 2))
     if topk < 0:
         pe.topk_blocks = -1
     pol = Policy(block_size=bs, cache_prune_type=c["prune"], cache_budget=c.get("budget", 128),
                  evict_freq=c.get("evict_freq", 2), decode_evict_method=decode, topk_blocks=topk,
+                 prompt_evict_method=c.get("prompt", "streamingLLM"),
                  disable_evict_prefill=c.get("disable_evict_prefill", False))
     return CacheConfig(block_size=bs, paged_evict_config=pe, max_num_seqs=c.get("max_num_seqs", 16)), pol
 
@@ -54,7 +55,9 @@ def run_case(c: Dict, device="cuda:0", num_layers=2, num_blocks=256, check_outpu
     eng = PagedEvictEngine(num_layers, Hq, Hkv, D, cache_config, num_blocks, device=device,
                            max_num_batched_tokens=c.get("max_num_batched_tokens", 1 << 30))
     assert pol is not None, "the harness drives eviction-enabled cases"
-    layers = [OracleLayer(Hq, D, D ** -0.5, Hkv, pol) for _ in range(num_layers)]
+    import random
+    rng = random.Random(1234)        # the oracle's twin of the engine's host RNG (HEAD: shared by all layers)
+    layers = [OracleLayer(Hq, D, D ** -0.5, Hkv, pol, rng=rng) for _ in range(num_layers)]
     kv_ref = [torch.zeros(2, num_blocks, bs * Hkv * D, dtype=torch.bfloat16) for _ in range(num_layers)]
     for i, L in enumerate(c["prompt_lens"]):
         eng.add_request(f"r{i}", L)

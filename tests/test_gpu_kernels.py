@@ -642,3 +642,47 @@ def test_decode_layer_fused_cache_write(Hq, Hkv, D, bs, B, max_len):
     assert torch.equal(s0, s1)
     assert any(int(x) % bs == 0 for x in kv_lens) and s1.abs().sum() > 0
     np.testing.assert_allclose(o1.float().numpy(), ref.numpy(), atol=8e-3, rtol=0)
+
+
+@pytest.mark.parametrize("repack", [True, False])
+@pytest.mark.parametrize("kind,D", [("value_l2", 64), ("inverse_key_l2", 128)])
+def test_prompt_token_prune_bit_exact(kind, D, repack):
+    """f3: pc_prompt_token_prune against oracle/token_prune.py (itself pinned to the reference's
+    prune_prompt_inplace): a batch of prompts below / at / above the budget, with duplicated
+    tokens so that equal scores straddle the cut (ties -> lowest token index goes first).  Pure
+    gather: bit-exact."""
+    from oracle import token_prune
+    from tests.util import token_prune_data
+    bs, budget, H = 16, 128, 4
+    lens = [300, 100, 131, 128, 1030, 161]
+    ks, vs = [], []
+    for i, L in enumerate(lens):
+        k, v = token_prune_data(500 + i, L, H, D)
+        if L > 200:      # ties: copy a few middle tokens over others (all heads / one head)
+            k[40:48], v[40:48] = k[60:68].clone(), v[60:68].clone()
+            k[90, 1], v[90, 1] = k[33, 1].clone(), v[33, 1].clone()
+        ks.append(k.to(torch.bfloat16))
+        vs.append(v.to(torch.bfloat16))
+    key, value = torch.cat(ks).to(DEV), torch.cat(vs).to(DEV)
+    tp6, moff, qoff = [], [0], [0]
+    src = dst = 0
+    want_k, want_v = [], []
+    for L, k, v in zip(lens, ks, vs):
+        first, mid, kd = token_prune.prune_layout(L, budget, bs)
+        tp6.append((src, L, first, mid, kd, dst))
+        moff.append(moff[-1] + mid)
+        qoff.append(qoff[-1] + L)
+        pk, pv = token_prune.prune_prompt(k.float().numpy(), v.float().numpy(), budget, bs, kind, repack=repack)
+        assert pk.shape[0] == L - kd
+        want_k.append(torch.from_numpy(pk).to(torch.bfloat16))
+        want_v.append(torch.from_numpy(pv).to(torch.bfloat16))
+        src += L
+        dst += L - kd
+    i32 = lambda x: torch.tensor(x, dtype=torch.int32, device=DEV)
+    out_k = torch.full_like(key, 7.0)
+    out_v = torch.full_like(value, 7.0)
+    ops.prompt_token_prune(key, value, out_k, out_v, i32(tp6), i32(moff), i32(qoff), qoff[-1], moff[-1], kind,
+                           head_mixing_repack=repack)
+    torch.cuda.synchronize()
+    assert torch.equal(out_k[:dst].cpu(), torch.cat(want_k)) and torch.equal(out_v[:dst].cpu(), torch.cat(want_v))
+    assert bool((out_k[dst:] == 7.0).all()) and bool((out_v[dst:] == 7.0).all())     # nothing written past the end

@@ -236,3 +236,31 @@ def test_value_l2_definition_properties():
         assert scoring.per_head_block_score(v[:, h:h + 1])[0] == ph[h]
     ref = scoring.reference_formula_fp32(v)
     assert abs(float(scoring.combine_heads(ph)) - ref) < 1e-5 * ref
+
+
+def test_token_prune_oracle_matches_reference():
+    """f3: oracle/token_prune.py against the reference's own prune_prompt_inplace output
+    (kvcache_prunner.py:220-279, run in fp32 on CPU by make_golden_token_prune.py): kept vectors
+    and the head-mixing re-pack order, bit for bit."""
+    from oracle import token_prune
+    from tests.util import TOKEN_PRUNE_METHODS, token_prune_data
+    g = load_npz("ref_token_prune.npz")
+    n_pruned = 0
+    for ci, (mi, bs, budget, q_len, H, D, seed, L) in enumerate(g["meta"].tolist()):
+        method = TOKEN_PRUNE_METHODS[mi]
+        k, v = token_prune_data(seed, q_len, H, D)
+        kind = "inverse_key_l2" if method == "inverse_key_l2" else "value_l2"
+        ok, ov = token_prune.prune_prompt(k.numpy(), v.numpy(), budget, bs, kind, repack=True)
+        assert ok.shape == (L, H, D)
+        want_k = torch.from_numpy(g[f"k_{ci}"]).view(torch.bfloat16).float().numpy()
+        want_v = torch.from_numpy(g[f"v_{ci}"]).view(torch.bfloat16).float().numpy()
+        assert np.array_equal(ok, want_k) and np.array_equal(ov, want_v), ci
+        n_pruned += int(L < q_len)
+        # the per-head variant keeps exactly the same (token, head) vectors, in their own columns
+        pk, _ = token_prune.prune_prompt(k.numpy(), v.numpy(), budget, bs, kind, repack=False)
+        assert pk.shape == ok.shape
+        first, mid, kd = token_prune.prune_layout(q_len, budget, bs)
+        if kd:
+            assert sorted(map(bytes, pk[first:first + mid - kd].reshape(-1, D))) == \
+                sorted(map(bytes, ok[first:first + mid - kd].reshape(-1, D)))
+    assert n_pruned >= 6

@@ -42,3 +42,17 @@ def trace_decode_method(cfg):
     if m in ("local", "global"):
         return ("random" if cfg.get("random_evict") else "value_l2"), (cfg.get("topk", 3) if m == "local" else -1)
     return m, -1
+
+
+def token_prune_data(seed, q_len, H, D):
+    """K / V [q_len, H, D] fp32 holding bf16-representable values with spread-out per-token norms
+    (the stream tests/golden/make_golden_token_prune.py fed to the reference)."""
+    rs = np.random.RandomState(seed)
+    k = torch.from_numpy(rs.standard_normal((q_len, H, D)).astype(np.float32)).to(torch.bfloat16).float()
+    sc = torch.from_numpy(rs.uniform(0.3, 3.0, size=(q_len, H, 1)).astype(np.float32))
+    v = (torch.from_numpy(rs.standard_normal((q_len, H, D)).astype(np.float32)) * sc).to(torch.bfloat16).float()
+    k = (k * torch.from_numpy(rs.uniform(0.3, 3.0, size=(q_len, H, 1)).astype(np.float32))).to(torch.bfloat16).float()
+    return k, v
+
+
+TOKEN_PRUNE_METHODS = ["global", "local", "inverse_key_l2"]

@@ -69,6 +69,9 @@ PROTOTYPES = {
                                                  _P, _I64, _I64, _P, _P]),
     "pc_prefill_attn_topleft_causal": (C.c_int, [_P, _P, _P, _P, _P, _I32, _I32, _I64, _I32, _I32, _I32, _F,
                                                  _I64, _I64, _I64, _I64, _P, _I32, _P]),
+    "pc_prompt_token_prune_workspace_bytes": (_SZ, [_I64, _I32]),
+    "pc_prompt_token_prune": (C.c_int, [_P, _P, _P, _P, _P, _P, _P, _I32, _I64, _I64, _I32, _I32, _I32, _I32,
+                                        _I64, _I64, _I64, _I64, _P, _SZ, _I32, _P]),
     "pc_zero_cache_slots": (C.c_int, [_P, _P, _P, _I32, _I32, _I32, _I32, _I64, _P]),
     "pc_zero_cache_slots_layers": (C.c_int, [_P, _P, _P, _I64, _I32, _I32, _I32, _I32, _I32, _I64, _P]),
     "pc_copy_blocks": (C.c_int, [_P, _P, _P, _I32, _I64, _P]),

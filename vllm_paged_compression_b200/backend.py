@@ -397,6 +397,10 @@ class TorchCUDASDPABackendImpl(AttentionImpl[TorchCUDASDPAMetadata]):
         # the flag reproduces HEAD for the golden traces.
         self.head_compat_uncompacted = bool(kwargs.get(
             "head_compat_uncompacted", os.environ.get("PC_HEAD_COMPAT_UNCOMPACTED", "0") == "1"))
+        # f3: True = the reference's `middle[mask].view(-1, H, D)` re-pack, which mixes source heads
+        # inside a column; False keeps each head's surviving tokens in its own column
+        self.head_mixing_repack = bool(kwargs.get(
+            "head_mixing_repack", os.environ.get("PC_HEAD_MIXING_REPACK", "1") == "1"))
         self.rng = kwargs.get("rng", None)
         if self.rng is None and self.enabled_paged_eviction and \
                 self.paged_evict_config.decode_evict_method in ("random", "inverse_key_l2"):
@@ -463,11 +467,24 @@ class TorchCUDASDPABackendImpl(AttentionImpl[TorchCUDASDPAMetadata]):
         if md.num_prefills > 0:
             seq_lens = md.seq_lens[:md.num_prefills]
             m5, m6, m6_full, toff = [], [], [], [0]
+            # f3: token-level prompt methods prune into a packed tensor first (rows dst ..), the
+            # cache write and the attention then read that tensor with an identity gather
+            tok = (cfg is not None and cfg.prompt_evict_method != "streamingLLM"
+                   and any(prompt_prune_layout(L, cfg, bs)[1] > 0 for L in seq_lens))
+            tp6, moff, qoff = [], [0], [0]
             src = dst = 0
             for L in seq_lens:
                 kept, pruned, first = prompt_prune_layout(L, cfg, bs)
-                m5.append((src, kept, first, pruned, dst))
-                m6.append((src, L, src, kept, first, pruned))
+                if tok:
+                    mid = (L - first - (bs + L % bs)) if pruned > 0 else 0
+                    tp6.append((src, L, first, mid, pruned, dst))
+                    moff.append(moff[-1] + mid)
+                    qoff.append(qoff[-1] + L)
+                    m5.append((dst, kept, kept, 0, dst))
+                    m6.append((src, L, dst, kept, kept, 0))
+                else:
+                    m5.append((src, kept, first, pruned, dst))
+                    m6.append((src, L, src, kept, first, pruned))
                 m6_full.append((src, L, src, L, L, 0))
                 toff.append(toff[-1] + -(-kept // bs))
                 src += L
@@ -479,6 +496,12 @@ class TorchCUDASDPABackendImpl(AttentionImpl[TorchCUDASDPAMetadata]):
             pack = [np.asarray(m5, np.int32).reshape(-1), np.asarray(toff, np.int32),
                     st["m6_host"].reshape(-1)]
             names = ["m5", "toff", "m6"]
+            st["token_prune"] = tok
+            if tok:
+                st["total_mid"], st["total_tokens"] = moff[-1], qoff[-1]
+                pack += [np.asarray(tp6, np.int32).reshape(-1), np.asarray(moff, np.int32),
+                         np.asarray(qoff, np.int32)]
+                names += ["tp6", "moff", "qoff"]
         else:
             kv = md.seq_kv_lens if md.seq_kv_lens else md.seq_lens
             if md.reqid_mapping_blocktables:
@@ -508,6 +531,8 @@ class TorchCUDASDPABackendImpl(AttentionImpl[TorchCUDASDPAMetadata]):
         if "m5" in st:
             st["m5"] = st["m5"].view(-1, 5)
             st["m6"] = st["m6"].view(-1, 6)
+        if "tp6" in st:
+            st["tp6"] = st["tp6"].view(-1, 6)
         md._pc_step = st
         return st
 
@@ -544,18 +569,28 @@ class TorchCUDASDPABackendImpl(AttentionImpl[TorchCUDASDPAMetadata]):
         return out.view(-1, self.num_heads * self.head_size)
 
     def _forward_prefill(self, q, k, v, out, md, st, kv_cache) -> None:
+        kc_src, vc_src = k, v
+        if st.get("token_prune"):
+            # f3 (kvcache_prunner.py:220-279): per head the lowest-scoring middle tokens go, the
+            # survivors are re-packed the reference's way; T rows so q / k / v share one TMA bound
+            kc_src, vc_src = torch.empty_like(k), torch.empty_like(v)
+            ops.prompt_token_prune(k, v, kc_src, vc_src, st["tp6"], st["moff"], st["qoff"], st["total_tokens"],
+                                   st["total_mid"], self.paged_evict_config.prompt_evict_method,
+                                   head_mixing_repack=self.head_mixing_repack)
         if kv_cache is not None:
             key_cache, value_cache, _ = self._caches(kv_cache)
             score = self._scores(q.device, kv_cache.shape[1]) if self._value_l2 else None
             if self.enabled_paged_eviction:
                 # R1 + W1 + S3 in one pass; slot_mapping has exactly `kept` entries per request
-                ops.prune_prompt_and_cache(k, v, key_cache, value_cache, md.slot_mapping, st["m5"],
+                ops.prune_prompt_and_cache(kc_src, vc_src, key_cache, value_cache, md.slot_mapping, st["m5"],
                                            st["toff"], st["total_tiles"], score)
             else:
                 ops.reshape_and_cache(k, v, key_cache, value_cache, md.slot_mapping)
         # A1: top-left aligned causal mask over the kept rows (or all rows when
         # disable_evict_prefill / eviction off) -- torch_cuda_sdpa.py:1069-1127
-        ops.prefill_attn_topleft_causal(out, q, k, v, st["m6"], md.max_query_len, self.scale,
+        if self.enabled_paged_eviction and self.paged_evict_config.disable_evict_prefill:
+            kc_src, vc_src = k, v
+        ops.prefill_attn_topleft_causal(out, q, kc_src, vc_src, st["m6"], md.max_query_len, self.scale,
                                         req_meta_host=st["m6_host"])
 
     def _decode_step_struct(self, q, k, v, out, md, st, blk_stride: int, bs: int):

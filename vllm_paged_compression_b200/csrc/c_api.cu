@@ -336,6 +336,34 @@ int pc_copy_blocks(void* key_cache, void* value_cache, const int64_t* pairs, int
                      block_bytes, static_cast<cudaStream_t>(stream));
 }
 
+size_t pc_prompt_token_prune_workspace_bytes(int64_t total_mid, int32_t num_kv_heads) {
+  return token_prune_workspace_bytes(total_mid, num_kv_heads);
+}
+
+int pc_prompt_token_prune(const void* key, const void* value, void* out_key, void* out_value,
+                          const int32_t* req_meta, const int32_t* mid_offsets, const int32_t* tok_offsets,
+                          int32_t num_reqs, int64_t total_tokens, int64_t total_mid, int32_t num_kv_heads,
+                          int32_t head_size, int32_t score_kind, int32_t head_mixing_repack,
+                          int64_t key_stride, int64_t value_stride, int64_t out_key_stride,
+                          int64_t out_value_stride, void* workspace, size_t workspace_bytes, int32_t dtype,
+                          void* stream) {
+  if (int rc = check_dtype(dtype)) return rc;
+  if (num_reqs == 0 || total_tokens == 0) return PC_OK;
+  if (!key || !value || !out_key || !out_value || !req_meta || !mid_offsets || !tok_offsets || !workspace)
+    return set_error(PC_ERR_INVALID, "pc_prompt_token_prune: null pointer");
+  if (score_kind != 0 && score_kind != 1)
+    return set_error(PC_ERR_INVALID, "pc_prompt_token_prune: score_kind must be 0 (value_l2) or 1 (inverse_key_l2)");
+  TokenPruneArgs a{};
+  a.key = key; a.value = value; a.out_key = out_key; a.out_value = out_value;
+  a.req_meta = req_meta; a.mid_offsets = mid_offsets; a.tok_offsets = tok_offsets;
+  a.num_reqs = num_reqs; a.total_tokens = total_tokens; a.total_mid = total_mid;
+  a.Hkv = num_kv_heads; a.D = head_size; a.score_kind = score_kind; a.repack = head_mixing_repack;
+  a.key_stride = key_stride; a.value_stride = value_stride;
+  a.out_key_stride = out_key_stride; a.out_value_stride = out_value_stride;
+  a.workspace = workspace; a.workspace_bytes = workspace_bytes;
+  return prompt_token_prune(a, static_cast<cudaStream_t>(stream));
+}
+
 int pc_zero_cache_slots(void* key_cache, void* value_cache, const int64_t* slots, int32_t num_slots,
                         int32_t num_kv_heads, int32_t head_size, int32_t block_size,
                         int64_t kv_block_stride, void* stream) {

@@ -132,6 +132,24 @@ void set_prefill_tc_tile(int tn);       // kv tile width of the tcgen05 kernel (
 void set_cache_write_block_heads(int hc);  // heads per CTA of cache_write_block_kernel, 0 = rule
 #endif
 
+struct TokenPruneArgs {
+  const void* key;
+  const void* value;
+  void* out_key;
+  void* out_value;
+  const int* req_meta;      // DEVICE [R][6] {src_start, q_len, first, mid, k_drop, dst_start}
+  const int* mid_offsets;   // DEVICE [R+1]
+  const int* tok_offsets;   // DEVICE [R+1]
+  int num_reqs;
+  long long total_tokens, total_mid;
+  int Hkv, D, score_kind, repack;
+  long long key_stride, value_stride, out_key_stride, out_value_stride;
+  void* workspace;
+  size_t workspace_bytes;
+};
+size_t token_prune_workspace_bytes(long long total_mid, int Hkv);
+int prompt_token_prune(const TokenPruneArgs& a, cudaStream_t stream);
+
 struct ZeroSlotsArgs {
   void* const* k_caches;   // DEVICE [num_layers] pool pointers, or nullptr: k0 / v0 is the one layer
   void* const* v_caches;

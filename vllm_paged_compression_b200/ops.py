@@ -383,6 +383,39 @@ def prefill_attn_topleft_causal(out: torch.Tensor, query: torch.Tensor, key: tor
     _launched()
 
 
+# ------------------------------------------------------------------------------ f3
+_TOKEN_SCORE_KIND = {"token_value_l2": 0, "value_l2": 0, "token_inverse_key_l2": 1, "inverse_key_l2": 1}
+
+
+def prompt_token_prune(key: torch.Tensor, value: torch.Tensor, out_key: torch.Tensor, out_value: torch.Tensor,
+                       req_meta: torch.Tensor, mid_offsets: torch.Tensor, tok_offsets: torch.Tensor,
+                       total_tokens: int, total_mid: int, kind: str, head_mixing_repack: bool = True,
+                       workspace: Optional[torch.Tensor] = None) -> None:
+    """Token-level prompt prune of local / global / inverse_key_l2 (kvcache_prunner.py:220-279) for a
+    prefill batch.  key/value [T, Hkv, D] -> out_key/out_value rows [dst_start, dst_start + q_len -
+    k_drop) per request.  req_meta int32 [R, 6] = {src_start, q_len, first, mid, k_drop, dst_start},
+    mid_offsets / tok_offsets int32 [R + 1] (device)."""
+    _req_cuda(key, value, out_key, out_value, req_meta, mid_offsets, tok_offsets)
+    T, Hkv, D = key.shape
+    for t in (key, value, out_key, out_value):
+        if t.dim() != 3 or t.shape[1:] != (Hkv, D) or t.stride()[1:] != (D, 1):
+            raise RuntimeError("key/value/out rows must be dense [Hkv, D]")
+    for t in (req_meta, mid_offsets, tok_offsets):
+        if t.dtype != torch.int32 or not t.is_contiguous():
+            raise RuntimeError("req_meta / mid_offsets / tok_offsets must be contiguous int32")
+    lib = _lib.load()
+    need = int(lib.pc_prompt_token_prune_workspace_bytes(int(total_mid), Hkv))
+    if workspace is None:
+        workspace = torch.empty(need, dtype=torch.uint8, device=key.device)
+    check(lib.pc_prompt_token_prune(
+        key.data_ptr(), value.data_ptr(), out_key.data_ptr(), out_value.data_ptr(), req_meta.data_ptr(),
+        mid_offsets.data_ptr(), tok_offsets.data_ptr(), req_meta.shape[0], int(total_tokens), int(total_mid),
+        Hkv, D, _TOKEN_SCORE_KIND[kind], 1 if head_mixing_repack else 0, key.stride(0), value.stride(0),
+        out_key.stride(0), out_value.stride(0), workspace.data_ptr(), workspace.numel(), _dtype_code(key),
+        _stream(key)))
+    _launched(4 if total_mid > 0 else 1)
+
+
 # ------------------------------------------------------------------------------ W2
 def zero_cache_slots(key_cache: torch.Tensor, value_cache: torch.Tensor, slots: torch.Tensor) -> None:
     """Zero the K and V rows (all kv heads) at `slots` (int64 on the device, negative = skip): the
