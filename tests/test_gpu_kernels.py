@@ -681,7 +681,7 @@ def test_prompt_token_prune_bit_exact(kind, D, repack):
     i32 = lambda x: torch.tensor(x, dtype=torch.int32, device=DEV)
     out_k = torch.full_like(key, 7.0)
     out_v = torch.full_like(value, 7.0)
-    ops.prompt_token_prune(key, value, out_k, out_v, i32(tp6), i32(moff), i32(qoff), qoff[-1], moff[-1], kind,
+    _ops().prompt_token_prune(key, value, out_k, out_v, i32(tp6), i32(moff), i32(qoff), qoff[-1], moff[-1], kind,
                            head_mixing_repack=repack)
     torch.cuda.synchronize()
     assert torch.equal(out_k[:dst].cpu(), torch.cat(want_k)) and torch.equal(out_v[:dst].cpu(), torch.cat(want_v))
