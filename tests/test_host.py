@@ -185,3 +185,89 @@ def test_ops_refuse_cpu_tensors():
     k = torch.zeros(1, 2, 64, dtype=torch.bfloat16)
     with pytest.raises(RuntimeError, match="no CPU fallback"):
         ops.reshape_and_cache(k, k, kc, vc, torch.zeros(1, dtype=torch.int64))
+
+
+# ------------------------------------------------------------- f1: the fork's real host objects
+def _product_builder_md(inter_records, seq_lens, query_lens, block_size, cfg, as_objects=None):
+    """Feed the product's TorchCUDASDPAMetadataBuilder an input builder holding `inter_data_list`
+    (recorded attribute values, or the reference's live objects) and build on CPU."""
+    import types
+    from vllm_paged_compression_b200.backend import TorchCUDASDPAMetadataBuilder
+    from vllm_paged_compression_b200.config import CacheConfig as CC
+    if as_objects is None:
+        inter = []
+        for r in inter_records:
+            inter.append(types.SimpleNamespace(
+                request_id=r["request_id"], is_prompt=r["is_prompt"], seq_ids=r["seq_ids"],
+                block_tables=None if r["block_tables"] is None else {int(k): v for k, v in r["block_tables"].items()},
+                input_tokens=[[0] * n for n in r["input_token_lens"]], orig_seq_lens=r["orig_seq_lens"],
+                seq_lens=r["seq_lens"], query_lens=r["query_lens"], context_lens=r["context_lens"],
+                seq_kv_lens=None if r["seq_kv_lens"] is None else {int(k): v for k, v in r["seq_kv_lens"].items()},
+                prefix_cache_hit=r["prefix_cache_hit"]))
+    else:
+        inter = as_objects
+    runner = types.SimpleNamespace(device="cpu", pin_memory=False,
+                                   cache_config=CC(block_size=block_size, paged_evict_config=cfg))
+    ib = types.SimpleNamespace(runner=runner, sliding_window=None, block_size=block_size,
+                               chunked_prefill_enabled=False, inter_data_list=inter)
+    return TorchCUDASDPAMetadataBuilder(ib).build(seq_lens, query_lens, -1, len(seq_lens))
+
+
+def _assert_md_equal(md, want):
+    for k in ("seq_lens", "seq_kv_lens"):
+        assert list(getattr(md, k)) == want[k], k
+    for k in ("num_prefills", "num_prefill_tokens", "num_decode_tokens", "max_query_len", "max_prefill_seq_len",
+              "max_decode_seq_len"):
+        assert int(getattr(md, k)) == want[k], k
+    for k in ("slot_mapping", "seq_lens_tensor", "seq_kv_lens_tensor", "block_tables", "query_start_loc",
+              "seq_start_loc", "context_lens_tensor"):
+        assert getattr(md, k).cpu().tolist() == want[k], k
+    got = {r: {str(s): list(t) for s, t in d.items()} for r, d in md.reqid_mapping_blocktables.items()}
+    assert got == want["reqid_mapping_blocktables"]
+
+
+@pytest.mark.parametrize("name", ["stream_b3", "stream1_b2_bs32", "global_b2", "invkey_b2"])
+def test_metadata_builder_on_reference_host_trace(name):
+    """f1: tests/golden/ref_host.json holds what the fork's REAL Scheduler + SelfAttnBlockSpaceManager
+    + ModelInputForGPUBuilder produced step by step (prefill, decode, eviction feedback) and the
+    metadata its own TorchCUDASDPAMetadataBuilder built from it.  (a) the product builder, fed the
+    same inter_data attribute values, builds identical metadata; (b) the product's block manager +
+    policy arithmetic, stepped on its own, reproduces the reference scheduler's block tables and
+    kv lengths (incl. the allocator's recycling order); (c) the impl's per-step host preparation
+    finds the same trigger rows the reference fed back."""
+    from vllm_paged_compression_b200.backend import TorchCUDASDPABackendImpl
+    from vllm_paged_compression_b200.block_manager import SelfAttnBlockSpaceManager
+    from vllm_paged_compression_b200.config import CacheConfig as CC
+    tr = load_json("ref_host.json")[name]
+    c = tr["cfg"]
+    bs = c["block_size"]
+    cfg = PagedEvictConfig(cache_prune_type="budget", evict_method=c["evict_method"], cache_budget=c["budget"])
+    bm = SelfAttnBlockSpaceManager(bs, 512, cfg)
+    impl = TorchCUDASDPABackendImpl(8, 64, 0.125, 2, None, None, "auto",
+                                    cache_config=CC(block_size=bs, paged_evict_config=cfg),
+                                    prefix="model.layers.0.self_attn.attn")
+    n_evict = 0
+    for si, rec in enumerate(tr["steps"]):
+        md = _product_builder_md(rec["inter"], rec["seq_lens"], rec["query_lens"], bs, cfg)
+        _assert_md_equal(md, rec["md"])
+        # (b) the product's own host bookkeeping
+        if si == 0:
+            for i, L in enumerate(c["prompt_lens"]):
+                bm.allocate(i, L)
+        else:
+            for i in range(len(c["prompt_lens"])):
+                bm.append_slots(i)
+        for i, r in enumerate(rec["inter"]):
+            assert bm.get_block_table(i) == r["block_tables"][str(i)] or si == 0
+            kv = bm.get_seq_kv_len(i)
+            if si > 0 and policy.decode_trigger(r["seq_lens"][0], kv, cfg, bs):
+                kv -= bs                                             # model_runner.py:540-543
+            assert kv == r["seq_kv_lens"][str(i)], (si, i)
+        # (c) the impl's host preparation on this metadata
+        if si > 0:
+            st = impl._prepare_step(md, "cpu", bs)
+            assert st["trigger_rows"] == sorted(int(k) for k in rec["rmv"]), si
+        for row, (rid, idx) in rec["rmv"].items():
+            bm.free_prunned_blocks(int(rid[1:]), idx)
+            n_evict += 1
+    assert (n_evict > 0) == (c["evict_method"] != "inverse_key_l2")
