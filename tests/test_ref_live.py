@@ -30,3 +30,15 @@ def test_product_builder_on_live_reference_objects(method, bs, budget, lens):
         _assert_md_equal(md, metadata_record(md_ref))
         n_evict += len(h.finish_step(md_ref))
     assert n_evict > 0
+
+
+def test_integration_patch_applies_to_the_fork():
+    """integration/vllm_fork.patch (selector + _custom_ops edits of INTEGRATION.md, Options A and B)
+    applies cleanly to the reference checkout (dry run: /root/reference is read-only)."""
+    import subprocess
+    repo = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    with open(os.path.join(repo, "integration", "vllm_fork.patch")) as f:
+        r = subprocess.run(["patch", "-p1", "--dry-run", "-d", "/root/reference"], stdin=f,
+                           stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    assert r.returncode == 0, r.stdout
+    assert "selector.py" in r.stdout and "_custom_ops.py" in r.stdout
