@@ -68,6 +68,9 @@ METRIC = "decode_tok_per_s_paged_eviction_hot_path"
 
 
 @dataclass(frozen=True)
+PREFILL_BATCH_TOKENS = 64 * 1024
+
+
 class Spec:
     """One workload: attention shapes of a model, a batch of equal prompts, an eviction setting.
     `batch` is the GLOBAL batch; under tensor parallelism every rank sees all rows and 1/tp of
@@ -334,7 +337,10 @@ class Arm:
             u = lambda w: (torch.rand(n_tok, w, device=self.device, generator=g) * 2 * s - s).to(torch.bfloat16)
             v = (u(self.Hkv * self.D).float() * (1 + 0.1 * layer)).to(torch.bfloat16)
             return u(self.Hq * self.D), u(self.Hkv * self.D), v
-        self.eng.max_num_batched_tokens = max(16 * 1024, self.spec.prompt_len)
+        # one prefill batch of up to 64 Ki tokens: the fork schedules prompts up to
+        # max_num_batched_tokens (>= max_model_len without chunked prefill, vllm/config.py), so the 64 x
+        # 1024-token prompts of the headline config are ONE prefill step there too
+        self.eng.max_num_batched_tokens = max(PREFILL_BATCH_TOKENS, self.spec.prompt_len)
         while self.eng.waiting:
             so = self.eng.step(qkv, keep_outputs=False)
             assert so.is_prompt
@@ -775,26 +781,29 @@ def main():
         if os.path.exists(ppath):
             with open(ppath) as f:
                 peaks = json.load(f)
-        # prompt-time kernels of the same workload.  A1: one layer's launch for 16 of the
-        # prompts (as the engine batches them), tcgen05 kernel, tensor-bound
-        row, _ = microbench_prefill.run(device, 16, spec.prompt_len, spec.Hq, spec.Hkv, spec.D,
+        # prompt-time kernels of the same workload.  A1: one layer's launch for one prefill batch
+        # (as the engine batches them: up to 64 Ki tokens), tcgen05 kernel, tensor-bound
+        pre_reqs = max(1, min(spec.batch, PREFILL_BATCH_TOKENS // spec.prompt_len))
+        row, _ = microbench_prefill.run(device, pre_reqs, spec.prompt_len, spec.Hq, spec.Hkv, spec.D,
                                         spec.evict_freq, 20)
         tpeak = float(peaks.get("bf16_tflops", 2250.0))
         line["prefill_roofline"] = {
             "bound": "tensor", "kernel": "prefill_attn_tc_kernel (tcgen05.mma, TMEM accumulators, TMA loads)",
             "achieved": row["tflops"], "peak": tpeak, "unit": "TFLOP/s", "frac": row["tflops"] / tpeak,
             "peak_source": "measured burst (MEASURED_PEAKS.json bf16_tflops)" if peaks else "nominal dense bf16",
-            "us_per_launch": row["us"], "launch": f"16 prompts x {spec.prompt_len} q, {row['kv_kept']} kept kv, "
+            "us_per_launch": row["us"], "launch": f"{pre_reqs} prompts x {spec.prompt_len} q, {row['kv_kept']} kept kv, "
             "top-left causal, one layer", "flops_per_launch": row["tflops"] * 1e12 * row["us"] * 1e-6}
         # W1 + R1 + S3: one layer's prompt prune + cache write + block scoring, HBM-bound
-        cw = microbench_cache_write.run(device, 16, spec.prompt_len, spec.Hkv, spec.D, spec.block_size,
+        cw = microbench_cache_write.run(device, pre_reqs, spec.prompt_len, spec.Hkv, spec.D, spec.block_size,
                                         spec.evict_freq)
         hpeak, hsrc = load_peaks()
         line["cache_write_roofline"] = {
-            "bound": "hbm", "kernel": "cache_write_kernel (prune gather + reshape_and_cache + block scores)",
+            "bound": "hbm", "kernel": "cache_write_stream_kernel (prune gather + reshape_and_cache + block scores, persistent TMA pipeline)",
             "achieved": cw["gbs"], "peak": hpeak, "unit": "GB/s", "frac": cw["gbs"] / hpeak, "peak_source": hsrc,
             "traffic": None, "algorithmic_bytes_per_launch": cw["bytes"], "us_per_launch": cw["us"],
-            "launch": cw["launch"]}
+            "launch": cw["launch"],
+            # the floor at this size: a plain device copy of the same bytes, timed the same way
+            "copy_same_bytes_us": cw["copy_same_bytes_us"], "frac_of_same_size_copy": cw["copy_same_bytes_us"] / cw["us"]}
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         carm = CpuArm(spec, min(4, spec.layers), 64)
         t0 = time.perf_counter()

@@ -61,7 +61,21 @@ def run(device, reqs, L, Hkv, D, bs, evict_freq, reps=40, score=True):
     e1.record()
     torch.cuda.synchronize()
     sec = e0.elapsed_time(e1) / 1e3 / reps
-    return {"us": sec * 1e6, "bytes": 2 * bytes_rw, "gbs": 2 * bytes_rw / sec / 1e9, "kept": kept, "sets": n_sets,
+    # the floor at this size: a plain device copy of the same bytes (read bytes_rw, write bytes_rw),
+    # rotating over the same number of buffer sets
+    nel = bytes_rw // 2
+    srcs = [torch.empty(nel, dtype=torch.bfloat16, device=device).normal_() for _ in range(n_sets)]
+    dsts = [torch.empty(nel, dtype=torch.bfloat16, device=device) for _ in range(n_sets)]
+    for i in range(n_sets):
+        dsts[i].copy_(srcs[i])
+    torch.cuda.synchronize()
+    e0.record()
+    for i in range(reps):
+        dsts[i % n_sets].copy_(srcs[i % n_sets])
+    e1.record()
+    torch.cuda.synchronize()
+    copy_us = e0.elapsed_time(e1) * 1e3 / reps
+    return {"us": sec * 1e6, "copy_same_bytes_us": copy_us, "bytes": 2 * bytes_rw, "gbs": 2 * bytes_rw / sec / 1e9, "kept": kept, "sets": n_sets,
             "launch": f"{reqs} prompts x {L} tokens, {kept} kept, Hkv {Hkv}, D {D}, block {bs}, one layer, "
                       f"{n_sets} rotating source/pool sets, scoring {'on' if score else 'off'}"}
 

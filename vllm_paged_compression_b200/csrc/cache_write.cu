@@ -346,6 +346,283 @@ static int launch_block_write(const CacheWriteParams& p, int tiles, cudaStream_t
   return check_launch("cache_write_block_kernel");
 }
 
+// ------------------------------------------------------------------------------------------
+// Prompt-time streaming path: PERSISTENT CTAs, one per SM, each walking a contiguous range of
+// work items (item = one cache block x HC kv heads) through a multi-stage shared-memory pipeline.
+//
+// The block kernel above is one short-lived CTA per item: request lookup -> slot check -> loads
+// -> stores are a dependent chain that every CTA pays again, and only ~3 CTAs per SM overlap
+// (ncu, profiles/r02_cache_write_block_ncu_summary.txt: 36 % warps active, 4.6 TB/s at 64
+// prompts).  Here one PRODUCER warp runs ahead of eight CONSUMER warps:
+//   producer : item -> (request, block) with the request carried in registers (items of a CTA are
+//              consecutive blocks, a request boundary is crossed every ~34 items), the block's slots
+//              prefetched one item ahead, then BS + BS TMA 1-D row copies (K rows and V rows of the
+//              item's HC heads, gathered: the streamingLLM prune is the row index) into stage s,
+//              completing on full[s]; NST stages (128 KiB of loads in flight per SM at D 128)
+//   consumers: K units [tok][u] -> [u][tok] from shared memory to the pool with 16-byte stores that
+//              are contiguous across the warp; V rows -> transposed block image (ldmatrix.trans +
+//              stmatrix) -> ONE bulk store per item (two images, the store of item i drains while
+//              item i+1 is transposed); prompt block scores from the staged V rows; then empty[s].
+struct StreamDesc {      // written by the producer, read by the consumers after full[s]
+  long long blk;         // physical block (whole items)
+  int ntok, whole, h0, pad;
+  long long pad1;        // 32 bytes: the per-token slots follow
+};
+static_assert(sizeof(StreamDesc) == 32, "StreamDesc must be 32 bytes");
+
+constexpr int kStreamConsumerWarps = 8;
+constexpr int kStreamThreads = (kStreamConsumerWarps + 1) * 32;
+
+template <int D, int BS, int HC, int NST>
+struct StreamSmem {
+  static constexpr int kRow = HC * D * 2;               // one token's rows of the item's heads
+  static constexpr int kPitch = kRow + 16;              // staging pitch (bank spread for ldmatrix / LDS.128)
+  static constexpr int kTensor = BS * kPitch;           // K (or V) rows of one item
+  static constexpr int kStageIn = 2 * kTensor;
+  static constexpr int kImage = HC * D * BS * 2;        // V block image of the item's heads
+  static constexpr int kDesc = 32 + BS * 8;             // StreamDesc + per-token slots
+  static constexpr int kOffImage = NST * kStageIn;
+  static constexpr int kOffDesc = kOffImage + 2 * kImage;
+  static constexpr int kOffBar = kOffDesc + NST * kDesc;
+  static constexpr int kBytes = kOffBar + 2 * NST * 8;
+};
+
+__device__ __forceinline__ void named_bar_sync(int id, int threads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
+}
+
+template <int D, int BS, int HC, int NST>
+__global__ void __launch_bounds__(kStreamThreads, 1) cache_write_stream_kernel(const CacheWriteParams p, int total_tiles) {
+  using L = StreamSmem<D, BS, HC, NST>;
+  extern __shared__ __align__(128) uint8_t smem[];
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + L::kOffBar);
+  uint64_t* empty = full + NST;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int HG = p.Hkv / HC;
+  const long long n_items = (long long)total_tiles * HG;
+  // contiguous item range of this CTA
+  const long long it_begin = n_items * blockIdx.x / gridDim.x;
+  const long long it_end = n_items * (blockIdx.x + 1) / gridDim.x;
+
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int s = 0; s < NST; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], kStreamConsumerWarps);
+    }
+    mbar_fence_init();
+  }
+  __syncthreads();
+
+  if (warp == kStreamConsumerWarps) {
+    // =============================================================== producer
+    if (it_begin >= it_end) return;
+    int r = 0, t_lo = 0, t_hi = 0;
+    int src_start = 0, kept = 0, first = 0, pruned = 0, dst_start = 0;
+    auto locate = [&](int tile, bool from_scratch) {   // all lanes, uniform result
+      if (from_scratch) {
+        int cnt = 0;   // r = #{1 <= i < R : tile_offsets[i] <= tile}: independent loads
+        for (int i = 1 + lane; i < p.num_reqs; i += 32) cnt += (__ldg(p.tile_offsets + i) <= tile) ? 1 : 0;
+#pragma unroll
+        for (int sh = 16; sh >= 1; sh >>= 1) cnt += __shfl_xor_sync(kFull, cnt, sh);
+        r = cnt;
+      } else {
+        int adv;
+        do {       // request ends are monotone: the lanes whose request ends at or before `tile` form a prefix
+          const int i = r + 1 + lane;
+          const int e = (i < p.num_reqs) ? __ldg(p.tile_offsets + i) : 0x7fffffff;
+          adv = __popc(__ballot_sync(kFull, e <= tile));
+          r += adv;
+        } while (adv == 32);
+      }
+      int v = 0;
+      if (lane < 5) v = __ldg(p.req_meta + r * 5 + lane);
+      else if (lane < 7) v = __ldg(p.tile_offsets + r + (lane - 5));
+      src_start = __shfl_sync(kFull, v, 0); kept = __shfl_sync(kFull, v, 1); first = __shfl_sync(kFull, v, 2);
+      pruned = __shfl_sync(kFull, v, 3); dst_start = __shfl_sync(kFull, v, 4);
+      t_lo = __shfl_sync(kFull, v, 5); t_hi = __shfl_sync(kFull, v, 6);
+    };
+    auto load_slot = [&](int tile) -> long long {     // lane's slot of the item's block (after locate)
+      const int j = tile - t_lo;
+      const int ntok = min(BS, kept - j * BS);
+      return (lane < ntok) ? __ldg(p.slot_mapping + dst_start + j * BS + lane) : -1;
+    };
+    int tile = (int)(it_begin / HG);
+    const int last_tile = (int)((it_end - 1) / HG);
+    int stage = 0;
+    uint32_t phase = 0;
+    long long it = it_begin;
+    bool first_locate = true;
+    constexpr int PF = 4;          // blocks whose slots are fetched together (one memory latency per group)
+    while (it < it_end) {
+      if (first_locate || tile >= t_hi) locate(tile, first_locate);
+      first_locate = false;
+      const int n = min(PF, min(t_hi - tile, last_tile - tile + 1));
+      long long sl[PF];
+#pragma unroll
+      for (int k = 0; k < PF; ++k) sl[k] = (k < n) ? load_slot(tile + k) : -1;
+#pragma unroll
+      for (int k = 0; k < PF; ++k) {
+        if (k >= n) break;
+        const long long slot = sl[k];
+        const int j = tile - t_lo;
+        const int ntok = min(BS, kept - j * BS);
+        // whole block, in slot order?
+        const long long slot0 = __shfl_sync(kFull, slot, 0);
+        const bool ok = (ntok == BS) && slot0 >= 0 && (slot0 % BS == 0);
+        const bool mine = (lane >= ntok) || (slot == slot0 + lane);
+        const bool whole = ok && (__ballot_sync(kFull, mine) == kFull);
+        // source row of this lane's token (the streamingLLM prune is index arithmetic)
+        const int jj = j * BS + lane;
+        const size_t srow = (size_t)src_start + (size_t)(jj < first ? jj : jj + pruned);
+        for (int hg = (int)(it - (long long)tile * HG); hg < HG && it < it_end; ++hg, ++it) {
+          mbar_wait(&empty[stage], phase ^ 1u);
+          uint8_t* st = smem + (size_t)stage * L::kStageIn;
+          StreamDesc* d = reinterpret_cast<StreamDesc*>(smem + L::kOffDesc + stage * L::kDesc);
+          if (lane < BS) reinterpret_cast<long long*>(d + 1)[lane] = slot;
+          if (lane == 0) {
+            d->blk = slot0 / BS; d->ntok = ntok; d->whole = whole ? 1 : 0; d->h0 = hg * HC; d->pad = 0;
+          }
+          __syncwarp();
+          if (ntok > 0) {
+            if (lane == 0) mbar_expect_tx(&full[stage], 2u * (uint32_t)ntok * L::kRow);
+            __syncwarp();
+            if (lane < ntok) {
+              tma_load_1d(st + lane * L::kPitch, p.key + srow * p.key_stride + (size_t)hg * HC * D, L::kRow, &full[stage]);
+              tma_load_1d(st + L::kTensor + lane * L::kPitch, p.value + srow * p.value_stride + (size_t)hg * HC * D,
+                          L::kRow, &full[stage]);
+            }
+          } else if (lane == 0) {
+            mbar_arrive(&full[stage]);
+          }
+          if (++stage == NST) { stage = 0; phase ^= 1u; }
+        }
+        ++tile;
+      }
+    }
+    return;
+  }
+
+  // ================================================================= consumers
+  const int ctid = threadIdx.x;                 // 0 .. 255
+  constexpr int CT = kStreamConsumerWarps * 32;
+  int stage = 0;
+  uint32_t phase = 0;
+  int ib = 0;                                    // V image buffer of this item
+  for (long long it = it_begin; it < it_end; ++it) {
+    // the bulk store that last read image `ib` (two items ago) must be done reading it
+    if (ctid == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+    mbar_wait(&full[stage], phase);
+    named_bar_sync(1, CT);
+    const uint8_t* kst = smem + (size_t)stage * L::kStageIn;
+    const uint8_t* vst = kst + L::kTensor;
+    uint8_t* vimage = smem + L::kOffImage + ib * L::kImage;
+    const StreamDesc d = *reinterpret_cast<const StreamDesc*>(smem + L::kOffDesc + stage * L::kDesc);
+    const long long* slots = reinterpret_cast<const long long*>(smem + L::kOffDesc + stage * L::kDesc + 32);
+    if (d.whole) {
+      const size_t gbase = (size_t)d.blk * p.kv_block_stride + (size_t)d.h0 * (D * BS);
+      // ---- K: unit g = u * BS + tok of the destination (contiguous across the warp)
+      {
+        uint4* kdst = reinterpret_cast<uint4*>(p.k_cache + gbase);
+        constexpr int UNITS = BS * L::kRow / 16;
+#pragma unroll 4
+        for (int g = ctid; g < UNITS; g += CT) {
+          const int u = g / BS, tok = g % BS;
+          kdst[g] = *reinterpret_cast<const uint4*>(kst + tok * L::kPitch + u * 16);
+        }
+      }
+      // ---- V: staged rows -> transposed block image
+      {
+        constexpr int TQ = BS / 8;                    // 8-token groups per block
+        constexpr int EG = 4 / TQ;                    // 8-element groups per ldmatrix.x4
+        constexpr int OPS = HC * D / (8 * EG);
+        const int mj = lane >> 3, rr = lane & 7;
+        const int tg = mj % TQ, eg = mj / TQ;
+        const uint32_t s_stage = smem_u32(vst), s_image = smem_u32(vimage);
+        for (int op = warp; op < OPS; op += kStreamConsumerWarps) {
+          const int e0 = op * 8 * EG;
+          uint32_t frag[4];
+          ldmatrix_x4_trans_(frag, s_stage + (uint32_t)((tg * 8 + rr) * L::kPitch + (e0 + 8 * eg) * 2));
+          stmatrix_x4(s_image + (uint32_t)((e0 + 8 * eg + rr) * (BS * 2) + tg * 16), frag);
+        }
+      }
+      fence_proxy_async();   // the image was written through the generic proxy
+      named_bar_sync(2, CT);
+      if (ctid == 0) {
+        bulk_store(p.v_cache + gbase, vimage, L::kImage);
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+      }
+      // ---- prompt block score per kv head, fixed fp32 order (one warp per head)
+      if (p.score.n_pools > 0) {
+        for (int h = warp; h < HC; h += kStreamConsumerWarps) {
+          const float sc = warp_value_l2_head_score<D, BS>([&](int tok, int dd) {
+            return __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(vst + tok * L::kPitch + (h * D + dd) * 2));
+          });
+          if (lane == 0) score_store(p.score, d.blk, d.h0 + h, sc);
+        }
+      }
+      ib ^= 1;
+    } else if (d.ntok > 0) {
+      // element-wise path (csrc/cache_kernels.cu:152-205 semantics; slot < 0 = skip), from the staged rows
+      for (int i = ctid; i < d.ntok * HC * D; i += CT) {
+        const int tl = i / (HC * D), e = i - tl * (HC * D);
+        const int h = e / D, dd = e - h * D;
+        const long long slot = slots[tl];
+        if (slot < 0) continue;
+        const long long blk = slot / BS;
+        const int off = (int)(slot - blk * BS);
+        const size_t base = (size_t)blk * p.kv_block_stride + (size_t)(d.h0 + h) * (D * BS);
+        p.k_cache[base + (size_t)((dd >> 3) * BS + off) * 8 + (dd & 7)] =
+            *reinterpret_cast<const __nv_bfloat16*>(kst + tl * L::kPitch + e * 2);
+        p.v_cache[base + (size_t)dd * BS + off] = *reinterpret_cast<const __nv_bfloat16*>(vst + tl * L::kPitch + e * 2);
+      }
+    }
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&empty[stage]);
+    if (++stage == NST) { stage = 0; phase ^= 1u; }
+  }
+  if (ctid == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+}
+
+template <int D, int BS, int HC, int NST>
+static int launch_stream_write(const CacheWriteParams& p, int tiles, cudaStream_t stream) {
+  using L = StreamSmem<D, BS, HC, NST>;
+  static_assert(L::kBytes <= 227 * 1024, "stream pipeline does not fit shared memory");
+  auto kern = cache_write_stream_kernel<D, BS, HC, NST>;
+  static std::atomic<int> opted[64];
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 0 || dev >= 64 || !opted[dev].load(std::memory_order_acquire)) {
+    const cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kBytes);
+    if (e != cudaSuccess) return set_cuda_error("cudaFuncSetAttribute(cache_write_stream)", e);
+    if (dev >= 0 && dev < 64) opted[dev].store(1, std::memory_order_release);
+  }
+  const int sms = device_sm_count();
+  if (sms <= 0) return PC_ERR_CUDA;
+  const long long items = (long long)tiles * (p.Hkv / HC);
+  const int grid = (int)(items < sms ? items : sms);
+  kern<<<grid, kStreamThreads, L::kBytes, stream>>>(p, tiles);
+  return check_launch("cache_write_stream_kernel");
+}
+
+// stages: as many as fit next to the two V images, at most 4
+template <int D, int BS, int HC>
+constexpr int stream_stages() {
+  int n = 4;
+  while (n > 2 && StreamSmem<D, BS, HC, 4>::kStageIn * n + 2 * StreamSmem<D, BS, HC, 4>::kImage + 4096 > 220 * 1024) --n;
+  return n;
+}
+// heads per item: as many as keep a stage at <= 64 KiB of rows (K + V)
+template <int D, int BS>
+static int dispatch_stream_write(const CacheWriteParams& p, int tiles, cudaStream_t stream) {
+  constexpr int kMaxHC = (D * BS <= 2048) ? 8 : (D * BS <= 4096 ? 4 : 2);   // 2 * BS * HC * D * 2 bytes per stage
+  constexpr int H8 = kMaxHC >= 8 ? 8 : kMaxHC, H4 = kMaxHC >= 4 ? 4 : kMaxHC;
+  if (p.Hkv % 8 == 0 && kMaxHC >= 8) return launch_stream_write<D, BS, H8, stream_stages<D, BS, H8>()>(p, tiles, stream);
+  if (p.Hkv % 4 == 0 && kMaxHC >= 4) return launch_stream_write<D, BS, H4, stream_stages<D, BS, H4>()>(p, tiles, stream);
+  if (p.Hkv % 2 == 0) return launch_stream_write<D, BS, 2, stream_stages<D, BS, 2>()>(p, tiles, stream);
+  return launch_stream_write<D, BS, 1, stream_stages<D, BS, 1>()>(p, tiles, stream);
+}
+
 #ifdef PC_DEBUG
 static int g_force_block_hc = 0;   // heads per CTA override (sweeps)
 void set_cache_write_block_heads(int hc) { g_force_block_hc = hc; }
@@ -401,7 +678,26 @@ int cache_write(const CacheWriteArgs& a, cudaStream_t stream) {
   p.score = a.score;
   const int tiles = a.req_meta ? a.total_tiles : (a.num_tokens + a.BS - 1) / a.BS;
   if (tiles <= 0) return 0;
-  if (a.req_meta != nullptr) {   // prompt-time: whole blocks, the block kernel
+  if (a.req_meta != nullptr) {   // prompt-time: whole blocks
+    // The streaming kernel hands ONE item at a time to all consumer warps: it wins when an item
+    // (block x heads per CTA) is 64 KiB of rows (us per launch, stream / block kernel, 285 MB:
+    // Hkv 8 53.7 / 62.2, block 32 67.2 / 77.8); with 1-4 kv heads per rank (TP 2 / 4 / 8) items are
+    // 8-32 KiB and many small concurrent CTAs (the block kernel) do better (Hkv 4 64.2 / 61.0,
+    // Hkv 2 101 / 62, Hkv 1 179 / 71) -- profiles/r02_cache_write_stream.txt.
+    const int hc = a.Hkv % 8 == 0 ? 8 : (a.Hkv % 4 == 0 ? 4 : (a.Hkv % 2 == 0 ? 2 : 1));
+    const int hc_cap = (a.D * a.BS <= 2048) ? 8 : (a.D * a.BS <= 4096 ? 4 : 2);
+    const long long item_bytes = 2LL * a.BS * (hc < hc_cap ? hc : hc_cap) * a.D * 2;
+    bool streaming = item_bytes >= 64 * 1024 || (item_bytes >= 32 * 1024 && a.Hkv >= 8);
+#ifdef PC_DEBUG
+    if (g_force_block_hc > 0) streaming = false;   // A/B runs: the block kernel with that many heads per CTA
+    if (g_force_block_hc < 0) streaming = true;
+#endif
+    if (streaming) {
+      if (a.D == 128 && a.BS == 16) return dispatch_stream_write<128, 16>(p, tiles, stream);
+      if (a.D == 128 && a.BS == 32) return dispatch_stream_write<128, 32>(p, tiles, stream);
+      if (a.D == 64 && a.BS == 16) return dispatch_stream_write<64, 16>(p, tiles, stream);
+      if (a.D == 64 && a.BS == 32) return dispatch_stream_write<64, 32>(p, tiles, stream);
+    }
     if (a.D == 128 && a.BS == 16) return dispatch_block_write<128, 16>(p, tiles, stream);
     if (a.D == 128 && a.BS == 32) return dispatch_block_write<128, 32>(p, tiles, stream);
     if (a.D == 64 && a.BS == 16) return dispatch_block_write<64, 16>(p, tiles, stream);
