@@ -35,7 +35,9 @@ namespace pc {
 namespace {
 
 constexpr int kTM = 128;       // query rows per CTA (UMMA M)
-constexpr int kTcThreads = 224;
+constexpr int kTcThreads = 384;   // warpgroup 0 softmax, 1 = K / V producers + MMA issuer (+ 1 idle warp), 2 = epilogue
+// register budgets per thread after setmaxnreg (two CTAs per SM: 2 x 128 x (128 + 40 + 72) = 60 K of 64 K)
+constexpr int kRegsSoftmax = 128, kRegsRoles = 40, kRegsEpilogue = 72;
 constexpr float kRescaleThreshold = 8.f;  // log2 domain
 
 struct PrefillTcParams {
@@ -64,14 +66,16 @@ struct TcSmem {
   static constexpr int oV = oK + 2 * kKV;      // 2 stages
   static constexpr int oP = oV + 2 * kKV;
   static constexpr int oBar = oP + kP;
-  // barriers: q_full, k_full[2], v_full[2], s_full[2], p_full[2], pv_done[2]  (11) + tmem slot
-  static constexpr int kBytes = oBar + 16 * 8;
+  // barriers: q_full, k_full[2], v_full[2], s_full[2], p_full[2], pv_done[2], l_full, o_free (13) + tmem slot
+  static constexpr int oLinv = oBar + 16 * 8;   // 1 / l of the item's rows, softmax -> epilogue warps, 2 x kTM floats
+  static constexpr int kBytes = oLinv + 2 * kTM * 4;
 };
 
 // p_full is double-buffered like the S / P buffers: the softmax warps may finish tile g + 1 while
 // the MMA thread still waits for V_g, and a single barrier would then be two phases ahead of its
 // waiter (parity aliasing -> deadlock).
-enum { B_QFULL = 0, B_KFULL = 1, B_VFULL = 3, B_SFULL = 5, B_PFULL = 7, B_PVDONE = 9, B_COUNT = 11 };
+enum { B_QFULL = 0, B_KFULL = 1, B_VFULL = 3, B_SFULL = 5, B_PFULL = 7, B_PVDONE = 9, B_LFULL = 11, B_OFREE = 12,
+       B_COUNT = 13 };
 
 }  // namespace
 
@@ -151,6 +155,7 @@ prefill_attn_tc_kernel(const PrefillTcParams p, const __grid_constant__ CUtensor
     mbar_init(&bar[B_SFULL], 1);  mbar_init(&bar[B_SFULL + 1], 1);
     mbar_init(&bar[B_PFULL], kTM); mbar_init(&bar[B_PFULL + 1], kTM);
     mbar_init(&bar[B_PVDONE], 1); mbar_init(&bar[B_PVDONE + 1], 1);
+    mbar_init(&bar[B_LFULL], kTM); mbar_init(&bar[B_OFREE], kTM);
     mbar_fence_init();
   }
   if (warp == 6) t5::tmem_alloc<kTmemCols>(tmem_slot);
@@ -159,7 +164,14 @@ prefill_attn_tc_kernel(const PrefillTcParams p, const __grid_constant__ CUtensor
   t5::fence_after_sync();
   const uint32_t tmem = *tmem_slot;
   const uint32_t tmem_o = tmem + 2 * kTN;
+  float* linv = reinterpret_cast<float*>(smem + L::oLinv);
+  // registers follow the roles (two CTAs per SM share the file): the softmax rows hold a whole
+  // 64-column tile per thread, the single-lane roles and the epilogue need few.  Each role branch
+  // starts with its setmaxnreg so that the allocator sees the budget of the code it dominates.
+  constexpr bool kRealloc = (TN == 64);
 
+  if (warp >= 4 && warp < 8) {
+  if constexpr (kRealloc) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kRegsRoles));
   if (warp == 4) {
     // ================================================= Q + K producer (one lane, TMA)
     if (lane == 0) {
@@ -226,6 +238,8 @@ prefill_attn_tc_kernel(const PrefillTcParams p, const __grid_constant__ CUtensor
           if (j + 1 < it.ntiles) issue_s(g + 1);
           mbar_wait(&bar[B_VFULL + st], (g >> 1) & 1);
           mbar_wait(&bar[B_PFULL + st], (g >> 1) & 1);
+          // the first P.V of an item overwrites O: the epilogue warps must have read the previous item's
+          if (j == 0 && n_item > 1) mbar_wait(&bar[B_OFREE], (n_item - 2) & 1);
           fence_proxy_async();
           t5::fence_after_sync();
 #pragma unroll
@@ -244,11 +258,13 @@ prefill_attn_tc_kernel(const PrefillTcParams p, const __grid_constant__ CUtensor
       }
     }
     __syncwarp();
-  } else {
+  }
+  } else if (warp < 4) {
     // ================================================= softmax warps (thread = query row)
+    if constexpr (kRealloc) asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(kRegsSoftmax));
     const uint32_t lane_base = (uint32_t)(warp * 32) << 16;
     uint8_t* sProw = smem + L::oP + tid * 16;
-    int g = 0;
+    int g = 0, n_item = 0;
     for (int k = blockIdx.x; k < total; k += gridDim.x) {
       const TcItem it = get_item(k);
       if (it.ntiles == 0) continue;
@@ -267,10 +283,14 @@ prefill_attn_tc_kernel(const PrefillTcParams p, const __grid_constant__ CUtensor
         if (need_mask) {
           const int lim = min(row, it.kv_len - 1) - j0;  // columns > lim are masked
 #pragma unroll
-          for (int c = 0; c < SC; ++c)
+          for (int c = 0; c < SC; ++c) {
+            // a 32-column chunk no row of the warp masks is skipped (warp-uniform test): on a
+            // diagonal tile only one warp in four has a partial chunk
+            if (__all_sync(kFull, lim >= c * 32 + 31)) continue;
 #pragma unroll
             for (int i = 0; i < 32; ++i)
               if (c * 32 + i > lim) sr[c][i] = 0xff800000u;  // -inf
+          }
         }
         float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll
@@ -347,16 +367,42 @@ prefill_attn_tc_kernel(const PrefillTcParams p, const __grid_constant__ CUtensor
         t5::fence_before_sync();
         t5::mbar_arrive(&bar[B_PFULL + sb]);
       }
-      // ---- epilogue of the item: O / l -> bf16 -> global (last tile index g - 1)
-      mbar_wait(&bar[B_PVDONE + ((g - 1) & 1)], ((g - 1) >> 1) & 1);
+      // ---- hand the row's 1 / l to the epilogue warps and move on to the next item: the softmax
+      // warps are the critical resource (MUFU), they neither wait for the last P.V nor drain O
+      linv[(n_item & 1) * kTM + tid] = 1.f / l_run;
+      t5::mbar_arrive(&bar[B_LFULL]);
+      ++n_item;
+    }
+  }
+  else {
+    // ================================================= epilogue warps: O / l -> bf16 -> global
+    if constexpr (kRealloc) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kRegsEpilogue));
+    // (TMEM lane quadrant = warp % 4; O is read as soon as the item's last P.V has completed and
+    // released to the MMA warp -- o_free -- before the conversion and the stores)
+    const int etid = tid - 256;
+    const uint32_t lane_base = (uint32_t)((warp & 3) * 32) << 16;
+    int g = 0, n_item = 0;
+    for (int k = blockIdx.x; k < total; k += gridDim.x) {
+      const TcItem it = get_item(k);
+      if (it.ntiles == 0) continue;
+      g += it.ntiles;
+      const int row = it.i0 + etid;
+      // (polling with a sleep: these warps idle most of an item and must not take issue slots
+      // from the softmax warps that share their schedulers)
+      t5::mbar_wait_sleep(&bar[B_LFULL], n_item & 1, 128);
+      const float inv = linv[(n_item & 1) * kTM + etid];
+      t5::mbar_wait_sleep(&bar[B_PVDONE + ((g - 1) & 1)], ((g - 1) >> 1) & 1, 64);
       t5::fence_after_sync();
-      const float inv = 1.f / l_run;
       __nv_bfloat16* dst = p.out + (size_t)(it.q_start + (row < it.q_len ? row : 0)) * p.out_stride + (size_t)it.hq * D;
 #pragma unroll
       for (int c = 0; c < D / 32; ++c) {
         uint32_t o[32];
         t5::tmem_ld32(o, tmem_o + lane_base + c * 32);
         t5::tmem_ld_wait();
+        if (c == D / 32 - 1) {          // O is in registers: the next item's first P.V may overwrite it
+          t5::fence_before_sync();
+          t5::mbar_arrive(&bar[B_OFREE]);
+        }
         if (row < it.q_len) {
 #pragma unroll
           for (int q4 = 0; q4 < 4; ++q4) {
@@ -369,9 +415,7 @@ prefill_attn_tc_kernel(const PrefillTcParams p, const __grid_constant__ CUtensor
           }
         }
       }
-      // the next item's first P.V (accumulate = 0) overwrites O only after these loads:
-      // its p_full needs this thread's arrival, which comes after this point
-      t5::fence_before_sync();
+      ++n_item;
     }
   }
 

@@ -161,5 +161,11 @@ __device__ __forceinline__ void mbar_wait_relaxed(uint64_t* bar, uint32_t parity
   }
 }
 
+__device__ __forceinline__ void mbar_wait_sleep(uint64_t* bar, uint32_t parity, unsigned ns) {
+  while (!mbar_try_wait(bar, parity)) {
+    __nanosleep(ns);
+  }
+}
+
 }  // namespace t5
 }  // namespace pc
