@@ -187,6 +187,25 @@ prefill_attn_tc_kernel(const PrefillTcParams p, const __grid_constant__ CUtensor
         for (int b = 0; b < D / 64; ++b)
           t5::tma_load_2d(smem + L::oQ + b * (kTM * 128), &tm_q, it.hq * D + b * 64, it.q_start + it.i0,
                           &bar[B_QFULL]);
+        // the NEXT item's Q tile (read exactly once: always a DRAM miss) and its first K / V tile go
+        // to L2 now, a whole item ahead of their TMA loads
+        for (int kn = k + gridDim.x; kn < total; kn += gridDim.x) {
+          const TcItem nx = get_item(kn);
+          if (nx.ntiles == 0) continue;
+#pragma unroll
+          for (int b = 0; b < D / 64; ++b) t5::tma_prefetch_l2_2d(&tm_q, nx.hq * D + b * 64, nx.q_start + nx.i0);
+#pragma unroll
+          for (int gg = 0; gg < kTN / kBoxRows; ++gg) {
+            const int jn = gg * kBoxRows;
+            const int src = nx.kv_src + (jn < nx.first ? jn : jn + nx.pruned);
+#pragma unroll
+            for (int b = 0; b < D / 64; ++b) {
+              t5::tma_prefetch_l2_2d(&tm_k, nx.hkv * D + b * 64, src);
+              t5::tma_prefetch_l2_2d(&tm_v, nx.hkv * D + b * 64, src);
+            }
+          }
+          break;
+        }
         for (int t = 0; t < it.ntiles; ++t, ++g) {
           const int st = g & 1;
           if (g >= 2) t5::mbar_wait_relaxed(&bar[B_SFULL + st], ((g - 2) >> 1) & 1);   // S_{g-2} done
