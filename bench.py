@@ -67,10 +67,10 @@ MODELS = {"8b": dict(name="Llama-3.1-8B", layers=32, Hq=32, Hkv=8, D=128),      
 METRIC = "decode_tok_per_s_paged_eviction_hot_path"
 
 
-@dataclass(frozen=True)
 PREFILL_BATCH_TOKENS = 64 * 1024
 
 
+@dataclass(frozen=True)
 class Spec:
     """One workload: attention shapes of a model, a batch of equal prompts, an eviction setting.
     `batch` is the GLOBAL batch; under tensor parallelism every rank sees all rows and 1/tp of
