@@ -686,3 +686,40 @@ def test_prompt_token_prune_bit_exact(kind, D, repack):
     torch.cuda.synchronize()
     assert torch.equal(out_k[:dst].cpu(), torch.cat(want_k)) and torch.equal(out_v[:dst].cpu(), torch.cat(want_v))
     assert bool((out_k[dst:] == 7.0).all()) and bool((out_v[dst:] == 7.0).all())     # nothing written past the end
+
+
+def test_torch_library_ops_match_ctypes_path():
+    """torch.ops.pagedevict_b200.* (and the fork's names after alias_vllm_ops) give the same bytes
+    as the ctypes wrappers: reshape_and_cache, paged_attention_v1/v2, zero_cache_slots."""
+    from vllm_paged_compression_b200 import torch_ops
+    ns = torch_ops.load()
+    torch_ops.alias_vllm_ops()
+    ops = _ops()
+    nb, bs, Hkv, Hq, D, B = 40, 16, 2, 8, 128, 5
+    s = D ** -0.5
+    kv = (rnd(71, 2, nb, bs * Hkv * D).float() * 0.5).to(torch.bfloat16).to(DEV)
+    kv2 = kv.clone()
+    key, value = rnd(72, 30, Hkv, D).to(DEV), rnd(73, 30, Hkv, D).to(DEV)
+    slots = torch.from_numpy(np.random.RandomState(3).permutation(nb * bs)[:30].astype(np.int64)).to(DEV)
+    kc, vc = paged_ops.split_kv_cache(kv, Hkv, D)
+    kc2, vc2 = paged_ops.split_kv_cache(kv2, Hkv, D)
+    ops.reshape_and_cache(key, value, kc, vc, slots)
+    torch.ops._C_cache_ops.reshape_and_cache(key, value, kc2, vc2, slots, "auto", 1.0, 1.0)
+    assert torch.equal(kv, kv2)
+    q = (rnd(74, B, Hq, D).float() * 0.3).to(torch.bfloat16).to(DEV)
+    lens = torch.tensor([1, 16, 37, 160, 99], dtype=torch.int32, device=DEV)
+    bt = torch.from_numpy(np.stack([np.random.RandomState(10 + i).permutation(nb)[:10] for i in range(B)])
+                          .astype(np.int32)).to(DEV)
+    o1, o2, o3 = torch.empty_like(q), torch.empty_like(q), torch.empty_like(q)
+    ops.paged_attention_v1(o1, q, kc, vc, Hkv, s, bt, lens, bs, 160)
+    ns.paged_attention_v1(o2, q, kc, vc, Hkv, s, bt, lens, bs, 160, None, "auto", 1.0, 1.0, 0, 0, 0, 64, 0)
+    dummy = torch.empty(1, device=DEV)
+    torch.ops._C.paged_attention_v2(o3, dummy, dummy, dummy, q, kc, vc, Hkv, s, bt, lens, bs, 160, None, "auto",
+                                    1.0, 1.0, 0, 0, 0, 64, 0)
+    assert torch.equal(o1, o2) and torch.equal(o1, o3)
+    z = torch.tensor([5, -1, 77], dtype=torch.int64, device=DEV)
+    ops.zero_cache_slots(kc, vc, z)
+    ns.zero_cache_slots(kc2, vc2, z)
+    assert torch.equal(kv, kv2)
+    with pytest.raises(RuntimeError):
+        ns.paged_attention_v1(o2, q, kc, vc, Hkv, s, bt, lens, bs, 160, None, "fp8", 1.0, 1.0, 0, 0, 0, 64, 0)

@@ -271,3 +271,29 @@ def test_metadata_builder_on_reference_host_trace(name):
             bm.free_prunned_blocks(int(rid[1:]), idx)
             n_evict += 1
     assert (n_evict > 0) == (c["evict_method"] != "inverse_key_l2")
+
+
+def test_torch_library_shim_registers_the_fork_schemas():
+    """The thin torch C++ extension (csrc/torch_shim.cpp): ops exist under pagedevict_b200 with the
+    fork's schemas (csrc/torch_bindings.cpp:27-51,444-450) and, after alias_vllm_ops(), under the
+    fork's own names torch.ops._C / torch.ops._C_cache_ops.  No compute without a GPU; CPU tensors
+    are refused loudly (no CPU fallback)."""
+    import torch
+    from vllm_paged_compression_b200 import torch_ops
+    ns = torch_ops.load()
+    for name in ("paged_attention_v1", "paged_attention_v2", "reshape_and_cache", "zero_cache_slots",
+                 "prefill_attn_topleft_causal"):
+        assert hasattr(ns, name)
+    s = str(ns.paged_attention_v1.default._schema)
+    assert "! -> ) out" in s and "int blocksparse_head_sliding_step" in s and "Tensor? alibi_slopes" in s
+    s = str(ns.reshape_and_cache.default._schema)
+    assert "! -> ) key_cache" in s and "str kv_cache_dtype" in s
+    torch_ops.alias_vllm_ops()
+    torch_ops.alias_vllm_ops()           # idempotent
+    assert str(torch.ops._C.paged_attention_v2.default._schema).startswith("_C::paged_attention_v2(")
+    assert str(torch.ops._C_cache_ops.reshape_and_cache.default._schema).startswith("_C_cache_ops::reshape_and_cache(")
+    k = torch.zeros(2, 2, 64, dtype=torch.bfloat16)
+    with pytest.raises((RuntimeError, NotImplementedError)):
+        ns.reshape_and_cache(k, k, torch.zeros(1, 2, 8, 16, 8, dtype=torch.bfloat16),
+                             torch.zeros(1, 2, 64, 16, dtype=torch.bfloat16), torch.zeros(2, dtype=torch.int64),
+                             "auto", 1.0, 1.0)
