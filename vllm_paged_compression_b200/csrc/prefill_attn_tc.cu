@@ -99,7 +99,7 @@ __global__ void __launch_bounds__(kTcThreads, (TN == 64 ? 2 : 1))
 prefill_attn_tc_kernel(const PrefillTcParams p, const __grid_constant__ CUtensorMap tm_q,
                                const __grid_constant__ CUtensorMap tm_k,
                                const __grid_constant__ CUtensorMap tm_v, const int q_tiles,
-                               const int num_reqs, const int heavy_major) {
+                               const int num_reqs, const int heavy_major, const int chunk_reqs) {
   using L = TcSmem<D, TN>;
   constexpr int kTN = TN;
   constexpr int kTmemCols = L::kTmemCols;
@@ -123,11 +123,24 @@ prefill_attn_tc_kernel(const PrefillTcParams p, const __grid_constant__ CUtensor
     // short prompts: static round-robin needs the global order).  Otherwise the query tiles of one
     // (request, head) are adjacent, heaviest first, so the CTAs in flight share few K/V streams
     // (4 x 8192 tokens: 134 MB of K/V > L2 when every stream is live at once: 1061 vs 1104 TFLOP/s).
-    int qt, rem;
-    if (heavy_major) { qt = q_tiles - 1 - k / per_qt; rem = k % per_qt; }
-    else             { rem = k / q_tiles; qt = q_tiles - 1 - (k - rem * q_tiles); }
-    const int r = rem / p.Hq;
-    it.hq = rem - r * p.Hq;
+    // The heavy-first order runs inside CHUNKS of `chunk_reqs` requests whose K/V fit L2 together:
+    // every query-tile level of a chunk re-reads the chunk's K/V, and with all 64 prompts of the
+    // bench batch in one level-major sweep (142 MB of K/V) those re-reads went to DRAM (ncu: 1.44 GB
+    // read for 0.68 GB algorithmic).
+    int qt, rem, r0 = 0;
+    if (heavy_major) {
+      const int per_chunk = q_tiles * p.Hq * chunk_reqs;
+      const int c = k / per_chunk, k2 = k - c * per_chunk;
+      r0 = c * chunk_reqs;
+      const int pq = p.Hq * min(chunk_reqs, num_reqs - r0);
+      qt = q_tiles - 1 - k2 / pq;
+      rem = k2 % pq;
+    } else {
+      rem = k / q_tiles;
+      qt = q_tiles - 1 - (k - rem * q_tiles);
+    }
+    const int r = r0 + rem / p.Hq;
+    it.hq = rem % p.Hq;
     it.hkv = it.hq / G;
     const int* m = p.req_meta + r * 6;
     it.q_start = m[0]; it.q_len = m[1]; it.kv_src = m[2]; it.kv_len = m[3]; it.first = m[4]; it.pruned = m[5];
@@ -461,7 +474,10 @@ prefill_attn_tc_kernel(const PrefillTcParams p, const __grid_constant__ CUtensor
 static int g_tc_persistent = -1;
 void set_prefill_tc_persistent(int v) { g_tc_persistent = v; }
 static int g_tc_tile_n = 64;
-void set_prefill_tc_tile(int tn) { g_tc_tile_n = (tn == 128) ? 128 : 64; }
+static int g_tc_chunk_reqs = 0;
+void set_prefill_tc_tile(int tn) {   // debug knob reused: values other than 64 / 128 set the requests per L2 chunk
+  if (tn == 64 || tn == 128) g_tc_tile_n = tn; else g_tc_chunk_reqs = tn;
+}
 #else
 constexpr int g_tc_persistent = -1;
 constexpr int g_tc_tile_n = 64;
@@ -517,8 +533,19 @@ static int launch_prefill_tc(const PrefillTcParams& p, const PrefillArgs& a, cud
   const long long slots = (long long)device_sm_count() * (TN == 64 ? 2 : 1);
   if (total > 0x7fffffffLL) return set_error(PC_ERR_INVALID, "prefill: too many query tiles");
   const int ctas = (int)((persist && total > slots) ? slots : total);
+  // requests per chunk of the heavy-first order: K + V of a chunk (bounded by the longest prompt) in ~40 MB of L2
+  const long long kv_req = (long long)a.max_q_len * a.Hkv * D * 4;
+  long long chunk = (40LL << 20) / (kv_req > 0 ? kv_req : 1);
+  if (chunk < 1) chunk = 1;
+  // (a batch whose K/V fit L2 anyway keeps the single heavy-first sweep: 16 x 1024 measured 753
+  // TFLOP/s in one sweep against 717 in chunks of 6, the chunk ends add light / heavy transitions)
+  if (chunk > a.num_reqs || kv_req * a.num_reqs <= (80LL << 20)) chunk = a.num_reqs;
+#ifdef PC_DEBUG
+  if (g_tc_chunk_reqs > 0) chunk = g_tc_chunk_reqs < a.num_reqs ? g_tc_chunk_reqs : a.num_reqs;
+#endif
   kern<<<ctas, kTcThreads, smem, stream>>>(p, tq, tk, tv, q_tiles, a.num_reqs,
-                                            (persist && g_tc_persistent != 2) ? 1 : 0);   // 2: debug, persistent + local order
+                                            (persist && g_tc_persistent != 2) ? 1 : 0,   // 2: debug, persistent + local order
+                                            (int)chunk);
   return check_launch("prefill_attn_tc_kernel");
 }
 
