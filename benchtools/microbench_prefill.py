@@ -99,8 +99,15 @@ def main():
     ap.add_argument("--D", type=int, default=128)
     ap.add_argument("--evict-freq", type=int, default=2)
     ap.add_argument("--reps", type=int, default=20)
+    ap.add_argument("--pp", type=int, default=-1, help="PC_DEBUG library: 1 = ping-pong kernel, 0 = off, -1 = rule")
     ap.add_argument("--modes", action="store_true", help="PC_DEBUG library: one-shot / persistent side by side")
     a = ap.parse_args()
+    if a.pp >= 0:
+        import ctypes
+        fn = _lib.load().pc_debug_set_prefill_pp
+        fn.argtypes = [ctypes.c_int32]
+        fn.restype = None
+        fn(a.pp)
     dev = torch.device("cuda", 0)
     row, ref = run(dev, a.reqs, a.len, a.Hq, a.Hkv, a.D, a.evict_freq, a.reps)
     print(json.dumps(row), flush=True)

@@ -66,7 +66,7 @@ struct TcSmem {
   static constexpr int oV = oK + 2 * kKV;      // 2 stages
   static constexpr int oP = oV + 2 * kKV;
   static constexpr int oBar = oP + kP;
-  // barriers: q_full, k_full[2], v_full[2], s_full[2], p_full[2], pv_done[2], l_full, o_free (13) + tmem slot
+  // barriers: q_full, k_full[2], v_full[2], s_full[2], p_full[2], pv_done[2], l_full[2], o_free (14) + tmem slot
   static constexpr int oLinv = oBar + 16 * 8;   // 1 / l of the item's rows, softmax -> epilogue warps, 2 x kTM floats
   static constexpr int kBytes = oLinv + 2 * kTM * 4;
 };
@@ -74,8 +74,8 @@ struct TcSmem {
 // p_full is double-buffered like the S / P buffers: the softmax warps may finish tile g + 1 while
 // the MMA thread still waits for V_g, and a single barrier would then be two phases ahead of its
 // waiter (parity aliasing -> deadlock).
-enum { B_QFULL = 0, B_KFULL = 1, B_VFULL = 3, B_SFULL = 5, B_PFULL = 7, B_PVDONE = 9, B_LFULL = 11, B_OFREE = 12,
-       B_COUNT = 13 };
+enum { B_QFULL = 0, B_KFULL = 1, B_VFULL = 3, B_SFULL = 5, B_PFULL = 7, B_PVDONE = 9, B_LFULL = 11 /* [item parity] */,
+       B_OFREE = 13, B_COUNT = 14 };
 
 }  // namespace
 
@@ -168,7 +168,7 @@ prefill_attn_tc_kernel(const PrefillTcParams p, const __grid_constant__ CUtensor
     mbar_init(&bar[B_SFULL], 1);  mbar_init(&bar[B_SFULL + 1], 1);
     mbar_init(&bar[B_PFULL], kTM); mbar_init(&bar[B_PFULL + 1], kTM);
     mbar_init(&bar[B_PVDONE], 1); mbar_init(&bar[B_PVDONE + 1], 1);
-    mbar_init(&bar[B_LFULL], kTM); mbar_init(&bar[B_OFREE], kTM);
+    mbar_init(&bar[B_LFULL], kTM); mbar_init(&bar[B_LFULL + 1], kTM); mbar_init(&bar[B_OFREE], kTM);
     mbar_fence_init();
   }
   if (warp == 6) t5::tmem_alloc<kTmemCols>(tmem_slot);
@@ -401,8 +401,11 @@ prefill_attn_tc_kernel(const PrefillTcParams p, const __grid_constant__ CUtensor
       }
       // ---- hand the row's 1 / l to the epilogue warps and move on to the next item: the softmax
       // warps are the critical resource (MUFU), they neither wait for the last P.V nor drain O
+      // (l_full is double-buffered by item parity: after a one-tile item the softmax warps can finish
+      // item n + 1 before the epilogue has looked at item n; a single barrier would then be two
+      // phases ahead of its waiter)
       linv[(n_item & 1) * kTM + tid] = 1.f / l_run;
-      t5::mbar_arrive(&bar[B_LFULL]);
+      t5::mbar_arrive(&bar[B_LFULL + (n_item & 1)]);
       ++n_item;
     }
   }
@@ -421,7 +424,7 @@ prefill_attn_tc_kernel(const PrefillTcParams p, const __grid_constant__ CUtensor
       const int row = it.i0 + etid;
       // (polling with a sleep: these warps idle most of an item and must not take issue slots
       // from the softmax warps that share their schedulers)
-      t5::mbar_wait_sleep(&bar[B_LFULL], n_item & 1, 128);
+      t5::mbar_wait_sleep(&bar[B_LFULL + (n_item & 1)], (n_item >> 1) & 1, 128);
       const float inv = linv[(n_item & 1) * kTM + etid];
       t5::mbar_wait_sleep(&bar[B_PVDONE + ((g - 1) & 1)], ((g - 1) >> 1) & 1, 64);
       t5::fence_after_sync();
@@ -478,6 +481,8 @@ static int g_tc_chunk_reqs = 0;
 void set_prefill_tc_tile(int tn) {   // debug knob reused: values other than 64 / 128 set the requests per L2 chunk
   if (tn == 64 || tn == 128) g_tc_tile_n = tn; else g_tc_chunk_reqs = tn;
 }
+static int g_prefill_pp = -1;
+void set_prefill_pp(int v) { g_prefill_pp = v; }
 #else
 constexpr int g_tc_persistent = -1;
 constexpr int g_tc_tile_n = 64;
@@ -574,6 +579,12 @@ int prefill_attn(const PrefillArgs& a, cudaStream_t stream) {
                          "prefill: first / pruned must be multiples of 16 tokens (whole blocks of 16 / 32)");
     }
   }
+#ifdef PC_DEBUG
+  // A/B runs: the ping-pong kernel (two q heads of a kv head per CTA, 128-wide kv tiles; prefill_attn_pp.cu).
+  // Measured 1-8 % slower than this kernel at every shape (profiles/r02_prefill_experiments.txt), so it is
+  // built into the PC_DEBUG library only.
+  if (g_prefill_pp > 0 && prefill_attn_pp_supported(a)) return prefill_attn_pp(a, stream);
+#endif
   PrefillTcParams p;
   p.out = static_cast<__nv_bfloat16*>(a.out);
   p.req_meta = a.req_meta;
