@@ -21,7 +21,7 @@
  *   key_cache   [num_blocks][num_kv_heads][head_size/8][block_size][8]
  *   value_cache [num_blocks][num_kv_heads][head_size][block_size]
  * kv_block_stride = elements between consecutive blocks (num_kv_heads*head_size*block_size
- * for a dense pool).  Supported: head_size 64|128, block_size 16|32, dtype bf16.
+ * for a dense pool).  Supported: head_size 64|128, block_size 8|16|32, dtype bf16.
  */
 #ifndef PAGEDEVICT_B200_H_
 #define PAGEDEVICT_B200_H_
@@ -261,11 +261,12 @@ int pc_evict_select_compact_layers(const int32_t* block_tables, int64_t table_st
  * K/V rows are read through the same gather as pc_prune_prompt_and_cache, so the
  * pruned K/V never exists in memory.  req_meta int32 [num_reqs][6] =
  * {q_start, q_len, kv_src_start, kv_len(kept), first, pruned}; first and pruned are
- * multiples of 16 (block sizes 16 / 32).  num_tokens = rows of query / key / value (the
+ * multiples of 8 (whole blocks of 8 / 16 / 32; 8-row TMA boxes are used when they are not multiples
+ * of 16, which needs req_meta_host).  num_tokens = rows of query / key / value (the
  * bound of the TMA tensor maps the tcgen05 kernel loads through).
  * req_meta_host: HOST copy of req_meta (the caller built it on the host anyway) or NULL.
  * When given, every row is validated before the launch (ranges inside num_tokens, first /
- * pruned multiples of 16) and a violation returns PC_ERR_INVALID; with NULL a violating row
+ * pruned multiples of 8) and a violation returns PC_ERR_INVALID; with NULL a violating row
  * reaches the kernel's own guard, which traps (and poisons the CUDA context). */
 int pc_prefill_attn_topleft_causal(void* out, const void* query, const void* key,
                                    const void* value, const int32_t* req_meta,

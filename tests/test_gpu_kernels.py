@@ -36,11 +36,11 @@ def _bits(t):
 
 # --------------------------------------------------------------------------- W1
 @pytest.mark.parametrize("D", [64, 128])
-@pytest.mark.parametrize("bs", [16, 32])
+@pytest.mark.parametrize("bs", [8, 16, 32])
 @pytest.mark.parametrize("n_tok", [1, 7, 200, 1000])
 def test_reshape_and_cache_exact(D, bs, n_tok):
     ops = _ops()
-    Hkv, nb = 4, 96
+    Hkv, nb = 4, 96 if bs >= 16 else 192
     rs = np.random.RandomState(n_tok * 7 + D + bs)
     slots = rs.permutation(nb * bs)[:n_tok].astype(np.int64)
     slots[rs.rand(n_tok) < 0.1] = -1                      # PAD_SLOT_ID rows are skipped
@@ -130,7 +130,7 @@ def _prompt_batch(prompt_lens, pol, nb, rs):
 
 
 @pytest.mark.parametrize("D,bs,Hkv", [(64, 16, 4), (128, 16, 4), (128, 32, 4), (128, 16, 8), (128, 16, 1),
-                                      (128, 32, 8), (64, 32, 6), (128, 16, 3)])
+                                      (128, 32, 8), (64, 32, 6), (128, 16, 3), (128, 8, 8), (64, 8, 4), (128, 8, 1)])
 @pytest.mark.parametrize("mode", ["budget", "percentage"])
 def test_prune_prompt_and_cache(D, bs, Hkv, mode):
     """R1 + W1 + S3.  Hkv 8 / 4 / 6 / 3 / 1 walk the block kernel's heads-per-CTA variants
@@ -320,7 +320,8 @@ def _decode_case(B, Hq, Hkv, D, bs, max_len, seed, ragged=True, nb=None):
 
 
 @pytest.mark.parametrize("Hq,Hkv,D,bs", [(32, 8, 128, 16), (32, 8, 64, 16), (8, 2, 128, 32), (16, 2, 64, 32),
-                                          (8, 8, 128, 16), (32, 2, 128, 16), (40, 8, 128, 16)])
+                                          (8, 8, 128, 16), (32, 2, 128, 16), (40, 8, 128, 16),
+                                          (32, 8, 128, 8), (8, 2, 64, 8)])       # block 8: scripts/diff_page_sizes.sh:16
 @pytest.mark.parametrize("B,max_len", [(1, 40), (3, 700), (16, 2100)])
 def test_paged_decode_attention(Hq, Hkv, D, bs, B, max_len):
     ops = _ops()
@@ -403,7 +404,7 @@ def test_paged_decode_streamk_schedule(B, max_len, zeros):
     assert torch.equal(outs[0], outs[1])
 
 
-@pytest.mark.parametrize("Hkv,D,bs", [(8, 128, 16), (8, 64, 16), (2, 128, 32), (4, 64, 32)])
+@pytest.mark.parametrize("Hkv,D,bs", [(8, 128, 16), (8, 64, 16), (2, 128, 32), (4, 64, 32), (8, 128, 8), (2, 64, 8)])
 def test_fused_last_block_score_bit_exact(Hkv, D, bs):
     """Rows with seq_len % bs == 0 get pool[last block id][head_offset + h] = per-head value_l2 of
     their last (just filled) block, bit-identical to oracle/scoring.py; written to every pool
@@ -595,7 +596,8 @@ def test_copy_and_swap_blocks():
 
 
 # --------------------------------------------------------------------------- W1 fused into A2
-@pytest.mark.parametrize("Hq,Hkv,D,bs", [(32, 8, 128, 16), (8, 2, 64, 16), (16, 2, 128, 32), (32, 2, 64, 32)])
+@pytest.mark.parametrize("Hq,Hkv,D,bs", [(32, 8, 128, 16), (8, 2, 64, 16), (16, 2, 128, 32), (32, 2, 64, 32),
+                                          (32, 8, 128, 8), (8, 2, 64, 8)])
 @pytest.mark.parametrize("B,max_len", [(5, 90), (33, 1300)])
 def test_decode_layer_fused_cache_write(Hq, Hkv, D, bs, B, max_len):
     """pc_decode_layer with fuse_cache_write: the attention kernel itself stores the step's
@@ -723,3 +725,42 @@ def test_torch_library_ops_match_ctypes_path():
     assert torch.equal(kv, kv2)
     with pytest.raises(RuntimeError):
         ns.paged_attention_v1(o2, q, kc, vc, Hkv, s, bt, lens, bs, 160, None, "fp8", 1.0, 1.0, 0, 0, 0, 64, 0)
+
+
+@pytest.mark.parametrize("D", [64, 128])
+def test_prefill_attention_block_size_8_gather(D):
+    """Block size 8 (scripts/diff_page_sizes.sh:16): the sink block is 8 tokens and the pruned run a
+    multiple of 8, so the streamingLLM gather runs on 8-row TMA boxes (picked from the host copy of
+    req_meta); without the host copy such a request is refused by the launch-time check only when
+    misaligned to 8."""
+    ops = _ops()
+    Hq, Hkv, bs = 8, 2, 8
+    pol = Policy(block_size=bs, cache_prune_type="budget", cache_budget=128)
+    prompt_lens = [5, 128, 137, 300, 1001]
+    T = sum(prompt_lens)
+    q = (rnd(41, T, Hq, D).float() * 0.5).to(torch.bfloat16)
+    k = (rnd(42, T, Hkv, D).float() * 0.5).to(torch.bfloat16)
+    v = rnd(43, T, Hkv, D)
+    meta, gidx, kept_l, s = [], [], [], 0
+    for L in prompt_lens:
+        kept, pruned, first = policy.prompt_prune_layout(L, pol)
+        meta.append([s, L, s, kept, first, pruned])
+        gidx.append(torch.from_numpy(policy.prompt_gather_index(L, pol)) + s)
+        kept_l.append(kept)
+        s += L
+    assert any((m[4] | m[5]) & 15 for m in meta if m[5]), "the case must need 8-row boxes"
+    gidx = torch.cat(gidx)
+    ref = paged_ops.prefill_attention(q, k[gidx], v[gidx], prompt_lens, kept_l, D ** -0.5).float()
+    out = torch.full((T, Hq, D), float("nan"), dtype=torch.bfloat16, device=DEV)
+    m = np.asarray(meta, np.int32)
+    ops.prefill_attn_topleft_causal(out, q.to(DEV), k.to(DEV), v.to(DEV), torch.from_numpy(m).to(DEV),
+                                    max(prompt_lens), D ** -0.5, req_meta_host=m)
+    torch.cuda.synchronize()
+    got = out.float().cpu()
+    assert torch.isfinite(got).all()
+    np.testing.assert_allclose(got.numpy(), ref.numpy(), atol=2e-2, rtol=0)
+    bad = m.copy()
+    bad[3, 5] += 4          # pruned run not a multiple of 8: refused before the launch
+    with pytest.raises(RuntimeError):
+        ops.prefill_attn_topleft_causal(out, q.to(DEV), k.to(DEV), v.to(DEV), torch.from_numpy(bad).to(DEV),
+                                        max(prompt_lens), D ** -0.5, req_meta_host=bad)

@@ -183,7 +183,7 @@ def add_cli_args(parser: argparse.ArgumentParser) -> argparse.ArgumentParser:
                         help="local / global as HEAD ships them (enable_random_evict = True, "
                              "torch_cuda_sdpa.py:802): random window block at decode time, token-level "
                              "value_l2 prompt prune.")
-    parser.add_argument("--block-size", type=int, default=16, choices=[16, 32],
+    parser.add_argument("--block-size", type=int, default=16, choices=[8, 16, 32],
                         help="Token block size")
     return parser
 

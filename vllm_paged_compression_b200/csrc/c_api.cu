@@ -162,7 +162,7 @@ size_t pc_paged_decode_workspace_bytes(int32_t batch, int32_t num_heads, int32_t
                                        int32_t max_kv_len) {
   const int sms = device_sm_count();
   if (sms <= 0 || batch <= 0 || num_kv_heads <= 0 || num_heads % num_kv_heads) return 0;
-  if ((head_size != 64 && head_size != 128) || (block_size != 16 && block_size != 32)) return 0;
+  if ((head_size != 64 && head_size != 128) || (block_size != 8 && block_size != 16 && block_size != 32)) return 0;
   return decode_workspace_bytes(batch, num_heads, num_kv_heads, head_size, block_size, max_kv_len, sms);
 }
 
@@ -174,8 +174,8 @@ int pc_paged_decode_plan(int32_t batch, int32_t num_heads, int32_t num_kv_heads,
   if (sms <= 0) return PC_ERR_CUDA;
   if (batch <= 0 || num_kv_heads <= 0 || num_heads % num_kv_heads)
     return set_error(PC_ERR_INVALID, "pc_paged_decode_plan: bad shape");
-  if ((head_size != 64 && head_size != 128) || (block_size != 16 && block_size != 32))
-    return set_error(PC_ERR_UNSUPPORTED, "Unsupported head size / block size (supported: head 64|128, block 16|32)");
+  if ((head_size != 64 && head_size != 128) || (block_size != 8 && block_size != 16 && block_size != 32))
+    return set_error(PC_ERR_UNSUPPORTED, "Unsupported head size / block size (supported: head 64|128, block 8|16|32)");
   int pl[2];
   decode_plan(batch, num_heads, num_kv_heads, head_size, block_size, max_kv_len, sms, pl);
   out_plan[0] = pl[0];

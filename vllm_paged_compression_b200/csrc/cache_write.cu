@@ -697,20 +697,26 @@ int cache_write(const CacheWriteArgs& a, cudaStream_t stream) {
       if (a.D == 128 && a.BS == 32) return dispatch_stream_write<128, 32>(p, tiles, stream);
       if (a.D == 64 && a.BS == 16) return dispatch_stream_write<64, 16>(p, tiles, stream);
       if (a.D == 64 && a.BS == 32) return dispatch_stream_write<64, 32>(p, tiles, stream);
+      if (a.D == 128 && a.BS == 8) return dispatch_stream_write<128, 8>(p, tiles, stream);
+      if (a.D == 64 && a.BS == 8) return dispatch_stream_write<64, 8>(p, tiles, stream);
     }
     if (a.D == 128 && a.BS == 16) return dispatch_block_write<128, 16>(p, tiles, stream);
     if (a.D == 128 && a.BS == 32) return dispatch_block_write<128, 32>(p, tiles, stream);
     if (a.D == 64 && a.BS == 16) return dispatch_block_write<64, 16>(p, tiles, stream);
     if (a.D == 64 && a.BS == 32) return dispatch_block_write<64, 32>(p, tiles, stream);
+    if (a.D == 128 && a.BS == 8) return dispatch_block_write<128, 8>(p, tiles, stream);
+    if (a.D == 64 && a.BS == 8) return dispatch_block_write<64, 8>(p, tiles, stream);
     return set_error(PC_ERR_UNSUPPORTED,
-                     "Unsupported head size / block size (supported: head 64|128, block 16|32)");
+                     "Unsupported head size / block size (supported: head 64|128, block 8|16|32)");
   }
   if (a.D == 128 && a.BS == 16) return launch_cache_write<128, 16>(p, tiles, stream);
   if (a.D == 128 && a.BS == 32) return launch_cache_write<128, 32>(p, tiles, stream);
   if (a.D == 64 && a.BS == 16) return launch_cache_write<64, 16>(p, tiles, stream);
   if (a.D == 64 && a.BS == 32) return launch_cache_write<64, 32>(p, tiles, stream);
+  if (a.D == 128 && a.BS == 8) return launch_cache_write<128, 8>(p, tiles, stream);
+  if (a.D == 64 && a.BS == 8) return launch_cache_write<64, 8>(p, tiles, stream);
   return set_error(PC_ERR_UNSUPPORTED,
-                   "Unsupported head size / block size (supported: head 64|128, block 16|32)");
+                   "Unsupported head size / block size (supported: head 64|128, block 8|16|32)");
 }
 
 }  // namespace pc

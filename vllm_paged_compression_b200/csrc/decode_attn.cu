@@ -171,7 +171,12 @@ paged_decode_attn_score_kernel(const DecodeParams p) {
   static_assert(kStages < kFifo, "descriptor fifo must outrun the page ring");
   constexpr int KSTEPS = D / 16;   // k-steps of the QK^T contraction
   constexpr int MT = D / 16;       // m-tiles (16 dims) of O^T
-  constexpr int TT = BS / 16;      // 16-token tiles per page
+  // 16-token MMA tiles per page.  Block size 8 (scripts/diff_page_sizes.sh:16): one tile per page whose
+  // upper 8 token rows do not exist -- their ldmatrix rows alias the lower 8 (finite values), their
+  // logits are masked, so their probabilities are exactly 0.  Twice the tensor work per byte on a
+  // kernel whose tensor pipe is 7 % busy.
+  constexpr int TT = (BS + 15) / 16;
+  constexpr bool kHalfTile = (BS == 8);
   constexpr int kSlot = 8 * D + 16;  // floats per partial slot (16-byte aligned stride)
 
   extern __shared__ __align__(1024) uint8_t smem[];
@@ -542,7 +547,7 @@ paged_decode_attn_score_kernel(const DecodeParams p) {
       {
         // ldmatrix.x4 row address: matrix mi = lane/8 -> (token half = mi&1, chunk = 2j + mi>>1)
         const int mi = lane >> 3, r = lane & 7;
-        const uint32_t koff = (uint32_t)(((mi >> 1) * BS + (mi & 1) * 8 + r) * 16);
+        const uint32_t koff = (uint32_t)(((mi >> 1) * BS + (kHalfTile ? 0 : (mi & 1) * 8) + r) * 16);
 #pragma unroll
         for (int j = 0; j < KSTEPS; ++j) {
           uint32_t a[J][4];
@@ -567,6 +572,7 @@ paged_decode_attn_score_kernel(const DecodeParams p) {
           if (tok >= kv_len) { x[jt][0] = -INFINITY; x[jt][1] = -INFINITY; }
           if (tok + 8 >= kv_len) { x[jt][2] = -INFINITY; x[jt][3] = -INFINITY; }
         }
+        if constexpr (kHalfTile) { x[jt][2] = -INFINITY; x[jt][3] = -INFINITY; }   // token rows 8..15 of an 8-token page
       }
       // ---------------- online softmax over the J*16 tokens (per head = per column; rows live
       // in lanes with equal t)
@@ -605,7 +611,7 @@ paged_decode_attn_score_kernel(const DecodeParams p) {
       {
         // matrix mi -> (dim half = mi&1, token half = mi>>1); row r = dim within the half
         const int mi = lane >> 3, r = lane & 7;
-        const uint32_t voff = (uint32_t)((((mi & 1) * 8 + r) * BS + (mi >> 1) * 8) * 2);
+        const uint32_t voff = (uint32_t)((((mi & 1) * 8 + r) * BS + (kHalfTile ? 0 : (mi >> 1) * 8)) * 2);
 #pragma unroll
         for (int jt = 0; jt < J; ++jt) {
 #pragma unroll
@@ -856,6 +862,7 @@ struct DecodeCfg { int warps, stages; };
 static DecodeCfg decode_cfg(int D, int BS) {
   if (D == 128 && BS == 32) return {4, 3};
   if (D == 64 && BS == 16) return {8, 6};
+  if (BS == 8) return {8, 6};      // (128, 8): 4 KiB stages, (64, 8): 2 KiB
   return {8, 3};   // (128, 16), (64, 32)
 }
 // dynamic shared memory of a launch (mirrors DecodeTraits::smem_bytes)
@@ -1044,10 +1051,10 @@ int paged_decode_attn_score(const DecodeArgs& a, cudaStream_t stream) {
     return set_error(PC_ERR_INVALID, "decode: out rows must be 16-byte aligned, query rows 4-byte aligned");
   const int num_sms = device_sm_count();
   if (num_sms <= 0) return PC_ERR_CUDA;
-  if (a.D != 64 && a.D != 128 || a.BS != 16 && a.BS != 32)
+  if (a.D != 64 && a.D != 128 || a.BS != 8 && a.BS != 16 && a.BS != 32)
     // mirrors TORCH_CHECK(false, "Unsupported head size / block size") in
     // csrc/attention/paged_attention_v1.cu:108-110,160-162
-    return set_error(PC_ERR_UNSUPPORTED, "Unsupported head size / block size (supported: head 64|128, block 16|32)");
+    return set_error(PC_ERR_UNSUPPORTED, "Unsupported head size / block size (supported: head 64|128, block 8|16|32)");
   const int team_cap = decode_team_cap(a.D, a.BS, a.B);
   const DecodePlan pl = plan_decode(a.B, a.Hq, a.Hkv, a.D, a.BS, a.max_kv_len, num_sms, team_cap);
   // with a device-side plan (graph replay) any plan up to max_kv_len may be in force
@@ -1107,6 +1114,8 @@ int paged_decode_attn_score(const DecodeArgs& a, cudaStream_t stream) {
   if (a.D == 128 && a.BS == 16) return launch_decode<128, 16, 8, 3>(p, num_sms, grid_teams, stream);
   if (a.D == 128 && a.BS == 32) return launch_decode<128, 32, 4, 3>(p, num_sms, grid_teams, stream);
   if (a.D == 64 && a.BS == 16) return launch_decode<64, 16, 8, 6>(p, num_sms, grid_teams, stream);
+  if (a.D == 128 && a.BS == 8) return launch_decode<128, 8, 8, 6>(p, num_sms, grid_teams, stream);
+  if (a.D == 64 && a.BS == 8) return launch_decode<64, 8, 8, 6>(p, num_sms, grid_teams, stream);
   return launch_decode<64, 32, 8, 3>(p, num_sms, grid_teams, stream);
 }
 

@@ -50,7 +50,8 @@ struct PrefillTcParams {
 #ifndef PC_P_TMEM
 #define PC_P_TMEM 1   // P as a TMEM A operand (0: P through shared memory, the first version)
 #endif
-constexpr int kBoxRows = 16;   // K/V TMA box = one 16-token run (first, pruned are multiples of 16)
+// K/V TMA box rows (template parameter BOX) = one run of kept tokens: 16 (first, pruned multiples of
+// 16: block sizes 16 / 32) or 8 (block size 8; a box of 8 rows is exactly one 1024-byte SW128 atom)
 
 // TN = kv rows per tile (UMMA N of S, K extent of P.V).  TN = 64 fits two CTAs per SM
 // (112 KB of shared memory and 256 TMEM columns each), TN = 128 one.
@@ -94,7 +95,7 @@ struct TcItem {
   int q_start, q_len, kv_src, kv_len, first, pruned, i0, hq, hkv, ntiles;
 };
 
-template <int D, int TN>
+template <int D, int TN, int BOX>
 __global__ void __launch_bounds__(kTcThreads, (TN == 64 ? 2 : 1))
 prefill_attn_tc_kernel(const PrefillTcParams p, const __grid_constant__ CUtensorMap tm_q,
                                const __grid_constant__ CUtensorMap tm_k,
@@ -151,12 +152,12 @@ prefill_attn_tc_kernel(const PrefillTcParams p, const __grid_constant__ CUtensor
   auto issue_kv = [&](const CUtensorMap* tm, uint8_t* dst, uint64_t* full, const TcItem& it, int t) {
     mbar_expect_tx(full, L::kKV);
 #pragma unroll
-    for (int g = 0; g < kTN / kBoxRows; ++g) {
-      const int j = t * kTN + g * kBoxRows;
+    for (int g = 0; g < kTN / BOX; ++g) {
+      const int j = t * kTN + g * BOX;
       const int src = it.kv_src + (j < it.first ? j : j + it.pruned);
 #pragma unroll
       for (int b = 0; b < D / 64; ++b)
-        t5::tma_load_2d(dst + b * (kTN * 128) + g * (kBoxRows * 128), tm, it.hkv * D + b * 64, src, full);
+        t5::tma_load_2d(dst + b * (kTN * 128) + g * (BOX * 128), tm, it.hkv * D + b * 64, src, full);
     }
   };
 
@@ -192,7 +193,7 @@ prefill_attn_tc_kernel(const PrefillTcParams p, const __grid_constant__ CUtensor
       for (int k = blockIdx.x; k < total; k += gridDim.x) {
         const TcItem it = get_item(k);
         if (it.ntiles == 0) continue;
-        if (it.pruned != 0 && (((it.first | it.pruned) & 15) != 0)) __trap();
+        if (it.pruned != 0 && (((it.first | it.pruned) & (BOX - 1)) != 0)) __trap();
         // Q buffer is free once the previous item's last S MMA (tile g - 1) has completed
         if (g > 0) t5::mbar_wait_relaxed(&bar[B_SFULL + ((g - 1) & 1)], ((g - 1) >> 1) & 1);
         mbar_expect_tx(&bar[B_QFULL], L::kQ);
@@ -208,8 +209,8 @@ prefill_attn_tc_kernel(const PrefillTcParams p, const __grid_constant__ CUtensor
 #pragma unroll
           for (int b = 0; b < D / 64; ++b) t5::tma_prefetch_l2_2d(&tm_q, nx.hq * D + b * 64, nx.q_start + nx.i0);
 #pragma unroll
-          for (int gg = 0; gg < kTN / kBoxRows; ++gg) {
-            const int jn = gg * kBoxRows;
+          for (int gg = 0; gg < kTN / BOX; ++gg) {
+            const int jn = gg * BOX;
             const int src = nx.kv_src + (jn < nx.first ? jn : jn + nx.pruned);
 #pragma unroll
             for (int b = 0; b < D / 64; ++b) {
@@ -522,14 +523,14 @@ static int make_rows_map(CUtensorMap* m, const void* base, long long rows, int i
   return 0;
 }
 
-template <int D, int TN>
+template <int D, int TN, int BOX>
 static int launch_prefill_tc(const PrefillTcParams& p, const PrefillArgs& a, cudaStream_t stream) {
   CUtensorMap tq, tk, tv;
   if (int rc = make_rows_map(&tq, a.q, a.num_tokens, a.Hq * D, a.q_stride, kTM)) return rc;
-  if (int rc = make_rows_map(&tk, a.k, a.num_tokens, a.Hkv * D, a.key_stride, kBoxRows)) return rc;
-  if (int rc = make_rows_map(&tv, a.v, a.num_tokens, a.Hkv * D, a.value_stride, kBoxRows)) return rc;
+  if (int rc = make_rows_map(&tk, a.k, a.num_tokens, a.Hkv * D, a.key_stride, BOX)) return rc;
+  if (int rc = make_rows_map(&tv, a.v, a.num_tokens, a.Hkv * D, a.value_stride, BOX)) return rc;
   const int smem = TcSmem<D, TN>::kBytes;
-  auto kern = prefill_attn_tc_kernel<D, TN>;
+  auto kern = prefill_attn_tc_kernel<D, TN, BOX>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   if (e != cudaSuccess) return set_cuda_error("cudaFuncSetAttribute(prefill_tc)", e);
   const bool persist = g_tc_persistent < 0 ? (a.max_q_len <= 2048) : (g_tc_persistent != 0);
@@ -555,8 +556,8 @@ static int launch_prefill_tc(const PrefillTcParams& p, const PrefillArgs& a, cud
 }
 
 // A1 entry: argument checks + launch.  The streamingLLM gather runs as TMA box coordinates, so
-// `first` and `pruned` of every pruned request must be multiples of 16 (true for block sizes
-// 16 / 32 with the reference's policies: both are whole blocks).  The check needs the HOST copy
+// `first` and `pruned` of every pruned request must be multiples of 8 (whole blocks of 8 / 16 / 32;
+// multiples of 16 take 16-row boxes, otherwise 8-row boxes: twice the TMA instructions).  The check needs the HOST copy
 // of req_meta; without one (req_meta_host == NULL) a violating request reaches the device-side
 // guard, which is a trap -- callers that cannot vouch for the alignment pass the host copy.
 int prefill_attn(const PrefillArgs& a, cudaStream_t stream) {
@@ -568,15 +569,17 @@ int prefill_attn(const PrefillArgs& a, cudaStream_t stream) {
        reinterpret_cast<uintptr_t>(a.v) | reinterpret_cast<uintptr_t>(a.out)) & 15)
     return set_error(PC_ERR_INVALID, "q/k/v/out pointers must be 16-byte aligned");
   if (a.num_tokens <= 0) return set_error(PC_ERR_INVALID, "prefill: num_tokens must be the row count of q/k/v");
+  bool box8 = false;
   if (a.req_meta_host != nullptr) {
     for (int r = 0; r < a.num_reqs; ++r) {
       const int* m = a.req_meta_host + r * 6;
       if (m[1] < 0 || m[3] < 0 || m[3] > m[1] || m[0] < 0 || m[2] < 0 || m[4] < 0 || m[5] < 0 ||
           (long long)m[0] + m[1] > a.num_tokens || (long long)m[2] + m[3] + m[5] > a.num_tokens)
         return set_error(PC_ERR_INVALID, "prefill: req_meta row out of range (q_len >= kv_len >= 0, rows inside num_tokens)");
-      if (m[5] != 0 && (((m[4] | m[5]) & 15) != 0))
+      if (m[5] != 0 && (((m[4] | m[5]) & 7) != 0))
         return set_error(PC_ERR_INVALID,
-                         "prefill: first / pruned must be multiples of 16 tokens (whole blocks of 16 / 32)");
+                         "prefill: first / pruned must be multiples of 8 tokens (whole blocks of 8 / 16 / 32)");
+      if (m[5] != 0 && (((m[4] | m[5]) & 15) != 0)) box8 = true;     // block size 8: 8-row TMA boxes
     }
   }
 #ifdef PC_DEBUG
@@ -597,8 +600,12 @@ int prefill_attn(const PrefillArgs& a, cudaStream_t stream) {
     if (a.D == 64) return launch_prefill_tc<64, 128>(p, a, stream);
   }
 #endif
-  if (a.D == 128) return launch_prefill_tc<128, 64>(p, a, stream);
-  if (a.D == 64) return launch_prefill_tc<64, 64>(p, a, stream);
+  if (box8) {
+    if (a.D == 128) return launch_prefill_tc<128, 64, 8>(p, a, stream);
+    if (a.D == 64) return launch_prefill_tc<64, 64, 8>(p, a, stream);
+  }
+  if (a.D == 128) return launch_prefill_tc<128, 64, 16>(p, a, stream);
+  if (a.D == 64) return launch_prefill_tc<64, 64, 16>(p, a, stream);
   return set_error(PC_ERR_UNSUPPORTED, "Unsupported head size (supported: 64|128)");
 }
 
