@@ -167,6 +167,9 @@ def parse_args():
     ap.add_argument("--no-io-prefetch", action="store_true",
                     help="e2e leg: upload a step's inputs inside that step (layer groups) instead of one "
                          "copy a step ahead")
+    ap.add_argument("--debug-knob", action="append", default=[], metavar="NAME=INT",
+                    help="PC_DEBUG library only (PC_LIB_PATH=...debug.so): call pc_debug_set_NAME(INT) before the run, "
+                         "e.g. decode_two_cta=1 (A/B runs; the product library has no such symbols)")
     ap.add_argument("--no-numa-bind", action="store_true",
                     help="do not bind the rank to the NUMA node of its GPU before allocating pinned memory")
     ap.add_argument("--tp-emulate", type=int, default=1,
@@ -717,7 +720,14 @@ def main():
     if spec.Hkv % spec.tp != 0:
         raise SystemExit(f"tensor parallel size {spec.tp} must divide {spec.Hkv} kv heads")
     from vllm_paged_compression_b200 import _lib
-    _lib.load()                                        # fail loudly if the CUDA library is missing
+    lib = _lib.load()                                  # fail loudly if the CUDA library is missing
+    for kv in args.debug_knob:                         # A/B runs with the PC_DEBUG library
+        import ctypes
+        name, val = kv.split("=")
+        fn = getattr(lib, "pc_debug_set_" + name)      # AttributeError with the product library
+        fn.argtypes = [ctypes.c_int32]
+        fn.restype = None
+        fn(int(val))
 
     if args.sweep:
         from benchtools import microbench

@@ -164,8 +164,8 @@ __device__ __forceinline__ void write_new_token(__nv_bfloat16* k_cache_w, __nv_b
   __syncwarp();
 }
 
-template <int D, int BS, int kWarps, int kStages>
-__global__ void __launch_bounds__(kWarps * 32, 1)
+template <int D, int BS, int kWarps, int kStages, int kCtasPerSm = 1>
+__global__ void __launch_bounds__(kWarps * 32, kCtasPerSm)
 paged_decode_attn_score_kernel(const DecodeParams p) {
   using T = DecodeTraits<D, BS, kWarps, kStages>;
   static_assert(kStages < kFifo, "descriptor fifo must outrun the page ring");
@@ -858,12 +858,26 @@ struct DecodePlan {
 };
 
 // kernel configuration per (D, BS): the ring (warps x stages x (K + V page)) must fit 227 KB
-struct DecodeCfg { int warps, stages; };
+// ctas = CTAs per SM: with TWO half-size CTAs (4 warps, 96 KiB of rings each) the prologue of the
+// next layer's CTA (schedule scan + first table entries + first page latency: 3-4.5 us during which
+// an SM with ONE resident CTA pulls nothing) overlaps the streaming of its sibling.
+struct DecodeCfg { int warps, stages, ctas; };
+// Measured (profiles/r02_decode_two_cta.txt): step 0.940-0.944 ms against 0.947-0.948 at the bench
+// shape, kernel alone 28.1 against 27.9 us, slightly slower at evict-freq 4 and at the TP-8 per-rank
+// shape -- within noise, so the one-CTA configuration stays and this one exists in the PC_DEBUG
+// library only.
+#ifdef PC_DEBUG
+static int g_decode_two_cta = 0;
+void set_decode_two_cta(int v) { g_decode_two_cta = v; ++g_plan_epoch; }   // (invalidates the worst-case memo)
+#else
+constexpr int g_decode_two_cta = 0;
+#endif
 static DecodeCfg decode_cfg(int D, int BS) {
-  if (D == 128 && BS == 32) return {4, 3};
-  if (D == 64 && BS == 16) return {8, 6};
-  if (BS == 8) return {8, 6};      // (128, 8): 4 KiB stages, (64, 8): 2 KiB
-  return {8, 3};   // (128, 16), (64, 32)
+  if (D == 128 && BS == 16 && g_decode_two_cta) return {4, 3, 2};
+  if (D == 128 && BS == 32) return {4, 3, 1};
+  if (D == 64 && BS == 16) return {8, 6, 1};
+  if (BS == 8) return {8, 6, 1};      // (128, 8): 4 KiB stages, (64, 8): 2 KiB
+  return {8, 3, 1};   // (128, 16), (64, 32)
 }
 // dynamic shared memory of a launch (mirrors DecodeTraits::smem_bytes)
 static size_t decode_smem_bytes(int D, int BS, int B, int team_cap) {
@@ -874,11 +888,12 @@ static size_t decode_smem_bytes(int D, int BS, int B, int team_cap) {
          followers * (32 * (D / 4) * 4 + 64) + ((size_t)B + 1) * 4 + 64;
 }
 constexpr size_t kSmemLimit = 227 * 1024;
+static size_t decode_smem_limit(int D, int BS) { return decode_cfg(D, BS).ctas == 2 ? (size_t)113 * 1024 : kSmemLimit; }
 // largest team whose hand-over buffers still fit next to the ring and the O(B) schedule
 static int decode_team_cap(int D, int BS, int B) {
   const DecodeCfg c = decode_cfg(D, BS);
   for (int t = c.warps; t > 1; t >>= 1)
-    if (decode_smem_bytes(D, BS, B, t) <= kSmemLimit) return t;
+    if (decode_smem_bytes(D, BS, B, t) <= decode_smem_limit(D, BS)) return t;
   return 1;
 }
 
@@ -930,7 +945,7 @@ static double plan_cost(const PlanModel& m, long long groups, long long max_bloc
 
 static DecodePlan plan_decode(int B, int Hq, int Hkv, int D, int BS, int max_kv_len, int num_sms, int team_cap) {
   DecodePlan pl;
-  const int warps = decode_cfg(D, BS).warps;
+  const int warps = decode_cfg(D, BS).warps * decode_cfg(D, BS).ctas;   // warps per SM
   const int G = Hq / Hkv;
   const int HG = (G + 7) / 8;
   const long long groups = (long long)B * Hkv * HG;
@@ -941,7 +956,7 @@ static DecodePlan plan_decode(int B, int Hq, int Hkv, int D, int BS, int max_kv_
   long long cp = max_blocks;
   int team = 1;
   double best = plan_cost(m, groups, max_blocks, cp, 1, num_sms, warps, page_bytes);
-  for (int T = 1; T <= team_cap && T <= warps; T <<= 1) {
+  for (int T = 1; T <= team_cap && T <= decode_cfg(D, BS).warps; T <<= 1) {
     const long long teams = workers / T;
     long long last_c = -1;
     for (long long nn = 1; nn <= max_blocks; nn = nn < 16 ? nn + 1 : nn + nn / 8) {
@@ -1003,14 +1018,14 @@ void decode_plan(int B, int Hq, int Hkv, int D, int BS, int max_kv_len, int num_
   out2[1] = pl.team;
 }
 
-template <int D, int BS, int kWarps, int kStages>
+template <int D, int BS, int kWarps, int kStages, int kCtasPerSm = 1>
 static int launch_decode(const DecodeParams& p, int num_sms, long long max_teams, cudaStream_t stream) {
   using T = DecodeTraits<D, BS, kWarps, kStages>;
-  auto kern = paged_decode_attn_score_kernel<D, BS, kWarps, kStages>;
+  auto kern = paged_decode_attn_score_kernel<D, BS, kWarps, kStages, kCtasPerSm>;
   const size_t smem = T::smem_bytes(p.B, p.team_cap);
   if (smem != decode_smem_bytes(D, BS, p.B, p.team_cap) || decode_cfg(D, BS).warps != kWarps)
     return set_error(PC_ERR_INVALID, "decode: internal shared-memory accounting mismatch");
-  if (smem > kSmemLimit) return set_error(PC_ERR_INVALID, "decode: batch too large for the in-kernel schedule");
+  if (smem > decode_smem_limit(D, BS)) return set_error(PC_ERR_INVALID, "decode: batch too large for the in-kernel schedule");
   // largest dynamic smem opted in so far, per device (monotone; a racing thread at worst
   // repeats the idempotent attribute call)
   static std::atomic<size_t> smem_set[64];
@@ -1025,7 +1040,8 @@ static int launch_decode(const DecodeParams& p, int num_sms, long long max_teams
       }
     }
   }
-  long long ctas = max_teams < (long long)num_sms ? max_teams : (long long)num_sms;  // spread over SMs first
+  const long long slots = (long long)num_sms * kCtasPerSm;
+  long long ctas = max_teams < slots ? max_teams : slots;  // spread over SMs first
   if (ctas < 1) ctas = 1;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3((unsigned)ctas);
@@ -1110,7 +1126,11 @@ int paged_decode_attn_score(const DecodeArgs& a, cudaStream_t stream) {
   }
 
   // a device-side plan may change between replays of a captured launch: full grid
-  const long long grid_teams = a.plan ? (long long)num_sms : pl.max_chunks;
+  const long long grid_teams = a.plan ? (long long)num_sms * decode_cfg(a.D, a.BS).ctas : pl.max_chunks;
+#ifdef PC_DEBUG
+  if (a.D == 128 && a.BS == 16 && decode_cfg(128, 16).ctas == 2)
+    return launch_decode<128, 16, 4, 3, 2>(p, num_sms, grid_teams, stream);
+#endif
   if (a.D == 128 && a.BS == 16) return launch_decode<128, 16, 8, 3>(p, num_sms, grid_teams, stream);
   if (a.D == 128 && a.BS == 32) return launch_decode<128, 32, 4, 3>(p, num_sms, grid_teams, stream);
   if (a.D == 64 && a.BS == 16) return launch_decode<64, 16, 8, 6>(p, num_sms, grid_teams, stream);

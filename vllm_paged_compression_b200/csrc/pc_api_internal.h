@@ -64,6 +64,7 @@ int paged_decode_attn_score(const DecodeArgs& a, cudaStream_t stream);
 #ifdef PC_DEBUG
 void set_decode_trace(void* buf);  // per-warp globaltimer stamps, nullptr = off
 void set_decode_plan_override(int chunk_pages, int team);  // 0 = planner's choice
+void set_decode_two_cta(int v);    // (128, 16): two 4-warp CTAs per SM instead of one 8-warp CTA
 #endif
 
 struct CacheWriteArgs {

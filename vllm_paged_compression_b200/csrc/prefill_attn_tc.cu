@@ -596,8 +596,8 @@ int prefill_attn(const PrefillArgs& a, cudaStream_t stream) {
   p.scale_log2 = a.scale * 1.4426950408889634f;
 #ifdef PC_DEBUG
   if (g_tc_tile_n == 128) {
-    if (a.D == 128) return launch_prefill_tc<128, 128>(p, a, stream);
-    if (a.D == 64) return launch_prefill_tc<64, 128>(p, a, stream);
+    if (a.D == 128) return launch_prefill_tc<128, 128, 16>(p, a, stream);
+    if (a.D == 64) return launch_prefill_tc<64, 128, 16>(p, a, stream);
   }
 #endif
   if (box8) {
