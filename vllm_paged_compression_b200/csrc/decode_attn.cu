@@ -187,6 +187,9 @@ paged_decode_attn_score_kernel(const DecodeParams p) {
   const int n_launched = gridDim.x * kWarps;
 
   const unsigned long long t_start = p.trace ? gtimer() : 0ull;
+  // the first pass of the schedule scan needs this row's kv length: request it before anything else,
+  // next to the plan words, so that the prologue pays ONE global-memory latency, not two in a row
+  const int len_first = ((int)threadIdx.x < p.B) ? __ldg(p.kv_lens + threadIdx.x) : 0;
   const int chunk_pages = (p.plan != nullptr) ? max(1, __ldg(p.plan)) : p.chunk_pages;
   // team geometry: TS warps per team (power of two), member tw of team `team_in_cta`
   int TS = (p.plan != nullptr) ? __ldg(p.plan + 1) : p.team;
@@ -230,7 +233,7 @@ paged_decode_attn_score_kernel(const DecodeParams p) {
       const int r = base + threadIdx.x;
       int n = 0;
       if (r < p.B) {
-        const int len = p.kv_lens[r];
+        const int len = (base == 0) ? len_first : __ldg(p.kv_lens + r);
         n = ((len + BS - 1) / BS + chunk_pages - 1) / chunk_pages;
         saw_empty |= (len == 0);
       }
