@@ -2,8 +2,9 @@
 second for the 8B block shape (block 16 x 8 kv heads x 128 x bf16 = 32 KiB per pool per block).
     python -m benchtools.microbench_block_ops
 copy_blocks: one launch copies `pairs` (src, dst) blocks inside the K and the V pool (read + write
-bytes counted).  swap_blocks: one cudaMemcpyAsync per pair between a device pool and a pinned host
-pool (the reference does the same, csrc/cache_kernels.cu:24-66)."""
+bytes counted).  swap_blocks: one cudaMemcpyAsync per run of consecutive pairs between a device pool
+and a pinned host pool (the reference issues one per pair, csrc/cache_kernels.cu:24-66); the lists
+used here are single runs."""
 from __future__ import annotations
 
 import json

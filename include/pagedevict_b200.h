@@ -320,7 +320,8 @@ int pc_zero_cache_slots_layers(void* const* key_caches /* DEVICE */, void* const
  * pc_copy_blocks replaces _C_cache_ops::copy_blocks (csrc/cache_kernels.cu:69-150) for
  * one layer: pairs int64 [num_pairs][2] = {src_block, dst_block}, same pool.
  * pc_swap_blocks replaces swap_blocks (csrc/cache_kernels.cu:24-66): block-granular
- * copies between two pools (either may be pinned host memory); pairs is a HOST array. */
+ * copies between two pools (either may be pinned host memory); pairs is a HOST array.  Runs of
+ * pairs whose source and destination blocks are both consecutive travel as one copy. */
 int pc_copy_blocks(void* key_cache, void* value_cache, const int64_t* pairs, int32_t num_pairs,
                    int64_t block_bytes, void* stream);
 int pc_swap_blocks(const void* src, void* dst, const int64_t* pairs /* HOST */,

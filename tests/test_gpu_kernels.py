@@ -593,6 +593,19 @@ def test_copy_and_swap_blocks():
     ops.swap_blocks(kv[0], host, torch.tensor([[3, 7], [4, 0]]))
     torch.cuda.synchronize()
     assert torch.equal(host[7], kv[0, 3].cpu()) and torch.equal(host[0], kv[0, 4].cpu())
+    # runs of consecutive (src, dst) pairs travel as one copy each: runs, a broken run, a lone pair
+    host.zero_()
+    m = torch.tensor([[10, 20], [11, 21], [12, 22], [13, 24], [14, 25], [2, 3], [30, 29], [31, 30]])
+    ops.swap_blocks(kv[0], host, m)
+    torch.cuda.synchronize()
+    want = torch.zeros_like(host)
+    for s_, d_ in m.tolist():
+        want[d_] = kv[0, s_].cpu()
+    assert torch.equal(host, want)
+    back = torch.zeros_like(kv[0])
+    ops.swap_blocks(host, back, torch.tensor([[20, 0], [21, 1], [22, 2], [24, 9]]))      # host -> device
+    torch.cuda.synchronize()
+    assert torch.equal(back[:3].cpu(), want[20:23]) and torch.equal(back[9].cpu(), want[24])
 
 
 # --------------------------------------------------------------------------- W1 fused into A2

@@ -397,13 +397,18 @@ int pc_swap_blocks(const void* src, void* dst, const int64_t* pairs, int32_t num
                    int64_t block_bytes, void* stream) {
   if (num_pairs == 0) return PC_OK;
   if (!src || !dst || !pairs) return set_error(PC_ERR_INVALID, "pc_swap_blocks: null pointer");
-  // one cudaMemcpyAsync per pair, like csrc/cache_kernels.cu:24-66 (direction inferred by UVA)
-  for (int i = 0; i < num_pairs; ++i) {
+  // one cudaMemcpyAsync per RUN of pairs whose source and destination blocks are both consecutive
+  // (csrc/cache_kernels.cu:24-66 issues one per pair: a 32 KiB block costs ~4 us per call = 8 GB/s;
+  // swap-in / swap-out lists of a sequence are mostly runs).  Direction inferred by UVA.
+  for (int i = 0; i < num_pairs;) {
+    int n = 1;
+    while (i + n < num_pairs && pairs[2 * (i + n)] == pairs[2 * i] + n && pairs[2 * (i + n) + 1] == pairs[2 * i + 1] + n) ++n;
     const char* s = static_cast<const char*>(src) + pairs[2 * i] * block_bytes;
     char* d = static_cast<char*>(dst) + pairs[2 * i + 1] * block_bytes;
-    const cudaError_t e = cudaMemcpyAsync(d, s, (size_t)block_bytes, cudaMemcpyDefault,
+    const cudaError_t e = cudaMemcpyAsync(d, s, (size_t)block_bytes * n, cudaMemcpyDefault,
                                           static_cast<cudaStream_t>(stream));
     if (e != cudaSuccess) return set_cuda_error("pc_swap_blocks cudaMemcpyAsync", e);
+    i += n;
   }
   return PC_OK;
 }
