@@ -23,6 +23,7 @@ kernels, same layer-0 feedback; tests/test_gpu_layer.py checks both paths bit fo
 """
 from __future__ import annotations
 
+import time
 from typing import Dict, List, Optional, Sequence, Tuple
 
 import numpy as np
@@ -30,6 +31,9 @@ import torch
 
 from . import ops
 from .policy import cdiv, random_victim, zero_slot
+
+
+_VICT_PENDING = -2      # sentinel in the pinned victims buffer (real entries are -1 or >= 1)
 
 
 class DecodeGraphRunner:
@@ -137,6 +141,8 @@ class DecodeGraphRunner:
             self.d_victims = torch.full((self.Lsel, B), -1, dtype=torch.int32, device=self.device)
         self.d_zero = m[o_zero:o_zero + 2 * L * B].view(torch.int64).view(L, B) if self.zeroing else None
         self._vict_host = torch.empty(B, dtype=torch.int32).pin_memory()
+        if not hasattr(self, "_vict_stream"):
+            self._vict_stream = torch.cuda.Stream(self.device)
 
         # ---- host mirror
         self.tab = np.zeros((B, M), dtype=np.int32)
@@ -224,10 +230,20 @@ class DecodeGraphRunner:
         if self.zeroing:     # W2: every layer's zeroed slots in one launch, ahead of the first attention
             ops.zero_cache_slots_layers(self.d_kptrs, self.d_vptrs, self.d_zero, eng.num_kv_heads,
                                         eng.head_size, self.bs, self.blk_stride)
+        early_victims = trig and self.value_l2
         if trig:
             ops.evict_select_compact_layers(self.d_tab, self.d_nblk, self.d_seq, ds.policy, self.d_pool_ptrs,
                                             self.heads_total if self.value_l2 else 0, self.d_compact,
                                             self.d_victims)
+        if early_victims:
+            # layer 0's victims leave for the host NOW, on a side stream, while the attention kernels of
+            # the step run: the host frees the blocks and prepares the next step during the step instead
+            # of after it (step() polls the pinned buffer for the copy; no device synchronisation)
+            ev = torch.cuda.Event()
+            ev.record(cur)
+            self._vict_stream.wait_event(ev)
+            with torch.cuda.stream(self._vict_stream):
+                self._vict_host.copy_(self.d_victims[0], non_blocking=True)
         for l in range(self.L):
             if io is not None and io.is_first[l]:
                 cur.wait_event(io.h2d_done[io.gidx[l]])
@@ -240,6 +256,8 @@ class DecodeGraphRunner:
             ops.decode_layer(ds_pdl if chained else ds, self.outs[l], q, k, v, kptr, vptr, score, None, tables)
             if io is not None:
                 io.put_out(l, self.out_flat[l])
+        if early_victims:
+            cur.wait_stream(self._vict_stream)
         if io is not None:
             cur.wait_stream(io.d2h_stream)
             cur.wait_stream(io.h2d_stream)
@@ -402,6 +420,8 @@ class DecodeGraphRunner:
         if self.io is not None and self.io.prefetch:
             par = self._io_par                           # landing buffer the previous step filled
             self._io_par = 1 - par
+        if any_trig and self.value_l2:
+            self._vict_host.fill_(_VICT_PENDING)             # host write; the step's copy overwrites it
         if self.use_graph:
             self._graph(any_trig, par).replay()
             ops._launched(self._launches[any_trig])      # kernel nodes of the replayed graph
@@ -427,9 +447,11 @@ class DecodeGraphRunner:
             if self.host_victims:                  # the host chose them: nothing to read back
                 idx = host_vict[0][rows].astype(np.int64)
             elif self.value_l2:
-                self._vict_host.copy_(self.d_victims[0], non_blocking=True)
-                torch.cuda.current_stream(self.device).synchronize()
-                vict = self._vict_host.numpy()
+                vict = self._vict_host.numpy()       # filled by the step's side-stream copy (_launch_layers)
+                t0 = time.perf_counter()
+                while (vict == _VICT_PENDING).any():
+                    if time.perf_counter() - t0 > 30.0:
+                        raise RuntimeError("victims of the trigger step did not arrive within 30 s")
                 rows = rows[vict[rows] >= 0]
                 idx = vict[rows].astype(np.int64)
             else:
