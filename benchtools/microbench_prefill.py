@@ -101,7 +101,14 @@ def main():
     ap.add_argument("--reps", type=int, default=20)
     ap.add_argument("--pp", type=int, default=-1, help="PC_DEBUG library: 1 = ping-pong kernel, 0 = off, -1 = rule")
     ap.add_argument("--modes", action="store_true", help="PC_DEBUG library: one-shot / persistent side by side")
+    ap.add_argument("--xitem", type=int, default=-1, help="PC_DEBUG library: 0 = no S MMA issue across item boundaries")
     a = ap.parse_args()
+    if a.xitem >= 0:
+        import ctypes
+        fn = _lib.load().pc_debug_set_prefill_tc_xitem
+        fn.argtypes = [ctypes.c_int32]
+        fn.restype = None
+        fn(a.xitem)
     if a.pp >= 0:
         import ctypes
         fn = _lib.load().pc_debug_set_prefill_pp

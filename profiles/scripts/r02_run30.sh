@@ -1,10 +1,15 @@
 set -x
 cd $GRAFT_REPO_ROOT; mkdir -p gpurun_out
 O=gpurun_out
-(time timeout 900 python -m pytest tests/test_gpu_kernels.py -m gpu -x -q -k "decode or fused") > $O/r02_pytest30.log 2>&1
-tail -4 $O/r02_pytest30.log
-B="--steps 64 --warmup 8 --no-legs --no-cpu-baseline --no-prefill --no-e2e"
-python bench.py $B > $O/r02_b30_a.json 2>> $O/r02_b30.err
-python bench.py $B > $O/r02_b30_b.json 2>> $O/r02_b30.err
-python bench.py $B --tp-emulate 8 > $O/r02_b30_tp8.json 2>> $O/r02_b30.err
-tail -3 $O/r02_b30.err
+(time timeout 200 python -m pytest tests/test_gpu_kernels.py -m gpu -x -q -k "prefill") > $O/r02_pytest30.log 2>&1
+tail -5 $O/r02_pytest30.log
+export PC_LIB_PATH=$GRAFT_REPO_ROOT/vllm_paged_compression_b200/libpagedevict_b200_debug.so
+PF="timeout 40 python -m benchtools.microbench_prefill"
+: > $O/r02_pf30.jsonl
+for pass in 1 2; do
+for args in "--reqs 16" "--reqs 64" "--reqs 16 --len 2048" "--reqs 64 --len 2048" "--reqs 4 --len 8192 --evict-freq 0"; do
+  echo "X0 $args" >> $O/r02_pf30.jsonl; $PF $args --xitem 0 >> $O/r02_pf30.jsonl 2>&1
+  echo "X1 $args" >> $O/r02_pf30.jsonl; $PF $args --xitem 1 >> $O/r02_pf30.jsonl 2>&1
+done
+done
+cat $O/r02_pf30.jsonl | cut -c1-60,100-230

@@ -135,6 +135,7 @@ int prefill_attn_pp(const PrefillArgs& a, cudaStream_t stream);  // measured, no
 void set_prefill_tc_persistent(int v);  // 1 = persistent CTAs, 0 = one CTA per query tile, -1 = rule
 void set_prefill_tc_tile(int tn);       // kv tile width of the tcgen05 kernel (64 | 128)
 void set_prefill_pp(int v);             // ping-pong kernel: 1 = always (when supported), 0 = never, -1 = rule
+void set_prefill_tc_xitem(int v);       // 1 = the next item's first S MMA is issued before the current item's last P.V (product), 0 = after
 void set_cache_write_block_heads(int hc);  // heads per CTA of cache_write_block_kernel, 0 = rule
 #endif
 

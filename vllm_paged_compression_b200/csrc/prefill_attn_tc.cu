@@ -36,7 +36,7 @@ namespace {
 
 constexpr int kTM = 128;       // query rows per CTA (UMMA M)
 constexpr int kTcThreads = 384;   // warpgroup 0 softmax, 1 = K / V producers + MMA issuer (+ 1 idle warp), 2 = epilogue
-// register budgets per thread after setmaxnreg (two CTAs per SM: 2 x 128 x (128 + 40 + 72) = 60 K of 64 K)
+// register budgets per thread after setmaxnreg (two CTAs per SM: 2 x 128 x (128 + 40 + 72) = 60 K of 64 K; the budgets of a CTA must add up to its launch allocation, 384 x 80: setmaxnreg.inc takes from the CTA's own pool and blocks forever otherwise)
 constexpr int kRegsSoftmax = 128, kRegsRoles = 40, kRegsEpilogue = 72;
 constexpr float kRescaleThreshold = 8.f;  // log2 domain
 
@@ -100,7 +100,8 @@ __global__ void __launch_bounds__(kTcThreads, (TN == 64 ? 2 : 1))
 prefill_attn_tc_kernel(const PrefillTcParams p, const __grid_constant__ CUtensorMap tm_q,
                                const __grid_constant__ CUtensorMap tm_k,
                                const __grid_constant__ CUtensorMap tm_v, const int q_tiles,
-                               const int num_reqs, const int heavy_major, const int chunk_reqs) {
+                               const int num_reqs, const int heavy_major, const int chunk_reqs,
+                               const int xitem) {
   using L = TcSmem<D, TN>;
   constexpr int kTN = TN;
   constexpr int kTmemCols = L::kTmemCols;
@@ -194,7 +195,10 @@ prefill_attn_tc_kernel(const PrefillTcParams p, const __grid_constant__ CUtensor
         const TcItem it = get_item(k);
         if (it.ntiles == 0) continue;
         if (it.pruned != 0 && (((it.first | it.pruned) & (BOX - 1)) != 0)) __trap();
-        // Q buffer is free once the previous item's last S MMA (tile g - 1) has completed
+        // K of the item's first tile goes out first (its stage only needs S_{g-2}); the Q buffer is free once
+        // the previous item's last S MMA (tile g - 1) has completed
+        if (g >= 2) t5::mbar_wait_relaxed(&bar[B_SFULL + (g & 1)], ((g - 2) >> 1) & 1);
+        issue_kv(&tm_k, smem + L::oK + (g & 1) * L::kKV, &bar[B_KFULL + (g & 1)], it, 0);
         if (g > 0) t5::mbar_wait_relaxed(&bar[B_SFULL + ((g - 1) & 1)], ((g - 1) >> 1) & 1);
         mbar_expect_tx(&bar[B_QFULL], L::kQ);
 #pragma unroll
@@ -220,7 +224,8 @@ prefill_attn_tc_kernel(const PrefillTcParams p, const __grid_constant__ CUtensor
           }
           break;
         }
-        for (int t = 0; t < it.ntiles; ++t, ++g) {
+        ++g;
+        for (int t = 1; t < it.ntiles; ++t, ++g) {
           const int st = g & 1;
           if (g >= 2) t5::mbar_wait_relaxed(&bar[B_SFULL + st], ((g - 2) >> 1) & 1);   // S_{g-2} done
           issue_kv(&tm_k, smem + L::oK + st * L::kKV, &bar[B_KFULL + st], it, t);
@@ -259,20 +264,45 @@ prefill_attn_tc_kernel(const PrefillTcParams p, const __grid_constant__ CUtensor
         }
         t5::commit(&bar[B_SFULL + st]);
       };
-      int g = 0, n_item = 0;
-      for (int k = blockIdx.x; k < total; k += gridDim.x) {
-        const TcItem it = get_item(k);
-        if (it.ntiles == 0) continue;
-        mbar_wait(&bar[B_QFULL], n_item & 1);
-        ++n_item;
-        issue_s(g);
-        for (int j = 0; j < it.ntiles; ++j, ++g) {
+      // The tile stream runs ACROSS items: the first S MMA of the next item (new Q, its K tile 0) is issued
+      // before the last P.V of the current one, exactly like S_{j+1} inside an item, so the softmax warps
+      // find the next item's scores ready when they hand over the last P (the item boundary used to cost
+      // them one S MMA + commit latency: the MMA thread waited for the last P before it looked at Q).
+      auto next_item = [&](int& kk) {     // tiles of the next non-empty item at or after kk (0: none left)
+        for (; kk < total; kk += gridDim.x) {
+          const int nt = get_item(kk).ntiles;
+          if (nt != 0) return nt;
+        }
+        return 0;
+      };
+      int g = 0, n_item = 0, n_q = 0, k = blockIdx.x;
+      int ntiles = next_item(k);
+      bool have = ntiles != 0;
+      if (have) {
+        mbar_wait(&bar[B_QFULL], 0);
+        n_q = 1;
+        issue_s(0);
+      }
+      while (have) {
+        int kn = k + gridDim.x, nt_nx = 0;
+        bool have_nx = false;
+        for (int j = 0; j < ntiles; ++j, ++g) {
           const int st = g & 1;
-          if (j + 1 < it.ntiles) issue_s(g + 1);
+          if (j + 1 < ntiles) {
+            issue_s(g + 1);
+          } else {
+            nt_nx = next_item(kn);
+            have_nx = nt_nx != 0;
+            if (have_nx && xitem) {
+              mbar_wait(&bar[B_QFULL], n_q & 1);
+              ++n_q;
+              issue_s(g + 1);
+            }
+          }
           mbar_wait(&bar[B_VFULL + st], (g >> 1) & 1);
           mbar_wait(&bar[B_PFULL + st], (g >> 1) & 1);
           // the first P.V of an item overwrites O: the epilogue warps must have read the previous item's
-          if (j == 0 && n_item > 1) mbar_wait(&bar[B_OFREE], (n_item - 2) & 1);
+          if (j == 0 && n_item > 0) mbar_wait(&bar[B_OFREE], (n_item - 1) & 1);
           fence_proxy_async();
           t5::fence_after_sync();
 #pragma unroll
@@ -288,6 +318,13 @@ prefill_attn_tc_kernel(const PrefillTcParams p, const __grid_constant__ CUtensor
           }
           t5::commit(&bar[B_PVDONE + st]);
         }
+        ++n_item;
+        if (have_nx && !xitem) {
+          mbar_wait(&bar[B_QFULL], n_q & 1);
+          ++n_q;
+          issue_s(g);
+        }
+        ntiles = nt_nx; k = kn; have = have_nx;
       }
     }
     __syncwarp();
@@ -484,7 +521,10 @@ void set_prefill_tc_tile(int tn) {   // debug knob reused: values other than 64 
 }
 static int g_prefill_pp = -1;
 void set_prefill_pp(int v) { g_prefill_pp = v; }
+static int g_tc_xitem = 1;
+void set_prefill_tc_xitem(int v) { g_tc_xitem = v; }
 #else
+constexpr int g_tc_xitem = 1;
 constexpr int g_tc_persistent = -1;
 constexpr int g_tc_tile_n = 64;
 #endif
@@ -551,7 +591,7 @@ static int launch_prefill_tc(const PrefillTcParams& p, const PrefillArgs& a, cud
 #endif
   kern<<<ctas, kTcThreads, smem, stream>>>(p, tq, tk, tv, q_tiles, a.num_reqs,
                                             (persist && g_tc_persistent != 2) ? 1 : 0,   // 2: debug, persistent + local order
-                                            (int)chunk);
+                                            (int)chunk, g_tc_xitem);
   return check_launch("prefill_attn_tc_kernel");
 }
 
