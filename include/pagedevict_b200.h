@@ -170,6 +170,30 @@ int pc_paged_decode_attn_score(void* out, const void* query, const void* key_cac
                                void* workspace, size_t workspace_bytes, int32_t dtype,
                                void* stream);
 
+/* ---- pc_paged_decode_attn_score without a caller workspace ------------------------------
+ * No counterpart in the reference: added for callers that
+ * cannot allocate device memory (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc).  Same arguments, semantics and results as pc_paged_decode_attn_score;
+ * the split-KV workspace is a file-scope device array inside the library of
+ * PC_DECODE_STATIC_SCRATCH_BYTES (16 MiB) that every GPU which loads the library holds until
+ * exit.  The call allocates nothing (no cudaMalloc / cudaFree, no allocating library routine):
+ * one cudaMemsetAsync of the counters + this launch's arrival tickets and one kernel launch on
+ * `stream`.  A launch whose plan needs more scratch than the array holds (very large batch x
+ * context products: > ~3000 split chunks at head size 128) is rejected with PC_ERR_INVALID and a
+ * message naming both sizes -- use pc_paged_decode_attn_score with a caller workspace then.
+ * EVERY call on a device shares the one array: calls that can overlap on the GPU (different
+ * streams, or graph branches without a dependency) race on it and must be serialised by the
+ * caller; calls on one stream are safe. */
+#define PC_DECODE_STATIC_SCRATCH_BYTES (16u << 20)
+int pc_paged_decode_attn_score_static(void* out, const void* query, const void* key_cache,
+                                      const void* value_cache, const int32_t* block_tables,
+                                      int64_t table_stride, const int32_t* kv_lens, int32_t batch,
+                                      int32_t num_heads, int32_t num_kv_heads, int32_t head_size,
+                                      int32_t block_size, int32_t max_kv_len, float scale,
+                                      int64_t q_stride, int64_t out_stride, int64_t kv_block_stride,
+                                      const int32_t* seq_lens, const pc_score_pool* score /* HOST */,
+                                      int32_t dtype, void* stream);
+
 /* ---- one decode step of one layer in ONE call --------------------------------------
  * The decode branch of TorchCUDASDPABackendImpl.forward (torch_cuda_sdpa.py:896-1062):
  * reshape_and_cache of the step's K/V -> [on steps where a row triggers: victim

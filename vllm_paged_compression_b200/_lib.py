@@ -64,6 +64,9 @@ PROTOTYPES = {
     "pc_paged_decode_attn_score": (C.c_int, [_P, _P, _P, _P, _P, _I64, _P, _I32, _I32, _I32, _I32, _I32,
                                              _I32, _F, _I64, _I64, _I64, _P, _SP, _P, _SZ,
                                              _I32, _P]),
+    # no caller workspace: the library's file-scope device scratch (PC_DECODE_STATIC_SCRATCH_BYTES)
+    "pc_paged_decode_attn_score_static": (C.c_int, [_P, _P, _P, _P, _P, _I64, _P, _I32, _I32, _I32, _I32, _I32,
+                                                    _I32, _F, _I64, _I64, _I64, _P, _SP, _I32, _P]),
     "pc_decode_layer": (C.c_int, [C.POINTER(PcDecodeStep), _P, _P, _P, _P, _P, _P, _SP, _P, _P, _I64]),
     "pc_evict_select_compact_layers": (C.c_int, [_P, _I64, _P, _P, _I32, _I32, C.POINTER(PcEvictPolicy), _P, _I32,
                                                  _P, _I64, _I64, _P, _P]),

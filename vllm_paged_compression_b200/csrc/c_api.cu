@@ -198,6 +198,28 @@ int pc_paged_decode_attn_score(void* out, const void* query, const void* key_cac
                           out_stride, kv_block_stride, seq_lens, score, workspace, workspace_bytes, dtype,
                           stream, none);
 }
+
+int pc_paged_decode_attn_score_static(void* out, const void* query, const void* key_cache,
+                                      const void* value_cache, const int32_t* block_tables,
+                                      int64_t table_stride, const int32_t* kv_lens, int32_t batch,
+                                      int32_t num_heads, int32_t num_kv_heads, int32_t head_size,
+                                      int32_t block_size, int32_t max_kv_len, float scale,
+                                      int64_t q_stride, int64_t out_stride, int64_t kv_block_stride,
+                                      const int32_t* seq_lens, const pc_score_pool* score,
+                                      int32_t dtype, void* stream) {
+  if (int rc = check_dtype(dtype)) return rc;
+  if (batch == 0) return PC_OK;
+  void* scratch = nullptr;
+  size_t scratch_bytes = 0;
+  if (int rc = decode_static_scratch(batch, num_heads, num_kv_heads, head_size, block_size, max_kv_len,
+                                     static_cast<cudaStream_t>(stream), &scratch, &scratch_bytes))
+    return rc;
+  const FuseExtras none = {nullptr, nullptr, nullptr, 0, 0, nullptr, 0};
+  return decode_attn_impl(out, query, key_cache, value_cache, block_tables, table_stride, kv_lens, batch,
+                          num_heads, num_kv_heads, head_size, block_size, max_kv_len, scale, q_stride,
+                          out_stride, kv_block_stride, seq_lens, score, scratch, scratch_bytes, dtype,
+                          stream, none);
+}
 }  // extern "C"
 #pragma GCC visibility pop
 

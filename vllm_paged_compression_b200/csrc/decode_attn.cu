@@ -50,6 +50,7 @@
 #include "pc_common.cuh"
 #include "score_common.cuh"
 #include <math.h>
+#include <stdio.h>
 #include <stdlib.h>
 #include <atomic>
 #include <type_traits>
@@ -1140,6 +1141,57 @@ int paged_decode_attn_score(const DecodeArgs& a, cudaStream_t stream) {
   if (a.D == 128 && a.BS == 8) return launch_decode<128, 8, 8, 6>(p, num_sms, grid_teams, stream);
   if (a.D == 64 && a.BS == 8) return launch_decode<64, 8, 8, 6>(p, num_sms, grid_teams, stream);
   return launch_decode<64, 32, 8, 3>(p, num_sms, grid_teams, stream);
+}
+
+// ---------------------------------------------------------------------------------------
+// Scratch for pc_paged_decode_attn_score_static: the split-KV workspace of the kernel above
+// (counters, tickets, partials) as a file-scope device array, for callers that cannot allocate.
+// PC_DECODE_STATIC_SCRATCH_BYTES (include/pagedevict_b200.h) per GPU that loads the library,
+// held until exit.  Every call on a device shares it.
+static __device__ __align__(256) unsigned char g_decode_static_scratch[PC_DECODE_STATIC_SCRATCH_BYTES];
+
+// Device address of the array for the CURRENT device (in host code the symbol's name is a
+// host-side stand-in, never a device pointer): looked up once per device with that device
+// current, kept afterwards.  Checks that this launch fits and clears what the kernel needs at
+// zero (chunk counter + the arrival tickets of this launch's groups) on `stream`.  Shapes the
+// kernel does not support are left to paged_decode_attn_score's own argument checks.
+int decode_static_scratch(int B, int Hq, int Hkv, int D, int BS, int max_kv_len, cudaStream_t stream,
+                          void** out_ptr, size_t* out_bytes) {
+  static std::atomic<void*> addr[64];
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return set_cuda_error("cudaGetDevice", e);
+  if (dev < 0 || dev >= 64) return set_error(PC_ERR_INVALID, "pc_paged_decode_attn_score_static: device ordinal above 63");
+  void* ptr = addr[dev].load(std::memory_order_acquire);
+  if (ptr == nullptr) {
+    e = cudaGetSymbolAddress(&ptr, g_decode_static_scratch);
+    if (e != cudaSuccess) return set_cuda_error("cudaGetSymbolAddress(decode static scratch)", e);
+    if (ptr == nullptr || (reinterpret_cast<uintptr_t>(ptr) & 255) != 0)
+      return set_error(PC_ERR_CUDA, "pc_paged_decode_attn_score_static: static scratch has no usable device address");
+    addr[dev].store(ptr, std::memory_order_release);   // (a racing thread stores the same address)
+  }
+  *out_ptr = ptr;
+  *out_bytes = (size_t)PC_DECODE_STATIC_SCRATCH_BYTES;
+  const bool shape_ok = B > 0 && Hkv > 0 && Hq % Hkv == 0 && (D == 64 || D == 128) && (BS == 8 || BS == 16 || BS == 32);
+  if (!shape_ok) return 0;
+  const int num_sms = device_sm_count();
+  if (num_sms <= 0) return PC_ERR_CUDA;
+  const DecodePlan pl = plan_decode(B, Hq, Hkv, D, BS, max_kv_len, num_sms, decode_team_cap(D, BS, B));
+  const size_t need = kOffPartials + (size_t)pl.max_chunks * slot_bytes(D);
+  if (need > (size_t)PC_DECODE_STATIC_SCRATCH_BYTES) {
+    char msg[224];
+    snprintf(msg, sizeof(msg),
+             "pc_paged_decode_attn_score_static: this launch needs %zu bytes of scratch, the static array holds %zu "
+             "(PC_DECODE_STATIC_SCRATCH_BYTES); use pc_paged_decode_attn_score with a caller workspace",
+             need, (size_t)PC_DECODE_STATIC_SCRATCH_BYTES);
+    return set_error(PC_ERR_INVALID, msg);
+  }
+  const int G = Hq / Hkv;
+  long long groups = (long long)B * Hkv * ((G + 7) / 8);
+  if (groups > kMaxGroups) groups = kMaxGroups;      // (rejected by paged_decode_attn_score)
+  e = cudaMemsetAsync(ptr, 0, kOffTickets + (size_t)groups * sizeof(int), stream);
+  if (e != cudaSuccess) return set_cuda_error("cudaMemsetAsync(decode static scratch)", e);
+  return 0;
 }
 
 }  // namespace pc

@@ -61,6 +61,10 @@ struct DecodeArgs {
 size_t decode_workspace_bytes(int B, int Hq, int Hkv, int D, int BS, int max_kv_len, int num_sms);
 void decode_plan(int B, int Hq, int Hkv, int D, int BS, int max_kv_len, int num_sms, int* out2);  // {chunk_pages, team}
 int paged_decode_attn_score(const DecodeArgs& a, cudaStream_t stream);
+// static-scratch variant (pc_paged_decode_attn_score_static): device address + size of the file-scope
+// workspace of the current device, size check for this launch, counters / tickets cleared on `stream`
+int decode_static_scratch(int B, int Hq, int Hkv, int D, int BS, int max_kv_len, cudaStream_t stream,
+                          void** out_ptr, size_t* out_bytes);
 #ifdef PC_DEBUG
 void set_decode_trace(void* buf);  // per-warp globaltimer stamps, nullptr = off
 void set_decode_plan_override(int chunk_pages, int team);  // 0 = planner's choice
