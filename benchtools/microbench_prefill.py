@@ -102,6 +102,7 @@ def main():
     ap.add_argument("--pp", type=int, default=-1, help="PC_DEBUG library: 1 = ping-pong kernel, 0 = off, -1 = rule")
     ap.add_argument("--modes", action="store_true", help="PC_DEBUG library: one-shot / persistent side by side")
     ap.add_argument("--xitem", type=int, default=-1, help="PC_DEBUG library: 0 = no S MMA issue across item boundaries")
+    ap.add_argument("--dq", type=int, default=-1, help="PC_DEBUG library: 1 = the dual-query-tile kernel")
     a = ap.parse_args()
     if a.xitem >= 0:
         import ctypes
@@ -109,6 +110,12 @@ def main():
         fn.argtypes = [ctypes.c_int32]
         fn.restype = None
         fn(a.xitem)
+    if a.dq >= 0:
+        import ctypes
+        fn = _lib.load().pc_debug_set_prefill_dq
+        fn.argtypes = [ctypes.c_int32]
+        fn.restype = None
+        fn(a.dq)
     if a.pp >= 0:
         import ctypes
         fn = _lib.load().pc_debug_set_prefill_pp

@@ -39,4 +39,13 @@ def _debug_library_knobs():
         fn.argtypes = [ctypes.c_int32]
         fn.restype = None
         fn(int(os.environ["PC_TEST_PREFILL_PP"]))
+    if os.environ.get("PC_TEST_PREFILL_DQ") in ("0", "1"):
+        import ctypes
+        from vllm_paged_compression_b200 import _lib
+        fn = getattr(_lib.load(), "pc_debug_set_prefill_dq", None)
+        if fn is None:
+            raise RuntimeError("PC_TEST_PREFILL_DQ needs the PC_DEBUG library (PC_LIB_PATH=...libpagedevict_b200_debug.so)")
+        fn.argtypes = [ctypes.c_int32]
+        fn.restype = None
+        fn(int(os.environ["PC_TEST_PREFILL_DQ"]))
     yield

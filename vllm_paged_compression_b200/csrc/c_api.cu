@@ -445,6 +445,7 @@ void pc_debug_set_prefill_tc_tile(int32_t tn) { pc::set_prefill_tc_tile(tn); }
 void pc_debug_set_prefill_tc_persistent(int32_t v) { pc::set_prefill_tc_persistent(v); }
 void pc_debug_set_cache_write_block_heads(int32_t hc) { pc::set_cache_write_block_heads(hc); }
 void pc_debug_set_prefill_pp(int32_t v) { pc::set_prefill_pp(v); }
+void pc_debug_set_prefill_dq(int32_t v) { pc::set_prefill_dq(v); }
 void pc_debug_set_prefill_tc_xitem(int32_t v) { pc::set_prefill_tc_xitem(v); }
 void pc_debug_set_decode_two_cta(int32_t v) { pc::set_decode_two_cta(v); }
 #endif

@@ -521,6 +521,8 @@ void set_prefill_tc_tile(int tn) {   // debug knob reused: values other than 64 
 }
 static int g_prefill_pp = -1;
 void set_prefill_pp(int v) { g_prefill_pp = v; }
+static int g_prefill_dq = 0;
+void set_prefill_dq(int v) { g_prefill_dq = v; }
 static int g_tc_xitem = 1;
 void set_prefill_tc_xitem(int v) { g_tc_xitem = v; }
 #else
@@ -548,8 +550,8 @@ static EncodeTiledFn encode_tiled_fn() {
 }
 // [rows, heads*D] bf16 matrix with row stride `stride` elements; box = 64 columns x box_rows,
 // SWIZZLE_128B (the UMMA SW128 canonical layouts), out-of-range rows read as zero.
-static int make_rows_map(CUtensorMap* m, const void* base, long long rows, int inner, long long stride,
-                         int box_rows) {
+int prefill_make_rows_map(CUtensorMap* m, const void* base, long long rows, int inner, long long stride,
+                          int box_rows) {
   EncodeTiledFn enc = encode_tiled_fn();
   if (enc == nullptr) return set_error(PC_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
   const cuuint64_t gdim[2] = {(cuuint64_t)inner, (cuuint64_t)rows};
@@ -566,9 +568,9 @@ static int make_rows_map(CUtensorMap* m, const void* base, long long rows, int i
 template <int D, int TN, int BOX>
 static int launch_prefill_tc(const PrefillTcParams& p, const PrefillArgs& a, cudaStream_t stream) {
   CUtensorMap tq, tk, tv;
-  if (int rc = make_rows_map(&tq, a.q, a.num_tokens, a.Hq * D, a.q_stride, kTM)) return rc;
-  if (int rc = make_rows_map(&tk, a.k, a.num_tokens, a.Hkv * D, a.key_stride, BOX)) return rc;
-  if (int rc = make_rows_map(&tv, a.v, a.num_tokens, a.Hkv * D, a.value_stride, BOX)) return rc;
+  if (int rc = prefill_make_rows_map(&tq, a.q, a.num_tokens, a.Hq * D, a.q_stride, kTM)) return rc;
+  if (int rc = prefill_make_rows_map(&tk, a.k, a.num_tokens, a.Hkv * D, a.key_stride, BOX)) return rc;
+  if (int rc = prefill_make_rows_map(&tv, a.v, a.num_tokens, a.Hkv * D, a.value_stride, BOX)) return rc;
   const int smem = TcSmem<D, TN>::kBytes;
   auto kern = prefill_attn_tc_kernel<D, TN, BOX>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
@@ -623,6 +625,8 @@ int prefill_attn(const PrefillArgs& a, cudaStream_t stream) {
     }
   }
 #ifdef PC_DEBUG
+  // A/B runs: two q heads of a kv head per CTA over one shared K/V ring (prefill_attn_dq.cu)
+  if (g_prefill_dq > 0 && prefill_attn_dq_supported(a)) return prefill_attn_dq(a, box8, stream);
   // A/B runs: the ping-pong kernel (two q heads of a kv head per CTA, 128-wide kv tiles; prefill_attn_pp.cu).
   // Measured 1-8 % slower than this kernel at every shape (profiles/r02_prefill_experiments.txt), so it is
   // built into the PC_DEBUG library only.
