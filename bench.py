@@ -798,7 +798,7 @@ def main():
                                         spec.evict_freq, 20)
         tpeak = float(peaks.get("bf16_tflops", 2250.0))
         line["prefill_roofline"] = {
-            "bound": "tensor", "kernel": "prefill_attn_tc_kernel (tcgen05.mma, TMEM accumulators, TMA loads)",
+            "bound": "tensor", "kernel": row["kernel"] + " (tcgen05.mma, TMEM accumulators, TMA loads)",
             "achieved": row["tflops"], "peak": tpeak, "unit": "TFLOP/s", "frac": row["tflops"] / tpeak,
             "peak_source": "measured burst (MEASURED_PEAKS.json bf16_tflops)" if peaks else "nominal dense bf16",
             "us_per_launch": row["us"], "launch": f"{pre_reqs} prompts x {spec.prompt_len} q, {row['kv_kept']} kept kv, "

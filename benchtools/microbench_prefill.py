@@ -50,7 +50,7 @@ def _debug_knobs(lib, tile, persistent):
         fn(v)
 
 
-def run(device, reqs, L, Hq, Hkv, D, evict_freq, reps, variant=0, check=None, tile=64, persistent=-1):
+def run(device, reqs, L, Hq, Hkv, D, evict_freq, reps, variant=0, check=None, tile=64, persistent=-1, dq=-1):
     g = torch.Generator(device=device)
     g.manual_seed(0)
     T = reqs * L
@@ -81,7 +81,11 @@ def run(device, reqs, L, Hq, Hkv, D, evict_freq, reps, variant=0, check=None, ti
     vis = sum(min(i + 1, kept) for i in range(L))
     flops = 4.0 * D * Hq * reqs * vis
     mode = {-1: "auto_", 0: "oneshot_", 1: "persist_", 2: "persist_localorder_"}[persistent]
-    row = {"kernel": f"prefill_attn_tc_{mode}kernel<TN={tile}>",
+    # the library's own rule (prefill_attn_tc.cu: prefill_attn): dual-query-tile kernel for head size 128, an even
+    # number of q heads per kv head and prompts <= 2048 tokens; PC_DEBUG knobs (--dq, tile) override it
+    rule_dq = D == 128 and (Hq // Hkv) % 2 == 0 and L <= 2048 and tile == 64 and persistent == -1
+    use_dq = rule_dq if dq < 0 else (dq == 1 and (Hq // Hkv) % 2 == 0)
+    row = {"kernel": "prefill_attn_dq_kernel" if use_dq else f"prefill_attn_tc_{mode}kernel<TN={tile}>",
            "reqs": reqs, "q_len": L, "kv_kept": kept, "Hq": Hq, "Hkv": Hkv, "D": D,
            "us": sec * 1e6, "tflops": flops / sec / 1e12,
            "frac_of_measured_bf16_peak": flops / sec / 1e12 / _peak_tflops()}
@@ -102,7 +106,7 @@ def main():
     ap.add_argument("--pp", type=int, default=-1, help="PC_DEBUG library: 1 = ping-pong kernel, 0 = off, -1 = rule")
     ap.add_argument("--modes", action="store_true", help="PC_DEBUG library: one-shot / persistent side by side")
     ap.add_argument("--xitem", type=int, default=-1, help="PC_DEBUG library: 0 = no S MMA issue across item boundaries")
-    ap.add_argument("--dq", type=int, default=-1, help="PC_DEBUG library: 1 = the dual-query-tile kernel")
+    ap.add_argument("--dq", type=int, default=-1, help="PC_DEBUG library: 1 = the dual-query-tile kernel always, 0 = never, -1 = rule")
     a = ap.parse_args()
     if a.xitem >= 0:
         import ctypes
@@ -123,7 +127,7 @@ def main():
         fn.restype = None
         fn(a.pp)
     dev = torch.device("cuda", 0)
-    row, ref = run(dev, a.reqs, a.len, a.Hq, a.Hkv, a.D, a.evict_freq, a.reps)
+    row, ref = run(dev, a.reqs, a.len, a.Hq, a.Hkv, a.D, a.evict_freq, a.reps, dq=a.dq)
     print(json.dumps(row), flush=True)
     if a.modes:
         for tile, pers in ((64, 0), (64, 1), (64, 2)):

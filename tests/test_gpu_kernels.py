@@ -490,6 +490,14 @@ def test_prefill_attention_topleft_causal(Hq, Hkv, D, mode):
     (4, 1, 128, 32, "budget", 256, [96, 640, 1111]),
     (8, 8, 64, 16, "budget", 128, [513, 64, 390]),
     (16, 2, 128, 16, "none", 0, [300, 1, 900]),
+    # kernel dispatch of the product library (prefill_attn_tc.cu: prefill_attn): head size 128 with an even
+    # number of q heads per kv head and prompts <= 2048 tokens runs the dual-query-tile kernel
+    # (prefill_attn_dq.cu, the cases above); these two reach the one-tile kernel at head size 128 --
+    # a prompt beyond 2048 tokens (one CTA per query tile) and three q heads per kv head (persistent CTAs)
+    (8, 2, 128, 16, "percentage", 2, [2304, 129, 1]),
+    (6, 2, 128, 16, "percentage", 2, [127, 640, 129, 1100]),
+    # and the dual-query-tile kernel at its longest prompt, ragged next to a one-token prompt
+    (8, 4, 128, 16, "percentage", 4, [2048, 1, 1999]),
 ])
 def test_prefill_attention_tile_edges_and_strided_rows(case):
     """q/k/v are column slices of one fused [T, (Hq + 2 Hkv) * D] buffer (row stride != H * D),
@@ -528,12 +536,13 @@ def test_prefill_attention_tile_edges_and_strided_rows(case):
 
 
 @pytest.mark.timeout(120)
-def test_prefill_attention_many_short_items_persistent_walk():
+@pytest.mark.parametrize("Hq,Hkv", [(16, 4), (12, 4)])    # dual-query-tile kernel / one-tile kernel (odd group)
+def test_prefill_attention_many_short_items_persistent_walk(Hq, Hkv):
     """More (tile, head, request) items than resident CTAs (2 x 148), so every CTA of the
     persistent launch walks several items back to back: phases of all mbarriers keep counting
     across items, Q is re-loaded behind the previous item's last S MMA, O / P buffers are reused."""
     ops = _ops()
-    Hq, Hkv, D, bs = 16, 4, 128, 16
+    D, bs = 128, 16
     pol = Policy(block_size=bs, cache_prune_type="percentage", cache_budget=128, evict_freq=2)
     g = torch.Generator().manual_seed(77)
     prompt_lens = [int(x) for x in torch.randint(1, 420, (40,), generator=g)] + [512, 384, 129]

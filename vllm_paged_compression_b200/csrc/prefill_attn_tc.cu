@@ -521,12 +521,13 @@ void set_prefill_tc_tile(int tn) {   // debug knob reused: values other than 64 
 }
 static int g_prefill_pp = -1;
 void set_prefill_pp(int v) { g_prefill_pp = v; }
-static int g_prefill_dq = 0;
-void set_prefill_dq(int v) { g_prefill_dq = v; }
+static int g_prefill_dq = -1;
+void set_prefill_dq(int v) { g_prefill_dq = v; }   // 1 = always (when supported), 0 = never, -1 = rule
 static int g_tc_xitem = 1;
 void set_prefill_tc_xitem(int v) { g_tc_xitem = v; }
 #else
 constexpr int g_tc_xitem = 1;
+constexpr int g_prefill_dq = -1;
 constexpr int g_tc_persistent = -1;
 constexpr int g_tc_tile_n = 64;
 #endif
@@ -624,9 +625,13 @@ int prefill_attn(const PrefillArgs& a, cudaStream_t stream) {
       if (m[5] != 0 && (((m[4] | m[5]) & 15) != 0)) box8 = true;     // block size 8: 8-row TMA boxes
     }
   }
+  // Dual-query-tile kernel (prefill_attn_dq.cu: two q heads of a kv head per CTA over one shared 5-stage
+  // K/V ring).  Rule from the same-box A/B in profiles/r02_prefill_dq_ab.jsonl: head size 128 and prompts of
+  // at most 2048 tokens (+11 % at 1024, +5 % at 2048; -1.5 % at 8192 and at head size 64, which stay here).
+  if (prefill_attn_dq_supported(a) &&
+      (g_prefill_dq > 0 || (g_prefill_dq < 0 && a.D == 128 && a.max_q_len <= kDqMaxQLen)))
+    return prefill_attn_dq(a, box8, stream);
 #ifdef PC_DEBUG
-  // A/B runs: two q heads of a kv head per CTA over one shared K/V ring (prefill_attn_dq.cu)
-  if (g_prefill_dq > 0 && prefill_attn_dq_supported(a)) return prefill_attn_dq(a, box8, stream);
   // A/B runs: the ping-pong kernel (two q heads of a kv head per CTA, 128-wide kv tiles; prefill_attn_pp.cu).
   // Measured 1-8 % slower than this kernel at every shape (profiles/r02_prefill_experiments.txt), so it is
   // built into the PC_DEBUG library only.
