@@ -82,8 +82,8 @@ def run(device, reqs, L, Hq, Hkv, D, evict_freq, reps, variant=0, check=None, ti
     flops = 4.0 * D * Hq * reqs * vis
     mode = {-1: "auto_", 0: "oneshot_", 1: "persist_", 2: "persist_localorder_"}[persistent]
     # the library's own rule (prefill_attn_tc.cu: prefill_attn): dual-query-tile kernel for head size 128, an even
-    # number of q heads per kv head and prompts <= 2048 tokens; PC_DEBUG knobs (--dq, tile) override it
-    rule_dq = D == 128 and (Hq // Hkv) % 2 == 0 and L <= 2048 and tile == 64 and persistent == -1
+    # number of q heads per kv head and prompts <= 6144 tokens; PC_DEBUG knobs (--dq, tile) override it
+    rule_dq = D == 128 and (Hq // Hkv) % 2 == 0 and L <= 6144 and tile == 64 and persistent == -1
     use_dq = rule_dq if dq < 0 else (dq == 1 and (Hq // Hkv) % 2 == 0)
     row = {"kernel": "prefill_attn_dq_kernel" if use_dq else f"prefill_attn_tc_{mode}kernel<TN={tile}>",
            "reqs": reqs, "q_len": L, "kv_kept": kept, "Hq": Hq, "Hkv": Hkv, "D": D,

@@ -491,13 +491,14 @@ def test_prefill_attention_topleft_causal(Hq, Hkv, D, mode):
     (8, 8, 64, 16, "budget", 128, [513, 64, 390]),
     (16, 2, 128, 16, "none", 0, [300, 1, 900]),
     # kernel dispatch of the product library (prefill_attn_tc.cu: prefill_attn): head size 128 with an even
-    # number of q heads per kv head and prompts <= 2048 tokens runs the dual-query-tile kernel
+    # number of q heads per kv head and prompts <= 6144 tokens runs the dual-query-tile kernel
     # (prefill_attn_dq.cu, the cases above); these two reach the one-tile kernel at head size 128 --
-    # a prompt beyond 2048 tokens (one CTA per query tile) and three q heads per kv head (persistent CTAs)
-    (8, 2, 128, 16, "percentage", 2, [2304, 129, 1]),
+    # a prompt beyond 6144 tokens (one CTA per query tile) and three q heads per kv head (persistent CTAs)
+    (4, 2, 128, 16, "percentage", 2, [6272, 129, 1]),
     (6, 2, 128, 16, "percentage", 2, [127, 640, 129, 1100]),
     # and the dual-query-tile kernel at its longest prompt, ragged next to a one-token prompt
-    (8, 4, 128, 16, "percentage", 4, [2048, 1, 1999]),
+    (4, 2, 128, 16, "percentage", 4, [6144, 1, 1999]),
+    (8, 4, 128, 16, "none", 0, [130, 1, 64, 1000, 2, 257]),     # short items next to empty ones (query tiles past a prompt's end)
 ])
 def test_prefill_attention_tile_edges_and_strided_rows(case):
     """q/k/v are column slices of one fused [T, (Hq + 2 Hkv) * D] buffer (row stride != H * D),

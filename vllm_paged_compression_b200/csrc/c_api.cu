@@ -446,6 +446,7 @@ void pc_debug_set_prefill_tc_persistent(int32_t v) { pc::set_prefill_tc_persiste
 void pc_debug_set_cache_write_block_heads(int32_t hc) { pc::set_cache_write_block_heads(hc); }
 void pc_debug_set_prefill_pp(int32_t v) { pc::set_prefill_pp(v); }
 void pc_debug_set_prefill_dq(int32_t v) { pc::set_prefill_dq(v); }
+int32_t pc_debug_prefill_dq_trace(int32_t on, void* host_out, size_t bytes) { return pc::prefill_dq_trace(on, host_out, bytes); }
 void pc_debug_set_prefill_tc_xitem(int32_t v) { pc::set_prefill_tc_xitem(v); }
 void pc_debug_set_decode_two_cta(int32_t v) { pc::set_decode_two_cta(v); }
 #endif

@@ -133,7 +133,7 @@ struct PrefillArgs {
 int prefill_attn(const PrefillArgs& a, cudaStream_t stream);     // tcgen05/TMEM kernels (prefill_attn_tc.cu: checks + dispatch)
 bool prefill_attn_dq_supported(const PrefillArgs& a);                        // dual-query-tile kernel (prefill_attn_dq.cu):
 int prefill_attn_dq(const PrefillArgs& a, bool box8, cudaStream_t stream);   // prefill_attn() sends it D 128, prompts <= kDqMaxQLen
-constexpr int kDqMaxQLen = 2048;
+constexpr int kDqMaxQLen = 6144;
 #ifdef PC_DEBUG
 bool prefill_attn_pp_supported(const PrefillArgs& a);            // two-query-tile ping-pong kernel (prefill_attn_pp.cu),
 int prefill_attn_pp(const PrefillArgs& a, cudaStream_t stream);  // measured, not adopted: PC_DEBUG library only
@@ -141,6 +141,7 @@ int prefill_attn_pp(const PrefillArgs& a, cudaStream_t stream);  // measured, no
 #ifdef PC_DEBUG
 void set_prefill_tc_persistent(int v);  // 1 = persistent CTAs, 0 = one CTA per query tile, -1 = rule
 void set_prefill_tc_tile(int tn);       // kv tile width of the tcgen05 kernel (64 | 128)
+int prefill_dq_trace(int on, void* host_out, size_t bytes);  // clock stamps of CTA 0 of the dual-query-tile kernel
 void set_prefill_dq(int v);             // dual-query-tile kernel: 1 = always (when supported), 0 = never, -1 = rule
 void set_prefill_pp(int v);             // ping-pong kernel: 1 = always (when supported), 0 = never, -1 = rule
 void set_prefill_tc_xitem(int v);       // 1 = the next item's first S MMA is issued before the current item's last P.V (product), 0 = after

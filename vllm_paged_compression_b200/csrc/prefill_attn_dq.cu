@@ -6,8 +6,14 @@
 // stages per CTA (96 KB each), so V_{g} is requested when P.V_{g-2} completes and two tiles cannot take
 // less than that latency: the MMA thread waits for V (and K), the softmax warps for S.  The two CTAs of
 // an SM mostly work on neighbouring q heads of the SAME kv head and each loads the same K/V tiles.
-// Here the two streams share the tiles: one ring of 5 K + 5 V stages (160 KB) feeds both -- three to
-// four tiles of look-ahead at half the L2 -> shared-memory traffic per flop.
+// Here the two streams share the tiles: one ring of K and V stages feeds both, at half the L2 -> shared-memory
+// traffic per flop.  Shared memory (head size 128, 226 KB): TWO Q pairs (4 x 32 KB, by item parity) + 3 K + 3 V
+// stages (16 KB each: two tiles of look-ahead).  A first version had one Q pair and 5 + 5 stages; a fit of its
+// launch times over 256-4096-token prompts gave ~2000 clk per kv tile plus ~6000 clk PER ITEM (31 % of the time at
+// 1024-token prompts): both streams reach an item boundary together, and the next Q pair could only be requested
+// when the item's last S MMAs had completed (TMA ~3000 clk + S ~1300 clk before the softmax warps see scores
+// again, with nothing else on the SM to fill the gap).  With two Q sets the next item's pair lands during the
+// current item and the first S of the next item is issued like any other tile's.
 //   * TMEM (512 columns): stream i at i * 256: S buffers [0, 64) [64, 128) (P_g bf16 over the first half
 //     of the S buffer it came from), O at [128, 256);
 //   * warpgroups 0 / 1 = softmax of stream 0 / 1 (thread = query row, 64 columns per tile),
@@ -34,7 +40,8 @@ namespace {
 
 constexpr int kTM = 128;        // query rows per tile (UMMA M)
 constexpr int kTN = 64;         // kv rows per tile
-constexpr int kStages = 5;      // K stages = V stages
+constexpr int kStages = 3;      // K stages = V stages
+constexpr int kQSets = 2;       // Q pairs in shared memory (by item parity): the next item's pair lands during this item
 constexpr int kDqThreads = 512;
 constexpr int kRegsSoftmaxDq = 176, kRegsRolesDq = 88, kRegsEpiDq = 72;   // 128 x (2 x 176 + 88 + 72) = 64 K
 constexpr float kRescaleThresholdDq = 8.f;   // log2 domain
@@ -51,8 +58,8 @@ template <int D>
 struct DqSmem {
   static constexpr int kQ = kTM * D * 2;         // one Q tile
   static constexpr int kKV = kTN * D * 2;        // one K or V stage
-  static constexpr int oQ = 0;                   // 2 tiles
-  static constexpr int oK = oQ + 2 * kQ;         // kStages
+  static constexpr int oQ = 0;                   // kQSets x 2 tiles
+  static constexpr int oK = oQ + kQSets * 2 * kQ;  // kStages
   static constexpr int oV = oK + kStages * kKV;  // kStages
   static constexpr int oBar = oV + kStages * kKV;
   static constexpr int oLinv = oBar + 48 * 8;    // [item parity][stream][kTM] floats
@@ -63,8 +70,8 @@ struct DqSmem {
 // every barrier a waiter can fall behind on is indexed so that the waiter is at most one phase late
 // (S / P / P.V by tile parity, l by item parity, the ring by stage)
 enum {
-  Q_QFULL = 0,
-  Q_KFULL = 1,                       // [stage]
+  Q_QFULL = 0,                       // [item parity]
+  Q_KFULL = 2,                       // [stage]
   Q_VFULL = Q_KFULL + kStages,
   Q_KFREE = Q_VFULL + kStages,       // S of both streams done with the stage (2 commits)
   Q_VFREE = Q_KFREE + kStages,       // P.V of both streams done with the stage (2 commits)
@@ -73,13 +80,47 @@ enum {
   Q_PVDONE = Q_PFULL + 4,
   Q_LFULL = Q_PVDONE + 4,            // [stream][item parity]
   Q_OFREE = Q_LFULL + 4,             // [stream]
-  Q_COUNT = Q_OFREE + 2
+  Q_QFREE = Q_OFREE + 2,             // [item parity]: the last S MMAs of both streams have read the Q pair (2 commits)
+  Q_COUNT = Q_QFREE + 2
 };
 static_assert(Q_COUNT + 1 <= 48, "barrier area");
 
 struct DqItem {
   int q_start, q_len, kv_src, kv_len, first, pruned, i0, hq0, hkv, ntiles;
 };
+
+#ifdef PC_DEBUG
+// per-role clock64 stamps of CTA 0 (profiles/tools_trace_prefill_dq.py): [role][kDqTraceCap] words of
+// code << 56 | (tile & 0xffff) << 40 | clock (40 bits)
+constexpr int kDqTraceRoles = 8, kDqTraceCap = 8192;
+__device__ unsigned long long g_dq_trace[kDqTraceRoles * kDqTraceCap];
+__device__ int g_dq_trace_on = 0;
+struct DqTracer {
+  unsigned long long* base;
+  int n;
+  __device__ __forceinline__ void init(int role, bool on) {
+    base = on ? g_dq_trace + role * kDqTraceCap : nullptr;
+    n = 0;
+  }
+  __device__ __forceinline__ void operator()(int code, int g) {
+    if (base != nullptr && n < kDqTraceCap)
+      base[n++] = ((unsigned long long)code << 56) | ((unsigned long long)(g & 0xffff) << 40) |
+                  ((unsigned long long)clock64() & 0xffffffffffull);
+  }
+};
+#define DQ_TRACER(name, role, on) DqTracer name; name.init(role, (on) && blockIdx.x == 0 && g_dq_trace_on != 0)
+#define DQ_TR(name, code, g) name(code, g)
+#else
+#define DQ_TRACER(name, role, on)
+#define DQ_TR(name, code, g)
+#endif
+
+// a load the compiler leaves where it is written (volatile asm keeps its order among the mbarrier / tcgen05 asm)
+__device__ __forceinline__ int ld_early(const int* p) {
+  int v;
+  asm volatile("ld.global.nc.s32 %0, [%1];" : "=r"(v) : "l"(p));
+  return v;
+}
 
 template <int D, int BOX>
 __global__ void __launch_bounds__(kDqThreads, 1)
@@ -103,7 +144,9 @@ prefill_attn_dq_kernel(const DqParams p, const __grid_constant__ CUtensorMap tm_
 
   // item k -> (chunk of requests, query tile descending, request, head pair): the order of
   // prefill_attn_tc.cu with pairs of q heads in the place of q heads
-  auto get_item = [&](int k) {
+  // EARLY: the six words are requested by volatile loads, which stay where they are written (a role asks for the
+  // NEXT item's descriptor at the top of an item and uses it at the end: no global-memory latency between items)
+  auto get_item = [&](int k, bool early = false) {
     DqItem it;
     const int per_chunk = q_tiles * pairs * chunk_reqs;
     const int c = k / per_chunk, k2 = k - c * per_chunk;
@@ -115,9 +158,29 @@ prefill_attn_dq_kernel(const DqParams p, const __grid_constant__ CUtensorMap tm_
     it.hq0 = 2 * (rem % pairs);
     it.hkv = it.hq0 / G;
     const int* m = p.req_meta + r * 6;
-    it.q_start = m[0]; it.q_len = m[1]; it.kv_src = m[2]; it.kv_len = m[3]; it.first = m[4]; it.pruned = m[5];
+    if (early) {
+      it.q_start = ld_early(m); it.q_len = ld_early(m + 1); it.kv_src = ld_early(m + 2);
+      it.kv_len = ld_early(m + 3); it.first = ld_early(m + 4); it.pruned = ld_early(m + 5);
+    } else {
+      it.q_start = m[0]; it.q_len = m[1]; it.kv_src = m[2]; it.kv_len = m[3]; it.first = m[4]; it.pruned = m[5];
+    }
     it.i0 = qt * kTM;
     it.ntiles = it.i0 < it.q_len ? (min(it.kv_len, it.i0 + kTM) + kTN - 1) / kTN : 0;
+    return it;
+  };
+  auto peek_item = [&](int kk) {       // item kk, requested now; ntiles 0 when kk is past the end (or the item is empty)
+    DqItem it;
+    it.ntiles = 0;
+    if (kk < total) it = get_item(kk, true);
+    return it;
+  };
+  auto seek_item = [&](int& kk) {      // the first non-empty item at or after kk (ntiles 0: none left)
+    DqItem it;
+    it.ntiles = 0;
+    for (; kk < total; kk += gridDim.x) {
+      it = get_item(kk);
+      if (it.ntiles != 0) break;
+    }
     return it;
   };
   auto item_tiles = [&](int& kk) {     // tiles of the next non-empty item at or after kk (0: none left)
@@ -141,7 +204,7 @@ prefill_attn_dq_kernel(const DqParams p, const __grid_constant__ CUtensorMap tm_
 
   if (tid == 0) {
     if ((smem_u32(smem) & 1023u) != 0u) __trap();
-    mbar_init(&bar[Q_QFULL], 1);
+    for (int s = 0; s < kQSets; ++s) { mbar_init(&bar[Q_QFULL + s], 1); mbar_init(&bar[Q_QFREE + s], 2); }
     for (int s = 0; s < kStages; ++s) {
       mbar_init(&bar[Q_KFULL + s], 1); mbar_init(&bar[Q_VFULL + s], 1);
       mbar_init(&bar[Q_KFREE + s], 2); mbar_init(&bar[Q_VFREE + s], 2);
@@ -165,40 +228,51 @@ prefill_attn_dq_kernel(const DqParams p, const __grid_constant__ CUtensorMap tm_
       // ================================================= K / V producer (one lane): runs ahead of the MMAs
       // by up to kStages tiles, across item boundaries
       if (lane == 0) {
-        int g = 0;
-        for (int k = blockIdx.x; k < total; k += gridDim.x) {
-          const DqItem it = get_item(k);
-          if (it.ntiles == 0) continue;
+        DQ_TRACER(tr, 5, true);
+        int g = 0, k = blockIdx.x;
+        DqItem it = seek_item(k);
+        while (it.ntiles != 0) {
+          int kn = k + gridDim.x;
+          DqItem nx = peek_item(kn);                   // requested now, used after this item's tiles
           if (it.pruned != 0 && (((it.first | it.pruned) & (BOX - 1)) != 0)) __trap();
           for (int t = 0; t < it.ntiles; ++t, ++g) {
             const int st = g % kStages, use = g / kStages;
             if (use > 0) t5::mbar_wait_relaxed(&bar[Q_KFREE + st], (use - 1) & 1);
+            DQ_TR(tr, 30, g);
             issue_kv(&tm_k, smem + L::oK + st * L::kKV, &bar[Q_KFULL + st], it, t);
             if (use > 0) t5::mbar_wait_relaxed(&bar[Q_VFREE + st], (use - 1) & 1);
+            DQ_TR(tr, 32, g);
             issue_kv(&tm_v, smem + L::oV + st * L::kKV, &bar[Q_VFULL + st], it, t);
           }
+          if (nx.ntiles == 0 && kn < total) {          // an empty item: look further
+            kn += gridDim.x;
+            nx = seek_item(kn);
+          }
+          it = nx;
+          k = kn;
         }
       }
       __syncwarp();
     } else if (warp == 10) {
       // ================================================= Q producer (one lane): the pair of Q tiles of an item
       if (lane == 0) {
-        int g = 0, gw = 0;   // tiles of the items before this one; tiles whose k_free this thread has seen
+        DQ_TRACER(tr, 6, true);
+        int n = 0;           // non-empty items before this one
         for (int k = blockIdx.x; k < total; k += gridDim.x) {
           const DqItem it = get_item(k);
           if (it.ntiles == 0) continue;
-          // both Q buffers are free once the previous item's last S MMAs (both streams) have completed (=
-          // k_free of that tile's stage).  The k_free phases are consumed ONE BY ONE: a parity wait passes at
-          // once on a barrier that is two phases behind, and nothing else throttles this thread (waiting for
-          // the last tile only let it run items ahead, overwrite Q tiles in use and overflow q_full's tx-count).
-          for (; gw < g; ++gw) t5::mbar_wait_relaxed(&bar[Q_KFREE + gw % kStages], (gw / kStages) & 1);
-          mbar_expect_tx(&bar[Q_QFULL], 2 * L::kQ);
+          // Q set n & 1 is free once the last S MMAs of item n - 2 (both streams) have completed.  The issuers
+          // cannot start item n before this load, so q_free[n & 1] is never more than one phase ahead of this wait.
+          const int qs = n & 1;
+          if (n >= kQSets) t5::mbar_wait_relaxed(&bar[Q_QFREE + qs], ((n >> 1) - 1) & 1);
+          DQ_TR(tr, 40, n);
+          mbar_expect_tx(&bar[Q_QFULL + qs], 2 * L::kQ);
 #pragma unroll
           for (int i = 0; i < 2; ++i)
 #pragma unroll
             for (int b = 0; b < D / 64; ++b)
-              t5::tma_load_2d(smem + L::oQ + i * L::kQ + b * (kTM * 128), &tm_q, (it.hq0 + i) * D + b * 64,
-                              it.q_start + it.i0, &bar[Q_QFULL]);
+              t5::tma_load_2d(smem + L::oQ + (qs * 2 + i) * L::kQ + b * (kTM * 128), &tm_q, (it.hq0 + i) * D + b * 64,
+                              it.q_start + it.i0, &bar[Q_QFULL + qs]);
           // the NEXT item's Q pair (read exactly once: always a DRAM miss) goes to L2 now
           for (int kn = k + gridDim.x; kn < total; kn += gridDim.x) {
             const DqItem nx = get_item(kn);
@@ -210,7 +284,7 @@ prefill_attn_dq_kernel(const DqParams p, const __grid_constant__ CUtensorMap tm_
                 t5::tma_prefetch_l2_2d(&tm_q, (nx.hq0 + i) * D + b * 64, nx.q_start + nx.i0);
             break;
           }
-          g += it.ntiles;
+          ++n;
         }
       }
       __syncwarp();
@@ -218,12 +292,16 @@ prefill_attn_dq_kernel(const DqParams p, const __grid_constant__ CUtensorMap tm_
       // ================================================= MMA issuer of stream i (one lane; warp 9 -> 0, warp 11 -> 1)
       if (lane == 0) {
         const int i = (warp == 9) ? 0 : 1;
-        const uint32_t sQ = smem_u32(smem + L::oQ) + i * L::kQ, sK = smem_u32(smem + L::oK), sV = smem_u32(smem + L::oV);
+        DQ_TRACER(tr, 2 + i, true);
+        const uint32_t sQ0 = smem_u32(smem + L::oQ) + i * L::kQ, sK = smem_u32(smem + L::oK), sV = smem_u32(smem + L::oV);
         const uint32_t tmem_i = tmem + i * 256;
-        // S_i(g) = Q_i K_g^T; the K stage is released when both streams' S MMAs have completed (2 commits)
-        auto issue_s = [&](int g) {
+        // S_i(g) = Q_i K_g^T with the Q pair of set qs; the K stage is released when both streams' S MMAs have
+        // completed (2 commits), the Q set likewise after an item's last S
+        auto issue_s = [&](int g, int qs, bool last_of_item) {
           const int st = g % kStages;
+          const uint32_t sQ = sQ0 + qs * (2 * L::kQ);
           mbar_wait(&bar[Q_KFULL + st], (g / kStages) & 1);
+          DQ_TR(tr, 10, g);
           t5::fence_after_sync();
 #pragma unroll
           for (int ks = 0; ks < KS; ++ks) {
@@ -233,35 +311,45 @@ prefill_attn_dq_kernel(const DqParams p, const __grid_constant__ CUtensorMap tm_
           }
           t5::commit(&bar[Q_SFULL + i * 2 + (g & 1)]);
           t5::commit(&bar[Q_KFREE + st]);
+          if (last_of_item) t5::commit(&bar[Q_QFREE + qs]);
         };
-        int g = 0, n_item = 0, n_q = 0, k = blockIdx.x;
+        int g = 0, n_item = 0, k = blockIdx.x;
         int ntiles = item_tiles(k);
         bool have = ntiles != 0;
         if (have) {
           mbar_wait(&bar[Q_QFULL], 0);
-          n_q = 1;
-          issue_s(0);
+          issue_s(0, 0, ntiles == 1);
         }
         while (have) {
           int kn = k + gridDim.x, nt_nx = 0;
           bool have_nx = false;
+          const int nt_peek = peek_item(kn).ntiles;   // requested now, used at this item's last tile
           for (int j = 0; j < ntiles; ++j, ++g) {
             const int st = g % kStages, sb = g & 1;
             if (j + 1 < ntiles) {
-              issue_s(g + 1);
+              issue_s(g + 1, n_item & 1, j + 2 == ntiles);
             } else {
-              nt_nx = item_tiles(kn);
+              nt_nx = nt_peek;
+              if (nt_nx == 0 && kn < total) {     // an empty item (a query tile past a short prompt): look further
+                kn += gridDim.x;
+                nt_nx = item_tiles(kn);
+              }
               have_nx = nt_nx != 0;
-              if (have_nx) {                      // the next item's first tile: new Q pair
-                mbar_wait(&bar[Q_QFULL], n_q & 1);
-                ++n_q;
-                issue_s(g + 1);
+              if (have_nx) {                      // the next item's first tile: the other Q set, loaded during this item
+                DQ_TR(tr, 15, g);
+                mbar_wait(&bar[Q_QFULL + ((n_item + 1) & 1)], ((n_item + 1) >> 1) & 1);
+                DQ_TR(tr, 16, g);
+                issue_s(g + 1, (n_item + 1) & 1, nt_nx == 1);
               }
             }
+            DQ_TR(tr, 11, g);
             mbar_wait(&bar[Q_VFULL + st], (g / kStages) & 1);
+            DQ_TR(tr, 12, g);
             mbar_wait(&bar[Q_PFULL + i * 2 + sb], (g >> 1) & 1);
+            DQ_TR(tr, 13, g);
             // the first P.V of an item overwrites O_i: the epilogue must have read the previous item's
             if (j == 0 && n_item > 0) mbar_wait(&bar[Q_OFREE + i], (n_item - 1) & 1);
+            DQ_TR(tr, 14, g);
             t5::fence_after_sync();
 #pragma unroll
             for (int kk = 0; kk < PK; ++kk) {
@@ -286,24 +374,28 @@ prefill_attn_dq_kernel(const DqParams p, const __grid_constant__ CUtensorMap tm_
     const uint32_t lane_base = (uint32_t)((warp & 3) * 32) << 16;
     const uint32_t tmem_s = tmem + i * 256 + lane_base;
     const uint32_t tmem_o = tmem + i * 256 + 128 + lane_base;
-    int g = 0, n_item = 0;
-    for (int k = blockIdx.x; k < total; k += gridDim.x) {
-      const DqItem it = get_item(k);
-      if (it.ntiles == 0) continue;
+    int g = 0, n_item = 0, k = blockIdx.x;
+    DQ_TRACER(tr, i, (warp & 3) == 0 && lane == 0);
+    DqItem it = seek_item(k);
+    while (it.ntiles != 0) {
+      int kn = k + gridDim.x;
+      DqItem nx = peek_item(kn);                       // requested now, used when this item is done
       const int row = it.i0 + rt;
       float m_use = -INFINITY, l_run = 0.f;
       for (int j = 0; j < it.ntiles; ++j, ++g) {
         const int sb = g & 1;
         const int j0 = j * kTN;
+        DQ_TR(tr, j == 0 ? 1 : 2, g);
         mbar_wait(&bar[Q_SFULL + i * 2 + sb], (g >> 1) & 1);
+        DQ_TR(tr, 3, g);
         t5::fence_after_sync();
         uint32_t sr[SC][32];
 #pragma unroll
         for (int c = 0; c < SC; ++c) t5::tmem_ld32(sr[c], tmem_s + sb * kTN + c * 32);
         t5::tmem_ld_wait();
         const bool need_mask = (j0 + kTN - 1 > it.i0) || (j0 + kTN > it.kv_len);
+        const int lim = need_mask ? min(row, it.kv_len - 1) - j0 : kTN;  // columns > lim are masked
         if (need_mask) {
-          const int lim = min(row, it.kv_len - 1) - j0;  // columns > lim are masked
 #pragma unroll
           for (int c = 0; c < SC; ++c) {
             if (__all_sync(kFull, lim >= c * 32 + 31)) continue;
@@ -328,7 +420,14 @@ prefill_attn_dq_kernel(const DqParams p, const __grid_constant__ CUtensorMap tm_
         float sum[4] = {0.f, 0.f, 0.f, 0.f};
         const float neg_m = -m_use;
 #pragma unroll
-        for (int c = 0; c < SC; ++c)
+        for (int c = 0; c < SC; ++c) {
+          // a chunk that is masked for every row of the warp (the upper rows of an item's diagonal tiles): P = 0
+          // without the exponentials (exp2(-inf) = 0: the same bits)
+          if (need_mask && __all_sync(kFull, lim < c * 32)) {
+#pragma unroll
+            for (int e = 0; e < 16; ++e) sr[c][e] = 0u;
+            continue;
+          }
 #pragma unroll
           for (int e = 0; e < 32; e += 2) {
             const float p0 = fast_exp2(fmaf(__uint_as_float(sr[c][e]), p.scale_log2, neg_m));
@@ -336,6 +435,7 @@ prefill_attn_dq_kernel(const DqParams p, const __grid_constant__ CUtensorMap tm_
             sum[(e >> 1) & 3] += p0 + p1;
             sr[c][e >> 1] = pack_bf16x2(p0, p1);
           }
+        }
         l_run += (sum[0] + sum[1]) + (sum[2] + sum[3]);
         // P_g has its own buffer (the S buffer it came from): only a rescale of O has to wait for the
         // previous P.V of this stream
@@ -364,12 +464,19 @@ prefill_attn_dq_kernel(const DqParams p, const __grid_constant__ CUtensorMap tm_
         t5::tmem_st_wait();
         t5::fence_before_sync();
         t5::mbar_arrive(&bar[Q_PFULL + i * 2 + sb]);
+        DQ_TR(tr, 4, g);
       }
       // 1 / l to the epilogue warps (l_full is double-buffered by item parity: a one-tile item lets this
       // warpgroup finish item n + 1 before the epilogue has looked at item n)
       linv[((n_item & 1) * 2 + i) * kTM + rt] = 1.f / l_run;
       t5::mbar_arrive(&bar[Q_LFULL + i * 2 + (n_item & 1)]);
       ++n_item;
+      if (nx.ntiles == 0 && kn < total) {              // an empty item: look further
+        kn += gridDim.x;
+        nx = seek_item(kn);
+      }
+      it = nx;
+      k = kn;
     }
   } else {
     // ================================================= epilogue warpgroup: O_i / l -> bf16 -> global, i = 0, 1
@@ -377,6 +484,7 @@ prefill_attn_dq_kernel(const DqParams p, const __grid_constant__ CUtensorMap tm_
     const int rt = tid & 127;
     const uint32_t lane_base = (uint32_t)((warp & 3) * 32) << 16;
     int g = 0, n_item = 0;
+    DQ_TRACER(tr, 4, (warp & 3) == 0 && lane == 0);
     for (int k = blockIdx.x; k < total; k += gridDim.x) {
       const DqItem it = get_item(k);
       if (it.ntiles == 0) continue;
@@ -384,9 +492,12 @@ prefill_attn_dq_kernel(const DqParams p, const __grid_constant__ CUtensorMap tm_
       const int row = it.i0 + rt;
 #pragma unroll 1
       for (int i = 0; i < 2; ++i) {
+        DQ_TR(tr, 20 + i, g - 1);
         t5::mbar_wait_sleep(&bar[Q_LFULL + i * 2 + (n_item & 1)], (n_item >> 1) & 1, 128);
+        DQ_TR(tr, 22 + i, g - 1);
         const float inv = linv[((n_item & 1) * 2 + i) * kTM + rt];
         t5::mbar_wait_sleep(&bar[Q_PVDONE + i * 2 + ((g - 1) & 1)], ((g - 1) >> 1) & 1, 64);
+        DQ_TR(tr, 24 + i, g - 1);
         t5::fence_after_sync();
         __nv_bfloat16* dst = p.out + (size_t)(it.q_start + (row < it.q_len ? row : 0)) * p.out_stride +
                              (size_t)(it.hq0 + i) * D;
@@ -398,6 +509,7 @@ prefill_attn_dq_kernel(const DqParams p, const __grid_constant__ CUtensorMap tm_
           if (c == D / 32 - 1) {          // O_i is in registers: the next item's first P.V may overwrite it
             t5::fence_before_sync();
             t5::mbar_arrive(&bar[Q_OFREE + i]);
+            DQ_TR(tr, 26 + i, g - 1);
           }
           if (row < it.q_len) {
 #pragma unroll
@@ -458,6 +570,17 @@ int launch_prefill_dq(const DqParams& p, const PrefillArgs& a, cudaStream_t stre
 }
 
 }  // namespace
+
+#ifdef PC_DEBUG
+int prefill_dq_trace(int on, void* host_out, size_t bytes) {   // on: set the flag; host_out != NULL: copy the stamps out
+  cudaError_t e = cudaMemcpyToSymbol(g_dq_trace_on, &on, sizeof(int));
+  if (e == cudaSuccess && host_out != nullptr) {
+    const size_t all = sizeof(unsigned long long) * kDqTraceRoles * kDqTraceCap;
+    e = cudaMemcpyFromSymbol(host_out, g_dq_trace, bytes < all ? bytes : all);
+  }
+  return e == cudaSuccess ? 0 : set_cuda_error("prefill_dq_trace", e);
+}
+#endif
 
 bool prefill_attn_dq_supported(const PrefillArgs& a) {
   return (a.D == 64 || a.D == 128) && a.Hkv > 0 && a.Hq % a.Hkv == 0 && ((a.Hq / a.Hkv) % 2) == 0;

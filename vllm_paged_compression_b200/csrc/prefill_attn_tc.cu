@@ -625,9 +625,10 @@ int prefill_attn(const PrefillArgs& a, cudaStream_t stream) {
       if (m[5] != 0 && (((m[4] | m[5]) & 15) != 0)) box8 = true;     // block size 8: 8-row TMA boxes
     }
   }
-  // Dual-query-tile kernel (prefill_attn_dq.cu: two q heads of a kv head per CTA over one shared 5-stage
-  // K/V ring).  Rule from the same-box A/B in profiles/r02_prefill_dq_ab.jsonl: head size 128 and prompts of
-  // at most 2048 tokens (+11 % at 1024, +5 % at 2048; -1.5 % at 8192 and at head size 64, which stay here).
+  // Dual-query-tile kernel (prefill_attn_dq.cu: two q heads of a kv head per CTA over one shared K/V ring).
+  // Rule from the same-box A/Bs in profiles/r02_prefill_dq_ab.jsonl and r02_prefill_dq_threshold_ab.jsonl: head
+  // size 128 and prompts of at most 6144 tokens (+26 % at 256 tokens, +19 % at 512, +11 % at 1024, +5-6 % at
+  // 2048 / 4096 / 6144; -2 % at 8192 without eviction and at head size 64, which stay with the kernel of this file).
   if (prefill_attn_dq_supported(a) &&
       (g_prefill_dq > 0 || (g_prefill_dq < 0 && a.D == 128 && a.max_q_len <= kDqMaxQLen)))
     return prefill_attn_dq(a, box8, stream);
