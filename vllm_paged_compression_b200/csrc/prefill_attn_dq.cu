@@ -227,7 +227,7 @@ prefill_attn_dq_kernel(const DqParams p, const __grid_constant__ CUtensorMap tm_
     if (warp == 8) {
       // ================================================= K / V producer (one lane): runs ahead of the MMAs
       // by up to kStages tiles, across item boundaries
-      if (lane == 0) {
+      if (t5::elect_one()) {
         DQ_TRACER(tr, 5, true);
         int g = 0, k = blockIdx.x;
         DqItem it = seek_item(k);
@@ -255,7 +255,7 @@ prefill_attn_dq_kernel(const DqParams p, const __grid_constant__ CUtensorMap tm_
       __syncwarp();
     } else if (warp == 10) {
       // ================================================= Q producer (one lane): the pair of Q tiles of an item
-      if (lane == 0) {
+      if (t5::elect_one()) {
         DQ_TRACER(tr, 6, true);
         int n = 0;           // non-empty items before this one
         for (int k = blockIdx.x; k < total; k += gridDim.x) {
@@ -290,7 +290,7 @@ prefill_attn_dq_kernel(const DqParams p, const __grid_constant__ CUtensorMap tm_
       __syncwarp();
     } else {
       // ================================================= MMA issuer of stream i (one lane; warp 9 -> 0, warp 11 -> 1)
-      if (lane == 0) {
+      if (t5::elect_one()) {
         const int i = (warp == 9) ? 0 : 1;
         DQ_TRACER(tr, 2 + i, true);
         const uint32_t sQ0 = smem_u32(smem + L::oQ) + i * L::kQ, sK = smem_u32(smem + L::oK), sV = smem_u32(smem + L::oV);

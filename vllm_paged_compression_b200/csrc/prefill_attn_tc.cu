@@ -189,7 +189,7 @@ prefill_attn_tc_kernel(const PrefillTcParams p, const __grid_constant__ CUtensor
   if constexpr (kRealloc) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kRegsRoles));
   if (warp == 4) {
     // ================================================= Q + K producer (one lane, TMA)
-    if (lane == 0) {
+    if (t5::elect_one()) {
       int g = 0;   // tiles issued so far by this CTA (all items)
       for (int k = blockIdx.x; k < total; k += gridDim.x) {
         const TcItem it = get_item(k);
@@ -235,7 +235,7 @@ prefill_attn_tc_kernel(const PrefillTcParams p, const __grid_constant__ CUtensor
     __syncwarp();
   } else if (warp == 5) {
     // ================================================= V producer (one lane, TMA)
-    if (lane == 0) {
+    if (t5::elect_one()) {
       int g = 0;
       for (int k = blockIdx.x; k < total; k += gridDim.x) {
         const TcItem it = get_item(k);
@@ -249,7 +249,7 @@ prefill_attn_tc_kernel(const PrefillTcParams p, const __grid_constant__ CUtensor
     __syncwarp();
   } else if (warp == 6) {
     // ================================================= MMA issuer (one lane)
-    if (lane == 0) {
+    if (t5::elect_one()) {
       const uint32_t sQ = smem_u32(smem + L::oQ), sK = smem_u32(smem + L::oK);
       const uint32_t sV = smem_u32(smem + L::oV), sP = smem_u32(smem + L::oP);
       auto issue_s = [&](int g) {

@@ -23,6 +23,18 @@ __device__ __forceinline__ void tmem_dealloc(uint32_t taddr) {
   asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "n"(COLS)
                : "memory");
 }
+// one lane of a converged warp (elect.sync): code under `if (elect_one())` is known to the compiler to run in a
+// single thread, so tcgen05.mma / TMA operands go to uniform registers directly -- under `if (lane == 0)` it wraps
+// every such instruction in an ELECT / R2UR.BROADCAST / BRA.U.ANY loop (~10 extra instructions per MMA)
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "elect.sync _|p, 0xffffffff;\n\t"
+      "selp.b32 %0, 1, 0, p;\n\t}"
+      : "=r"(pred));
+  return pred != 0;
+}
 __device__ __forceinline__ void fence_before_sync() {
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
 }
