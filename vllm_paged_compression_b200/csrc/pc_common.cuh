@@ -46,6 +46,16 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   }
 }
 
+// one lane of a converged warp (elect.sync); see tcgen05.cuh: elect_one
+__device__ __forceinline__ bool elect_one_lane() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "elect.sync _|p, 0xffffffff;\n\t"
+      "selp.b32 %0, 1, 0, p;\n\t}"
+      : "=r"(pred));
+  return pred != 0;
+}
 // ------------------------------------------------ TMA 1-D bulk copy global -> smem
 // dst/src 16-byte aligned, bytes a multiple of 16.  Completion is signalled on `bar`
 // (complete_tx::bytes).  Lowered to UBLKCP.

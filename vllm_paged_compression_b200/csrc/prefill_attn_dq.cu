@@ -88,6 +88,12 @@ static_assert(Q_COUNT + 1 <= 48, "barrier area");
 struct DqItem {
   int q_start, q_len, kv_src, kv_len, first, pruned, i0, hq0, hkv, ntiles;
 };
+struct ItemIter {   // position of a CTA in the item order
+  int k;            // item index (>= total: past the end)
+  int qt;           // query tile (descending inside a chunk of requests)
+  int r0, nreq;     // the chunk: first request, requests in it
+  int rr, pr;       // request inside the chunk, pair of q heads
+};
 
 #ifdef PC_DEBUG
 // per-role clock64 stamps of CTA 0 (profiles/tools_trace_prefill_dq.py): [role][kDqTraceCap] words of
@@ -143,52 +149,69 @@ prefill_attn_dq_kernel(const DqParams p, const __grid_constant__ CUtensorMap tm_
   const int total = q_tiles * pairs * num_reqs;
 
   // item k -> (chunk of requests, query tile descending, request, head pair): the order of
-  // prefill_attn_tc.cu with pairs of q heads in the place of q heads
+  // prefill_attn_tc.cu with pairs of q heads in the place of q heads.  A CTA visits k = blockIdx.x,
+  // + gridDim.x, ...: the position is kept as an ItemIter and stepped WITHOUT divisions -- the six
+  // integer divisions of the closed form went through the XU pipe (I2F / RCP / F2I) behind the softmax
+  // warps' exponentials and cost the softmax warps 1200-2100 clk between items (clock trace,
+  // profiles/r02_prefill_dq_trace_1024_elect.txt).
+  const int step_rr = (int)gridDim.x / pairs, step_pr = (int)gridDim.x - step_rr * pairs;
+  auto it_begin = [&]() {
+    ItemIter s;
+    s.k = blockIdx.x; s.qt = 0; s.r0 = 0; s.nreq = 1; s.rr = 0; s.pr = 0;
+    if (s.k < total) {
+      const int per_chunk = q_tiles * pairs * chunk_reqs;
+      const int c = s.k / per_chunk, k2 = s.k - c * per_chunk;
+      s.r0 = c * chunk_reqs;
+      s.nreq = min(chunk_reqs, num_reqs - s.r0);
+      const int pq = pairs * s.nreq, lv = k2 / pq, rem = k2 - lv * pq;
+      s.qt = q_tiles - 1 - lv;
+      s.rr = rem / pairs;
+      s.pr = rem - s.rr * pairs;
+    }
+    return s;
+  };
+  auto it_next = [&](ItemIter& s) {    // k += gridDim.x
+    s.k += gridDim.x;
+    if (s.k >= total) return;
+    s.pr += step_pr; s.rr += step_rr;
+    if (s.pr >= pairs) { s.pr -= pairs; ++s.rr; }
+    while (s.rr >= s.nreq) {           // past the chunk's requests at this query-tile level
+      s.rr -= s.nreq;
+      if (--s.qt < 0) { s.qt = q_tiles - 1; s.r0 += s.nreq; s.nreq = min(chunk_reqs, num_reqs - s.r0); }
+    }
+  };
   // EARLY: the six words are requested by volatile loads, which stay where they are written (a role asks for the
   // NEXT item's descriptor at the top of an item and uses it at the end: no global-memory latency between items)
-  auto get_item = [&](int k, bool early = false) {
+  auto get_item = [&](const ItemIter& s, bool early = false) {
     DqItem it;
-    const int per_chunk = q_tiles * pairs * chunk_reqs;
-    const int c = k / per_chunk, k2 = k - c * per_chunk;
-    const int r0 = c * chunk_reqs;
-    const int pq = pairs * min(chunk_reqs, num_reqs - r0);
-    const int qt = q_tiles - 1 - k2 / pq;
-    const int rem = k2 % pq;
-    const int r = r0 + rem / pairs;
-    it.hq0 = 2 * (rem % pairs);
-    it.hkv = it.hq0 / G;
-    const int* m = p.req_meta + r * 6;
+    it.hq0 = 2 * s.pr;
+    it.hkv = it.hq0 / G;               // (dead code except in the K/V producer)
+    const int* m = p.req_meta + (s.r0 + s.rr) * 6;
     if (early) {
       it.q_start = ld_early(m); it.q_len = ld_early(m + 1); it.kv_src = ld_early(m + 2);
       it.kv_len = ld_early(m + 3); it.first = ld_early(m + 4); it.pruned = ld_early(m + 5);
     } else {
       it.q_start = m[0]; it.q_len = m[1]; it.kv_src = m[2]; it.kv_len = m[3]; it.first = m[4]; it.pruned = m[5];
     }
-    it.i0 = qt * kTM;
+    it.i0 = s.qt * kTM;
     it.ntiles = it.i0 < it.q_len ? (min(it.kv_len, it.i0 + kTM) + kTN - 1) / kTN : 0;
     return it;
   };
-  auto peek_item = [&](int kk) {       // item kk, requested now; ntiles 0 when kk is past the end (or the item is empty)
+  auto peek_item = [&](ItemIter& s) {  // steps s once; that item, requested now (ntiles 0: past the end, or empty)
     DqItem it;
     it.ntiles = 0;
-    if (kk < total) it = get_item(kk, true);
+    it_next(s);
+    if (s.k < total) it = get_item(s, true);
     return it;
   };
-  auto seek_item = [&](int& kk) {      // the first non-empty item at or after kk (ntiles 0: none left)
+  auto seek_item = [&](ItemIter& s) {  // the first non-empty item at or after s (ntiles 0: none left)
     DqItem it;
     it.ntiles = 0;
-    for (; kk < total; kk += gridDim.x) {
-      it = get_item(kk);
+    for (; s.k < total; it_next(s)) {
+      it = get_item(s);
       if (it.ntiles != 0) break;
     }
     return it;
-  };
-  auto item_tiles = [&](int& kk) {     // tiles of the next non-empty item at or after kk (0: none left)
-    for (; kk < total; kk += gridDim.x) {
-      const int nt = get_item(kk).ntiles;
-      if (nt != 0) return nt;
-    }
-    return 0;
   };
   auto issue_kv = [&](const CUtensorMap* tm, uint8_t* dst, uint64_t* full, const DqItem& it, int t) {
     mbar_expect_tx(full, L::kKV);
@@ -229,11 +252,12 @@ prefill_attn_dq_kernel(const DqParams p, const __grid_constant__ CUtensorMap tm_
       // by up to kStages tiles, across item boundaries
       if (t5::elect_one()) {
         DQ_TRACER(tr, 5, true);
-        int g = 0, k = blockIdx.x;
-        DqItem it = seek_item(k);
+        int g = 0;
+        ItemIter cur = it_begin();
+        DqItem it = seek_item(cur);
         while (it.ntiles != 0) {
-          int kn = k + gridDim.x;
-          DqItem nx = peek_item(kn);                   // requested now, used after this item's tiles
+          ItemIter nxi = cur;
+          DqItem nx = peek_item(nxi);                  // requested now, used after this item's tiles
           if (it.pruned != 0 && (((it.first | it.pruned) & (BOX - 1)) != 0)) __trap();
           for (int t = 0; t < it.ntiles; ++t, ++g) {
             const int st = g % kStages, use = g / kStages;
@@ -244,12 +268,12 @@ prefill_attn_dq_kernel(const DqParams p, const __grid_constant__ CUtensorMap tm_
             DQ_TR(tr, 32, g);
             issue_kv(&tm_v, smem + L::oV + st * L::kKV, &bar[Q_VFULL + st], it, t);
           }
-          if (nx.ntiles == 0 && kn < total) {          // an empty item: look further
-            kn += gridDim.x;
-            nx = seek_item(kn);
+          if (nx.ntiles == 0 && nxi.k < total) {       // an empty item: look further
+            it_next(nxi);
+            nx = seek_item(nxi);
           }
           it = nx;
-          k = kn;
+          cur = nxi;
         }
       }
       __syncwarp();
@@ -258,9 +282,11 @@ prefill_attn_dq_kernel(const DqParams p, const __grid_constant__ CUtensorMap tm_
       if (t5::elect_one()) {
         DQ_TRACER(tr, 6, true);
         int n = 0;           // non-empty items before this one
-        for (int k = blockIdx.x; k < total; k += gridDim.x) {
-          const DqItem it = get_item(k);
-          if (it.ntiles == 0) continue;
+        ItemIter cur = it_begin();
+        DqItem it = seek_item(cur);
+        while (it.ntiles != 0) {
+          it_next(cur);
+          const DqItem nx = seek_item(cur);            // the next non-empty item (ntiles 0: none)
           // Q set n & 1 is free once the last S MMAs of item n - 2 (both streams) have completed.  The issuers
           // cannot start item n before this load, so q_free[n & 1] is never more than one phase ahead of this wait.
           const int qs = n & 1;
@@ -274,16 +300,14 @@ prefill_attn_dq_kernel(const DqParams p, const __grid_constant__ CUtensorMap tm_
               t5::tma_load_2d(smem + L::oQ + (qs * 2 + i) * L::kQ + b * (kTM * 128), &tm_q, (it.hq0 + i) * D + b * 64,
                               it.q_start + it.i0, &bar[Q_QFULL + qs]);
           // the NEXT item's Q pair (read exactly once: always a DRAM miss) goes to L2 now
-          for (int kn = k + gridDim.x; kn < total; kn += gridDim.x) {
-            const DqItem nx = get_item(kn);
-            if (nx.ntiles == 0) continue;
+          if (nx.ntiles != 0) {
 #pragma unroll
             for (int i = 0; i < 2; ++i)
 #pragma unroll
               for (int b = 0; b < D / 64; ++b)
                 t5::tma_prefetch_l2_2d(&tm_q, (nx.hq0 + i) * D + b * 64, nx.q_start + nx.i0);
-            break;
           }
+          it = nx;
           ++n;
         }
       }
@@ -313,26 +337,28 @@ prefill_attn_dq_kernel(const DqParams p, const __grid_constant__ CUtensorMap tm_
           t5::commit(&bar[Q_KFREE + st]);
           if (last_of_item) t5::commit(&bar[Q_QFREE + qs]);
         };
-        int g = 0, n_item = 0, k = blockIdx.x;
-        int ntiles = item_tiles(k);
+        int g = 0, n_item = 0;
+        ItemIter cur = it_begin();
+        int ntiles = seek_item(cur).ntiles;
         bool have = ntiles != 0;
         if (have) {
           mbar_wait(&bar[Q_QFULL], 0);
           issue_s(0, 0, ntiles == 1);
         }
         while (have) {
-          int kn = k + gridDim.x, nt_nx = 0;
+          int nt_nx = 0;
           bool have_nx = false;
-          const int nt_peek = peek_item(kn).ntiles;   // requested now, used at this item's last tile
+          ItemIter nxi = cur;
+          const int nt_peek = peek_item(nxi).ntiles;  // requested now, used at this item's last tile
           for (int j = 0; j < ntiles; ++j, ++g) {
             const int st = g % kStages, sb = g & 1;
             if (j + 1 < ntiles) {
               issue_s(g + 1, n_item & 1, j + 2 == ntiles);
             } else {
               nt_nx = nt_peek;
-              if (nt_nx == 0 && kn < total) {     // an empty item (a query tile past a short prompt): look further
-                kn += gridDim.x;
-                nt_nx = item_tiles(kn);
+              if (nt_nx == 0 && nxi.k < total) {  // an empty item (a query tile past a short prompt): look further
+                it_next(nxi);
+                nt_nx = seek_item(nxi).ntiles;
               }
               have_nx = nt_nx != 0;
               if (have_nx) {                      // the next item's first tile: the other Q set, loaded during this item
@@ -361,7 +387,7 @@ prefill_attn_dq_kernel(const DqParams p, const __grid_constant__ CUtensorMap tm_
             t5::commit(&bar[Q_VFREE + st]);
           }
           ++n_item;
-          ntiles = nt_nx; k = kn; have = have_nx;
+          ntiles = nt_nx; cur = nxi; have = have_nx;
         }
       }
       __syncwarp();
@@ -374,12 +400,13 @@ prefill_attn_dq_kernel(const DqParams p, const __grid_constant__ CUtensorMap tm_
     const uint32_t lane_base = (uint32_t)((warp & 3) * 32) << 16;
     const uint32_t tmem_s = tmem + i * 256 + lane_base;
     const uint32_t tmem_o = tmem + i * 256 + 128 + lane_base;
-    int g = 0, n_item = 0, k = blockIdx.x;
+    int g = 0, n_item = 0;
     DQ_TRACER(tr, i, (warp & 3) == 0 && lane == 0);
-    DqItem it = seek_item(k);
+    ItemIter cur = it_begin();
+    DqItem it = seek_item(cur);
     while (it.ntiles != 0) {
-      int kn = k + gridDim.x;
-      DqItem nx = peek_item(kn);                       // requested now, used when this item is done
+      ItemIter nxi = cur;
+      DqItem nx = peek_item(nxi);                      // requested now, used when this item is done
       const int row = it.i0 + rt;
       float m_use = -INFINITY, l_run = 0.f;
       for (int j = 0; j < it.ntiles; ++j, ++g) {
@@ -471,12 +498,12 @@ prefill_attn_dq_kernel(const DqParams p, const __grid_constant__ CUtensorMap tm_
       linv[((n_item & 1) * 2 + i) * kTM + rt] = 1.f / l_run;
       t5::mbar_arrive(&bar[Q_LFULL + i * 2 + (n_item & 1)]);
       ++n_item;
-      if (nx.ntiles == 0 && kn < total) {              // an empty item: look further
-        kn += gridDim.x;
-        nx = seek_item(kn);
+      if (nx.ntiles == 0 && nxi.k < total) {           // an empty item: look further
+        it_next(nxi);
+        nx = seek_item(nxi);
       }
       it = nx;
-      k = kn;
+      cur = nxi;
     }
   } else {
     // ================================================= epilogue warpgroup: O_i / l -> bf16 -> global, i = 0, 1
@@ -485,8 +512,8 @@ prefill_attn_dq_kernel(const DqParams p, const __grid_constant__ CUtensorMap tm_
     const uint32_t lane_base = (uint32_t)((warp & 3) * 32) << 16;
     int g = 0, n_item = 0;
     DQ_TRACER(tr, 4, (warp & 3) == 0 && lane == 0);
-    for (int k = blockIdx.x; k < total; k += gridDim.x) {
-      const DqItem it = get_item(k);
+    for (ItemIter cur = it_begin(); cur.k < total; it_next(cur)) {
+      const DqItem it = get_item(cur);
       if (it.ntiles == 0) continue;
       g += it.ntiles;
       const int row = it.i0 + rt;

@@ -185,11 +185,17 @@ prefill_attn_tc_kernel(const PrefillTcParams p, const __grid_constant__ CUtensor
   // starts with its setmaxnreg so that the allocator sees the budget of the code it dominates.
   constexpr bool kRealloc = (TN == 64);
 
+  // the one thread of a single-lane role: elect.sync lets the compiler keep tcgen05.mma / TMA operands in uniform
+  // registers (tcgen05.cuh: elect_one); head size 64 measured 2 % slower with it (profiles/r02_prefill_elect_ab.jsonl)
+  // and keeps lane 0
+  auto role_lane = [&]() {
+    if constexpr (D == 64) return lane == 0; else return t5::elect_one();
+  };
   if (warp >= 4 && warp < 8) {
   if constexpr (kRealloc) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kRegsRoles));
   if (warp == 4) {
     // ================================================= Q + K producer (one lane, TMA)
-    if (t5::elect_one()) {
+    if (role_lane()) {
       int g = 0;   // tiles issued so far by this CTA (all items)
       for (int k = blockIdx.x; k < total; k += gridDim.x) {
         const TcItem it = get_item(k);
@@ -235,7 +241,7 @@ prefill_attn_tc_kernel(const PrefillTcParams p, const __grid_constant__ CUtensor
     __syncwarp();
   } else if (warp == 5) {
     // ================================================= V producer (one lane, TMA)
-    if (t5::elect_one()) {
+    if (role_lane()) {
       int g = 0;
       for (int k = blockIdx.x; k < total; k += gridDim.x) {
         const TcItem it = get_item(k);
@@ -249,7 +255,7 @@ prefill_attn_tc_kernel(const PrefillTcParams p, const __grid_constant__ CUtensor
     __syncwarp();
   } else if (warp == 6) {
     // ================================================= MMA issuer (one lane)
-    if (t5::elect_one()) {
+    if (role_lane()) {
       const uint32_t sQ = smem_u32(smem + L::oQ), sK = smem_u32(smem + L::oK);
       const uint32_t sV = smem_u32(smem + L::oV), sP = smem_u32(smem + L::oP);
       auto issue_s = [&](int g) {
