@@ -355,11 +355,9 @@ paged_decode_attn_score_kernel(const DecodeParams p) {
   auto issue_page = [&]() {  // issue the page under the cursor into the next ring slot
     const int slot = issue_slot;
     issue_slot = (issue_slot + 1 == depth) ? 0 : issue_slot + 1;
-#ifdef PC_DECODE_ELECT   // A/B build: one elected lane (no ELECT / R2UR / BRA.U.ANY loop around the bulk copies)
+    // one elected lane (elect.sync): under `lane == 0` the compiler wraps the mbarrier / bulk-copy instructions in an
+    // ELECT / R2UR / BRA.U.ANY loop each; same-box A/B +0.3-1.1 % (profiles/r02_decode_elect_ab.jsonl)
     if (elect_one_lane()) {
-#else
-    if (lane == 0) {
-#endif
       uint8_t* dst = my_stages + (size_t)slot * T::kStageBytes;
       const size_t off = ((size_t)phys_next * p.kv_block_stride) + (size_t)is_h * (D * BS);
       mbar_expect_tx(&my_bars[slot], T::kStageBytes);
