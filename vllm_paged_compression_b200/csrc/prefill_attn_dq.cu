@@ -306,17 +306,8 @@ prefill_attn_dq_kernel(const DqParams p, const __grid_constant__ CUtensorMap tm_
 #pragma unroll
               for (int b = 0; b < D / 64; ++b)
                 t5::tma_prefetch_l2_2d(&tm_q, (nx.hq0 + i) * D + b * 64, nx.q_start + nx.i0);
-            // and its first K / V tile (the ring looks two tiles ahead; a kv head's first rows may come from DRAM)
-#pragma unroll
-            for (int gg = 0; gg < kTN / BOX; ++gg) {
-              const int jn = gg * BOX;
-              const int src = nx.kv_src + (jn < nx.first ? jn : jn + nx.pruned);
-#pragma unroll
-              for (int b = 0; b < D / 64; ++b) {
-                t5::tma_prefetch_l2_2d(&tm_k, nx.hkv * D + b * 64, src);
-                t5::tma_prefetch_l2_2d(&tm_v, nx.hkv * D + b * 64, src);
-              }
-            }
+            // (the next item's first K / V tile prefetched here as well measured 0.4-1.4 % SLOWER:
+            // profiles/r02_prefill_dq_kvprefetch_ab.jsonl)
           }
           it = nx;
           ++n;
