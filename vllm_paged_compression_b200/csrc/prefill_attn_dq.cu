@@ -252,28 +252,42 @@ prefill_attn_dq_kernel(const DqParams p, const __grid_constant__ CUtensorMap tm_
       // by up to kStages tiles, across item boundaries
       if (t5::elect_one()) {
         DQ_TRACER(tr, 5, true);
-        int g = 0;
-        ItemIter cur = it_begin();
-        DqItem it = seek_item(cur);
-        while (it.ntiles != 0) {
-          ItemIter nxi = cur;
-          DqItem nx = peek_item(nxi);                  // requested now, used after this item's tiles
-          if (it.pruned != 0 && (((it.first | it.pruned) & (BOX - 1)) != 0)) __trap();
-          for (int t = 0; t < it.ntiles; ++t, ++g) {
-            const int st = g % kStages, use = g / kStages;
-            if (use > 0) t5::mbar_wait_relaxed(&bar[Q_KFREE + st], (use - 1) & 1);
-            DQ_TR(tr, 30, g);
-            issue_kv(&tm_k, smem + L::oK + st * L::kKV, &bar[Q_KFULL + st], it, t);
-            if (use > 0) t5::mbar_wait_relaxed(&bar[Q_VFREE + st], (use - 1) & 1);
-            DQ_TR(tr, 32, g);
-            issue_kv(&tm_v, smem + L::oV + st * L::kKV, &bar[Q_VFULL + st], it, t);
+        // K runs ONE TILE AHEAD of V: K0 K1 V0 K2 V1 ...  With K_g V_g K_g+1 in turn, K_g+1 waited behind V_g's
+        // stage (free when P.V_g-3 is done, a tile later than S_g-2), which left K less than two tile periods
+        // of lead against ~3000 clk of TMA latency under load.
+        struct Cur { ItemIter pos, npos; DqItem it, nx; int t, g; };
+        auto cur_begin = [&](Cur& c) {
+          c.pos = it_begin(); c.it = seek_item(c.pos); c.t = 0; c.g = 0;
+          c.npos = c.pos; c.nx.ntiles = 0;
+          if (c.it.ntiles != 0) c.nx = peek_item(c.npos);        // the next item's descriptor, requested a whole item ahead
+        };
+        auto cur_step = [&](Cur& c) {                             // next tile (of the next non-empty item after an item's last)
+          ++c.g;
+          if (++c.t == c.it.ntiles) {
+            if (c.nx.ntiles == 0 && c.npos.k < total) { it_next(c.npos); c.nx = seek_item(c.npos); }
+            c.it = c.nx; c.pos = c.npos; c.t = 0;
+            if (c.it.ntiles != 0) c.nx = peek_item(c.npos);
           }
-          if (nx.ntiles == 0 && nxi.k < total) {       // an empty item: look further
-            it_next(nxi);
-            nx = seek_item(nxi);
-          }
-          it = nx;
-          cur = nxi;
+        };
+        Cur ck, cv;
+        cur_begin(ck);
+        cur_begin(cv);
+        auto put_k = [&]() {
+          const int st = ck.g % kStages, use = ck.g / kStages;
+          if (ck.t == 0 && ck.it.pruned != 0 && (((ck.it.first | ck.it.pruned) & (BOX - 1)) != 0)) __trap();
+          if (use > 0) t5::mbar_wait_relaxed(&bar[Q_KFREE + st], (use - 1) & 1);
+          DQ_TR(tr, 30, ck.g);
+          issue_kv(&tm_k, smem + L::oK + st * L::kKV, &bar[Q_KFULL + st], ck.it, ck.t);
+          cur_step(ck);
+        };
+        if (ck.it.ntiles != 0) put_k();
+        while (cv.it.ntiles != 0) {
+          if (ck.it.ntiles != 0) put_k();
+          const int st = cv.g % kStages, use = cv.g / kStages;
+          if (use > 0) t5::mbar_wait_relaxed(&bar[Q_VFREE + st], (use - 1) & 1);
+          DQ_TR(tr, 32, cv.g);
+          issue_kv(&tm_v, smem + L::oV + st * L::kKV, &bar[Q_VFULL + st], cv.it, cv.t);
+          cur_step(cv);
         }
       }
       __syncwarp();
