@@ -25,7 +25,12 @@
 //     (k_free / v_free: 2 commits);
 //   * the K/V producer runs ahead across work items (the Q pair has its own producer), each issuer
 //     treats the tiles of consecutive items as one stream: S of tile g + 1 (the next item's first tile
-//     included) is issued before P.V of tile g.
+//     included) is issued before P.V of tile g.  K is requested one tile ahead of V (K0 K1 V0 K2 V1 ...);
+//   * the single-lane roles run under elect.sync (t5::elect_one), which keeps the tcgen05.mma / TMA operands in
+//     uniform registers: under `lane == 0` every such instruction sat in an ELECT / R2UR / BRA.U.ANY loop and the
+//     issuer thread's loop WAS the tile period (clock trace, profiles/r02_prefill_dq_trace_1024*.txt);
+//   * work items are walked with an ItemIter (no divisions) and every role asks for the next item's descriptor at
+//     the top of the current item.
 // Semantics, numerics, masks, the TMA box gather of the streamingLLM prune, the lazy rescale and the
 // item order are those of prefill_attn_tc.cu (same tests).  Needs an even number of q heads per kv
 // head; everything else goes to prefill_attn_tc.cu.
